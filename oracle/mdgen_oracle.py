@@ -1,0 +1,359 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU fp32 restatement of the reference's denoising hot path.
+
+This file is the parity checker.  Only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import it; the product package
+(mdgen_finetune_b200/) never does.
+
+It restates, as plain functional PyTorch on CPU tensors driven by a reference-layout
+state_dict, what /root/reference/src computes on the path SURVEY.md section 8(a) names.
+Each function cites the reference file:line it follows.  PARITY PIN: the restatement is
+checked (tests/test_oracle_golden.py) against golden vectors produced by running the
+UNMODIFIED reference modules in the build container (oracle/make_golden.py ->
+tests/golden/*.pt).  The two third-party arithmetic pieces (fair-esm RoPE, torchdiffeq
+Euler) have no tests in the reference: at those two boundaries parity is "unpinned" and
+rests on the published algorithms restated in `rope_tables` / `euler_sample`.
+
+Frames are passed as (rot [B,L,3,3], trans [B,L,3]) tuples instead of Rigid objects.
+"""
+import math
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+# ------------------------------------------------------------------------------------
+# small helpers
+def _lin(sd, p, x):
+    """nn.Linear / primitives.Linear forward (primitives.py:194-206)."""
+    return F.linear(x, sd[p + ".weight"], sd.get(p + ".bias"))
+
+
+def gelu_erf(x):
+    """layers.py:78-85."""
+    return x * 0.5 * (1.0 + torch.erf(x / math.sqrt(2.0)))
+
+
+def modulate(x, shift, scale):
+    """layers.py:14-15 (broadcast over dim 1)."""
+    return x * (1 + scale.unsqueeze(1)) + shift.unsqueeze(1)
+
+
+def ln_plain(x):
+    """nn.LayerNorm(C, elementwise_affine=False, eps=1e-6) (latent_model.py:371,376,449,454)."""
+    return F.layer_norm(x, x.shape[-1:], None, None, 1e-6)
+
+
+def timestep_embedding(t, dim=256, max_period=10000):
+    """layers.py:30-50: [cos | sin]."""
+    half = dim // 2
+    freqs = torch.exp(-math.log(max_period) * torch.arange(half, dtype=torch.float32) / half)
+    a = t[:, None].float() * freqs[None]
+    return torch.cat([torch.cos(a), torch.sin(a)], -1)
+
+
+def t_embedder(sd, t):
+    """layers.py:52-55: Linear(256,C) -> SiLU -> Linear(C,C)."""
+    h = _lin(sd, "t_embedder.mlp.0", timestep_embedding(t))
+    return _lin(sd, "t_embedder.mlp.2", F.silu(h))
+
+
+# ------------------------------------------------------------------------------------
+# fair-esm rotary embedding (third-party; call sites mha.py:129-130,356-357)
+def rope_tables(n, dim):
+    inv_freq = 1.0 / (10000 ** (torch.arange(0, dim, 2).float() / dim))
+    t = torch.arange(n).float()
+    fr = torch.einsum("i,j->ij", t, inv_freq)
+    emb = torch.cat((fr, fr), -1)
+    return emb.cos(), emb.sin()
+
+
+def _rot_half(x):
+    x1, x2 = x.chunk(2, -1)
+    return torch.cat((-x2, x1), -1)
+
+
+def mha(sd, p, x, mask, heads, rope=True):
+    """AttentionWithRoPE + MultiheadAttention as reached from the model.
+
+    latent_model.py:334-338, mha.py:258-286,356-397.  x [Nb,S,C] batch-first,
+    mask [Nb,S] (1 = valid).  Returns [Nb,S,C].
+    """
+    Nb, S, C = x.shape
+    d = C // heads
+    q = _lin(sd, p + ".attn.q_proj", x) * d ** -0.5                     # mha.py:260-263
+    k = _lin(sd, p + ".attn.k_proj", x)
+    v = _lin(sd, p + ".attn.v_proj", x)
+    bk = sd[p + ".attn.bias_k"].reshape(1, 1, C).expand(Nb, 1, C)       # mha.py:265-268
+    bv = sd[p + ".attn.bias_v"].reshape(1, 1, C).expand(Nb, 1, C)
+    k = torch.cat([k, bk], 1)
+    v = torch.cat([v, bv], 1)
+    pad = torch.cat([1 - mask, mask.new_zeros(Nb, 1)], 1) != 0          # mha.py:273-280, 374
+    q = q.view(Nb, S, heads, d).transpose(1, 2)                         # [Nb,H,S,d]
+    k = k.view(Nb, S + 1, heads, d).transpose(1, 2)
+    v = v.view(Nb, S + 1, heads, d).transpose(1, 2)
+    if rope:                                                            # mha.py:356-357
+        cos, sin = rope_tables(S + 1, d)
+        q = q * cos[:S] + _rot_half(q) * sin[:S]
+        k = k * cos + _rot_half(k) * sin
+    a = q @ k.transpose(-1, -2)                                         # mha.py:359
+    a = a.masked_fill(pad[:, None, None, :], float("-inf"))             # mha.py:370-376
+    a = F.softmax(a, -1, dtype=torch.float32)                           # mha.py:381
+    o = (a @ v).transpose(1, 2).reshape(Nb, S, C)                       # mha.py:389-396
+    return _lin(sd, p + ".attn.out_proj", o)
+
+
+# ------------------------------------------------------------------------------------
+# rigid helpers (rigid_utils.py)
+def rot_apply(rot, pts):
+    """rot_vec_mul (rigid_utils.py:64-86); rot [*,3,3], pts [*,3]."""
+    return (rot * pts[..., None, :]).sum(-1)
+
+
+def rigid_invert(rot, trans):
+    """Rigid.invert (rigid_utils.py:1075-1085)."""
+    ri = rot.transpose(-1, -2)
+    return ri, -rot_apply(ri, trans)
+
+
+def rigid_compose(r1, t1, r2, t2):
+    """Rigid.compose (rigid_utils.py:1031-1045)."""
+    return r1 @ r2, rot_apply(r1, t2) + t1
+
+
+def rot_to_quat(rot):
+    """rigid_utils.py:191-215: top eigenvector of the 4x4 K matrix (torch.linalg.eigh)."""
+    xx, xy, xz = rot[..., 0, 0], rot[..., 0, 1], rot[..., 0, 2]
+    yx, yy, yz = rot[..., 1, 0], rot[..., 1, 1], rot[..., 1, 2]
+    zx, zy, zz = rot[..., 2, 0], rot[..., 2, 1], rot[..., 2, 2]
+    k = [[xx + yy + zz, zy - yz, xz - zx, yx - xy],
+         [zy - yz, xx - yy - zz, xy + yx, xz + zx],
+         [xz - zx, xy + yx, yy - xx - zz, yz + zy],
+         [yx - xy, xz + zx, yz + zy, zz - xx - yy]]
+    k = (1.0 / 3.0) * torch.stack([torch.stack(r, -1) for r in k], -2)
+    _, vec = torch.linalg.eigh(k)
+    return vec[..., -1]
+
+
+def to_tensor_7(rot, trans):
+    """Rigid.to_tensor_7 (rigid_utils.py:1143-1155)."""
+    return torch.cat([rot_to_quat(rot), trans], -1)
+
+
+def relative_7(start, end):
+    """latent_model.py:198-199: start^-1 o end and end^-1 o start as 7-vectors."""
+    si = rigid_invert(*start)
+    ei = rigid_invert(*end)
+    x_f = to_tensor_7(*rigid_compose(*si, *end))
+    x_r = to_tensor_7(*rigid_compose(*ei, *start))
+    return x_f, x_r
+
+
+# ------------------------------------------------------------------------------------
+# invariant point attention, c_z = 0  (ipa.py:92-255)
+def ipa(sd, p, s, rot, trans, mask, H=4, c=32, Pq=8, Pv=8, inf=1e5, eps=1e-8):
+    """s [B,L,C]; rot [B,L,3,3]; trans [B,L,3]; mask [B,L] -> [B,L,C]."""
+    B, L, _ = s.shape
+    q = _lin(sd, p + ".linear_q", s).view(B, L, H, c)                    # ipa.py:113-117
+    kv = _lin(sd, p + ".linear_kv", s).view(B, L, H, 2 * c)              # ipa.py:114-123
+    k, v = kv[..., :c], kv[..., c:]
+
+    def points(name, n):
+        x = _lin(sd, p + name, s)                                        # [B,L,3*n], laid out (xyz, n)
+        x = x.view(B, L, 3, n).transpose(-1, -2)                         # ipa.py:130-131 -> [B,L,n,3]
+        return rot_apply(rot[:, :, None], x) + trans[:, :, None]         # ipa.py:132 Rigid.apply
+
+    q_pts = points(".linear_q_points", H * Pq).view(B, L, H, Pq, 3)      # ipa.py:126-135
+    kv_pts = points(".linear_kv_points", H * (Pq + Pv)).view(B, L, H, Pq + Pv, 3)
+    k_pts, v_pts = kv_pts[..., :Pq, :], kv_pts[..., Pq:, :]              # ipa.py:149-151
+
+    a = torch.einsum("bihc,bjhc->bhij", q, k) * math.sqrt(1.0 / (3 * c))  # ipa.py:161-166
+    d2 = ((q_pts[:, :, None] - k_pts[:, None]) ** 2).sum(-1)             # [B,i,j,H,Pq]  ipa.py:171-175
+    hw = F.softplus(sd[p + ".head_weights"]) * math.sqrt(1.0 / (3 * (Pq * 9.0 / 2)))  # ipa.py:176-181
+    pt = (d2 * hw.view(1, 1, 1, H, 1)).sum(-1) * (-0.5)                  # ipa.py:182-185
+    a = a + pt.permute(0, 3, 1, 2)                                       # ipa.py:193-196
+    sq = inf * (mask[:, :, None] * mask[:, None, :] - 1)                 # ipa.py:188-190
+    a = a + sq[:, None]                                                  # ipa.py:198
+    a = torch.softmax(a, -1)                                             # ipa.py:203
+
+    o = torch.einsum("bhij,bjhc->bihc", a, v).reshape(B, L, H * c)       # ipa.py:209-212
+    o_pt = torch.einsum("bhij,bjhpx->bihpx", a, v_pts)                   # ipa.py:216-225
+    o_pt = o_pt - trans[:, :, None, None]                                # ipa.py:226 invert_apply
+    o_pt = rot_apply(rot.transpose(-1, -2)[:, :, None, None], o_pt)
+    o_norm = torch.sqrt((o_pt ** 2).sum(-1) + eps).reshape(B, L, H * Pv)  # ipa.py:229-231
+    o_pt = o_pt.reshape(B, L, H * Pv, 3)                                 # ipa.py:234
+    cat = torch.cat([o, o_pt[..., 0], o_pt[..., 1], o_pt[..., 2], o_norm], -1)   # ipa.py:250-251
+    return _lin(sd, p + ".linear_out", cat)
+
+
+def ipa_layer(sd, p, s, t, mask, rot, trans, heads=16):
+    """IPALayer.forward (latent_model.py:378-394).  s [B,L,C], t [B,C], mask [B,L]."""
+    mod = _lin(sd, p + ".adaLN_modulation.1", F.silu(t))
+    sh_a, sc_a, g_a, sh_m, sc_m, g_m = mod.chunk(6, -1)
+    C = s.shape[-1]
+    n = F.layer_norm(s, (C,), sd[p + ".ipa_norm.weight"], sd[p + ".ipa_norm.bias"], 1e-5)
+    s = s + ipa(sd, p + ".ipa", n, rot, trans, mask)
+    h = modulate(ln_plain(s), sh_a, sc_a)
+    s = s + g_a.unsqueeze(1) * mha(sd, p + ".mha_l", h, mask, heads)
+    h = modulate(ln_plain(s), sh_m, sc_m)
+    s = s + g_m.unsqueeze(1) * _lin(sd, p + ".fc2", gelu_erf(_lin(sd, p + ".fc1", h)))
+    return s
+
+
+def main_layer(sd, p, x, t, mask, heads=16):
+    """LatentMDGenLayer.forward (latent_model.py:456-493).  x [B,T,L,C], t [B,1,C], mask [B,T,L]."""
+    B, T, L, C = x.shape
+    mod = _lin(sd, p + ".adaLN_modulation.1", F.silu(t))
+    sh_l, sc_l, g_l, sh_t, sc_t, g_t, sh_m, sc_m, g_m = mod.chunk(9, -1)
+    h = modulate(ln_plain(x), sh_l, sc_l)
+    y = mha(sd, p + ".mha_l", h.reshape(B * T, L, C), mask.reshape(B * T, L), heads)
+    x = x + g_l.unsqueeze(1) * y.reshape(B, T, L, C)
+    h = modulate(ln_plain(x), sh_t, sc_t)
+    y = mha(sd, p + ".mha_t", h.transpose(1, 2).reshape(B * L, T, C),
+            mask.transpose(1, 2).reshape(B * L, T), heads)
+    x = x + g_t.unsqueeze(1) * y.reshape(B, L, T, C).transpose(1, 2)
+    h = modulate(ln_plain(x), sh_m, sc_m)
+    x = x + g_m.unsqueeze(1) * _lin(sd, p + ".fc2", gelu_erf(_lin(sd, p + ".fc1", h)))
+    return x
+
+
+def run_ipa(sd, args, t, mask, start, end, aatype, x_d=None):
+    """LatentMDGenModel.run_ipa (latent_model.py:179-214); t [B,C], mask [B,L] (Q1 semantics)."""
+    B, L = mask.shape
+    n = args.num_layers
+    if args.sim_condition or args.mpnn:
+        s = torch.zeros(B, L, args.embed_dim)
+        if aatype is not None and not args.no_aa_emb:
+            s = s + sd["aatype_to_emb.weight"][aatype]
+        if args.design:
+            s = s + _lin(sd, "x_d_to_emb", x_d)
+        for i in range(n):
+            s = ipa_layer(sd, f"ipa_layers.{i}", s, t, mask, *start, heads=args.mha_heads)
+        return s
+    x_f7, x_r7 = relative_7(start, end)
+    x_f = _lin(sd, "latent_to_emb_f", x_f7)
+    x_r = _lin(sd, "latent_to_emb_r", x_r7)
+    if aatype is not None and not args.no_aa_emb:
+        e = sd["aatype_to_emb.weight"][aatype]
+        x_f, x_r = x_f + e, x_r + e
+    if args.design:
+        e = _lin(sd, "x_d_to_emb", x_d)
+        x_f, x_r = x_f + e, x_r + e
+    for i in range(n):
+        x_r = ipa_layer(sd, f"ipa_layers.{i}", x_r, t, mask, *start, heads=args.mha_heads)
+        x_f = ipa_layer(sd, f"ipa_layers.{i}", x_f, t, mask, *end, heads=args.mha_heads)
+    return x_r + x_f
+
+
+def forward(sd, args, x, t, mask, start=None, end=None, x_cond=None, x_cond_mask=None, aatype=None):
+    """LatentMDGenModel.forward (latent_model.py:216-269), Q1 = mask[:, 0] for run_ipa."""
+    if mask.dim() == 2:
+        mask = mask.repeat(x.shape[0], 1, 1)                              # latent_model.py:233-234
+    x_d = x[..., -20:].mean(1) if args.design else None                   # :237-240
+    h = _lin(sd, "latent_to_emb", x)                                      # :242
+    if args.abs_pos_emb:
+        h = h + sd["pos_embed"]                                           # :243-244
+    if getattr(args, "abs_time_emb", False):
+        h = h + sd["time_embed"][:, :, None]
+    if x_cond is not None:
+        h = h + _lin(sd, "cond_to_emb", x_cond) + sd["mask_to_emb.weight"][x_cond_mask]   # :249-250
+    te = t_embedder(sd, t.float() * args.time_multiplier)                 # :252
+    if args.prepend_ipa:
+        h = h + run_ipa(sd, args, te, mask[:, 0], start, end, aatype, x_d)[:, None]       # :254-255
+    for i in range(args.num_layers):
+        h = main_layer(sd, f"layers.{i}", h, te[:, None], mask, args.mha_heads)           # :257-258
+    mod = _lin(sd, "emb_to_latent.adaLN_modulation.1", F.silu(te[:, None]))               # layers.py:71-75
+    shift, scale = mod.chunk(2, -1)
+    latent = _lin(sd, "emb_to_latent.linear", modulate(ln_plain(h), shift, scale))
+    if args.design:                                                       # :262-268
+        xl = _lin(sd, "fc2", gelu_erf(_lin(sd, "fc1", h))).mean(1)
+        logits = _lin(sd, "emb_to_logits", gelu_erf(_lin(sd, "fc3", xl)))
+        latent = torch.cat([latent[..., :-20], latent[..., -20:] + logits[:, None]], -1)
+    return latent
+
+
+# ------------------------------------------------------------------------------------
+# design-mode Dirichlet conditional flow (utils.py:33-57, latent_model.py:279-326)
+class DirichletFlowTables:
+    """DirichletConditionalFlow (utils.py:33-43) with the model's constructor arguments
+    (latent_model.py:125-126: K=20, alpha_spacing=0.001, alpha_max=args.alpha_max)."""
+
+    def __init__(self, K=20, alpha_min=1, alpha_max=8, alpha_spacing=0.001):
+        import scipy.special
+        self.alphas = np.arange(alpha_min, alpha_max + alpha_spacing, alpha_spacing)
+        self.bs = np.linspace(0, 1, 1000)
+        cdfs = np.array([scipy.special.betainc(a, K - 1, self.bs) for a in self.alphas])
+        self.deriv = np.diff(cdfs, axis=0) / alpha_spacing
+        self.alpha_spacing = alpha_spacing
+        self.K = K
+
+    def c_factor(self, bs, alpha):
+        """utils.py:45-57."""
+        import scipy.special
+        beta = scipy.special.beta(alpha, self.K - 1)
+        with np.errstate(all="ignore"):
+            beta_div = np.where(bs < 1, beta / ((1 - bs) ** (self.K - 1)), 0)
+            beta_div_full = np.where((bs ** (alpha - 1)) > 0, beta_div / (bs ** (alpha - 1)), 0)
+        I_func = self.deriv[np.argmin(np.abs(alpha - self.alphas))]
+        return -np.interp(bs, self.bs, I_func) * beta_div_full
+
+
+_tables = {}
+
+
+def forward_inference(sd, args, x, t, mask, start=None, end=None, x_cond=None, x_cond_mask=None,
+                      aatype=None):
+    """LatentMDGenModel.forward_inference (latent_model.py:272-326)."""
+    if not args.design or args.dynamic_mpnn or args.mpnn:
+        return forward(sd, args, x, t, mask, start, end, x_cond, x_cond_mask, aatype)
+    xd = x[..., -20:]
+    latent = forward(sd, args, x, t, mask, start, end, x_cond, x_cond_mask, aatype)
+    probs = F.softmax(latent[..., -20:] / args.dirichlet_flow_temp, -1)        # :296
+    alpha = float(1 * (1 - t[0]) + t[0] * args.alpha_max)                      # transport.py:52-57
+    dalpha = args.alpha_max - 1
+    key = float(args.alpha_max)
+    if key not in _tables:
+        _tables[key] = DirichletFlowTables(alpha_max=args.alpha_max)
+    tab = _tables[key]
+    if alpha > args.alpha_max:                                                 # :308-309
+        alpha = args.alpha_max - tab.alpha_spacing
+    cf = torch.from_numpy(tab.c_factor(xd.numpy(), alpha)).to(xd)              # :310-311
+    if torch.isnan(cf).any():
+        if args.allow_nan_cfactor:
+            cf = torch.nan_to_num(cf)
+        else:
+            raise RuntimeError("NAN cfactor")
+    eye = torch.eye(20)
+    cond_flows = (eye - xd.unsqueeze(-1)) * cf.unsqueeze(-2)                   # :322-323
+    flow = (probs.unsqueeze(-2) * cond_flows).sum(-1) * dalpha                 # :324
+    return torch.cat([latent[..., :-20], flow], -1)
+
+
+# ------------------------------------------------------------------------------------
+# sampler: Sampler.sample_ode(sampling_method='euler') -> ode.sample -> torchdiffeq Euler
+def euler_sample(velocity, x0, num_steps=50, return_all=False):
+    """transport.py:407-450 + integrators.py:74-114 + torchdiffeq fixed-grid Euler.
+
+    grid = linspace(0,1,num_steps) (fp32); per step t_vec = ones(B)*t_i,
+    y_{i+1} = y_i + (t_{i+1}-t_i) * f(t_i, y_i).  Q3: 49 evaluations, the last at t=48/49.
+    """
+    grid = torch.linspace(0, 1, num_steps)
+    y = x0
+    ys = [y]
+    for i in range(num_steps - 1):
+        tv = torch.ones(x0.shape[0]) * grid[i]
+        y = y + (grid[i + 1] - grid[i]) * velocity(y, tv)
+        if return_all:
+            ys.append(y)
+    return torch.stack(ys, 0) if return_all else y
+
+
+def rerandomize_zero_params(sd, seed=0, std=0.02):
+    """Q2: adaLN-Zero / final / IPA linear_out are zero-initialised
+    (latent_model.py:144-177) so a fresh model outputs exactly 0; redraw them."""
+    g = torch.Generator().manual_seed(seed)
+    for k in sorted(sd.keys()):
+        v = sd[k]
+        if v.dtype.is_floating_point and v.numel() > 1 and not v.any() and "pos_embed" not in k:
+            sd[k] = torch.randn(v.shape, generator=g) * std
+    return sd
