@@ -1,0 +1,136 @@
+/* mdgen_b200.h -- C ABI of the B200-native MDGen denoiser (libmdgen_b200.so).
+ *
+ * The reference (lucascimeca/mdgen_finetune) has no FFI layer: its boundary for this path is
+ * the Python API of LatentMDGenModel / Sampler.  Each entry point below
+ * names the reference interface it replaces.  All pointers are plain device (or, where stated,
+ * host) pointers; no torch types cross this boundary.  Every call returns 0 on success and a
+ * negative MDGEN_E* code otherwise; mdgen_last_error() returns the message of the last failure
+ * on the calling thread.  A handle is bound to the CUDA device that was current at
+ * mdgen_create(); calls are asynchronous on the stream passed in and are CUDA-graph capturable
+ * after the first mdgen_set_conditioning() of a given shape (no allocation in the step).
+ */
+#ifndef MDGEN_B200_H
+#define MDGEN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct MdgenHandle MdgenHandle;
+typedef void* mdgen_stream_t; /* cudaStream_t */
+
+enum {
+  MDGEN_OK = 0,
+  MDGEN_EINVAL = -1,   /* bad argument / shape (reference: assert / ValueError)            */
+  MDGEN_ECUDA = -2,    /* CUDA runtime error                                               */
+  MDGEN_ESTATE = -3,   /* call order violated (weights not finalised, no conditioning set) */
+  MDGEN_ENOTFOUND = -4 /* unknown weight name                                              */
+};
+
+/* task flags: the argparse flags LatentMDGenModel reads (src/mdgen/parsing.py) */
+enum {
+  MDGEN_F_SIM = 1 << 0,         /* args.sim_condition                     */
+  MDGEN_F_TPS = 1 << 1,         /* args.tps_condition                     */
+  MDGEN_F_INPAINT = 1 << 2,     /* args.inpainting                        */
+  MDGEN_F_DESIGN = 1 << 3,      /* args.design                            */
+  MDGEN_F_NO_AA_EMB = 1 << 4,   /* args.no_aa_emb                         */
+  MDGEN_F_ABS_POS = 1 << 5,     /* args.abs_pos_emb                       */
+  MDGEN_F_ABS_TIME = 1 << 6,    /* args.abs_time_emb                      */
+  MDGEN_F_NO_ROPE = 1 << 7,     /* args.no_rope                           */
+  MDGEN_F_PREPEND_IPA = 1 << 8  /* args.prepend_ipa                       */
+};
+
+enum { MDGEN_PREC_BF16 = 0, MDGEN_PREC_FP32_CHECK = 1 };
+
+/* Replaces the constructor arguments LatentMDGenModel(args, latent_dim)
+ * (src/mdgen/model/latent_model.py:43-126). */
+typedef struct MdgenConfig {
+  int32_t embed_dim;      /* args.embed_dim   (384) */
+  int32_t num_layers;     /* args.num_layers  (5)   */
+  int32_t mha_heads;      /* args.mha_heads   (16)  */
+  int32_t ipa_heads;      /* args.ipa_heads   (4)   */
+  int32_t ipa_head_dim;   /* args.ipa_head_dim(32)  */
+  int32_t ipa_qk;         /* args.ipa_qk      (8)   */
+  int32_t ipa_v;          /* args.ipa_v       (8)   */
+  int32_t latent_dim;     /* latent_dim (21 / 28 / 48) */
+  int32_t crop;           /* args.crop (rows of pos_embed) */
+  int32_t num_frames;     /* args.num_frames (rows of time_embed) */
+  int32_t flags;          /* MDGEN_F_* */
+  int32_t precision;      /* MDGEN_PREC_* : bf16 tensor-core path or fp32 check mode */
+  float time_multiplier;  /* args.time_multiplier (100) */
+} MdgenConfig;
+
+/* lifetime ---------------------------------------------------------------------------- */
+int mdgen_create(const MdgenConfig* cfg, MdgenHandle** out);
+int mdgen_destroy(MdgenHandle* h);
+const char* mdgen_last_error(void);
+int mdgen_abi_version(void);
+
+/* weights: one call per state_dict entry (names and shapes of SURVEY 8b; replaces
+ * nn.Module.load_state_dict, latent_model.py:50-126).  `data` is fp32, device memory if
+ * is_device != 0 else host memory; it is copied (the caller keeps ownership). */
+int mdgen_load_weight(MdgenHandle* h, const char* name, const float* data, const int64_t* shape,
+                      int32_t ndim, int32_t is_device, mdgen_stream_t stream);
+/* Packs the loaded weights for the kernels (bf16 copies, fused QKV, folded q scaling).
+ * Must be called after the last mdgen_load_weight and again after any weight update. */
+int mdgen_finalize_weights(MdgenHandle* h, mdgen_stream_t stream);
+
+/* Step-invariant conditioning of one batch: everything forward() receives besides (x, t)
+ * (latent_model.py:216-220).  Replaces the per-call recomputation of
+ * pos_embed + cond_to_emb(x_cond) + mask_to_emb(x_cond_mask) (latent_model.py:243-250)
+ * and the frame inputs of run_ipa (latent_model.py:179-214).
+ *   mask        [B,T,L] f32 (1 = valid)
+ *   start_rot   [B,L,3,3] f32, start_trans [B,L,3] f32    (Rigid start_frames)
+ *   end_rot/end_trans: same for end_frames, NULL unless TPS / inpainting
+ *   rel_f7/rel_r7 [B,L,7] f32: to_tensor_7 of start^-1 o end and end^-1 o start
+ *       (latent_model.py:198-199); NULL => computed on device with the closed-form
+ *       quaternion (w >= 0) instead of the reference's sign-ambiguous eigh
+ *   x_cond      [B,T,L,cond_dim] f32 or NULL;  x_cond_mask [B,T,L] i64 or NULL
+ *   aatype      [B,L] i64 or NULL
+ * All device pointers; borrowed only for the duration of the call. */
+int mdgen_set_conditioning(MdgenHandle* h, int32_t B, int32_t T, int32_t L, const float* mask,
+                           const float* start_rot, const float* start_trans,
+                           const float* end_rot, const float* end_trans, const float* rel_f7,
+                           const float* rel_r7, const float* x_cond, const int64_t* x_cond_mask,
+                           const int64_t* aatype, mdgen_stream_t stream);
+
+/* One velocity evaluation: LatentMDGenModel.forward / forward_inference
+ * (latent_model.py:216-269, 272-278).  x [B,T,L,D] f32, t [B] f32, out [B,T,L,D] f32. */
+int mdgen_forward(MdgenHandle* h, const float* x, const float* t, float* out,
+                  mdgen_stream_t stream);
+
+/* Fixed-grid Euler sampler: Sampler.sample_ode(sampling_method="euler", num_steps)
+ * (transport.py:407-450, integrators.py:74-114, torchdiffeq fixed-grid Euler).
+ * grid = linspace(0,1,num_steps); num_steps-1 velocity evaluations.
+ *   x0 [B,T,L,D] f32; out_final [B,T,L,D] f32; traj: NULL or [num_steps,B,T,L,D] f32
+ * (the reference returns the whole stack, callers take [-1], wrapper.py:478). */
+int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, float* traj,
+                        float* out_final, mdgen_stream_t stream);
+
+/* introspection ------------------------------------------------------------------------ */
+/* Number of kernels one mdgen_forward launches for the current conditioning shape. */
+int mdgen_launches_per_forward(MdgenHandle* h);
+/* Bytes of device workspace currently held by the handle. */
+int64_t mdgen_workspace_bytes(MdgenHandle* h);
+
+/* unit-test entry points (tests/ only): run one kernel family on caller buffers --------- */
+/* C[M,N] = A[M,K] . W[N,K]^T + bias, A/W fp32 on device (converted to bf16 inside when
+ * use_tc != 0 -> tcgen05 path; fp32 SIMT path otherwise). */
+int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float* W,
+                    const float* bias, float* C, int32_t use_tc, int32_t block_n,
+                    mdgen_stream_t stream);
+/* Attention core as reached from MultiheadAttention (mha.py:258-397) on packed qkv:
+ * qkv [rows, 3C] f32 (q already scaled), rows = nb * S * inner, token (b, s, i) at row
+ * (b*S + s)*inner + i  (inner = 1 ... residue axis: L tokens contiguous; frame axis: stride L).
+ * bias_k/bias_v [C]; key_valid [nb*S*inner] f32 in the same row order; out [rows, C] f32. */
+int mdgen_test_attention(int32_t nb, int32_t S, int32_t inner, int32_t heads, int32_t head_dim,
+                         const float* qkv, const float* bias_k, const float* bias_v,
+                         const float* key_valid, float* out, int32_t use_tc, int32_t rope,
+                         mdgen_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MDGEN_B200_H */

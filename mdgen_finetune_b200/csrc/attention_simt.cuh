@@ -1,0 +1,217 @@
+// attention_simt.cuh -- fp32 flash-style attention core of MultiheadAttention as reached from
+// AttentionWithRoPE (mha.py:258-397, latent_model.py:334-338): learned bias-KV token appended as
+// key S (mha.py:265-268), RoPE on q (positions 0..S-1) and k (0..S) with rotate_half pairing
+// (fair-esm), -inf key-padding fill (mha.py:370-376), fp32 softmax (mha.py:381), P.V.
+// One thread = one query; keys streamed through shared memory in chunks with online softmax.
+// This is the fp32-check-mode core and the short-sequence (residue axis, L = 4) core.
+#pragma once
+#include <math.h>
+
+#include "common.cuh"
+
+namespace mdgen {
+
+template <typename AT>
+struct AttnParams {
+  const AT* qkv;  // [rows, ld]: q | k | v, each C = H*HD wide; q pre-scaled by HD^-0.5
+  int ld;
+  AT* out;        // [rows, ldo]
+  int ldo;
+  int nb, S, inner, H;
+  const float* bias_k;     // [C]
+  const float* bias_v;     // [C]
+  const float* key_valid;  // [mask_mod] 1 = valid, indexed by row % mask_mod
+  int mask_mod;
+  const float* cs;  // [S+1, HD/2] or null (no rope)
+  const float* sn;
+};
+
+__host__ __device__ __forceinline__ size_t attn_row(int nbi, int s, int S, int inner) {
+  return (size_t)(nbi / inner) * S * inner + (size_t)s * inner + (nbi % inner);
+}
+
+constexpr int AS_THREADS = 128;
+constexpr int AS_CHUNK = 64;
+
+template <typename AT, int HD>
+__global__ void __launch_bounds__(AS_THREADS)
+attention_simt_kernel(AttnParams<AT> p) {
+  constexpr int HALF = HD / 2;
+  __shared__ float Ks[AS_CHUNK][HD + 1];
+  __shared__ float Vs[AS_CHUNK][HD + 1];
+  __shared__ float valid[AS_CHUNK];
+  const int nbi = blockIdx.x / p.H, h = blockIdx.x % p.H;
+  const int C = p.H * HD;
+  const int qi = blockIdx.y * AS_THREADS + threadIdx.x;
+  const bool active = qi < p.S;
+
+  float q[HD], acc[HD];
+#pragma unroll
+  for (int i = 0; i < HD; ++i) acc[i] = 0.f;
+  if (active) {
+    const AT* qr = p.qkv + attn_row(nbi, qi, p.S, p.inner) * p.ld + h * HD;
+    float raw[HD];
+#pragma unroll
+    for (int i = 0; i < HD; ++i) raw[i] = to_f(qr[i]);
+    if (p.cs) {
+#pragma unroll
+      for (int i = 0; i < HALF; ++i) {
+        float c = p.cs[qi * HALF + i], s = p.sn[qi * HALF + i];
+        q[i] = raw[i] * c - raw[i + HALF] * s;
+        q[i + HALF] = raw[i + HALF] * c + raw[i] * s;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < HD; ++i) q[i] = raw[i];
+    }
+  }
+  float mrun = -INFINITY, lrun = 0.f;
+  const int nkeys = p.S + 1;
+  for (int k0 = 0; k0 < nkeys; k0 += AS_CHUNK) {
+    __syncthreads();
+    // cooperative load: (key, pair) items
+    for (int it = threadIdx.x; it < AS_CHUNK * HALF; it += AS_THREADS) {
+      int kk = it / HALF, i = it % HALF, key = k0 + kk;
+      float a = 0.f, b = 0.f, va = 0.f, vb = 0.f;
+      if (key < p.S) {
+        const AT* kr = p.qkv + attn_row(nbi, key, p.S, p.inner) * p.ld + C + h * HD;
+        a = to_f(kr[i]);
+        b = to_f(kr[i + HALF]);
+        va = to_f(kr[C + i]);
+        vb = to_f(kr[C + i + HALF]);
+      } else if (key == p.S) {
+        a = p.bias_k[h * HD + i];
+        b = p.bias_k[h * HD + i + HALF];
+        va = p.bias_v[h * HD + i];
+        vb = p.bias_v[h * HD + i + HALF];
+      }
+      if (p.cs && key <= p.S) {
+        float c = p.cs[key * HALF + i], s = p.sn[key * HALF + i];
+        float ra = a * c - b * s, rb = b * c + a * s;
+        a = ra;
+        b = rb;
+      }
+      Ks[kk][i] = a;
+      Ks[kk][i + HALF] = b;
+      Vs[kk][i] = va;
+      Vs[kk][i + HALF] = vb;
+    }
+    for (int kk = threadIdx.x; kk < AS_CHUNK; kk += AS_THREADS) {
+      int key = k0 + kk;
+      float v = 0.f;
+      if (key < p.S) v = p.key_valid[attn_row(nbi, key, p.S, p.inner) % p.mask_mod];
+      else if (key == p.S) v = 1.f;
+      valid[kk] = v;
+    }
+    __syncthreads();
+    if (!active) continue;
+    const int kend = min(AS_CHUNK, nkeys - k0);
+    for (int kk = 0; kk < kend; ++kk) {
+      if (valid[kk] == 0.f) continue;  // -inf logit: contributes exactly 0
+      float s = 0.f;
+#pragma unroll
+      for (int i = 0; i < HD; ++i) s = fmaf(q[i], Ks[kk][i], s);
+      if (s > mrun) {
+        float corr = expf(mrun - s);  // mrun = -inf -> 0
+        lrun *= corr;
+#pragma unroll
+        for (int i = 0; i < HD; ++i) acc[i] *= corr;
+        mrun = s;
+      }
+      float pr = expf(s - mrun);
+      lrun += pr;
+#pragma unroll
+      for (int i = 0; i < HD; ++i) acc[i] = fmaf(pr, Vs[kk][i], acc[i]);
+    }
+  }
+  if (active) {
+    AT* o = p.out + attn_row(nbi, qi, p.S, p.inner) * p.ldo + h * HD;
+    const float inv = 1.0f / lrun;
+#pragma unroll
+    for (int i = 0; i < HD; ++i) o[i] = from_f<AT>(acc[i] * inv);
+  }
+}
+
+// Short sequences (residue axis of the tetrapeptide configs: S = L = 4, 5 keys): one thread per
+// (token, head); the S+1 keys are read straight from global/L1 -- no shared memory, no idle lanes.
+template <typename AT, int HD>
+__global__ void __launch_bounds__(256)
+attention_short_kernel(AttnParams<AT> p, long long total) {
+  constexpr int HALF = HD / 2;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int h = (int)(idx % p.H);
+  const long long tok = idx / p.H;           // (nbi, qi) with qi fastest
+  const int qi = (int)(tok % p.S), nbi = (int)(tok / p.S);
+  const int C = p.H * HD;
+  float q[HD], acc[HD];
+  {
+    const AT* qr = p.qkv + attn_row(nbi, qi, p.S, p.inner) * p.ld + h * HD;
+#pragma unroll
+    for (int i = 0; i < HALF; ++i) {
+      float a = to_f(qr[i]), b = to_f(qr[i + HALF]);
+      float c = 1.f, s = 0.f;
+      if (p.cs) { c = p.cs[qi * HALF + i]; s = p.sn[qi * HALF + i]; }
+      q[i] = a * c - b * s;
+      q[i + HALF] = b * c + a * s;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < HD; ++i) acc[i] = 0.f;
+  float mrun = -INFINITY, lrun = 0.f;
+  for (int key = 0; key <= p.S; ++key) {
+    float kv[HD], vv[HD];
+    if (key < p.S) {
+      const size_t r = attn_row(nbi, key, p.S, p.inner);
+      if (p.key_valid[r % p.mask_mod] == 0.f) continue;
+      const AT* kr = p.qkv + r * p.ld + C + h * HD;
+#pragma unroll
+      for (int i = 0; i < HD; ++i) { kv[i] = to_f(kr[i]); vv[i] = to_f(kr[C + i]); }
+    } else {
+#pragma unroll
+      for (int i = 0; i < HD; ++i) { kv[i] = p.bias_k[h * HD + i]; vv[i] = p.bias_v[h * HD + i]; }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < HALF; ++i) {
+      float c = 1.f, sn = 0.f;
+      if (p.cs) { c = p.cs[key * HALF + i]; sn = p.sn[key * HALF + i]; }
+      float a = kv[i] * c - kv[i + HALF] * sn, b = kv[i + HALF] * c + kv[i] * sn;
+      s = fmaf(q[i], a, s);
+      s = fmaf(q[i + HALF], b, s);
+    }
+    if (s > mrun) {
+      float corr = expf(mrun - s);
+      lrun *= corr;
+#pragma unroll
+      for (int i = 0; i < HD; ++i) acc[i] *= corr;
+      mrun = s;
+    }
+    float pr = expf(s - mrun);
+    lrun += pr;
+#pragma unroll
+    for (int i = 0; i < HD; ++i) acc[i] = fmaf(pr, vv[i], acc[i]);
+  }
+  AT* o = p.out + attn_row(nbi, qi, p.S, p.inner) * p.ldo + h * HD;
+  const float inv = 1.0f / lrun;
+#pragma unroll
+  for (int i = 0; i < HD; ++i) o[i] = from_f<AT>(acc[i] * inv);
+}
+
+template <typename AT>
+inline int launch_attention_simt(const AttnParams<AT>& p, int head_dim, cudaStream_t st) {
+  MD_CHECK(head_dim == 24, "attention_simt: head_dim must be 24");
+  if (p.nb <= 0 || p.S <= 0) return 0;
+  if (p.S <= 16) {
+    long long total = (long long)p.nb * p.S * p.H;
+    attention_short_kernel<AT, 24><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(p, total);
+  } else {
+    dim3 grid(p.nb * p.H, (p.S + AS_THREADS - 1) / AS_THREADS);
+    attention_simt_kernel<AT, 24><<<grid, AS_THREADS, 0, st>>>(p);
+  }
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace mdgen

@@ -1,0 +1,87 @@
+// common.cuh -- shared helpers for the mdgen_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+namespace mdgen {
+
+typedef __nv_bfloat16 bf16;
+
+// ---- error plumbing (host) -----------------------------------------------------------
+void set_error(const std::string& msg);
+#define MD_CUDA(call)                                                                       \
+  do {                                                                                      \
+    cudaError_t e__ = (call);                                                               \
+    if (e__ != cudaSuccess) {                                                               \
+      mdgen::set_error(std::string(#call) + ": " + cudaGetErrorString(e__) + " @" +         \
+                       __FILE__ + ":" + std::to_string(__LINE__));                          \
+      return -2;                                                                            \
+    }                                                                                       \
+  } while (0)
+#define MD_CHECK(cond, msg)                                                                 \
+  do {                                                                                      \
+    if (!(cond)) {                                                                          \
+      mdgen::set_error(std::string(msg) + " (" #cond ") @" + __FILE__ + ":" +               \
+                       std::to_string(__LINE__));                                           \
+      return -1;                                                                            \
+    }                                                                                       \
+  } while (0)
+#define MD_TRY(call)                                                                        \
+  do {                                                                                      \
+    int r__ = (call);                                                                       \
+    if (r__ != 0) return r__;                                                               \
+  } while (0)
+
+// launch counter: every kernel launch of the library goes through MD_LAUNCHED()
+extern thread_local long long g_launches;
+#define MD_LAUNCHED() (++mdgen::g_launches)
+
+// ---- device helpers ------------------------------------------------------------------
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// exact erf GELU (layers.py:78-85)
+__device__ __forceinline__ float gelu_erf(float x) {
+  return x * 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+}
+__device__ __forceinline__ float silu(float x) { return x / (1.0f + expf(-x)); }
+
+// epilogue kinds shared by the SIMT and the tcgen05 GEMM
+enum Epi : int {
+  EPI_STORE = 0,       // out = acc + bias
+  EPI_GELU = 1,        // out = gelu(acc + bias)
+  EPI_GATE_RESID = 2,  // resid[m,n] += gate[batch(m)][n] * (acc + bias)     (fp32 resid)
+  EPI_RESID = 3,       // resid[m,n] += acc + bias
+  EPI_EULER = 4        // v = acc + bias; out[m,n] = v; state[m,n] += dt * v  (fp32)
+};
+
+struct EpiParams {
+  const float* bias = nullptr;   // [N] or null
+  void* out = nullptr;           // [M, ldo] of OT (STORE/GELU/EULER: velocity out, fp32)
+  int ldo = 0;
+  float* resid = nullptr;        // [M, ldr] fp32 (GATE_RESID / RESID) or Euler state
+  int ldr = 0;
+  const float* gate = nullptr;   // gate[b * gate_stride + n]
+  int gate_stride = 0;
+  int rows_per_batch = 1;        // batch(m) = (m / rows_per_batch) % nbatch
+  int nbatch = 1;
+  float dt = 0.f;
+};
+
+}  // namespace mdgen

@@ -1,0 +1,205 @@
+// elementwise.cuh -- HBM-bound glue kernels: LayerNorm+adaLN modulate, token embedding,
+// timestep embedding, adaLN table, RoPE tables.  One warp per 384-wide row, float4 lanes.
+#pragma once
+#include "common.cuh"
+
+namespace mdgen {
+
+// ---- LayerNorm (no affine, eps) + modulate ------------------------------------------
+// out[m,:] = LN(x[m,:]) * (1 + scale[b]) + shift[b],  b = (m / rows_per_batch) % nbatch.
+// latent_model.py:385,390,467,475,489 + layers.py:14-15,73.  If shift == nullptr: affine
+// LayerNorm with weight/bias (ipa_norm, latent_model.py:360,382; eps 1e-5).
+template <typename OT, int C>
+__global__ void __launch_bounds__(256)
+ln_modulate_kernel(const float* __restrict__ x, OT* __restrict__ out, int M, const float* __restrict__ shift,
+                   const float* __restrict__ scale, int mod_stride, int rows_per_batch, int nbatch,
+                   const float* __restrict__ w, const float* __restrict__ bvec, float eps) {
+  static_assert(C % 128 == 0, "C must be a multiple of 128");
+  constexpr int V = C / 128;  // float4 per lane
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= M) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)warp * C);
+  float4 v[V];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    v[i] = xr[lane + 32 * i];
+    s += v[i].x + v[i].y + v[i].z + v[i].w;
+  }
+  const float mean = warp_sum(s) * (1.0f / C);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+    q += a * a + b * b + c * c + d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.0f / C) + eps);
+  const int b = (warp / rows_per_batch) % nbatch;
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int c0 = (lane + 32 * i) * 4;
+    float r[4] = {(v[i].x - mean) * rstd, (v[i].y - mean) * rstd, (v[i].z - mean) * rstd,
+                  (v[i].w - mean) * rstd};
+    if (shift) {
+      const float4 sh = *reinterpret_cast<const float4*>(shift + (size_t)b * mod_stride + c0);
+      const float4 sc = *reinterpret_cast<const float4*>(scale + (size_t)b * mod_stride + c0);
+      r[0] = r[0] * (1.f + sc.x) + sh.x;
+      r[1] = r[1] * (1.f + sc.y) + sh.y;
+      r[2] = r[2] * (1.f + sc.z) + sh.z;
+      r[3] = r[3] * (1.f + sc.w) + sh.w;
+    } else if (w) {
+      const float4 ww = *reinterpret_cast<const float4*>(w + c0);
+      const float4 bb = *reinterpret_cast<const float4*>(bvec + c0);
+      r[0] = r[0] * ww.x + bb.x;
+      r[1] = r[1] * ww.y + bb.y;
+      r[2] = r[2] * ww.z + bb.z;
+      r[3] = r[3] * ww.w + bb.w;
+    }
+    OT* o = out + (size_t)warp * C + c0;
+    if constexpr (sizeof(OT) == 4) {
+      *reinterpret_cast<float4*>(o) = make_float4(r[0], r[1], r[2], r[3]);
+    } else {
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(r[0], r[1]);
+      __nv_bfloat162 p1 = __floats2bfloat162_rn(r[2], r[3]);
+      uint2 pk;
+      pk.x = *reinterpret_cast<uint32_t*>(&p0);
+      pk.y = *reinterpret_cast<uint32_t*>(&p1);
+      *reinterpret_cast<uint2*>(o) = pk;
+    }
+  }
+}
+
+// ---- token embedding -------------------------------------------------------------------
+// emb[m,:] = W_x x[m] + W_c x_cond[m] + b_x + b_c + mask_emb[cm[m]] + pos[l] + time[t] + ipa[b,l]
+// latent_model.py:242-255.  One block = EMB_TOK tokens, thread = channel.
+constexpr int EMB_TOK = 16;
+template <int C>
+__global__ void __launch_bounds__(C)
+embed_kernel(const float* __restrict__ x, int D, const float* __restrict__ xc, int Dc,
+             const int64_t* __restrict__ cm, const float* __restrict__ Wx, const float* __restrict__ bx,
+             const float* __restrict__ Wc, const float* __restrict__ bc, const float* __restrict__ mask_emb,
+             const float* __restrict__ pos, const float* __restrict__ time_emb,
+             const float* __restrict__ ipa, float* __restrict__ out, int N, int T, int L) {
+  extern __shared__ float sm[];  // [EMB_TOK][D + Dc]
+  const int c = threadIdx.x;
+  const int m0 = blockIdx.x * EMB_TOK;
+  const int DD = D + Dc;
+  for (int i = threadIdx.x; i < EMB_TOK * DD; i += C) {
+    int tk = i / DD, d = i % DD, m = m0 + tk;
+    float v = 0.f;
+    if (m < N) v = d < D ? x[(size_t)m * D + d] : xc[(size_t)m * Dc + (d - D)];
+    sm[i] = v;
+  }
+  __syncthreads();
+  float base = bx[c] + (xc ? bc[c] : 0.f);
+  for (int tk = 0; tk < EMB_TOK; ++tk) {
+    int m = m0 + tk;
+    if (m >= N) break;
+    float acc = base;
+    const float* row = sm + tk * DD;
+    for (int d = 0; d < D; ++d) acc = fmaf(Wx[(size_t)c * D + d], row[d], acc);
+    for (int d = 0; d < Dc; ++d) acc = fmaf(Wc[(size_t)c * Dc + d], row[D + d], acc);
+    int l = m % L, t = (m / L) % T, b = m / (L * T);
+    if (cm) acc += mask_emb[(size_t)cm[m] * C + c];
+    if (pos) acc += pos[(size_t)l * C + c];
+    if (time_emb) acc += time_emb[(size_t)t * C + c];
+    if (ipa) acc += ipa[((size_t)b * L + l) * C + c];
+    out[(size_t)m * C + c] = acc;
+  }
+}
+
+// ---- small dense layer for a handful of rows: y[r, j] = act(b[j] + sum_k W[j,k] x[r,k]) ----
+// One warp per output j (lanes along k, coalesced W reads), loops over rows r (<= MAXR per pass).
+// Used for t_embedder (layers.py:52-55), the adaLN table (latent_model.py:380,461; layers.py:72),
+// the 7-vector / x_d / design-head linears.  in_act: 0 none, 1 SiLU on the input; out_act: 0 none, 2 GELU.
+__global__ void __launch_bounds__(256)
+rowvec_linear_kernel(const float* __restrict__ x, int ldx, int R, const float* __restrict__ W, int K,
+                     const float* __restrict__ bias, int J, float* __restrict__ y, int ldy, int in_act,
+                     int out_act, int accumulate) {
+  const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (j >= J) return;
+  const float* wr = W + (size_t)j * K;
+  for (int r = 0; r < R; ++r) {
+    float acc = 0.f;
+    for (int k = lane; k < K; k += 32) {
+      float xv = x[(size_t)r * ldx + k];
+      if (in_act == 1) xv = silu(xv);
+      acc = fmaf(wr[k], xv, acc);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      acc += bias ? bias[j] : 0.f;
+      if (out_act == 2) acc = gelu_erf(acc);
+      float* o = y + (size_t)r * ldy + j;
+      *o = accumulate ? *o + acc : acc;
+    }
+  }
+}
+
+// sinusoidal timestep features, layers.py:30-50: [cos(t f_i) | sin(t f_i)], f_i = exp(-ln(1e4) i/128)
+__global__ void timestep_features_kernel(const float* __restrict__ t, float mult, int R, float* __restrict__ out) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= R * 128) return;
+  int r = idx / 128, i = idx % 128;
+  float f = expf(-9.210340371976184f * (float)i / 128.0f);
+  float a = t[r] * mult * f;
+  out[(size_t)r * 256 + i] = cosf(a);
+  out[(size_t)r * 256 + 128 + i] = sinf(a);
+}
+
+// RoPE tables (fair-esm): cos/sin[s, i] of s * inv_freq[i], s in [0, n), i in [0, half)
+__global__ void rope_table_kernel(const float* __restrict__ inv_freq, int half, int n, float* __restrict__ cs,
+                                  float* __restrict__ sn) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n * half) return;
+  int s = idx / half, i = idx % half;
+  float a = (float)s * inv_freq[i];
+  cs[idx] = cosf(a);
+  sn[idx] = sinf(a);
+}
+
+// aatype embedding + optional adds: s[r,:] (+)= table[idx[r % idx_mod], :]
+__global__ void gather_rows_kernel(const float* __restrict__ table, const int64_t* __restrict__ idx, int idx_mod,
+                                   int R, int C, float* __restrict__ out, int accumulate) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= R * C) return;
+  int r = i / C, c = i % C;
+  float v = table[(size_t)idx[r % idx_mod] * C + c];
+  out[i] = accumulate ? out[i] + v : v;
+}
+
+// mean over the frame axis of a [B,T,L,W] tensor slice: out[b,l,w] = mean_t in[b,t,l,off+w]
+template <typename IT>
+__global__ void mean_over_T_kernel(const IT* __restrict__ in, int ld, int off, int B, int T, int L, int W,
+                                   float* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * L * W) return;
+  int w = i % W, l = (i / W) % L, b = i / (W * L);
+  float s = 0.f;
+  for (int t = 0; t < T; ++t) s += to_f(in[((size_t)(b * T + t) * L + l) * ld + off + w]);
+  out[i] = s / (float)T;
+}
+
+// design head tail: latent[b,t,l,D-20+k] += logits[b,l,k]   (latent_model.py:268)
+__global__ void add_logits_kernel(float* __restrict__ latent, int D, const float* __restrict__ logits, int B, int T,
+                                  int L) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * T * L * 20) return;
+  int k = i % 20, m = i / 20, l = m % L, b = m / (L * T);
+  latent[(size_t)m * D + D - 20 + k] += logits[((size_t)b * L + l) * 20 + k];
+}
+
+__global__ void axpy_kernel(float* __restrict__ y, const float* __restrict__ x, float a, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] += a * x[i];
+}
+__global__ void fill_kernel(float* __restrict__ y, float v, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = v;
+}
+__global__ void f32_to_bf16_kernel(const float* __restrict__ x, bf16* __restrict__ y, size_t n, float scale) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = __float2bfloat16_rn(x[i] * scale);
+}
+
+}  // namespace mdgen

@@ -1,0 +1,180 @@
+// ipa.cuh -- InvariantPointAttention with c_z = 0 (src/mdgen/model/ipa.py:92-255), fp32 throughout
+// (the reference keeps IPA geometry out of AMP: primitives.py:201-204, rigid_utils.py:28-30,70-71).
+// Pipeline per IPA call:  proj GEMM  n[M,C] -> P[M, 672] = [q 128 | kv 256 | q_pts 96 | kv_pts 192]
+//   -> ipa_points_kernel (Rigid.apply of the points, ipa.py:130-143)
+//   -> ipa_attention_kernel (logits ipa.py:161-198, softmax :203, o / o_pt / inverse rigid / norm :209-234)
+//   -> linear_out GEMM with residual epilogue (ipa.py:250-254, latent_model.py:382).
+#pragma once
+#include <math.h>
+
+#include "common.cuh"
+
+namespace mdgen {
+
+struct IpaDims {
+  int H, c, Pq, Pv;  // 4, 32, 8, 8
+  __host__ __device__ int proj_width() const { return H * c * 3 + H * Pq * 3 + H * (Pq + Pv) * 3; }
+  __host__ __device__ int off_kv() const { return H * c; }
+  __host__ __device__ int off_qp() const { return H * c * 3; }
+  __host__ __device__ int off_kvp() const { return H * c * 3 + H * Pq * 3; }
+  __host__ __device__ int cat_width() const { return H * (c + 4 * Pv); }
+};
+
+// Gq[m][h*Pq+p][3], Gkv[m][h*(Pq+Pv)+j][3]: points mapped to the global frame, x_g = R x + t.
+__global__ void ipa_points_kernel(const float* __restrict__ P, int ldp, IpaDims d, const float* __restrict__ rot,
+                                  const float* __restrict__ trans, int M, float* __restrict__ Gq,
+                                  float* __restrict__ Gkv) {
+  const int nq = d.H * d.Pq, nkv = d.H * (d.Pq + d.Pv);
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= M * (nq + nkv)) return;
+  const int m = idx / (nq + nkv), pt = idx % (nq + nkv);
+  const float* R = rot + (size_t)m * 9;
+  const float* t = trans + (size_t)m * 3;
+  const float* row = P + (size_t)m * ldp;
+  float x, y, z;
+  float* dst;
+  if (pt < nq) {  // raw layout (xyz, H*Pq): ipa.py:130-131
+    x = row[d.off_qp() + pt];
+    y = row[d.off_qp() + nq + pt];
+    z = row[d.off_qp() + 2 * nq + pt];
+    dst = Gq + ((size_t)m * nq + pt) * 3;
+  } else {
+    const int q = pt - nq;
+    x = row[d.off_kvp() + q];
+    y = row[d.off_kvp() + nkv + q];
+    z = row[d.off_kvp() + 2 * nkv + q];
+    dst = Gkv + ((size_t)m * nkv + q) * 3;
+  }
+  dst[0] = R[0] * x + R[1] * y + R[2] * z + t[0];  // rot_vec_mul, rigid_utils.py:64-86
+  dst[1] = R[3] * x + R[4] * y + R[5] * z + t[1];
+  dst[2] = R[6] * x + R[7] * y + R[8] * z + t[2];
+}
+
+// One block per query row i; warp h = head h (H warps).  Requires c == 32, Pq == Pv == 8.
+// mask index = row % mask_mod (mask is [B,L]; rows are (stream, b, l)).
+__global__ void __launch_bounds__(128)
+ipa_attention_kernel(const float* __restrict__ P, int ldp, IpaDims d, const float* __restrict__ Gq,
+                     const float* __restrict__ Gkv, const float* __restrict__ rot,
+                     const float* __restrict__ trans, const float* __restrict__ head_w,
+                     const float* __restrict__ mask, int mask_mod, int L, float* __restrict__ cat,
+                     float inf, float eps) {
+  extern __shared__ float smem[];  // per warp: L logits + 32 q + 24 q-points + 24 o_pt
+  const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int i = blockIdx.x;
+  const int g0 = (i / L) * L;  // first row of this (stream, b) group
+  float* lg = smem + (size_t)h * (L + 80);
+  float* qs = lg + L;
+  float* qp = qs + 32;
+  float* op = qp + 24;
+  const int nq = d.H * d.Pq, nkv = d.H * (d.Pq + d.Pv);
+  qs[lane] = P[(size_t)i * ldp + h * d.c + lane];
+  if (lane < 24) qp[lane] = Gq[((size_t)i * nq + h * d.Pq) * 3 + lane];
+  __syncwarp();
+  const float sp = log1pf(expf(head_w[h]));  // softplus (ipa.py:176)
+  const float hw = sp * sqrtf(1.0f / (3.0f * (d.Pq * 9.0f / 2.0f)));
+  const float qk_scale = sqrtf(1.0f / (3.0f * d.c));
+  const float mi = mask[i % mask_mod];
+  float mx = -INFINITY;
+  for (int j = lane; j < L; j += 32) {
+    const int rj = g0 + j;
+    const float* kr = P + (size_t)rj * ldp + d.off_kv() + h * 2 * d.c;
+    float s = 0.f;
+#pragma unroll 8
+    for (int c = 0; c < 32; ++c) s = fmaf(qs[c], kr[c], s);
+    const float* kp = Gkv + ((size_t)rj * nkv + h * (d.Pq + d.Pv)) * 3;
+    float d2 = 0.f;
+#pragma unroll
+    for (int e = 0; e < 24; ++e) {
+      float df = qp[e] - kp[e];
+      d2 = fmaf(df, df, d2);
+    }
+    float a = s * qk_scale - 0.5f * hw * d2 + inf * (mi * mask[rj % mask_mod] - 1.0f);
+    lg[j] = a;
+    mx = fmaxf(mx, a);
+  }
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int j = lane; j < L; j += 32) {
+    float e = expf(lg[j] - mx);
+    lg[j] = e;
+    sum += e;
+  }
+  sum = warp_sum(sum);
+  __syncwarp();
+  const float inv = 1.0f / sum;
+  // o[h, c = lane] and o_pt[h, p, x] (lane < 24 -> p = lane / 3, x = lane % 3)
+  float o = 0.f, opt = 0.f;
+  for (int j = 0; j < L; ++j) {
+    const int rj = g0 + j;
+    const float a = lg[j];
+    o = fmaf(a, P[(size_t)rj * ldp + d.off_kv() + h * 2 * d.c + d.c + lane], o);
+    if (lane < 24) opt = fmaf(a, Gkv[((size_t)rj * nkv + h * (d.Pq + d.Pv) + d.Pq) * 3 + lane], opt);
+  }
+  float* crow = cat + (size_t)i * d.cat_width();
+  crow[h * d.c + lane] = o * inv;
+  if (lane < 24) op[lane] = opt * inv;
+  __syncwarp();
+  if (lane < 8) {  // invert_apply (rigid_utils.py:1061-1073): R^T (x - t)
+    const float* R = rot + (size_t)i * 9;
+    const float* t = trans + (size_t)i * 3;
+    float vx = op[lane * 3 + 0] - t[0], vy = op[lane * 3 + 1] - t[1], vz = op[lane * 3 + 2] - t[2];
+    float lx = R[0] * vx + R[3] * vy + R[6] * vz;
+    float ly = R[1] * vx + R[4] * vy + R[7] * vz;
+    float lz = R[2] * vx + R[5] * vy + R[8] * vz;
+    const int base = d.H * d.c, np = d.H * d.Pv, pi = h * d.Pv + lane;
+    crow[base + pi] = lx;
+    crow[base + np + pi] = ly;
+    crow[base + 2 * np + pi] = lz;
+    crow[base + 3 * np + pi] = sqrtf(lx * lx + ly * ly + lz * lz + eps);  // ipa.py:229-231
+  }
+}
+
+// Relative rigid 7-vectors of latent_model.py:198-199 with a closed-form quaternion (w >= 0):
+//   f7 = to_tensor_7(start^-1 o end), r7 = to_tensor_7(end^-1 o start).
+__device__ inline void rot_to_quat_closed(const float* R, float* q) {
+  // Shepperd's method: pick the largest of (trace, R00, R11, R22) for conditioning.
+  float xx = R[0], yy = R[4], zz = R[8];
+  float tr = xx + yy + zz;
+  float w, x, y, z;
+  if (tr >= xx && tr >= yy && tr >= zz) {
+    float s = sqrtf(fmaxf(1.f + tr, 0.f)) * 2.f;
+    w = 0.25f * s; x = (R[7] - R[5]) / s; y = (R[2] - R[6]) / s; z = (R[3] - R[1]) / s;
+  } else if (xx >= yy && xx >= zz) {
+    float s = sqrtf(fmaxf(1.f + xx - yy - zz, 0.f)) * 2.f;
+    w = (R[7] - R[5]) / s; x = 0.25f * s; y = (R[1] + R[3]) / s; z = (R[2] + R[6]) / s;
+  } else if (yy >= zz) {
+    float s = sqrtf(fmaxf(1.f + yy - xx - zz, 0.f)) * 2.f;
+    w = (R[2] - R[6]) / s; x = (R[1] + R[3]) / s; y = 0.25f * s; z = (R[5] + R[7]) / s;
+  } else {
+    float s = sqrtf(fmaxf(1.f + zz - xx - yy, 0.f)) * 2.f;
+    w = (R[3] - R[1]) / s; x = (R[2] + R[6]) / s; y = (R[5] + R[7]) / s; z = 0.25f * s;
+  }
+  float n = rsqrtf(w * w + x * x + y * y + z * z);
+  if (w < 0.f) n = -n;
+  q[0] = w * n; q[1] = x * n; q[2] = y * n; q[3] = z * n;
+}
+
+__device__ inline void rel7(const float* Ra, const float* ta, const float* Rb, const float* tb, float* out) {
+  // a^-1 o b : rot = Ra^T Rb ; trans = Ra^T (tb - ta)      (rigid_utils.py:1031-1045,1075-1085)
+  float R[9];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) R[r * 3 + c] = Ra[r] * Rb[c] + Ra[3 + r] * Rb[3 + c] + Ra[6 + r] * Rb[6 + c];
+  rot_to_quat_closed(R, out);
+  float dx = tb[0] - ta[0], dy = tb[1] - ta[1], dz = tb[2] - ta[2];
+  out[4] = Ra[0] * dx + Ra[3] * dy + Ra[6] * dz;
+  out[5] = Ra[1] * dx + Ra[4] * dy + Ra[7] * dz;
+  out[6] = Ra[2] * dx + Ra[5] * dy + Ra[8] * dz;
+}
+
+__global__ void relative_frames_kernel(const float* __restrict__ srot, const float* __restrict__ strans,
+                                       const float* __restrict__ erot, const float* __restrict__ etrans, int n,
+                                       float* __restrict__ f7, float* __restrict__ r7) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  rel7(srot + (size_t)i * 9, strans + (size_t)i * 3, erot + (size_t)i * 9, etrans + (size_t)i * 3, f7 + (size_t)i * 7);
+  rel7(erot + (size_t)i * 9, etrans + (size_t)i * 3, srot + (size_t)i * 9, strans + (size_t)i * 3, r7 + (size_t)i * 7);
+}
+
+}  // namespace mdgen
