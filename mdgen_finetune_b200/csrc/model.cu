@@ -198,6 +198,7 @@ struct MdgenHandle {
   // conditioning / workspace (valid after set_conditioning)
   int B = 0, T = 0, L = 0;
   bool has_cond = false;
+  bool has_aatype = false;
   std::vector<DevBuf> ws_owned;
   size_t ws_bytes = 0;
   // step-invariant
@@ -412,3 +413,638 @@ static int finalize_weights(MdgenHandle* h, cudaStream_t st) {
 }
 
 }  // namespace mdgen
+
+// =============================================================================================
+// conditioning + workspace
+// =============================================================================================
+namespace mdgen {
+
+static void free_workspace(MdgenHandle* h) {
+  for (auto& b : h->ws_owned) cudaFree(b.p);
+  h->ws_owned.clear();
+  h->ws_bytes = 0;
+  h->has_cond = false;
+}
+
+__global__ void take_first_frame_mask_kernel(const float* __restrict__ mask, int B, int T, int L, float* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * L) return;
+  int b = i / L, l = i % L;
+  out[i] = mask[(size_t)b * T * L + l];
+}
+
+static int alloc_workspace(MdgenHandle* h, int B, int T, int L) {
+  free_workspace(h);
+  const int C = h->C(), D = h->D(), Dc = h->Dc();
+  const size_t N = (size_t)B * T * L;
+  const int streams = h->two_stream() ? 2 : 1;
+  const size_t Mi = (size_t)streams * B * L;
+  const size_t rows = N > Mi ? N : Mi;
+  const size_t asz = h->bf16_mode() ? 2 : 4;
+  const IpaDims d{h->cfg.ipa_heads, h->cfg.ipa_head_dim, h->cfg.ipa_qk, h->cfg.ipa_v};
+#define WS(ptr, bytes) MD_TRY(dev_alloc(h, (void**)&(ptr), (bytes)))
+  WS(h->mask, N * 4);
+  WS(h->mask_bl, (size_t)B * L * 4);
+  WS(h->x_cond, N * Dc * 4);
+  WS(h->cond_mask, N * 8);
+  WS(h->aatype, (size_t)B * L * 8);
+  WS(h->frames_rot, Mi * 9 * 4);
+  WS(h->frames_trans, Mi * 3 * 4);
+  WS(h->rel7, (size_t)2 * B * L * 7 * 4);
+  const int half = C / h->cfg.mha_heads / 2;
+  WS(h->rope_l_cs, (size_t)(L + 1) * half * 4);
+  WS(h->rope_l_sn, (size_t)(L + 1) * half * 4);
+  WS(h->rope_t_cs, (size_t)(T + 1) * half * 4);
+  WS(h->rope_t_sn, (size_t)(T + 1) * half * 4);
+  WS(h->tbuf, (size_t)B * 4);
+  WS(h->tfeat, (size_t)B * 256 * 4);
+  WS(h->th1, (size_t)B * C * 4);
+  WS(h->temb, (size_t)B * C * 4);
+  WS(h->ada, (size_t)B * h->ada_cols * 4);
+  WS(h->xres, N * C * 4);
+  WS(h->hbuf, rows * C * asz);
+  WS(h->qkv, rows * 3 * C * asz);
+  WS(h->att, rows * C * asz);
+  WS(h->mlp, rows * 4 * C * asz);
+  WS(h->vel, N * D * 4);
+  WS(h->ipa_s, Mi * C * 4);
+  WS(h->ipa_n, Mi * C * 4);
+  WS(h->ipa_p, Mi * d.proj_width() * 4);
+  WS(h->ipa_gq, Mi * d.H * d.Pq * 3 * 4);
+  WS(h->ipa_gkv, Mi * d.H * (d.Pq + d.Pv) * 3 * 4);
+  WS(h->ipa_cat, Mi * d.cat_width() * 4);
+  WS(h->ipa_out, (size_t)B * L * C * 4);
+  WS(h->xd, (size_t)B * L * 20 * 4);
+  WS(h->dh_mean, (size_t)B * L * C * 4);
+  WS(h->dh_a, (size_t)B * L * C * 4);
+  WS(h->dh_b, (size_t)B * L * C * 4);
+  WS(h->dh_logits, (size_t)B * L * 20 * 4);
+#undef WS
+  h->B = B;
+  h->T = T;
+  h->L = L;
+  h->streams = streams;
+  return 0;
+}
+
+static int set_conditioning(MdgenHandle* h, int B, int T, int L, const float* mask, const float* srot,
+                            const float* strans, const float* erot, const float* etrans, const float* f7,
+                            const float* r7, const float* x_cond, const int64_t* cmask, const int64_t* aatype,
+                            cudaStream_t st) {
+  MD_CHECK(h->finalized, "weights not finalised");
+  MD_CHECK(B > 0 && T > 0 && L > 0 && mask, "bad shape / mask");
+  if (h->flag(MDGEN_F_ABS_POS)) MD_CHECK(L == h->cfg.crop, "abs_pos_emb needs L == crop (latent_model.py:243-244)");
+  if (h->flag(MDGEN_F_ABS_TIME)) MD_CHECK(T == h->cfg.num_frames, "abs_time_emb needs T == num_frames");
+  const bool pre = h->flag(MDGEN_F_PREPEND_IPA);
+  if (pre) MD_CHECK(srot && strans, "prepend_ipa needs start_frames");
+  if (pre && h->two_stream()) MD_CHECK(erot && etrans, "tps/inpainting needs end_frames");
+  if (B != h->B || T != h->T || L != h->L) MD_TRY(alloc_workspace(h, B, T, L));
+  const size_t N = (size_t)B * T * L, BL = (size_t)B * L;
+  const int Dc = h->Dc();
+  MD_CUDA(cudaMemcpyAsync(h->mask, mask, N * 4, cudaMemcpyDeviceToDevice, st));
+  take_first_frame_mask_kernel<<<(unsigned)((BL + 255) / 256), 256, 0, st>>>(h->mask, B, T, L, h->mask_bl);
+  h->has_cond = false;
+  if (x_cond) {
+    MD_CHECK(cmask, "x_cond needs x_cond_mask");
+    MD_CUDA(cudaMemcpyAsync(h->x_cond, x_cond, N * Dc * 4, cudaMemcpyDeviceToDevice, st));
+    MD_CUDA(cudaMemcpyAsync(h->cond_mask, cmask, N * 8, cudaMemcpyDeviceToDevice, st));
+    h->has_cond = true;
+  }
+  if (aatype) MD_CUDA(cudaMemcpyAsync(h->aatype, aatype, BL * 8, cudaMemcpyDeviceToDevice, st));
+  else MD_CUDA(cudaMemsetAsync(h->aatype, 0xff, BL * 8, st));  // -1 = "None"
+  h->has_aatype = aatype != nullptr;
+  if (pre) {
+    MD_CUDA(cudaMemcpyAsync(h->frames_rot, srot, BL * 36, cudaMemcpyDeviceToDevice, st));
+    MD_CUDA(cudaMemcpyAsync(h->frames_trans, strans, BL * 12, cudaMemcpyDeviceToDevice, st));
+    if (h->two_stream()) {
+      MD_CUDA(cudaMemcpyAsync(h->frames_rot + BL * 9, erot, BL * 36, cudaMemcpyDeviceToDevice, st));
+      MD_CUDA(cudaMemcpyAsync(h->frames_trans + BL * 3, etrans, BL * 12, cudaMemcpyDeviceToDevice, st));
+      float* dr7 = h->rel7;           // stream 0: x_r
+      float* df7 = h->rel7 + BL * 7;  // stream 1: x_f
+      if (f7 && r7) {
+        MD_CUDA(cudaMemcpyAsync(df7, f7, BL * 28, cudaMemcpyDeviceToDevice, st));
+        MD_CUDA(cudaMemcpyAsync(dr7, r7, BL * 28, cudaMemcpyDeviceToDevice, st));
+      } else {
+        relative_frames_kernel<<<(unsigned)((BL + 127) / 128), 128, 0, st>>>(srot, strans, erot, etrans, (int)BL, df7, dr7);
+      }
+    }
+  }
+  if (!h->flag(MDGEN_F_NO_ROPE)) {
+    const int half = h->C() / h->cfg.mha_heads / 2;
+    const Tensor* fl = find_w(h, "layers.0.mha_l.attn.rot_emb.inv_freq");
+    const Tensor* ft = find_w(h, "layers.0.mha_t.attn.rot_emb.inv_freq");
+    MD_CHECK(fl && ft, "missing rot_emb.inv_freq buffers");
+    rope_table_kernel<<<((L + 1) * half + 127) / 128, 128, 0, st>>>(fl->d, half, L + 1, h->rope_l_cs, h->rope_l_sn);
+    rope_table_kernel<<<((T + 1) * half + 127) / 128, 128, 0, st>>>(ft->d, half, T + 1, h->rope_t_cs, h->rope_t_sn);
+  }
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace mdgen
+
+// =============================================================================================
+// forward
+// =============================================================================================
+namespace mdgen {
+
+template <typename AT>
+struct Fwd {
+  MdgenHandle* h;
+  cudaStream_t st;
+  int C, H, hd;
+
+  // y = A . W^T with epilogue; A is the AT activation buffer
+  int gemm(const AT* A, int lda, const LinearW& w, int M, int epi, EpiParams ep, bool out_act) {
+    ep.bias = w.b;
+    if constexpr (sizeof(AT) == 2) {
+      return launch_gemm_tc((const bf16*)A, lda, w.wb, w.K, M, w.N, w.K, epi, out_act, ep, 0, st);
+    } else {
+      return launch_gemm_simt<float, float>(A, lda, w.w, w.K, M, w.N, w.K, epi, ep, st);
+    }
+  }
+  int gemm_f32(const float* A, int lda, const LinearW& w, int M, int epi, EpiParams ep) {
+    ep.bias = w.b;
+    return launch_gemm_simt<float, float>(A, lda, w.w, w.K, M, w.N, w.K, epi, ep, st);
+  }
+  int lnmod(const float* x, AT* out, int M, const float* shift, const float* scale, int rows_per_batch, int nbatch) {
+    if (M <= 0) return 0;
+    ln_modulate_kernel<AT, 384><<<(M * 32 + 255) / 256, 256, 0, st>>>(x, out, M, shift, scale, h->ada_cols,
+                                                                       rows_per_batch, nbatch, nullptr, nullptr, 1e-6f);
+    MD_LAUNCHED();
+    MD_CUDA(cudaGetLastError());
+    return 0;
+  }
+  int attention(const MhaW& m, int nb, int S, int inner, const float* key_valid, int mask_mod, bool frame_axis) {
+    AttnParams<AT> p;
+    p.qkv = (const AT*)h->qkv;
+    p.ld = 3 * C;
+    p.out = (AT*)h->att;
+    p.ldo = C;
+    p.nb = nb;
+    p.S = S;
+    p.inner = inner;
+    p.H = H;
+    p.bias_k = m.bias_k;
+    p.bias_v = m.bias_v;
+    p.key_valid = key_valid;
+    p.mask_mod = mask_mod;
+    const bool rope = !h->flag(MDGEN_F_NO_ROPE);
+    p.cs = rope ? (frame_axis ? h->rope_t_cs : h->rope_l_cs) : nullptr;
+    p.sn = rope ? (frame_axis ? h->rope_t_sn : h->rope_l_sn) : nullptr;
+    return launch_attention_simt<AT>(p, hd, st);
+  }
+  // x += gate * MHA(modulate(LN(x)))      (latent_model.py:384-387, 466-486)
+  int attn_block(float* x, int M, const MhaW& m, const float* ada_row, int chunk0, int rows_per_batch, int nbatch,
+                 int nb, int S, int inner, const float* key_valid, int mask_mod, bool frame_axis) {
+    const float* shift = ada_row + (size_t)chunk0 * C;
+    const float* scale = ada_row + (size_t)(chunk0 + 1) * C;
+    const float* gate = ada_row + (size_t)(chunk0 + 2) * C;
+    MD_TRY(lnmod(x, (AT*)h->hbuf, M, shift, scale, rows_per_batch, nbatch));
+    EpiParams e1;
+    e1.out = h->qkv;
+    e1.ldo = 3 * C;
+    MD_TRY(gemm((const AT*)h->hbuf, C, m.qkv, M, EPI_STORE, e1, true));
+    MD_TRY(attention(m, nb, S, inner, key_valid, mask_mod, frame_axis));
+    EpiParams e2;
+    e2.resid = x;
+    e2.ldr = C;
+    e2.gate = gate;
+    e2.gate_stride = h->ada_cols;
+    e2.rows_per_batch = rows_per_batch;
+    e2.nbatch = nbatch;
+    return gemm((const AT*)h->att, C, m.out, M, EPI_GATE_RESID, e2, false);
+  }
+  // x += gate * fc2(gelu(fc1(modulate(LN(x)))))   (latent_model.py:389-392, 488-491)
+  int mlp_block(float* x, int M, const LinearW& fc1, const LinearW& fc2, const float* ada_row, int chunk0,
+                int rows_per_batch, int nbatch) {
+    const float* shift = ada_row + (size_t)chunk0 * C;
+    const float* scale = ada_row + (size_t)(chunk0 + 1) * C;
+    const float* gate = ada_row + (size_t)(chunk0 + 2) * C;
+    MD_TRY(lnmod(x, (AT*)h->hbuf, M, shift, scale, rows_per_batch, nbatch));
+    EpiParams e1;
+    e1.out = h->mlp;
+    e1.ldo = fc1.N;
+    MD_TRY(gemm((const AT*)h->hbuf, C, fc1, M, EPI_GELU, e1, true));
+    EpiParams e2;
+    e2.resid = x;
+    e2.ldr = C;
+    e2.gate = gate;
+    e2.gate_stride = h->ada_cols;
+    e2.rows_per_batch = rows_per_batch;
+    e2.nbatch = nbatch;
+    return gemm((const AT*)h->mlp, fc1.N, fc2, M, EPI_GATE_RESID, e2, false);
+  }
+};
+
+}  // namespace mdgen
+
+namespace mdgen {
+
+static int rowvec(cudaStream_t st, const float* x, int ldx, int R, const float* W, int K, const float* b, int J,
+                  float* y, int ldy, int in_act, int out_act, int accumulate) {
+  rowvec_linear_kernel<<<(J * 32 + 255) / 256, 256, 0, st>>>(x, ldx, R, W, K, b, J, y, ldy, in_act, out_act, accumulate);
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// run_ipa (latent_model.py:179-214): rows are (stream, b, l); stream 0 = x_r / sim stream with
+// start_frames, stream 1 = x_f with end_frames.  Result ipa_out[b,l,:] = sum over streams.
+template <typename AT>
+static int run_ipa(Fwd<AT>& f, const float* x_in) {
+  MdgenHandle* h = f.h;
+  cudaStream_t st = f.st;
+  const int C = f.C, B = h->B, T = h->T, L = h->L, BL = B * L, M = h->streams * BL;
+  const IpaDims d{h->cfg.ipa_heads, h->cfg.ipa_head_dim, h->cfg.ipa_qk, h->cfg.ipa_v};
+  // ---- initial embedding
+  if (h->two_stream()) {
+    const Tensor* wf = find_w(h, "latent_to_emb_f.weight");
+    const Tensor* bf_ = find_w(h, "latent_to_emb_f.bias");
+    const Tensor* wr = find_w(h, "latent_to_emb_r.weight");
+    const Tensor* br = find_w(h, "latent_to_emb_r.bias");
+    MD_CHECK(wf && bf_ && wr && br, "missing latent_to_emb_f/r");
+    EpiParams e;
+    e.out = h->ipa_s;
+    e.ldo = C;
+    e.bias = br->d;
+    MD_TRY((launch_gemm_simt<float, float>(h->rel7, 7, wr->d, 7, BL, C, 7, EPI_STORE, e, st)));
+    e.out = h->ipa_s + (size_t)BL * C;
+    e.bias = bf_->d;
+    MD_TRY((launch_gemm_simt<float, float>(h->rel7 + (size_t)BL * 7, 7, wf->d, 7, BL, C, 7, EPI_STORE, e, st)));
+  } else {
+    MD_CUDA(cudaMemsetAsync(h->ipa_s, 0, (size_t)M * C * 4, st));
+  }
+  if (h->has_aatype && !h->flag(MDGEN_F_NO_AA_EMB)) {
+    const Tensor* tab = find_w(h, "aatype_to_emb.weight");
+    MD_CHECK(tab, "missing aatype_to_emb.weight");
+    gather_rows_kernel<<<(M * C + 255) / 256, 256, 0, st>>>(tab->d, h->aatype, BL, M, C, h->ipa_s, 1);
+    MD_LAUNCHED();
+  }
+  if (h->flag(MDGEN_F_DESIGN)) {  // x_d = x[..., -20:].mean(1)  (latent_model.py:237-240, 193-194, 205-207)
+    const int D = h->D();
+    mean_over_T_kernel<float><<<(BL * 20 + 255) / 256, 256, 0, st>>>(x_in, D, D - 20, B, T, L, 20, h->xd);
+    MD_LAUNCHED();
+    const Tensor* w = find_w(h, "x_d_to_emb.weight");
+    const Tensor* b = find_w(h, "x_d_to_emb.bias");
+    MD_CHECK(w && b, "missing x_d_to_emb");
+    for (int s = 0; s < h->streams; ++s) {
+      EpiParams e;
+      e.resid = h->ipa_s + (size_t)s * BL * C;
+      e.ldr = C;
+      e.bias = b->d;
+      MD_TRY((launch_gemm_simt<float, float>(h->xd, 20, w->d, 20, BL, C, 20, EPI_RESID, e, st)));
+    }
+  }
+  // ---- layers
+  for (size_t i = 0; i < h->ipa.size(); ++i) {
+    const IpaLayerW& Lw = h->ipa[i];
+    const float* ada_row = h->ada + Lw.ada_off;
+    ln_modulate_kernel<float, 384><<<(M * 32 + 255) / 256, 256, 0, st>>>(h->ipa_s, h->ipa_n, M, nullptr, nullptr, 0, 1, 1,
+                                                                         Lw.norm_w, Lw.norm_b, 1e-5f);
+    MD_LAUNCHED();
+    EpiParams e;
+    e.out = h->ipa_p;
+    e.ldo = d.proj_width();
+    MD_TRY(f.gemm_f32(h->ipa_n, C, Lw.proj, M, EPI_STORE, e));
+    const int npts = M * d.H * (2 * d.Pq + d.Pv);
+    ipa_points_kernel<<<(npts + 255) / 256, 256, 0, st>>>(h->ipa_p, d.proj_width(), d, h->frames_rot, h->frames_trans, M,
+                                                          h->ipa_gq, h->ipa_gkv);
+    MD_LAUNCHED();
+    const size_t smem = (size_t)d.H * (L + 80) * 4;
+    ipa_attention_kernel<<<M, d.H * 32, smem, st>>>(h->ipa_p, d.proj_width(), d, h->ipa_gq, h->ipa_gkv, h->frames_rot,
+                                                   h->frames_trans, Lw.head_w, h->mask_bl, BL, L, h->ipa_cat, 1e5f, 1e-8f);
+    MD_LAUNCHED();
+    MD_CUDA(cudaGetLastError());
+    EpiParams eo;
+    eo.resid = h->ipa_s;
+    eo.ldr = C;
+    MD_TRY(f.gemm_f32(h->ipa_cat, d.cat_width(), Lw.lin_out, M, EPI_RESID, eo));
+    MD_TRY(f.attn_block(h->ipa_s, M, Lw.mha, ada_row, 0, L, B, M / L, L, 1, h->mask_bl, BL, false));
+    MD_TRY(f.mlp_block(h->ipa_s, M, Lw.fc1, Lw.fc2, ada_row, 3, L, B));
+  }
+  // ---- sum streams
+  MD_CUDA(cudaMemcpyAsync(h->ipa_out, h->ipa_s, (size_t)BL * C * 4, cudaMemcpyDeviceToDevice, st));
+  if (h->streams == 2) {
+    axpy_kernel<<<(BL * C + 255) / 256, 256, 0, st>>>(h->ipa_out, h->ipa_s + (size_t)BL * C, 1.f, (size_t)BL * C);
+    MD_LAUNCHED();
+  }
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// One velocity evaluation.  If `state` != null the final epilogue also does state += dt * v
+// (the Euler step fused into the last projection; SURVEY Q4: no clamp on conditioned frames).
+template <typename AT>
+static int forward_impl(MdgenHandle* h, const float* x, const float* t, float* out, float* state, float dt,
+                        cudaStream_t st) {
+  Fwd<AT> f{h, st, h->C(), h->cfg.mha_heads, h->C() / h->cfg.mha_heads};
+  const int C = f.C, B = h->B, T = h->T, L = h->L, D = h->D(), Dc = h->Dc();
+  const int N = B * T * L;
+  const long long l0 = g_launches;
+  // ---- timestep embedding + all adaLN modulations (layers.py:52-55; latent_model.py:252,380,461)
+  const Tensor* w0 = find_w(h, "t_embedder.mlp.0.weight");
+  const Tensor* b0 = find_w(h, "t_embedder.mlp.0.bias");
+  const Tensor* w2 = find_w(h, "t_embedder.mlp.2.weight");
+  const Tensor* b2 = find_w(h, "t_embedder.mlp.2.bias");
+  MD_CHECK(w0 && b0 && w2 && b2, "missing t_embedder weights");
+  timestep_features_kernel<<<(B * 128 + 127) / 128, 128, 0, st>>>(t, h->cfg.time_multiplier, B, h->tfeat);
+  MD_LAUNCHED();
+  MD_TRY(rowvec(st, h->tfeat, 256, B, w0->d, 256, b0->d, C, h->th1, C, 0, 0, 0));
+  MD_TRY(rowvec(st, h->th1, C, B, w2->d, C, b2->d, C, h->temb, C, 1, 0, 0));
+  MD_TRY(rowvec(st, h->temb, C, B, h->ada_w, C, h->ada_b, h->ada_cols, h->ada, h->ada_cols, 1, 0, 0));
+  // ---- prepended IPA stack
+  const bool pre = h->flag(MDGEN_F_PREPEND_IPA);
+  if (pre) MD_TRY(run_ipa<AT>(f, x));
+  // ---- token embedding (latent_model.py:242-255)
+  {
+    const Tensor* wx = find_w(h, "latent_to_emb.weight");
+    const Tensor* bx = find_w(h, "latent_to_emb.bias");
+    const Tensor* wc = find_w(h, "cond_to_emb.weight");
+    const Tensor* bc = find_w(h, "cond_to_emb.bias");
+    const Tensor* me = find_w(h, "mask_to_emb.weight");
+    const Tensor* pe = h->flag(MDGEN_F_ABS_POS) ? find_w(h, "pos_embed") : nullptr;
+    const Tensor* te = h->flag(MDGEN_F_ABS_TIME) ? find_w(h, "time_embed") : nullptr;
+    MD_CHECK(wx && bx && wc && bc && me, "missing embedding weights");
+    if (h->flag(MDGEN_F_ABS_POS)) MD_CHECK(pe, "missing pos_embed");
+    const bool hc = h->has_cond;
+    const size_t smem = (size_t)EMB_TOK * (D + (hc ? Dc : 0)) * 4;
+    embed_kernel<384><<<(N + EMB_TOK - 1) / EMB_TOK, 384, smem, st>>>(
+        x, D, hc ? h->x_cond : nullptr, hc ? Dc : 0, hc ? h->cond_mask : nullptr, wx->d, bx->d, wc->d, bc->d, me->d,
+        pe ? pe->d : nullptr, te ? te->d : nullptr, pre ? h->ipa_out : nullptr, h->xres, N, T, L);
+    MD_LAUNCHED();
+    MD_CUDA(cudaGetLastError());
+  }
+  // ---- factorised spatio-temporal blocks (latent_model.py:456-493)
+  for (size_t i = 0; i < h->layers.size(); ++i) {
+    const MainLayerW& Lw = h->layers[i];
+    const float* ada_row = h->ada + Lw.ada_off;
+    MD_TRY(f.attn_block(h->xres, N, Lw.mha_l, ada_row, 0, T * L, B, B * T, L, 1, h->mask, N, false));
+    MD_TRY(f.attn_block(h->xres, N, Lw.mha_t, ada_row, 3, T * L, B, B * L, T, L, h->mask, N, true));
+    MD_TRY(f.mlp_block(h->xres, N, Lw.fc1, Lw.fc2, ada_row, 6, T * L, B));
+  }
+  // ---- final layer (layers.py:71-75) with optional fused Euler update
+  const bool design = h->flag(MDGEN_F_DESIGN);
+  {
+    const float* ada_row = h->ada + h->ada_final_off;
+    MD_TRY(f.lnmod(h->xres, (AT*)h->hbuf, N, ada_row, ada_row + C, T * L, B));
+    EpiParams e;
+    e.out = out;
+    e.ldo = D;
+    e.resid = design ? nullptr : state;
+    e.ldr = D;
+    e.dt = dt;
+    MD_TRY(f.gemm((const AT*)h->hbuf, C, h->final_lin, N, EPI_EULER, e, false));
+  }
+  if (design) {  // latent_model.py:262-268; mean over T commutes with the linear fc2
+    EpiParams e;
+    e.out = h->mlp;
+    e.ldo = C;
+    // NB: fc1 acts on the un-normalised residual stream x; bf16 mode needs it as AT
+    if constexpr (sizeof(AT) == 2) {
+      f32_to_bf16_kernel<<<(unsigned)(((size_t)N * C + 255) / 256), 256, 0, st>>>(h->xres, (bf16*)h->hbuf, (size_t)N * C, 1.f);
+      MD_LAUNCHED();
+      MD_TRY(f.gemm((const AT*)h->hbuf, C, h->design_fc1, N, EPI_GELU, e, true));
+    } else {
+      MD_TRY(f.gemm((const AT*)h->xres, C, h->design_fc1, N, EPI_GELU, e, true));
+    }
+    mean_over_T_kernel<AT><<<(B * L * C + 255) / 256, 256, 0, st>>>((const AT*)h->mlp, C, 0, B, T, L, C, h->dh_mean);
+    MD_LAUNCHED();
+    const int BL = B * L;
+    EpiParams e2;
+    e2.out = h->dh_a;
+    e2.ldo = C;
+    MD_TRY(f.gemm_f32(h->dh_mean, C, h->design_fc2, BL, EPI_STORE, e2));
+    e2.out = h->dh_b;
+    MD_TRY(f.gemm_f32(h->dh_a, C, h->design_fc3, BL, EPI_GELU, e2));
+    e2.out = h->dh_logits;
+    e2.ldo = 20;
+    MD_TRY(f.gemm_f32(h->dh_b, C, h->design_logits, BL, EPI_STORE, e2));
+    add_logits_kernel<<<(N * 20 + 255) / 256, 256, 0, st>>>(out, D, h->dh_logits, B, T, L);
+    MD_LAUNCHED();
+    if (state) {
+      axpy_kernel<<<(unsigned)(((size_t)N * D + 255) / 256), 256, 0, st>>>(state, out, dt, (size_t)N * D);
+      MD_LAUNCHED();
+    }
+  }
+  MD_CUDA(cudaGetLastError());
+  h->launches_last_forward = (int)(g_launches - l0);
+  return 0;
+}
+
+}  // namespace mdgen
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+namespace mdgen {
+__global__ void fill_t_kernel(float* t, int B, float v) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B) t[i] = v;
+}
+// torch.linspace(0, 1, n) in fp32: start + step*i below the midpoint, end - step*(n-1-i) above it
+static float linspace01(int i, int n) {
+  const float step = 1.0f / (float)(n - 1);
+  return i < n / 2 ? step * (float)i : 1.0f - step * (float)(n - 1 - i);
+}
+static int forward_dispatch(MdgenHandle* h, const float* x, const float* t, float* out, float* state, float dt,
+                            cudaStream_t st) {
+  return h->bf16_mode() ? forward_impl<bf16>(h, x, t, out, state, dt, st) : forward_impl<float>(h, x, t, out, state, dt, st);
+}
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+}  // namespace mdgen
+
+extern "C" {
+
+int mdgen_abi_version(void) { return 1; }
+const char* mdgen_last_error(void) { return g_err.c_str(); }
+
+int mdgen_create(const MdgenConfig* cfg, MdgenHandle** out) {
+  MD_CHECK(cfg && out, "null argument");
+  MD_CHECK(cfg->embed_dim == 384, "kernels are specialised for embed_dim = 384 (parsing.py:86)");
+  MD_CHECK(cfg->mha_heads > 0 && cfg->embed_dim / cfg->mha_heads == 24, "kernels are specialised for head_dim = 24");
+  MD_CHECK(cfg->num_layers > 0 && cfg->latent_dim > 0, "bad config");
+  if (cfg->flags & MDGEN_F_DESIGN) MD_CHECK(cfg->flags & MDGEN_F_PREPEND_IPA, "design requires prepend_ipa (latent_model.py:47-48)");
+  int ndev = 0;
+  MD_CUDA(cudaGetDeviceCount(&ndev));
+  MD_CHECK(ndev > 0, "no CUDA device: libmdgen_b200 has no CPU fallback");
+  MdgenHandle* h = new MdgenHandle();
+  h->cfg = *cfg;
+  MD_CUDA(cudaGetDevice(&h->device));
+  cudaDeviceProp prop;
+  MD_CUDA(cudaGetDeviceProperties(&prop, h->device));
+  if (cfg->precision == MDGEN_PREC_BF16 && prop.major != 10) {
+    delete h;
+    set_error("bf16 tensor-core path needs an sm_100 device (tcgen05/TMEM)");
+    return MDGEN_EINVAL;
+  }
+  *out = h;
+  return MDGEN_OK;
+}
+
+int mdgen_destroy(MdgenHandle* h) {
+  if (!h) return MDGEN_OK;
+  DeviceGuard g(h->device);
+  free_workspace(h);
+  for (void* p : h->packed) cudaFree(p);
+  for (auto& kv : h->weights) cudaFree(kv.second.d);
+  delete h;
+  return MDGEN_OK;
+}
+
+int mdgen_load_weight(MdgenHandle* h, const char* name, const float* data, const int64_t* shape, int32_t ndim,
+                      int32_t is_device, mdgen_stream_t stream) {
+  MD_CHECK(h && name && data && shape && ndim >= 1 && ndim <= 4, "bad argument");
+  DeviceGuard g(h->device);
+  Tensor t;
+  t.shape.assign(shape, shape + ndim);
+  const size_t bytes = t.numel() * 4;
+  auto it = h->weights.find(name);
+  if (it != h->weights.end() && it->second.numel() == t.numel()) {
+    t.d = it->second.d;
+  } else {
+    if (it != h->weights.end()) cudaFree(it->second.d);
+    MD_CUDA(cudaMalloc((void**)&t.d, bytes ? bytes : 16));
+  }
+  MD_CUDA(cudaMemcpyAsync(t.d, data, bytes, is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                          (cudaStream_t)stream));
+  h->weights[name] = t;
+  h->finalized = false;
+  return MDGEN_OK;
+}
+
+int mdgen_finalize_weights(MdgenHandle* h, mdgen_stream_t stream) {
+  MD_CHECK(h, "null handle");
+  DeviceGuard g(h->device);
+  return finalize_weights(h, (cudaStream_t)stream);
+}
+
+int mdgen_set_conditioning(MdgenHandle* h, int32_t B, int32_t T, int32_t L, const float* mask, const float* start_rot,
+                           const float* start_trans, const float* end_rot, const float* end_trans,
+                           const float* rel_f7, const float* rel_r7, const float* x_cond, const int64_t* x_cond_mask,
+                           const int64_t* aatype, mdgen_stream_t stream) {
+  MD_CHECK(h, "null handle");
+  DeviceGuard g(h->device);
+  return set_conditioning(h, B, T, L, mask, start_rot, start_trans, end_rot, end_trans, rel_f7, rel_r7, x_cond,
+                          x_cond_mask, aatype, (cudaStream_t)stream);
+}
+
+int mdgen_forward(MdgenHandle* h, const float* x, const float* t, float* out, mdgen_stream_t stream) {
+  MD_CHECK(h && x && t && out, "null argument");
+  if (!h->finalized || h->B == 0) {
+    set_error("mdgen_forward before finalize_weights / set_conditioning");
+    return MDGEN_ESTATE;
+  }
+  DeviceGuard g(h->device);
+  return forward_dispatch(h, x, t, out, nullptr, 0.f, (cudaStream_t)stream);
+}
+
+int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, float* traj, float* out_final,
+                        mdgen_stream_t stream) {
+  MD_CHECK(h && x0 && out_final && num_steps >= 2, "bad argument");
+  if (!h->finalized || h->B == 0) {
+    set_error("mdgen_euler_rollout before finalize_weights / set_conditioning");
+    return MDGEN_ESTATE;
+  }
+  MD_CHECK(!h->flag(MDGEN_F_DESIGN), "design-mode Dirichlet flow sampler not implemented (DESIGN.md, row N3)");
+  DeviceGuard g(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t n = (size_t)h->B * h->T * h->L * h->D();
+  if (out_final != x0) MD_CUDA(cudaMemcpyAsync(out_final, x0, n * 4, cudaMemcpyDeviceToDevice, st));
+  if (traj) MD_CUDA(cudaMemcpyAsync(traj, x0, n * 4, cudaMemcpyDeviceToDevice, st));
+  for (int i = 0; i < num_steps - 1; ++i) {
+    const float t0 = linspace01(i, num_steps), t1 = linspace01(i + 1, num_steps);
+    fill_t_kernel<<<(h->B + 127) / 128, 128, 0, st>>>(h->tbuf, h->B, t0);
+    MD_LAUNCHED();
+    MD_TRY(forward_dispatch(h, out_final, h->tbuf, h->vel, out_final, t1 - t0, st));
+    if (traj) MD_CUDA(cudaMemcpyAsync(traj + (size_t)(i + 1) * n, out_final, n * 4, cudaMemcpyDeviceToDevice, st));
+  }
+  return MDGEN_OK;
+}
+
+int mdgen_launches_per_forward(MdgenHandle* h) { return h ? h->launches_last_forward : 0; }
+int64_t mdgen_workspace_bytes(MdgenHandle* h) { return h ? (int64_t)h->ws_bytes : 0; }
+
+}  // extern "C"
+
+// ---- unit-test entry points ------------------------------------------------------------------
+extern "C" {
+
+int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float* W, const float* bias, float* Cout,
+                    int32_t use_tc, int32_t block_n, mdgen_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  EpiParams ep;
+  ep.bias = bias;
+  ep.out = Cout;
+  ep.ldo = N;
+  if (!use_tc) return launch_gemm_simt<float, float>(A, K, W, K, M, N, K, EPI_STORE, ep, st);
+  bf16 *Ab = nullptr, *Wb = nullptr;
+  MD_CUDA(cudaMalloc((void**)&Ab, (size_t)M * K * 2));
+  MD_CUDA(cudaMalloc((void**)&Wb, (size_t)N * K * 2));
+  f32_to_bf16_kernel<<<(unsigned)(((size_t)M * K + 255) / 256), 256, 0, st>>>(A, Ab, (size_t)M * K, 1.f);
+  f32_to_bf16_kernel<<<(unsigned)(((size_t)N * K + 255) / 256), 256, 0, st>>>(W, Wb, (size_t)N * K, 1.f);
+  int r = launch_gemm_tc(Ab, K, Wb, K, M, N, K, EPI_STORE, false, ep, block_n, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  cudaFree(Ab);
+  cudaFree(Wb);
+  if (r == 0 && e != cudaSuccess) {
+    set_error(std::string("gemm_tc kernel: ") + cudaGetErrorString(e));
+    return MDGEN_ECUDA;
+  }
+  return r;
+}
+
+int mdgen_test_attention(int32_t nb, int32_t S, int32_t inner, int32_t heads, int32_t head_dim, const float* qkv,
+                         const float* bias_k, const float* bias_v, const float* key_valid, float* out, int32_t use_tc,
+                         int32_t rope, mdgen_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  MD_CHECK(!use_tc, "tcgen05 attention core not built yet");
+  const int C = heads * head_dim, half = head_dim / 2;
+  float *cs = nullptr, *sn = nullptr, *inv = nullptr;
+  if (rope) {
+    std::vector<float> f(half);
+    for (int i = 0; i < half; ++i) f[i] = 1.0f / powf(10000.0f, (float)(2 * i) / (float)head_dim);
+    MD_CUDA(cudaMalloc((void**)&inv, half * 4));
+    MD_CUDA(cudaMalloc((void**)&cs, (size_t)(S + 1) * half * 4));
+    MD_CUDA(cudaMalloc((void**)&sn, (size_t)(S + 1) * half * 4));
+    MD_CUDA(cudaMemcpyAsync(inv, f.data(), half * 4, cudaMemcpyHostToDevice, st));
+    rope_table_kernel<<<((S + 1) * half + 127) / 128, 128, 0, st>>>(inv, half, S + 1, cs, sn);
+  }
+  AttnParams<float> p;
+  p.qkv = qkv;
+  p.ld = 3 * C;
+  p.out = out;
+  p.ldo = C;
+  p.nb = nb;
+  p.S = S;
+  p.inner = inner;
+  p.H = heads;
+  p.bias_k = bias_k;
+  p.bias_v = bias_v;
+  p.key_valid = key_valid;
+  p.mask_mod = nb * S;
+  p.cs = cs;
+  p.sn = sn;
+  int r = launch_attention_simt<float>(p, head_dim, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  cudaFree(cs);
+  cudaFree(sn);
+  cudaFree(inv);
+  if (r == 0 && e != cudaSuccess) {
+    set_error(std::string("attention kernel: ") + cudaGetErrorString(e));
+    return MDGEN_ECUDA;
+  }
+  return r;
+}
+
+}  // extern "C"
