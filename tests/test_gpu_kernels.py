@@ -1,0 +1,91 @@
+"""Kernel-level parity on the B200, through the C-ABI test entry points."""
+import ctypes
+
+import pytest
+import torch
+
+from mdgen_finetune_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+
+
+def _p(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _gemm(A, W, b, use_tc, block_n=0):
+    M, K = A.shape
+    N = W.shape[0]
+    C = torch.full((M, N), float("nan"), device="cuda")
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(_lib.lib().mdgen_test_gemm(M, N, K, _p(A), _p(W), _p(b), _p(C), use_tc, block_n, st), "test_gemm")
+    torch.cuda.synchronize()
+    return C
+
+
+@pytest.mark.parametrize("M,N,K", [(64, 64, 16), (100, 72, 40), (257, 672, 384), (33, 384, 256), (5, 20, 7)])
+def test_gemm_simt_fp32(M, N, K):
+    g = torch.Generator().manual_seed(M + N + K)
+    A, W, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g), torch.randn(N, generator=g)
+    C = _gemm(A.cuda(), W.cuda(), b.cuda(), 0).cpu()
+    ref = (A.double() @ W.double().T + b.double()).float()
+    assert float((C - ref).norm() / ref.norm()) < 2e-6
+
+
+@pytest.mark.parametrize("M,N,K,bn", [(128, 128, 64, 128), (128, 128, 384, 128), (256, 256, 384, 128),
+                                      (4000, 1152, 384, 0), (4000, 384, 1536, 0), (1000, 384, 384, 64),
+                                      (777, 1536, 384, 128), (300, 21, 384, 0), (129, 48, 384, 64)])
+def test_gemm_tcgen05_bf16(M, N, K, bn):
+    g = torch.Generator().manual_seed(M + N + K)
+    A, W, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5, torch.randn(N, generator=g)
+    C = _gemm(A.cuda(), W.cuda(), b.cuda(), 1, bn).cpu()
+    ref = (A.bfloat16().double() @ W.bfloat16().double().T + b.double()).float()   # same bf16 operands
+    assert torch.isfinite(C).all(), "unwritten / non-finite outputs"
+    err = float((C - ref).norm() / ref.norm())
+    assert err < 1e-5, err          # fp32 accumulation of identical bf16 products
+
+
+def _attn_ref(qkv, bk, bv, valid, nb, S, inner, H, hd, rope):
+    from oracle import mdgen_oracle as O
+    C = H * hd
+    rows = torch.tensor([[(b // inner) * S * inner + s * inner + (b % inner) for s in range(S)] for b in range(nb)])
+    x = qkv[rows]                                           # [nb,S,3C]
+    q, k, v = x[..., :C], x[..., C:2 * C], x[..., 2 * C:]
+    k = torch.cat([k, bk.view(1, 1, C).expand(nb, 1, C)], 1)
+    v = torch.cat([v, bv.view(1, 1, C).expand(nb, 1, C)], 1)
+    pad = torch.cat([valid[rows] == 0, torch.zeros(nb, 1, dtype=torch.bool)], 1)
+    q = q.view(nb, S, H, hd).transpose(1, 2)
+    k = k.view(nb, S + 1, H, hd).transpose(1, 2)
+    v = v.view(nb, S + 1, H, hd).transpose(1, 2)
+    if rope:
+        cos, sin = O.rope_tables(S + 1, hd)
+        q = q * cos[:S] + O._rot_half(q) * sin[:S]
+        k = k * cos + O._rot_half(k) * sin
+    a = (q @ k.transpose(-1, -2)).masked_fill(pad[:, None, None, :], float("-inf")).softmax(-1)
+    o = (a @ v).transpose(1, 2).reshape(nb, S, C)
+    out = torch.zeros(nb * S, C)
+    out[rows.reshape(-1)] = o.reshape(nb * S, C)
+    return out
+
+
+@pytest.mark.parametrize("nb,S,inner,rope", [(6, 4, 1, 1), (8, 37, 4, 1), (4, 200, 2, 1), (3, 130, 1, 0), (2, 1000, 2, 1)])
+def test_attention_simt(nb, S, inner, rope):
+    H, hd = 16, 24
+    C = H * hd
+    g = torch.Generator().manual_seed(nb * 1000 + S)
+    qkv = torch.randn(nb * S, 3 * C, generator=g) * 0.7
+    bk, bv = torch.randn(C, generator=g), torch.randn(C, generator=g)
+    valid = (torch.rand(nb * S, generator=g) > 0.2).float()
+    valid[:S * inner] = 1.0
+    if nb > 2:
+        valid[attn_rows(1, S, inner)] = 0.0      # one fully padded sequence: only the bias token is attended
+    out = torch.empty(nb * S, C, device="cuda")
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(_lib.lib().mdgen_test_attention(nb, S, inner, H, hd, _p(qkv.cuda()), _p(bk.cuda()), _p(bv.cuda()),
+                                               _p(valid.cuda()), _p(out), 0, rope, st), "test_attention")
+    ref = _attn_ref(qkv, bk, bv, valid, nb, S, inner, H, hd, rope)
+    assert float((out.cpu() - ref).norm() / ref.norm()) < 1e-5
+
+
+def attn_rows(b, S, inner):
+    return torch.tensor([(b // inner) * S * inner + s * inner + (b % inner) for s in range(S)])
