@@ -112,8 +112,16 @@ int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, floa
 /* introspection ------------------------------------------------------------------------ */
 /* Number of kernels one mdgen_forward launches for the current conditioning shape. */
 int mdgen_launches_per_forward(MdgenHandle* h);
+/* Total kernels launched by the library on the calling thread since load. */
+long long mdgen_launch_count(void);
 /* Bytes of device workspace currently held by the handle. */
 int64_t mdgen_workspace_bytes(MdgenHandle* h);
+
+/* Per-kernel-family device timing (CUDA events on the launching stream) for bench.py's roofline:
+ * between begin and end every launch of the library is bracketed by two events.  ncat <= 10. */
+int mdgen_profile_begin(void);
+int mdgen_profile_end(float* ms_by_cat, int32_t* launches_by_cat, int32_t ncat);
+const char* mdgen_profile_category_name(int32_t i);
 
 /* unit-test entry points (tests/ only): run one kernel family on caller buffers --------- */
 /* C[M,N] = A[M,K] . W[N,K]^T + bias, A/W fp32 on device (converted to bf16 inside when

@@ -20,7 +20,8 @@ F_SIM, F_TPS, F_INPAINT, F_DESIGN, F_NO_AA_EMB, F_ABS_POS, F_ABS_TIME, F_NO_ROPE
 PREC_BF16, PREC_FP32_CHECK = 0, 1
 EXPORTS = ["mdgen_create", "mdgen_destroy", "mdgen_last_error", "mdgen_abi_version", "mdgen_load_weight",
            "mdgen_finalize_weights", "mdgen_set_conditioning", "mdgen_forward", "mdgen_euler_rollout",
-           "mdgen_launches_per_forward", "mdgen_workspace_bytes", "mdgen_test_gemm", "mdgen_test_attention"]
+           "mdgen_launches_per_forward", "mdgen_launch_count", "mdgen_workspace_bytes", "mdgen_profile_begin", "mdgen_profile_end",
+           "mdgen_profile_category_name", "mdgen_test_gemm", "mdgen_test_attention"]
 
 
 class MdgenConfig(ctypes.Structure):
@@ -80,10 +81,15 @@ def lib():
     L.mdgen_launches_per_forward.argtypes = [vp]
     L.mdgen_workspace_bytes.argtypes = [vp]
     L.mdgen_workspace_bytes.restype = ctypes.c_int64
+    L.mdgen_launch_count.restype = ctypes.c_int64
     L.mdgen_test_gemm.argtypes = [i32, i32, i32, fp, fp, fp, fp, i32, i32, vp]
     L.mdgen_test_attention.argtypes = [i32] * 5 + [fp] * 5 + [i32, i32, vp]
+    L.mdgen_profile_end.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int32), i32]
+    L.mdgen_profile_category_name.argtypes = [i32]
+    L.mdgen_profile_category_name.restype = ctypes.c_char_p
     for name in EXPORTS:
-        if name not in ("mdgen_last_error", "mdgen_workspace_bytes"):
+        if name not in ("mdgen_last_error", "mdgen_workspace_bytes", "mdgen_profile_category_name",
+                        "mdgen_launch_count"):
             getattr(L, name).restype = ctypes.c_int32
     _lib = L
     return L
@@ -97,3 +103,18 @@ def check(status, what="mdgen"):
     if status == -1:
         raise ValueError(f"{what}: {msg}")
     raise RuntimeError(f"{what} failed ({status}): {msg}")
+
+
+NCAT = 10
+
+
+def profile_begin():
+    check(lib().mdgen_profile_begin(), "mdgen_profile_begin")
+
+
+def profile_end():
+    """{category: (total_ms, launches)} for the launches since profile_begin()."""
+    ms = (ctypes.c_float * NCAT)()
+    n = (ctypes.c_int32 * NCAT)()
+    check(lib().mdgen_profile_end(ms, n, NCAT), "mdgen_profile_end")
+    return {lib().mdgen_profile_category_name(i).decode(): (float(ms[i]), int(n[i])) for i in range(NCAT) if n[i]}

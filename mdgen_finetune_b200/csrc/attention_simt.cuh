@@ -202,6 +202,7 @@ template <typename AT>
 inline int launch_attention_simt(const AttnParams<AT>& p, int head_dim, cudaStream_t st) {
   MD_CHECK(head_dim == 24, "attention_simt: head_dim must be 24");
   if (p.nb <= 0 || p.S <= 0) return 0;
+  ProfScope ps(p.S <= 16 ? PC_ATTN_SHORT : PC_ATTN_SIMT, st);
   if (p.S <= 16) {
     long long total = (long long)p.nb * p.S * p.H;
     attention_short_kernel<AT, 24><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(p, total);

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 namespace mdgen {
 
@@ -38,6 +39,33 @@ void set_error(const std::string& msg);
 // launch counter: every kernel launch of the library goes through MD_LAUNCHED()
 extern thread_local long long g_launches;
 #define MD_LAUNCHED() (++mdgen::g_launches)
+
+// optional per-kernel-family timing with CUDA events on the launching stream (bench.py roofline)
+enum ProfCat : int { PC_GEMM_TC = 0, PC_GEMM_SIMT, PC_ATTN_TC, PC_ATTN_SIMT, PC_ATTN_SHORT, PC_LN, PC_EMBED, PC_IPA,
+                     PC_ADALN, PC_MISC, PC_COUNT };
+struct ProfRec { int cat; cudaEvent_t a, b; };
+struct Profiler {
+  bool on = false;
+  std::vector<ProfRec> recs;
+};
+extern Profiler g_prof;
+struct ProfScope {
+  cudaStream_t st;
+  bool active;
+  ProfRec r;
+  ProfScope(int cat, cudaStream_t s) : st(s), active(g_prof.on) {
+    if (!active) return;
+    r.cat = cat;
+    cudaEventCreate(&r.a);
+    cudaEventCreate(&r.b);
+    cudaEventRecord(r.a, st);
+  }
+  ~ProfScope() {
+    if (!active) return;
+    cudaEventRecord(r.b, st);
+    g_prof.recs.push_back(r);
+  }
+};
 
 // ---- device helpers ------------------------------------------------------------------
 __device__ __forceinline__ float to_f(float v) { return v; }

@@ -83,6 +83,7 @@ template <typename AT, typename OT>
 inline int launch_gemm_simt(const AT* A, int lda, const float* W, int ldw, int M, int N, int K, int epi,
                             const EpiParams& p, cudaStream_t st) {
   if (M <= 0 || N <= 0) return 0;
+  ProfScope ps(PC_GEMM_SIMT, st);
   dim3 grid((N + SG_BN - 1) / SG_BN, (M + SG_BM - 1) / SG_BM);
   gemm_simt_kernel<AT, OT><<<grid, 256, 0, st>>>(A, lda, W, ldw, M, N, K, epi, p);
   MD_LAUNCHED();

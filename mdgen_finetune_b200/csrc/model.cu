@@ -23,6 +23,7 @@ namespace mdgen {
 
 static thread_local std::string g_err;
 thread_local long long g_launches = 0;
+Profiler g_prof;
 void set_error(const std::string& msg) { g_err = msg; }
 
 // ---- driver entry point for TMA descriptors (no link-time dependency on libcuda) ----------
@@ -79,6 +80,7 @@ static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, int M, i
   }
   int tiles = ((M + tc::BLOCK_M - 1) / tc::BLOCK_M) * ((N + BN - 1) / BN);
   int grid = tiles < num_sms() ? tiles : num_sms();
+  ProfScope ps(PC_GEMM_TC, st);
   kern<<<grid, tc::NUM_THREADS, tc::smem_bytes(BN), st>>>(ta, tw, M, N, K, ep);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
@@ -569,6 +571,7 @@ struct Fwd {
   }
   int lnmod(const float* x, AT* out, int M, const float* shift, const float* scale, int rows_per_batch, int nbatch) {
     if (M <= 0) return 0;
+    ProfScope ps(PC_LN, st);
     ln_modulate_kernel<AT, 384><<<(M * 32 + 255) / 256, 256, 0, st>>>(x, out, M, shift, scale, h->ada_cols,
                                                                        rows_per_batch, nbatch, nullptr, nullptr, 1e-6f);
     MD_LAUNCHED();
@@ -643,6 +646,7 @@ namespace mdgen {
 
 static int rowvec(cudaStream_t st, const float* x, int ldx, int R, const float* W, int K, const float* b, int J,
                   float* y, int ldy, int in_act, int out_act, int accumulate) {
+  ProfScope ps(PC_ADALN, st);
   rowvec_linear_kernel<<<(J * 32 + 255) / 256, 256, 0, st>>>(x, ldx, R, W, K, b, J, y, ldy, in_act, out_act, accumulate);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
@@ -708,6 +712,8 @@ static int run_ipa(Fwd<AT>& f, const float* x_in) {
     e.ldo = d.proj_width();
     MD_TRY(f.gemm_f32(h->ipa_n, C, Lw.proj, M, EPI_STORE, e));
     const int npts = M * d.H * (2 * d.Pq + d.Pv);
+    {
+    ProfScope ps(PC_IPA, st);
     ipa_points_kernel<<<(npts + 255) / 256, 256, 0, st>>>(h->ipa_p, d.proj_width(), d, h->frames_rot, h->frames_trans, M,
                                                           h->ipa_gq, h->ipa_gkv);
     MD_LAUNCHED();
@@ -715,6 +721,7 @@ static int run_ipa(Fwd<AT>& f, const float* x_in) {
     ipa_attention_kernel<<<M, d.H * 32, smem, st>>>(h->ipa_p, d.proj_width(), d, h->ipa_gq, h->ipa_gkv, h->frames_rot,
                                                    h->frames_trans, Lw.head_w, h->mask_bl, BL, L, h->ipa_cat, 1e5f, 1e-8f);
     MD_LAUNCHED();
+    }
     MD_CUDA(cudaGetLastError());
     EpiParams eo;
     eo.resid = h->ipa_s;
@@ -769,6 +776,7 @@ static int forward_impl(MdgenHandle* h, const float* x, const float* t, float* o
     if (h->flag(MDGEN_F_ABS_POS)) MD_CHECK(pe, "missing pos_embed");
     const bool hc = h->has_cond;
     const size_t smem = (size_t)EMB_TOK * (D + (hc ? Dc : 0)) * 4;
+    ProfScope ps(PC_EMBED, st);
     embed_kernel<384><<<(N + EMB_TOK - 1) / EMB_TOK, 384, smem, st>>>(
         x, D, hc ? h->x_cond : nullptr, hc ? Dc : 0, hc ? h->cond_mask : nullptr, wx->d, bx->d, wc->d, bc->d, me->d,
         pe ? pe->d : nullptr, te ? te->d : nullptr, pre ? h->ipa_out : nullptr, h->xres, N, T, L);
@@ -972,6 +980,38 @@ int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, floa
   return MDGEN_OK;
 }
 
+int mdgen_profile_begin(void) {
+  g_prof.recs.clear();
+  g_prof.on = true;
+  return MDGEN_OK;
+}
+int mdgen_profile_end(float* ms_by_cat, int32_t* launches_by_cat, int32_t ncat) {
+  g_prof.on = false;
+  for (int i = 0; i < ncat; ++i) {
+    ms_by_cat[i] = 0.f;
+    launches_by_cat[i] = 0;
+  }
+  for (auto& r : g_prof.recs) {
+    cudaEventSynchronize(r.b);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    if (r.cat < ncat) {
+      ms_by_cat[r.cat] += ms;
+      launches_by_cat[r.cat] += 1;
+    }
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  g_prof.recs.clear();
+  return MDGEN_OK;
+}
+const char* mdgen_profile_category_name(int32_t i) {
+  static const char* names[PC_COUNT] = {"gemm_tcgen05", "gemm_simt_fp32", "attention_tcgen05", "attention_simt",
+                                        "attention_short", "layernorm_modulate", "embed", "ipa", "adaln_rowvec", "misc"};
+  return (i >= 0 && i < PC_COUNT) ? names[i] : "";
+}
+
+long long mdgen_launch_count(void) { return g_launches; }
 int mdgen_launches_per_forward(MdgenHandle* h) { return h ? h->launches_last_forward : 0; }
 int64_t mdgen_workspace_bytes(MdgenHandle* h) { return h ? (int64_t)h->ws_bytes : 0; }
 

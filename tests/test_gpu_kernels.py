@@ -81,8 +81,9 @@ def test_attention_simt(nb, S, inner, rope):
         valid[attn_rows(1, S, inner)] = 0.0      # one fully padded sequence: only the bias token is attended
     out = torch.empty(nb * S, C, device="cuda")
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-    _lib.check(_lib.lib().mdgen_test_attention(nb, S, inner, H, hd, _p(qkv.cuda()), _p(bk.cuda()), _p(bv.cuda()),
-                                               _p(valid.cuda()), _p(out), 0, rope, st), "test_attention")
+    dq, dk, dv, dm = qkv.cuda(), bk.cuda(), bv.cuda(), valid.cuda()     # keep alive across the call
+    _lib.check(_lib.lib().mdgen_test_attention(nb, S, inner, H, hd, _p(dq), _p(dk), _p(dv), _p(dm), _p(out), 0,
+                                               rope, st), "test_attention")
     ref = _attn_ref(qkv, bk, bv, valid, nb, S, inner, H, hd, rope)
     assert float((out.cpu() - ref).norm() / ref.norm()) < 1e-5
 

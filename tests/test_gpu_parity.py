@@ -66,7 +66,7 @@ def test_euler_rollout_vs_reference_sampler(name, prec):
         assert rel_l2(traj, g["euler_traj"]) < TOL[prec] * 2
     # the generic python loop over m.forward must agree with the fused C-ABI rollout
     loop = fn(inp["x0"].cuda(), lambda x, t, **k: m.forward(x, t, **kw)).cpu()
-    assert rel_l2(loop[-1], traj[-1]) < 1e-5
+    assert rel_l2(loop[-1], traj[-1]) < (1e-5 if prec == "fp32" else 2e-3)
 
 
 def test_closed_form_quaternion_matches_eigh_up_to_sign():
