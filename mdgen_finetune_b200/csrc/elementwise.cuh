@@ -202,4 +202,9 @@ __global__ void f32_to_bf16_kernel(const float* __restrict__ x, bf16* __restrict
   if (i < n) y[i] = __float2bfloat16_rn(x[i] * scale);
 }
 
+__global__ void bf16_to_f32_kernel(const bf16* __restrict__ x, float* __restrict__ y, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = __bfloat162float(x[i]);
+}
+
 }  // namespace mdgen

@@ -2,7 +2,7 @@
 //   C[M,N] = A[M,K] . W[N,K]^T (+ fused epilogue), A and W both K-major bf16 in HBM.
 // Persistent, warp-specialised: warp 0 = TMA producer (cp.async.bulk.tensor, SWIZZLE_128B),
 // warp 1 = single-thread tcgen05.mma issuer (accumulators in TMEM, 2 accumulator stages so the
-// epilogue of tile i overlaps the main loop of tile i+1), warps 2..5 = epilogue
+// epilogue of tile i overlaps the main loop of tile i+1), warps 2..9 = epilogue
 // (tcgen05.ld -> bias / erf-GELU / adaLN gate + residual / Euler -> global).
 // Covers q/k/v (fused N = 3C), out_proj, fc1, fc2 of every block (latent_model.py:385-392,466-491;
 // mha.py:260-262,397) and the final projection (layers.py:74).
@@ -17,7 +17,8 @@ namespace tc {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_EPI_WARPS = 8;          // two warps per TMEM lane quarter, each takes half of the columns
+constexpr int NUM_THREADS = 64 + 32 * NUM_EPI_WARPS;
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
 
 __host__ __device__ constexpr int stage_bytes(int bn) { return A_STAGE_BYTES + bn * BLOCK_K * 2; }
@@ -98,6 +99,21 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// erf-GELU (layers.py:78-85) with erf from Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7) on the MUFU
+// ex2/rcp units: the exact erff costs ~3x more issue slots than the tile's MMA time allows.
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  float t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-z * z * 1.4426950408889634f));
+  float poly = fmaf(t, 1.061405429f, -1.453152027f);
+  poly = fmaf(t, poly, 1.421413741f);
+  poly = fmaf(t, poly, -0.284496736f);
+  poly = fmaf(t, poly, 0.254829592f);
+  const float erf_abs = fmaf(-poly * t, e, 1.0f);
+  return 0.5f * x * (1.0f + copysignf(erf_abs, x));
+}
+
 // ---- epilogue on 32 consecutive accumulator columns of one row --------------------------
 template <int EPI, typename OT>
 __device__ __forceinline__ void epilogue_chunk(const EpiParams& p, int m, int n0, int N, const uint32_t* r) {
@@ -108,7 +124,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& p, int m, int n0
   if constexpr (EPI == EPI_STORE || EPI == EPI_GELU) {
     if constexpr (EPI == EPI_GELU) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+      for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
     }
     OT* o = reinterpret_cast<OT*>(p.out) + (size_t)m * p.ldo + n0;
     if (full && (p.ldo % 8 == 0)) {
@@ -193,7 +209,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4);
+      mbar_init(&tmem_empty[s], NUM_EPI_WARPS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -265,8 +281,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       }
     }
   } else {
-    // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4 =====
-    const int quarter = warp & 3;
+    // ===== epilogue warps 2..9: TMEM lane quarter = warp % 4, column half = (warp - 2) / 4 =====
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    constexpr int CHUNKS = BN / 32;                      // 32-column chunks per tile
+    constexpr int PER = (CHUNKS + 1) / 2;                // chunks per warp
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -275,17 +293,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       tcgen05_fence_after();
       const int m = mb * BLOCK_M + quarter * 32 + lane;
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+      uint32_t r[PER][32];
 #pragma unroll
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        const int n0 = nb * BN + c * 32;
-        if (m < M && n0 < N) epilogue_chunk<EPI, OT>(ep, m, n0, N, r);
+      for (int i = 0; i < PER; ++i) {
+        const int c = half * PER + i;
+        if (c < CHUNKS) tmem_ld_32x32b_x32(taddr + c * 32, r[i]);
       }
+      tmem_ld_wait();
+      // accumulator is in registers: hand the TMEM stage back before the math / stores
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+#pragma unroll
+      for (int i = 0; i < PER; ++i) {
+        const int c = half * PER + i;
+        const int n0 = nb * BN + c * 32;
+        if (c < CHUNKS && m < M && n0 < N) epilogue_chunk<EPI, OT>(ep, m, n0, N, r[i]);
+      }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;

@@ -13,6 +13,7 @@
 
 #include "../../include/mdgen_b200.h"
 #include "attention_simt.cuh"
+#include "attention_tc.cuh"
 #include "common.cuh"
 #include "elementwise.cuh"
 #include "gemm_simt.cuh"
@@ -595,6 +596,9 @@ struct Fwd {
     const bool rope = !h->flag(MDGEN_F_NO_ROPE);
     p.cs = rope ? (frame_axis ? h->rope_t_cs : h->rope_l_cs) : nullptr;
     p.sn = rope ? (frame_axis ? h->rope_t_sn : h->rope_l_sn) : nullptr;
+    if constexpr (sizeof(AT) == 2) {
+      if (attention_tc_supported(p, hd) && !getenv("MDGEN_NO_ATTN_TC")) return launch_attention_tc(p, hd, st);
+    }
     return launch_attention_simt<AT>(p, hd, st);
   }
   // x += gate * MHA(modulate(LN(x)))      (latent_model.py:384-387, 466-486)
@@ -1048,7 +1052,6 @@ int mdgen_test_attention(int32_t nb, int32_t S, int32_t inner, int32_t heads, in
                          const float* bias_k, const float* bias_v, const float* key_valid, float* out, int32_t use_tc,
                          int32_t rope, mdgen_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
-  MD_CHECK(!use_tc, "tcgen05 attention core not built yet");
   const int C = heads * head_dim, half = head_dim / 2;
   float *cs = nullptr, *sn = nullptr, *inv = nullptr;
   if (rope) {
@@ -1075,8 +1078,24 @@ int mdgen_test_attention(int32_t nb, int32_t S, int32_t inner, int32_t heads, in
   p.mask_mod = nb * S;
   p.cs = cs;
   p.sn = sn;
-  int r = launch_attention_simt<float>(p, head_dim, st);
+  int r = 0;
+  bf16 *qb = nullptr, *ob = nullptr;
+  if (use_tc) {
+    const size_t rows = (size_t)nb * S;
+    MD_CUDA(cudaMalloc((void**)&qb, rows * 3 * C * 2));
+    MD_CUDA(cudaMalloc((void**)&ob, rows * C * 2));
+    f32_to_bf16_kernel<<<(unsigned)((rows * 3 * C + 255) / 256), 256, 0, st>>>(qkv, qb, rows * 3 * C, 1.f);
+    AttnParams<bf16> pb;
+    pb.qkv = qb; pb.ld = 3 * C; pb.out = ob; pb.ldo = C; pb.nb = nb; pb.S = S; pb.inner = inner; pb.H = heads;
+    pb.bias_k = bias_k; pb.bias_v = bias_v; pb.key_valid = key_valid; pb.mask_mod = nb * S; pb.cs = cs; pb.sn = sn;
+    r = launch_attention_tc(pb, head_dim, st);
+    if (r == 0) bf16_to_f32_kernel<<<(unsigned)((rows * C + 255) / 256), 256, 0, st>>>(ob, out, rows * C);
+  } else {
+    r = launch_attention_simt<float>(p, head_dim, st);
+  }
   cudaError_t e = cudaStreamSynchronize(st);
+  cudaFree(qb);
+  cudaFree(ob);
   cudaFree(cs);
   cudaFree(sn);
   cudaFree(inv);
