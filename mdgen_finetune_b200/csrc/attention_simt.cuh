@@ -30,6 +30,41 @@ __host__ __device__ __forceinline__ size_t attn_row(int nbi, int s, int S, int i
   return (size_t)(nbi / inner) * S * inner + (size_t)s * inner + (nbi % inner);
 }
 
+// 24 contiguous elements (16-byte aligned) -> fp32 registers with 128-bit loads
+__device__ __forceinline__ void load24(const float* p, float* o) {
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p) + i);
+    o[4 * i] = v.x; o[4 * i + 1] = v.y; o[4 * i + 2] = v.z; o[4 * i + 3] = v.w;
+  }
+}
+__device__ __forceinline__ void load24(const bf16* p, float* o) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p) + i);
+    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = __bfloat1622float2(h2[j]);
+      o[8 * i + 2 * j] = f.x; o[8 * i + 2 * j + 1] = f.y;
+    }
+  }
+}
+__device__ __forceinline__ void store24(float* p, const float* o) {
+#pragma unroll
+  for (int i = 0; i < 6; ++i) reinterpret_cast<float4*>(p)[i] = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+}
+__device__ __forceinline__ void store24(bf16* p, const float* o) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    uint4 v;
+    __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) h2[j] = __floats2bfloat162_rn(o[8 * i + 2 * j], o[8 * i + 2 * j + 1]);
+    reinterpret_cast<uint4*>(p)[i] = v;
+  }
+}
+
 constexpr int AS_THREADS = 128;
 constexpr int AS_CHUNK = 64;
 
@@ -146,10 +181,11 @@ attention_short_kernel(AttnParams<AT> p, long long total) {
   const int C = p.H * HD;
   float q[HD], acc[HD];
   {
-    const AT* qr = p.qkv + attn_row(nbi, qi, p.S, p.inner) * p.ld + h * HD;
+    float raw[HD];
+    load24(p.qkv + attn_row(nbi, qi, p.S, p.inner) * p.ld + h * HD, raw);
 #pragma unroll
     for (int i = 0; i < HALF; ++i) {
-      float a = to_f(qr[i]), b = to_f(qr[i + HALF]);
+      float a = raw[i], b = raw[i + HALF];
       float c = 1.f, s = 0.f;
       if (p.cs) { c = p.cs[qi * HALF + i]; s = p.sn[qi * HALF + i]; }
       q[i] = a * c - b * s;
@@ -165,8 +201,8 @@ attention_short_kernel(AttnParams<AT> p, long long total) {
       const size_t r = attn_row(nbi, key, p.S, p.inner);
       if (p.key_valid[r % p.mask_mod] == 0.f) continue;
       const AT* kr = p.qkv + r * p.ld + C + h * HD;
-#pragma unroll
-      for (int i = 0; i < HD; ++i) { kv[i] = to_f(kr[i]); vv[i] = to_f(kr[C + i]); }
+      load24(kr, kv);
+      load24(kr + C, vv);
     } else {
 #pragma unroll
       for (int i = 0; i < HD; ++i) { kv[i] = p.bias_k[h * HD + i]; vv[i] = p.bias_v[h * HD + i]; }
@@ -192,10 +228,10 @@ attention_short_kernel(AttnParams<AT> p, long long total) {
 #pragma unroll
     for (int i = 0; i < HD; ++i) acc[i] = fmaf(pr, vv[i], acc[i]);
   }
-  AT* o = p.out + attn_row(nbi, qi, p.S, p.inner) * p.ldo + h * HD;
   const float inv = 1.0f / lrun;
 #pragma unroll
-  for (int i = 0; i < HD; ++i) o[i] = from_f<AT>(acc[i] * inv);
+  for (int i = 0; i < HD; ++i) acc[i] *= inv;
+  store24(p.out + attn_row(nbi, qi, p.S, p.inner) * p.ldo + h * HD, acc);
 }
 
 template <typename AT>

@@ -71,40 +71,63 @@ ln_modulate_kernel(const float* __restrict__ x, OT* __restrict__ out, int M, con
 
 // ---- token embedding -------------------------------------------------------------------
 // emb[m,:] = W_x x[m] + W_c x_cond[m] + b_x + b_c + mask_emb[cm[m]] + pos[l] + time[t] + ipa[b,l]
-// latent_model.py:242-255.  One block = EMB_TOK tokens, thread = channel.
-constexpr int EMB_TOK = 16;
-template <int C>
+// latent_model.py:242-255.  thread = channel (its weight column lives in registers, read coalesced
+// from the transposed weight WT [D + Dc, C]); one block = EMB_TOK tokens staged in shared memory.
+constexpr int EMB_TOK = 64;
+template <int C, int DDP>
 __global__ void __launch_bounds__(C)
 embed_kernel(const float* __restrict__ x, int D, const float* __restrict__ xc, int Dc,
-             const int64_t* __restrict__ cm, const float* __restrict__ Wx, const float* __restrict__ bx,
-             const float* __restrict__ Wc, const float* __restrict__ bc, const float* __restrict__ mask_emb,
-             const float* __restrict__ pos, const float* __restrict__ time_emb,
+             const int64_t* __restrict__ cm, const float* __restrict__ WT, const float* __restrict__ bsum,
+             const float* __restrict__ mask_emb, const float* __restrict__ pos, const float* __restrict__ time_emb,
              const float* __restrict__ ipa, float* __restrict__ out, int N, int T, int L) {
-  extern __shared__ float sm[];  // [EMB_TOK][D + Dc]
+  __shared__ __align__(16) float sm[EMB_TOK][DDP];
   const int c = threadIdx.x;
   const int m0 = blockIdx.x * EMB_TOK;
   const int DD = D + Dc;
-  for (int i = threadIdx.x; i < EMB_TOK * DD; i += C) {
-    int tk = i / DD, d = i % DD, m = m0 + tk;
+  float w[DDP];
+#pragma unroll
+  for (int d = 0; d < DDP; ++d) w[d] = d < DD ? WT[(size_t)d * C + c] : 0.f;
+  for (int i = threadIdx.x; i < EMB_TOK * DDP; i += C) {
+    const int tk = i / DDP, d = i % DDP, m = m0 + tk;
     float v = 0.f;
-    if (m < N) v = d < D ? x[(size_t)m * D + d] : xc[(size_t)m * Dc + (d - D)];
-    sm[i] = v;
+    if (m < N && d < DD) v = d < D ? x[(size_t)m * D + d] : xc[(size_t)m * Dc + (d - D)];
+    sm[tk][d] = v;
   }
   __syncthreads();
-  float base = bx[c] + (xc ? bc[c] : 0.f);
+  const float base = bsum[c];
   for (int tk = 0; tk < EMB_TOK; ++tk) {
-    int m = m0 + tk;
+    const int m = m0 + tk;
     if (m >= N) break;
     float acc = base;
-    const float* row = sm + tk * DD;
-    for (int d = 0; d < D; ++d) acc = fmaf(Wx[(size_t)c * D + d], row[d], acc);
-    for (int d = 0; d < Dc; ++d) acc = fmaf(Wc[(size_t)c * Dc + d], row[D + d], acc);
-    int l = m % L, t = (m / L) % T, b = m / (L * T);
+#pragma unroll
+    for (int d = 0; d < DDP; d += 4) {
+      const float4 xv = *reinterpret_cast<const float4*>(&sm[tk][d]);
+      acc = fmaf(w[d], xv.x, acc);
+      acc = fmaf(w[d + 1], xv.y, acc);
+      acc = fmaf(w[d + 2], xv.z, acc);
+      acc = fmaf(w[d + 3], xv.w, acc);
+    }
+    const int l = m % L, t = (m / L) % T, b = m / (L * T);
     if (cm) acc += mask_emb[(size_t)cm[m] * C + c];
     if (pos) acc += pos[(size_t)l * C + c];
     if (time_emb) acc += time_emb[(size_t)t * C + c];
     if (ipa) acc += ipa[((size_t)b * L + l) * C + c];
     out[(size_t)m * C + c] = acc;
+  }
+}
+
+// WT[d, c] = d < D ? Wx[c, d] : Wc[c, d - D];  bsum[c] = bx[c] + bc[c]
+__global__ void pack_embed_weights_kernel(const float* __restrict__ Wx, int D, const float* __restrict__ Wc, int Dc,
+                                          const float* __restrict__ bx, const float* __restrict__ bc, int C,
+                                          float* __restrict__ WT, float* __restrict__ bsum, float* __restrict__ bx_only) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < (D + Dc) * C) {
+    const int d = i / C, c = i % C;
+    WT[i] = d < D ? Wx[(size_t)c * D + d] : Wc[(size_t)c * Dc + (d - D)];
+  }
+  if (i < C) {
+    bsum[i] = bx[i] + bc[i];
+    bx_only[i] = bx[i];
   }
 }
 
@@ -189,6 +212,14 @@ __global__ void add_logits_kernel(float* __restrict__ latent, int D, const float
   latent[(size_t)m * D + D - 20 + k] += logits[((size_t)b * L + l) * 20 + k];
 }
 
+// dst[s, j, :] = src[s, :] for j < nt   (chunk elements per source row-block)
+__global__ void broadcast_rows_kernel(const float* __restrict__ src, float* __restrict__ dst, int streams, int nt,
+                                      int chunk) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)streams * nt * chunk) return;
+  const size_t e = i % chunk, s = i / ((size_t)nt * chunk);
+  dst[i] = src[s * chunk + e];
+}
 __global__ void axpy_kernel(float* __restrict__ y, const float* __restrict__ x, float a, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) y[i] += a * x[i];

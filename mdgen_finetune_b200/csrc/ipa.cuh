@@ -21,15 +21,17 @@ struct IpaDims {
 };
 
 // Gq[m][h*Pq+p][3], Gkv[m][h*(Pq+Pv)+j][3]: points mapped to the global frame, x_g = R x + t.
+// Rows are (stream, step, b, l); frames are per (stream, b, l): frame row = (m / ntBL) * BL + m % BL.
 __global__ void ipa_points_kernel(const float* __restrict__ P, int ldp, IpaDims d, const float* __restrict__ rot,
-                                  const float* __restrict__ trans, int M, float* __restrict__ Gq,
+                                  const float* __restrict__ trans, int M, int ntBL, int BL, float* __restrict__ Gq,
                                   float* __restrict__ Gkv) {
   const int nq = d.H * d.Pq, nkv = d.H * (d.Pq + d.Pv);
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= M * (nq + nkv)) return;
   const int m = idx / (nq + nkv), pt = idx % (nq + nkv);
-  const float* R = rot + (size_t)m * 9;
-  const float* t = trans + (size_t)m * 3;
+  const int fr = (m / ntBL) * BL + (m % BL);
+  const float* R = rot + (size_t)fr * 9;
+  const float* t = trans + (size_t)fr * 3;
   const float* row = P + (size_t)m * ldp;
   float x, y, z;
   float* dst;
@@ -55,7 +57,7 @@ __global__ void ipa_points_kernel(const float* __restrict__ P, int ldp, IpaDims 
 __global__ void __launch_bounds__(128)
 ipa_attention_kernel(const float* __restrict__ P, int ldp, IpaDims d, const float* __restrict__ Gq,
                      const float* __restrict__ Gkv, const float* __restrict__ rot,
-                     const float* __restrict__ trans, const float* __restrict__ head_w,
+                     const float* __restrict__ trans, int ntBL, const float* __restrict__ head_w,
                      const float* __restrict__ mask, int mask_mod, int L, float* __restrict__ cat,
                      float inf, float eps) {
   extern __shared__ float smem[];  // per warp: L logits + 32 q + 24 q-points + 24 o_pt
@@ -115,8 +117,9 @@ ipa_attention_kernel(const float* __restrict__ P, int ldp, IpaDims d, const floa
   if (lane < 24) op[lane] = opt * inv;
   __syncwarp();
   if (lane < 8) {  // invert_apply (rigid_utils.py:1061-1073): R^T (x - t)
-    const float* R = rot + (size_t)i * 9;
-    const float* t = trans + (size_t)i * 3;
+    const int fr = (i / ntBL) * mask_mod + (i % mask_mod);
+    const float* R = rot + (size_t)fr * 9;
+    const float* t = trans + (size_t)fr * 3;
     float vx = op[lane * 3 + 0] - t[0], vy = op[lane * 3 + 1] - t[1], vz = op[lane * 3 + 2] - t[2];
     float lx = R[0] * vx + R[3] * vy + R[6] * vz;
     float ly = R[1] * vx + R[4] * vy + R[7] * vz;

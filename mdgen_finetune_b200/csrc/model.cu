@@ -194,6 +194,7 @@ struct MdgenHandle {
   std::vector<IpaLayerW> ipa;
   std::vector<MainLayerW> layers;
   LinearW final_lin, design_fc1, design_fc2, design_fc3, design_logits;
+  float *emb_wt = nullptr, *emb_bsum = nullptr, *emb_bx = nullptr;  // transposed [D+Dc, C] embedding weights
   float* ada_w = nullptr;  // [ada_cols, C]
   float* ada_b = nullptr;
   int ada_cols = 0, ada_final_off = 0;
@@ -202,8 +203,12 @@ struct MdgenHandle {
   int B = 0, T = 0, L = 0;
   bool has_cond = false;
   bool has_aatype = false;
-  std::vector<DevBuf> ws_owned;
+  std::vector<DevBuf> ws_owned;    // conditioning buffers (per shape)
+  std::vector<DevBuf> scratch_owned;  // per-step / per-rollout scratch (per shape and time-row capacity)
   size_t ws_bytes = 0;
+  int nt_cap = 0;                   // time rows (sampler steps) the scratch can batch
+  int nt_cur = 1;                   // time rows of the tables currently held in ada / ipa_out
+  float* ipa_emb0 = nullptr;        // [streams*B*L, C] step-invariant initial IPA embedding
   // step-invariant
   float* mask = nullptr;      // [N]
   float* mask_bl = nullptr;   // [B*L]  (mask[:, 0])
@@ -238,6 +243,7 @@ struct MdgenHandle {
 
 namespace mdgen {
 
+static bool g_alloc_scratch = false;
 static int dev_alloc(MdgenHandle* h, void** out, size_t bytes, bool packed = false) {
   void* p = nullptr;
   if (bytes == 0) bytes = 16;
@@ -247,7 +253,7 @@ static int dev_alloc(MdgenHandle* h, void** out, size_t bytes, bool packed = fal
     DevBuf b;
     b.p = p;
     b.bytes = bytes;
-    h->ws_owned.push_back(b);
+    (g_alloc_scratch ? h->scratch_owned : h->ws_owned).push_back(b);
     h->ws_bytes += bytes;
   }
   *out = p;
@@ -404,6 +410,20 @@ static int finalize_weights(MdgenHandle* h, cudaStream_t st) {
   }
   h->ada_final_off = off;
   MD_TRY(put_ada("emb_to_latent.adaLN_modulation.1", 2 * C));
+  {
+    NEED_W(wx, "latent_to_emb.weight");
+    NEED_W(bx, "latent_to_emb.bias");
+    NEED_W(wc, "cond_to_emb.weight");
+    NEED_W(bc, "cond_to_emb.bias");
+    const int D = h->D(), Dc = h->Dc();
+    MD_CHECK((int)wx->shape[1] == D && (int)wc->shape[1] == Dc, "embedding weight shapes");
+    MD_TRY(dev_alloc(h, (void**)&h->emb_wt, (size_t)(D + Dc) * C * 4, true));
+    MD_TRY(dev_alloc(h, (void**)&h->emb_bsum, (size_t)C * 4, true));
+    MD_TRY(dev_alloc(h, (void**)&h->emb_bx, (size_t)C * 4, true));
+    pack_embed_weights_kernel<<<((D + Dc) * C + 255) / 256, 256, 0, st>>>(wx->d, D, wc->d, Dc, bx->d, bc->d, C, h->emb_wt,
+                                                                         h->emb_bsum, h->emb_bx);
+    MD_CUDA(cudaGetLastError());
+  }
   MD_TRY(pack_linear(h, "emb_to_latent.linear", &h->final_lin, bfm, st));
   if (h->flag(MDGEN_F_DESIGN)) {
     MD_TRY(pack_linear(h, "fc1", &h->design_fc1, bfm, st));
@@ -422,7 +442,16 @@ static int finalize_weights(MdgenHandle* h, cudaStream_t st) {
 // =============================================================================================
 namespace mdgen {
 
+static void free_scratch(MdgenHandle* h) {
+  for (auto& b : h->scratch_owned) {
+    cudaFree(b.p);
+    h->ws_bytes -= b.bytes;
+  }
+  h->scratch_owned.clear();
+  h->nt_cap = 0;
+}
 static void free_workspace(MdgenHandle* h) {
+  free_scratch(h);
   for (auto& b : h->ws_owned) cudaFree(b.p);
   h->ws_owned.clear();
   h->ws_bytes = 0;
@@ -438,13 +467,10 @@ __global__ void take_first_frame_mask_kernel(const float* __restrict__ mask, int
 
 static int alloc_workspace(MdgenHandle* h, int B, int T, int L) {
   free_workspace(h);
-  const int C = h->C(), D = h->D(), Dc = h->Dc();
+  const int C = h->C(), Dc = h->Dc();
   const size_t N = (size_t)B * T * L;
   const int streams = h->two_stream() ? 2 : 1;
   const size_t Mi = (size_t)streams * B * L;
-  const size_t rows = N > Mi ? N : Mi;
-  const size_t asz = h->bf16_mode() ? 2 : 4;
-  const IpaDims d{h->cfg.ipa_heads, h->cfg.ipa_head_dim, h->cfg.ipa_qk, h->cfg.ipa_v};
 #define WS(ptr, bytes) MD_TRY(dev_alloc(h, (void**)&(ptr), (bytes)))
   WS(h->mask, N * 4);
   WS(h->mask_bl, (size_t)B * L * 4);
@@ -459,11 +485,35 @@ static int alloc_workspace(MdgenHandle* h, int B, int T, int L) {
   WS(h->rope_l_sn, (size_t)(L + 1) * half * 4);
   WS(h->rope_t_cs, (size_t)(T + 1) * half * 4);
   WS(h->rope_t_sn, (size_t)(T + 1) * half * 4);
-  WS(h->tbuf, (size_t)B * 4);
-  WS(h->tfeat, (size_t)B * 256 * 4);
-  WS(h->th1, (size_t)B * C * 4);
-  WS(h->temb, (size_t)B * C * 4);
-  WS(h->ada, (size_t)B * h->ada_cols * 4);
+  WS(h->ipa_emb0, Mi * C * 4);
+#undef WS
+  h->B = B;
+  h->T = T;
+  h->L = L;
+  h->streams = streams;
+  return 0;
+}
+
+// scratch for `nt` batched time rows (1 for a plain forward, num_steps-1 for a rollout)
+static int ensure_scratch(MdgenHandle* h, int nt) {
+  if (nt <= h->nt_cap) return 0;
+  free_scratch(h);
+  g_alloc_scratch = true;
+  const int C = h->C(), D = h->D(), B = h->B, T = h->T, L = h->L;
+  const size_t N = (size_t)B * T * L;
+  const size_t Mi = (size_t)h->streams * B * L * nt;
+  const size_t rows = N > Mi ? N : Mi;
+  const size_t asz = h->bf16_mode() ? 2 : 4;
+  const size_t R = (size_t)nt * B;
+  const IpaDims d{h->cfg.ipa_heads, h->cfg.ipa_head_dim, h->cfg.ipa_qk, h->cfg.ipa_v};
+  int rc = 0;
+#define WS(ptr, bytes)                                         \
+  if (rc == 0) rc = dev_alloc(h, (void**)&(ptr), (bytes))
+  WS(h->tbuf, R * 4);
+  WS(h->tfeat, R * 256 * 4);
+  WS(h->th1, R * C * 4);
+  WS(h->temb, R * C * 4);
+  WS(h->ada, R * h->ada_cols * 4);
   WS(h->xres, N * C * 4);
   WS(h->hbuf, rows * C * asz);
   WS(h->qkv, rows * 3 * C * asz);
@@ -476,17 +526,46 @@ static int alloc_workspace(MdgenHandle* h, int B, int T, int L) {
   WS(h->ipa_gq, Mi * d.H * d.Pq * 3 * 4);
   WS(h->ipa_gkv, Mi * d.H * (d.Pq + d.Pv) * 3 * 4);
   WS(h->ipa_cat, Mi * d.cat_width() * 4);
-  WS(h->ipa_out, (size_t)B * L * C * 4);
+  WS(h->ipa_out, (size_t)nt * B * L * C * 4);
   WS(h->xd, (size_t)B * L * 20 * 4);
   WS(h->dh_mean, (size_t)B * L * C * 4);
   WS(h->dh_a, (size_t)B * L * C * 4);
   WS(h->dh_b, (size_t)B * L * C * 4);
   WS(h->dh_logits, (size_t)B * L * 20 * 4);
 #undef WS
-  h->B = B;
-  h->T = T;
-  h->L = L;
-  h->streams = streams;
+  g_alloc_scratch = false;
+  if (rc == 0) h->nt_cap = nt;
+  return rc;
+}
+
+// Step-invariant part of run_ipa's input (latent_model.py:188-207 without the design x_d term):
+// stream 0 = latent_to_emb_r(r7) / zeros (sim), stream 1 = latent_to_emb_f(f7); + aatype embedding.
+static int ipa_initial_embedding(MdgenHandle* h, cudaStream_t st) {
+  const int C = h->C(), BL = h->B * h->L, M = h->streams * BL;
+  if (h->two_stream()) {
+    const Tensor* wf = find_w(h, "latent_to_emb_f.weight");
+    const Tensor* bf_ = find_w(h, "latent_to_emb_f.bias");
+    const Tensor* wr = find_w(h, "latent_to_emb_r.weight");
+    const Tensor* br = find_w(h, "latent_to_emb_r.bias");
+    MD_CHECK(wf && bf_ && wr && br, "missing latent_to_emb_f/r");
+    EpiParams e;
+    e.out = h->ipa_emb0;
+    e.ldo = C;
+    e.bias = br->d;
+    MD_TRY((launch_gemm_simt<float, float>(h->rel7, 7, wr->d, 7, BL, C, 7, EPI_STORE, e, st)));
+    e.out = h->ipa_emb0 + (size_t)BL * C;
+    e.bias = bf_->d;
+    MD_TRY((launch_gemm_simt<float, float>(h->rel7 + (size_t)BL * 7, 7, wf->d, 7, BL, C, 7, EPI_STORE, e, st)));
+  } else {
+    MD_CUDA(cudaMemsetAsync(h->ipa_emb0, 0, (size_t)M * C * 4, st));
+  }
+  if (h->has_aatype && !h->flag(MDGEN_F_NO_AA_EMB)) {
+    const Tensor* tab = find_w(h, "aatype_to_emb.weight");
+    MD_CHECK(tab, "missing aatype_to_emb.weight");
+    gather_rows_kernel<<<(M * C + 255) / 256, 256, 0, st>>>(tab->d, h->aatype, BL, M, C, h->ipa_emb0, 1);
+    MD_LAUNCHED();
+  }
+  MD_CUDA(cudaGetLastError());
   return 0;
 }
 
@@ -502,6 +581,7 @@ static int set_conditioning(MdgenHandle* h, int B, int T, int L, const float* ma
   if (pre) MD_CHECK(srot && strans, "prepend_ipa needs start_frames");
   if (pre && h->two_stream()) MD_CHECK(erot && etrans, "tps/inpainting needs end_frames");
   if (B != h->B || T != h->T || L != h->L) MD_TRY(alloc_workspace(h, B, T, L));
+  MD_TRY(ensure_scratch(h, 1));
   const size_t N = (size_t)B * T * L, BL = (size_t)B * L;
   const int Dc = h->Dc();
   MD_CUDA(cudaMemcpyAsync(h->mask, mask, N * 4, cudaMemcpyDeviceToDevice, st));
@@ -540,6 +620,7 @@ static int set_conditioning(MdgenHandle* h, int B, int T, int L, const float* ma
     rope_table_kernel<<<((L + 1) * half + 127) / 128, 128, 0, st>>>(fl->d, half, L + 1, h->rope_l_cs, h->rope_l_sn);
     rope_table_kernel<<<((T + 1) * half + 127) / 128, 128, 0, st>>>(ft->d, half, T + 1, h->rope_t_cs, h->rope_t_sn);
   }
+  if (pre) MD_TRY(ipa_initial_embedding(h, st));
   MD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -648,6 +729,12 @@ struct Fwd {
 
 namespace mdgen {
 
+// torch.linspace(0, 1, n) in fp32: start + step*i below the midpoint, end - step*(n-1-i) above it
+static float linspace01(int i, int n) {
+  const float step = 1.0f / (float)(n - 1);
+  return i < n / 2 ? step * (float)i : 1.0f - step * (float)(n - 1 - i);
+}
+
 static int rowvec(cudaStream_t st, const float* x, int ldx, int R, const float* W, int K, const float* b, int J,
                   float* y, int ldy, int in_act, int out_act, int accumulate) {
   ProfScope ps(PC_ADALN, st);
@@ -657,140 +744,146 @@ static int rowvec(cudaStream_t st, const float* x, int ldx, int R, const float* 
   return 0;
 }
 
-// run_ipa (latent_model.py:179-214): rows are (stream, b, l); stream 0 = x_r / sim stream with
-// start_frames, stream 1 = x_f with end_frames.  Result ipa_out[b,l,:] = sum over streams.
+// fp32 linear for the IPA geometry path: warp-per-output kernel for skinny M, tiled SIMT GEMM otherwise
+static int linear_f32(cudaStream_t st, const float* A, int lda, const LinearW& w, int M, float* out, int ldo,
+                      bool accumulate) {
+  if (M <= 128) return rowvec(st, A, lda, M, w.w, w.K, w.b, w.N, out, ldo, 0, 0, accumulate ? 1 : 0);
+  EpiParams e;
+  e.bias = w.b;
+  if (accumulate) {
+    e.resid = out;
+    e.ldr = ldo;
+  } else {
+    e.out = out;
+    e.ldo = ldo;
+  }
+  return launch_gemm_simt<float, float>(A, lda, w.w, w.K, M, w.N, w.K, accumulate ? EPI_RESID : EPI_STORE, e, st);
+}
+
+// Timestep embedding, every adaLN modulation and the prepended IPA stack for `nt` time rows at once
+// (layers.py:52-55; latent_model.py:252-255,179-214,380,461).  t is [nt*B] ordered (step, b).
+// IPA rows are ordered (stream, step, b, l): stream 0 = x_r / sim stream with start_frames, stream 1 =
+// x_f with end_frames.  Results: ada [nt*B, ada_cols], ipa_out [nt, B*L, C] (sum over streams).
+// None of this depends on x (except design's x_d, which forces nt == 1), so a sampler call does it
+// ONCE for all its steps instead of once per step.
 template <typename AT>
-static int run_ipa(Fwd<AT>& f, const float* x_in) {
+static int time_tables(Fwd<AT>& f, const float* t, int nt, const float* x_for_design) {
   MdgenHandle* h = f.h;
   cudaStream_t st = f.st;
-  const int C = f.C, B = h->B, T = h->T, L = h->L, BL = B * L, M = h->streams * BL;
+  const int C = f.C, B = h->B, T = h->T, L = h->L, BL = B * L, R = nt * B;
+  MD_CHECK(nt >= 1 && nt <= h->nt_cap, "time_tables: scratch too small");
+  const Tensor* w0 = find_w(h, "t_embedder.mlp.0.weight");
+  const Tensor* b0 = find_w(h, "t_embedder.mlp.0.bias");
+  const Tensor* w2 = find_w(h, "t_embedder.mlp.2.weight");
+  const Tensor* b2 = find_w(h, "t_embedder.mlp.2.bias");
+  MD_CHECK(w0 && b0 && w2 && b2, "missing t_embedder weights");
+  timestep_features_kernel<<<(R * 128 + 127) / 128, 128, 0, st>>>(t, h->cfg.time_multiplier, R, h->tfeat);
+  MD_LAUNCHED();
+  MD_TRY(rowvec(st, h->tfeat, 256, R, w0->d, 256, b0->d, C, h->th1, C, 0, 0, 0));
+  MD_TRY(rowvec(st, h->th1, C, R, w2->d, C, b2->d, C, h->temb, C, 1, 0, 0));
+  MD_TRY(rowvec(st, h->temb, C, R, h->ada_w, C, h->ada_b, h->ada_cols, h->ada, h->ada_cols, 1, 0, 0));
+  h->nt_cur = nt;
+  if (!h->flag(MDGEN_F_PREPEND_IPA)) return 0;
+  const int ntBL = nt * BL, M = h->streams * ntBL;
   const IpaDims d{h->cfg.ipa_heads, h->cfg.ipa_head_dim, h->cfg.ipa_qk, h->cfg.ipa_v};
-  // ---- initial embedding
-  if (h->two_stream()) {
-    const Tensor* wf = find_w(h, "latent_to_emb_f.weight");
-    const Tensor* bf_ = find_w(h, "latent_to_emb_f.bias");
-    const Tensor* wr = find_w(h, "latent_to_emb_r.weight");
-    const Tensor* br = find_w(h, "latent_to_emb_r.bias");
-    MD_CHECK(wf && bf_ && wr && br, "missing latent_to_emb_f/r");
-    EpiParams e;
-    e.out = h->ipa_s;
-    e.ldo = C;
-    e.bias = br->d;
-    MD_TRY((launch_gemm_simt<float, float>(h->rel7, 7, wr->d, 7, BL, C, 7, EPI_STORE, e, st)));
-    e.out = h->ipa_s + (size_t)BL * C;
-    e.bias = bf_->d;
-    MD_TRY((launch_gemm_simt<float, float>(h->rel7 + (size_t)BL * 7, 7, wf->d, 7, BL, C, 7, EPI_STORE, e, st)));
-  } else {
-    MD_CUDA(cudaMemsetAsync(h->ipa_s, 0, (size_t)M * C * 4, st));
-  }
-  if (h->has_aatype && !h->flag(MDGEN_F_NO_AA_EMB)) {
-    const Tensor* tab = find_w(h, "aatype_to_emb.weight");
-    MD_CHECK(tab, "missing aatype_to_emb.weight");
-    gather_rows_kernel<<<(M * C + 255) / 256, 256, 0, st>>>(tab->d, h->aatype, BL, M, C, h->ipa_s, 1);
-    MD_LAUNCHED();
-  }
+  // ---- initial embedding, broadcast over the time rows
+  broadcast_rows_kernel<<<(unsigned)(((size_t)M * C + 255) / 256), 256, 0, st>>>(h->ipa_emb0, h->ipa_s, h->streams, nt, BL * C);
+  MD_LAUNCHED();
   if (h->flag(MDGEN_F_DESIGN)) {  // x_d = x[..., -20:].mean(1)  (latent_model.py:237-240, 193-194, 205-207)
+    MD_CHECK(nt == 1 && x_for_design, "design mode cannot batch time rows (x_d depends on x)");
     const int D = h->D();
-    mean_over_T_kernel<float><<<(BL * 20 + 255) / 256, 256, 0, st>>>(x_in, D, D - 20, B, T, L, 20, h->xd);
+    mean_over_T_kernel<float><<<(BL * 20 + 255) / 256, 256, 0, st>>>(x_for_design, D, D - 20, B, T, L, 20, h->xd);
     MD_LAUNCHED();
     const Tensor* w = find_w(h, "x_d_to_emb.weight");
     const Tensor* b = find_w(h, "x_d_to_emb.bias");
     MD_CHECK(w && b, "missing x_d_to_emb");
-    for (int s = 0; s < h->streams; ++s) {
-      EpiParams e;
-      e.resid = h->ipa_s + (size_t)s * BL * C;
-      e.ldr = C;
-      e.bias = b->d;
-      MD_TRY((launch_gemm_simt<float, float>(h->xd, 20, w->d, 20, BL, C, 20, EPI_RESID, e, st)));
-    }
+    LinearW lw;
+    lw.w = w->d;
+    lw.b = b->d;
+    lw.N = C;
+    lw.K = 20;
+    for (int s = 0; s < h->streams; ++s) MD_TRY(linear_f32(st, h->xd, 20, lw, BL, h->ipa_s + (size_t)s * BL * C, C, true));
   }
   // ---- layers
   for (size_t i = 0; i < h->ipa.size(); ++i) {
     const IpaLayerW& Lw = h->ipa[i];
     const float* ada_row = h->ada + Lw.ada_off;
-    ln_modulate_kernel<float, 384><<<(M * 32 + 255) / 256, 256, 0, st>>>(h->ipa_s, h->ipa_n, M, nullptr, nullptr, 0, 1, 1,
-                                                                         Lw.norm_w, Lw.norm_b, 1e-5f);
-    MD_LAUNCHED();
-    EpiParams e;
-    e.out = h->ipa_p;
-    e.ldo = d.proj_width();
-    MD_TRY(f.gemm_f32(h->ipa_n, C, Lw.proj, M, EPI_STORE, e));
-    const int npts = M * d.H * (2 * d.Pq + d.Pv);
     {
-    ProfScope ps(PC_IPA, st);
-    ipa_points_kernel<<<(npts + 255) / 256, 256, 0, st>>>(h->ipa_p, d.proj_width(), d, h->frames_rot, h->frames_trans, M,
-                                                          h->ipa_gq, h->ipa_gkv);
-    MD_LAUNCHED();
-    const size_t smem = (size_t)d.H * (L + 80) * 4;
-    ipa_attention_kernel<<<M, d.H * 32, smem, st>>>(h->ipa_p, d.proj_width(), d, h->ipa_gq, h->ipa_gkv, h->frames_rot,
-                                                   h->frames_trans, Lw.head_w, h->mask_bl, BL, L, h->ipa_cat, 1e5f, 1e-8f);
-    MD_LAUNCHED();
+      ProfScope ps(PC_LN, st);
+      ln_modulate_kernel<float, 384><<<(M * 32 + 255) / 256, 256, 0, st>>>(h->ipa_s, h->ipa_n, M, nullptr, nullptr, 0, 1, 1,
+                                                                           Lw.norm_w, Lw.norm_b, 1e-5f);
+      MD_LAUNCHED();
     }
-    MD_CUDA(cudaGetLastError());
-    EpiParams eo;
-    eo.resid = h->ipa_s;
-    eo.ldr = C;
-    MD_TRY(f.gemm_f32(h->ipa_cat, d.cat_width(), Lw.lin_out, M, EPI_RESID, eo));
-    MD_TRY(f.attn_block(h->ipa_s, M, Lw.mha, ada_row, 0, L, B, M / L, L, 1, h->mask_bl, BL, false));
-    MD_TRY(f.mlp_block(h->ipa_s, M, Lw.fc1, Lw.fc2, ada_row, 3, L, B));
+    MD_TRY(linear_f32(st, h->ipa_n, C, Lw.proj, M, h->ipa_p, d.proj_width(), false));
+    {
+      ProfScope ps(PC_IPA, st);
+      const int npts = M * d.H * (2 * d.Pq + d.Pv);
+      ipa_points_kernel<<<(npts + 255) / 256, 256, 0, st>>>(h->ipa_p, d.proj_width(), d, h->frames_rot, h->frames_trans, M,
+                                                            ntBL, BL, h->ipa_gq, h->ipa_gkv);
+      MD_LAUNCHED();
+      const size_t smem = (size_t)d.H * (L + 80) * 4;
+      ipa_attention_kernel<<<M, d.H * 32, smem, st>>>(h->ipa_p, d.proj_width(), d, h->ipa_gq, h->ipa_gkv, h->frames_rot,
+                                                     h->frames_trans, ntBL, Lw.head_w, h->mask_bl, BL, L, h->ipa_cat, 1e5f,
+                                                     1e-8f);
+      MD_LAUNCHED();
+      MD_CUDA(cudaGetLastError());
+    }
+    MD_TRY(linear_f32(st, h->ipa_cat, d.cat_width(), Lw.lin_out, M, h->ipa_s, C, true));
+    MD_TRY(f.attn_block(h->ipa_s, M, Lw.mha, ada_row, 0, L, R, M / L, L, 1, h->mask_bl, BL, false));
+    MD_TRY(f.mlp_block(h->ipa_s, M, Lw.fc1, Lw.fc2, ada_row, 3, L, R));
   }
-  // ---- sum streams
-  MD_CUDA(cudaMemcpyAsync(h->ipa_out, h->ipa_s, (size_t)BL * C * 4, cudaMemcpyDeviceToDevice, st));
+  // ---- sum streams: ipa_out[step, b, l] = s[0, step, b, l] (+ s[1, step, b, l])
+  MD_CUDA(cudaMemcpyAsync(h->ipa_out, h->ipa_s, (size_t)ntBL * C * 4, cudaMemcpyDeviceToDevice, st));
   if (h->streams == 2) {
-    axpy_kernel<<<(BL * C + 255) / 256, 256, 0, st>>>(h->ipa_out, h->ipa_s + (size_t)BL * C, 1.f, (size_t)BL * C);
+    axpy_kernel<<<(unsigned)(((size_t)ntBL * C + 255) / 256), 256, 0, st>>>(h->ipa_out, h->ipa_s + (size_t)ntBL * C, 1.f,
+                                                                          (size_t)ntBL * C);
     MD_LAUNCHED();
   }
   MD_CUDA(cudaGetLastError());
   return 0;
 }
 
-// One velocity evaluation.  If `state` != null the final epilogue also does state += dt * v
-// (the Euler step fused into the last projection; SURVEY Q4: no clamp on conditioned frames).
+// Embedding + 5 factorised blocks + final projection for time row `step` of the current tables.
+// If `state` != null the final epilogue also does state += dt * v (the Euler step fused into the
+// last projection; SURVEY Q4: no clamp on conditioned frames).
 template <typename AT>
-static int forward_impl(MdgenHandle* h, const float* x, const float* t, float* out, float* state, float dt,
-                        cudaStream_t st) {
-  Fwd<AT> f{h, st, h->C(), h->cfg.mha_heads, h->C() / h->cfg.mha_heads};
+static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state, float dt) {
+  MdgenHandle* h = f.h;
+  cudaStream_t st = f.st;
   const int C = f.C, B = h->B, T = h->T, L = h->L, D = h->D(), Dc = h->Dc();
   const int N = B * T * L;
-  const long long l0 = g_launches;
-  // ---- timestep embedding + all adaLN modulations (layers.py:52-55; latent_model.py:252,380,461)
-  const Tensor* w0 = find_w(h, "t_embedder.mlp.0.weight");
-  const Tensor* b0 = find_w(h, "t_embedder.mlp.0.bias");
-  const Tensor* w2 = find_w(h, "t_embedder.mlp.2.weight");
-  const Tensor* b2 = find_w(h, "t_embedder.mlp.2.bias");
-  MD_CHECK(w0 && b0 && w2 && b2, "missing t_embedder weights");
-  timestep_features_kernel<<<(B * 128 + 127) / 128, 128, 0, st>>>(t, h->cfg.time_multiplier, B, h->tfeat);
-  MD_LAUNCHED();
-  MD_TRY(rowvec(st, h->tfeat, 256, B, w0->d, 256, b0->d, C, h->th1, C, 0, 0, 0));
-  MD_TRY(rowvec(st, h->th1, C, B, w2->d, C, b2->d, C, h->temb, C, 1, 0, 0));
-  MD_TRY(rowvec(st, h->temb, C, B, h->ada_w, C, h->ada_b, h->ada_cols, h->ada, h->ada_cols, 1, 0, 0));
-  // ---- prepended IPA stack
+  MD_CHECK(step >= 0 && step < h->nt_cur, "trunk: time row out of range");
+  const float* ada = h->ada + (size_t)step * B * h->ada_cols;
   const bool pre = h->flag(MDGEN_F_PREPEND_IPA);
-  if (pre) MD_TRY(run_ipa<AT>(f, x));
+  const float* ipa_out = pre ? h->ipa_out + (size_t)step * B * L * C : nullptr;
   // ---- token embedding (latent_model.py:242-255)
   {
-    const Tensor* wx = find_w(h, "latent_to_emb.weight");
-    const Tensor* bx = find_w(h, "latent_to_emb.bias");
-    const Tensor* wc = find_w(h, "cond_to_emb.weight");
-    const Tensor* bc = find_w(h, "cond_to_emb.bias");
     const Tensor* me = find_w(h, "mask_to_emb.weight");
     const Tensor* pe = h->flag(MDGEN_F_ABS_POS) ? find_w(h, "pos_embed") : nullptr;
     const Tensor* te = h->flag(MDGEN_F_ABS_TIME) ? find_w(h, "time_embed") : nullptr;
-    MD_CHECK(wx && bx && wc && bc && me, "missing embedding weights");
+    MD_CHECK(me, "missing embedding weights");
     if (h->flag(MDGEN_F_ABS_POS)) MD_CHECK(pe, "missing pos_embed");
     const bool hc = h->has_cond;
-    const size_t smem = (size_t)EMB_TOK * (D + (hc ? Dc : 0)) * 4;
+    const int DD = D + (hc ? Dc : 0);
+    MD_CHECK(DD <= 80, "latent_dim + cond_dim > 80 not supported by the embedding kernel");
     ProfScope ps(PC_EMBED, st);
-    embed_kernel<384><<<(N + EMB_TOK - 1) / EMB_TOK, 384, smem, st>>>(
-        x, D, hc ? h->x_cond : nullptr, hc ? Dc : 0, hc ? h->cond_mask : nullptr, wx->d, bx->d, wc->d, bc->d, me->d,
-        pe ? pe->d : nullptr, te ? te->d : nullptr, pre ? h->ipa_out : nullptr, h->xres, N, T, L);
+    const dim3 grid((N + EMB_TOK - 1) / EMB_TOK);
+#define MD_EMBED(DDP)                                                                                               \
+  embed_kernel<384, DDP><<<grid, 384, 0, st>>>(x, D, hc ? h->x_cond : nullptr, hc ? Dc : 0,                          \
+                                               hc ? h->cond_mask : nullptr, h->emb_wt, hc ? h->emb_bsum : h->emb_bx, \
+                                               me->d, pe ? pe->d : nullptr, te ? te->d : nullptr, ipa_out, h->xres, \
+                                               N, T, L)
+    if (DD <= 48) MD_EMBED(48);
+    else if (DD <= 64) MD_EMBED(64);
+    else MD_EMBED(80);
+#undef MD_EMBED
     MD_LAUNCHED();
     MD_CUDA(cudaGetLastError());
   }
   // ---- factorised spatio-temporal blocks (latent_model.py:456-493)
   for (size_t i = 0; i < h->layers.size(); ++i) {
     const MainLayerW& Lw = h->layers[i];
-    const float* ada_row = h->ada + Lw.ada_off;
+    const float* ada_row = ada + Lw.ada_off;
     MD_TRY(f.attn_block(h->xres, N, Lw.mha_l, ada_row, 0, T * L, B, B * T, L, 1, h->mask, N, false));
     MD_TRY(f.attn_block(h->xres, N, Lw.mha_t, ada_row, 3, T * L, B, B * L, T, L, h->mask, N, true));
     MD_TRY(f.mlp_block(h->xres, N, Lw.fc1, Lw.fc2, ada_row, 6, T * L, B));
@@ -798,7 +891,7 @@ static int forward_impl(MdgenHandle* h, const float* x, const float* t, float* o
   // ---- final layer (layers.py:71-75) with optional fused Euler update
   const bool design = h->flag(MDGEN_F_DESIGN);
   {
-    const float* ada_row = h->ada + h->ada_final_off;
+    const float* ada_row = ada + h->ada_final_off;
     MD_TRY(f.lnmod(h->xres, (AT*)h->hbuf, N, ada_row, ada_row + C, T * L, B));
     EpiParams e;
     e.out = out;
@@ -812,8 +905,7 @@ static int forward_impl(MdgenHandle* h, const float* x, const float* t, float* o
     EpiParams e;
     e.out = h->mlp;
     e.ldo = C;
-    // NB: fc1 acts on the un-normalised residual stream x; bf16 mode needs it as AT
-    if constexpr (sizeof(AT) == 2) {
+    if constexpr (sizeof(AT) == 2) {  // fc1 acts on the un-normalised residual stream: bf16 copy for the MMA
       f32_to_bf16_kernel<<<(unsigned)(((size_t)N * C + 255) / 256), 256, 0, st>>>(h->xres, (bf16*)h->hbuf, (size_t)N * C, 1.f);
       MD_LAUNCHED();
       MD_TRY(f.gemm((const AT*)h->hbuf, C, h->design_fc1, N, EPI_GELU, e, true));
@@ -840,7 +932,41 @@ static int forward_impl(MdgenHandle* h, const float* x, const float* t, float* o
     }
   }
   MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// One velocity evaluation (LatentMDGenModel.forward): tables for this t, then the trunk.
+template <typename AT>
+static int forward_impl(MdgenHandle* h, const float* x, const float* t, float* out, cudaStream_t st) {
+  Fwd<AT> f{h, st, h->C(), h->cfg.mha_heads, h->C() / h->cfg.mha_heads};
+  const long long l0 = g_launches;
+  MD_TRY(time_tables<AT>(f, t, 1, x));
+  MD_TRY(trunk<AT>(f, x, 0, out, nullptr, 0.f));
   h->launches_last_forward = (int)(g_launches - l0);
+  return 0;
+}
+
+// Fixed-grid Euler solve: tables for all steps once, then one trunk per step with the AXPY fused in.
+template <typename AT>
+static int rollout_impl(MdgenHandle* h, float* state, int num_steps, float* traj, cudaStream_t st) {
+  Fwd<AT> f{h, st, h->C(), h->cfg.mha_heads, h->C() / h->cfg.mha_heads};
+  const int nt = num_steps - 1, B = h->B;
+  const size_t n = (size_t)B * h->T * h->L * h->D();
+  std::vector<float> tv((size_t)nt * B), dts(nt);
+  for (int i = 0; i < nt; ++i) {
+    const float t0 = linspace01(i, num_steps), t1 = linspace01(i + 1, num_steps);
+    dts[i] = t1 - t0;
+    for (int b = 0; b < B; ++b) tv[(size_t)i * B + b] = t0;   // t_vec = ones(B) * t_i  (integrators.py:98-99)
+  }
+  MD_CUDA(cudaMemcpyAsync(h->tbuf, tv.data(), tv.size() * 4, cudaMemcpyHostToDevice, st));
+  MD_CUDA(cudaStreamSynchronize(st));   // tv is a stack-lifetime host buffer
+  MD_TRY(time_tables<AT>(f, h->tbuf, nt, nullptr));
+  for (int i = 0; i < nt; ++i) {
+    const long long l0 = g_launches;
+    MD_TRY(trunk<AT>(f, state, i, h->vel, state, dts[i]));
+    h->launches_last_forward = (int)(g_launches - l0);
+    if (traj) MD_CUDA(cudaMemcpyAsync(traj + (size_t)(i + 1) * n, state, n * 4, cudaMemcpyDeviceToDevice, st));
+  }
   return 0;
 }
 
@@ -854,14 +980,8 @@ __global__ void fill_t_kernel(float* t, int B, float v) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B) t[i] = v;
 }
-// torch.linspace(0, 1, n) in fp32: start + step*i below the midpoint, end - step*(n-1-i) above it
-static float linspace01(int i, int n) {
-  const float step = 1.0f / (float)(n - 1);
-  return i < n / 2 ? step * (float)i : 1.0f - step * (float)(n - 1 - i);
-}
-static int forward_dispatch(MdgenHandle* h, const float* x, const float* t, float* out, float* state, float dt,
-                            cudaStream_t st) {
-  return h->bf16_mode() ? forward_impl<bf16>(h, x, t, out, state, dt, st) : forward_impl<float>(h, x, t, out, state, dt, st);
+static int forward_dispatch(MdgenHandle* h, const float* x, const float* t, float* out, cudaStream_t st) {
+  return h->bf16_mode() ? forward_impl<bf16>(h, x, t, out, st) : forward_impl<float>(h, x, t, out, st);
 }
 struct DeviceGuard {
   int prev = -1;
@@ -958,7 +1078,7 @@ int mdgen_forward(MdgenHandle* h, const float* x, const float* t, float* out, md
     return MDGEN_ESTATE;
   }
   DeviceGuard g(h->device);
-  return forward_dispatch(h, x, t, out, nullptr, 0.f, (cudaStream_t)stream);
+  return forward_dispatch(h, x, t, out, (cudaStream_t)stream);
 }
 
 int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, float* traj, float* out_final,
@@ -974,14 +1094,9 @@ int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, floa
   const size_t n = (size_t)h->B * h->T * h->L * h->D();
   if (out_final != x0) MD_CUDA(cudaMemcpyAsync(out_final, x0, n * 4, cudaMemcpyDeviceToDevice, st));
   if (traj) MD_CUDA(cudaMemcpyAsync(traj, x0, n * 4, cudaMemcpyDeviceToDevice, st));
-  for (int i = 0; i < num_steps - 1; ++i) {
-    const float t0 = linspace01(i, num_steps), t1 = linspace01(i + 1, num_steps);
-    fill_t_kernel<<<(h->B + 127) / 128, 128, 0, st>>>(h->tbuf, h->B, t0);
-    MD_LAUNCHED();
-    MD_TRY(forward_dispatch(h, out_final, h->tbuf, h->vel, out_final, t1 - t0, st));
-    if (traj) MD_CUDA(cudaMemcpyAsync(traj + (size_t)(i + 1) * n, out_final, n * 4, cudaMemcpyDeviceToDevice, st));
-  }
-  return MDGEN_OK;
+  MD_TRY(ensure_scratch(h, num_steps - 1));
+  return h->bf16_mode() ? rollout_impl<bf16>(h, out_final, num_steps, traj, st)
+                        : rollout_impl<float>(h, out_final, num_steps, traj, st);
 }
 
 int mdgen_profile_begin(void) {
