@@ -2,13 +2,17 @@
 // configs, 257 / 251 keys of ATLAS).  Semantics = attention_simt.cuh (mha.py:258-397): bias-KV token as
 // key S, RoPE on q/k, key-padding -> -inf, fp32 softmax statistics, P.V.
 //
-// One CTA = one (sequence, head, chunk of <= 4 query tiles of 128).  The whole K (RoPE'd, d 24 -> 32
-// zero padded) and V^T of the head live in shared memory as bf16 UMMA operands (no-swizzle K-major
-// core-matrix layout).  Per query tile, two passes over the key blocks of 128:
-//   pass 1: S = Q.K^T (tcgen05.mma, fp32 in TMEM)  -> row max            (no O rescaling needed later)
-//   pass 2: S again -> P = exp2((S - max) log2e) -> bf16 P tile in smem -> O += P.V (tcgen05.mma)
-// S is double buffered in TMEM so the MMA of block k+1 overlaps the softmax of block k.
-// Warps 0-3: softmax / epilogue (thread = query row = TMEM lane), warp 4: MMA issuer, all 8 warps load K/V.
+// head_dim = 24 makes this kernel MUFU(ex2)-bound, not tensor-bound (one exp per 96 MMA FLOPs), so the
+// design minimises per-score instruction count and keeps two softmax warps resident per SM sub-partition:
+//   * one CTA = one (sequence, head, chunk of query tiles); K (RoPE'd) and V of the head are staged ONCE in
+//     shared memory as no-swizzle UMMA operands [key block][d group of 8][128 keys][8] (cp.async, 16 B units);
+//     V is consumed MN-major, so no transpose is ever materialised; d is zero-padded 24 -> 32 and padding
+//     column 24 of V is set to 1, which makes O[:, 24] the softmax row sum for free.
+//   * single pass, online softmax with lazy rescaling: S = Q.K^T block (128x128, fp32 in TMEM) -> registers
+//     -> P = exp2(S log2e - m) as packed bf16 back into TMEM -> O += P.V with P as the TMEM A operand.  O is
+//     rescaled only when the running max grows by more than 2^8.
+//   * two softmax warpgroups (warps 4-7, 8-11) work on two query tiles at once (own S/P/O TMEM columns);
+//     warp 0 lane 0 issues every tcgen05.mma; warps 1-3 stage K/V/Q (cp.async, RoPE in shared memory).
 #pragma once
 #include "attention_simt.cuh"
 #include "gemm_tc.cuh"
@@ -30,24 +34,53 @@ using tc::umma_bf16;
 constexpr int HD = 24, DP = 32;          // head dim and its MMA-padded width
 constexpr int QT = 128, KB = 128;        // query tile rows, key block width
 constexpr int MAX_KEYS = 1024;           // S + 1 <= 1024
-constexpr int QT_PER_ITEM = 4;
-constexpr int THREADS = 256;
-// shared memory map (bytes)
-constexpr int K_BYTES = MAX_KEYS * DP * 2;        // 65536  rows = keys,  LBO 128, SBO 512
-constexpr int VT_BYTES = DP * MAX_KEYS * 2;       // 65536  rows = d,     LBO 128, SBO 16384
-constexpr int Q_BYTES = QT * DP * 2;              // 8192   rows = q,     LBO 128, SBO 512
-constexpr int P_BYTES = QT * KB * 2;              // 32768  rows = q,     LBO 128, SBO 2048   (x2 buffers)
-constexpr int BIAS_BYTES = MAX_KEYS * 4;          // additive key bias: 0 or -inf
-constexpr int OFF_K = 0, OFF_VT = OFF_K + K_BYTES, OFF_Q = OFF_VT + VT_BYTES, OFF_P = OFF_Q + Q_BYTES,
-              OFF_BIAS = OFF_P + 2 * P_BYTES, OFF_BAR = OFF_BIAS + BIAS_BYTES, SMEM_BYTES = OFF_BAR + 256 + 128;
+constexpr int NKB_MAX = MAX_KEYS / KB;
+constexpr int THREADS = 384, PREP_THREADS = 96;
+constexpr int BLK_BYTES = 4 * KB * 16;   // one 128-row operand block: [4 d-groups][128 rows][8 bf16] = 8 KB
+constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups (K-major LBO / MN-major SBO)
+constexpr int OFF_K = 0, OFF_V = OFF_K + NKB_MAX * BLK_BYTES, OFF_Q = OFF_V + NKB_MAX * BLK_BYTES,
+              OFF_MASK = OFF_Q + 4 * BLK_BYTES, OFF_BAR = OFF_MASK + NKB_MAX * 4 * 4,
+              SMEM_BYTES = OFF_BAR + 256 + 128;
 constexpr uint32_t TMEM_COLS = 512;
-constexpr uint32_t TM_S0 = 0, TM_S1 = 128, TM_O = 256;
+// per-warpgroup TMEM columns: S fp32 [128], P packed bf16 [64], O fp32 [32]
+constexpr uint32_t TM_WG = 224, TM_S = 0, TM_P = 128, TM_O = 192;
+constexpr float RESCALE_TAU = 8.0f;      // log2 units: P <= 2^8 between rescales
 
-// no-swizzle K-major descriptor: start>>4 | LBO>>4 << 16 | SBO>>4 << 32 | version 1 << 46 | layout 0
+struct Bars {
+  uint64_t s_full[2], s_empty[2], p_full[2], pv_done[2], q_ready[2][2], q_free[2][2], kv_ready[NKB_MAX];
+  uint32_t tmem_base;
+};
+
+// no-swizzle descriptor: start>>4 | LBO>>4 << 16 | SBO>>4 << 32 | version 1 << 46 | layout 0
 __device__ __forceinline__ uint64_t desc_nosw(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
   return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) |
          ((uint64_t)1 << 46);
 }
+// bf16 x bf16 -> f32, A K-major, B K-major or MN-major (bit 16)
+__host__ __device__ constexpr uint32_t idesc(int M, int N, bool b_mn_major) {
+  return tc::make_idesc_bf16(M, N) | (b_mn_major ? (1u << 16) : 0u);
+}
+// D[tmem] (+)= A[tmem] . B[smem desc]
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t id, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(id), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t* r) {
+  tmem_st_32x32b_x16(taddr, r);
+  tmem_st_32x32b_x16(taddr + 16, r + 16);
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -57,269 +90,346 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-// core-matrix offset of element (row, col) in a K-major no-swizzle tile with the given SBO (LBO = 128)
-__device__ __forceinline__ uint32_t cm_off(int row, int col, int sbo) {
-  return (uint32_t)((row >> 3) * sbo + (col >> 3) * 128 + (row & 7) * 16 + (col & 7) * 2);
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void prep_bar() { asm volatile("bar.sync 1, %0;" ::"n"(PREP_THREADS) : "memory"); }
+
+// rotate one 24-wide row held as 3 x (8 bf16) groups: pairs (i, i+12), fair-esm rotate_half
+__device__ __forceinline__ void rope_row(uint4* g, const float* __restrict__ cs, const float* __restrict__ sn) {
+  float f[HD];
+  const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(g);
+#pragma unroll
+  for (int i = 0; i < HD / 2; ++i) {
+    const float2 v = __bfloat1622float2(h2[i]);
+    f[2 * i] = v.x;
+    f[2 * i + 1] = v.y;
+  }
+  const float4* c4 = reinterpret_cast<const float4*>(cs);
+  const float4* s4 = reinterpret_cast<const float4*>(sn);
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float4 c = __ldg(c4 + j), s = __ldg(s4 + j);
+    const float cc[4] = {c.x, c.y, c.z, c.w}, ss[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int i = 4 * j + e;
+      const float a = f[i], b = f[i + HD / 2];
+      f[i] = a * cc[e] - b * ss[e];
+      f[i + HD / 2] = b * cc[e] + a * ss[e];
+    }
+  }
+  uint32_t* o = reinterpret_cast<uint32_t*>(g);
+#pragma unroll
+  for (int i = 0; i < HD / 2; ++i) o[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
 }
 
-struct Bars {
-  uint64_t s_full[2], s_empty[2], p_full[2], p_empty[2], q_full, o_full, o_empty;
-  uint32_t tmem_base;
-};
-
 __global__ void __launch_bounds__(THREADS, 1)
-attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq) {
+attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
-  float* kbias = reinterpret_cast<float*>(smem + OFF_BIAS);
+  uint32_t* kmask = reinterpret_cast<uint32_t*>(smem + OFF_MASK);   // bit j of word w: key 32 w + j is attendable
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
   const int item = blockIdx.x;
   const int chunk = item % chunks_per_seq, h = (item / chunks_per_seq) % p.H, nbi = item / (chunks_per_seq * p.H);
   const int C = p.H * HD, S = p.S, nkeys = S + 1;
   const int nkb = (nkeys + KB - 1) / KB;
-  const int q_begin = chunk * QT_PER_ITEM * QT;
-  const int q_end = min(S, q_begin + QT_PER_ITEM * QT);
+  const int last_keys = nkeys - (nkb - 1) * KB;              // keys in the last block (1..128)
+  const int last_cols = (last_keys + 15) & ~15;              // MMA N / K extent of the last block
+  const int q_begin = chunk * tiles_per_item * QT;
+  const int q_end = min(S, q_begin + tiles_per_item * QT);
   const int ntiles = (q_end - q_begin + QT - 1) / QT;
+  const int npairs = (ntiles + 1) >> 1;
 
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars->s_full[i], 1);
       mbar_init(&bars->s_empty[i], 4);
       mbar_init(&bars->p_full[i], 4);
-      mbar_init(&bars->p_empty[i], 1);
+      mbar_init(&bars->pv_done[i], 1);
+      for (int j = 0; j < 2; ++j) {
+        mbar_init(&bars->q_ready[i][j], 3);
+        mbar_init(&bars->q_free[i][j], 1);
+      }
     }
-    mbar_init(&bars->q_full, 4);
-    mbar_init(&bars->o_full, 1);
-    mbar_init(&bars->o_empty, 4);
+    for (int i = 0; i < NKB_MAX; ++i) mbar_init(&bars->kv_ready[i], 3);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) {
+  if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // ---- load K (RoPE'd) and V^T of this head into shared memory: one key per thread-iteration -------
-  for (int key = tid; key < nkb * KB; key += THREADS) {
-    float kf[HD], vf[HD];
-    bool valid = false;
-    if (key < S) {
-      const size_t r = attn_row(nbi, key, S, p.inner);
-      const uint4* src = reinterpret_cast<const uint4*>(p.qkv + r * p.ld + C + h * HD);
-      const uint4* srcv = reinterpret_cast<const uint4*>(p.qkv + r * p.ld + 2 * C + h * HD);
-      uint4 kr[3] = {src[0], src[1], src[2]}, vr[3] = {srcv[0], srcv[1], srcv[2]};
-      const bf16* kb16 = reinterpret_cast<const bf16*>(kr);
-      const bf16* vb16 = reinterpret_cast<const bf16*>(vr);
-#pragma unroll
-      for (int i = 0; i < HD; ++i) { kf[i] = __bfloat162float(kb16[i]); vf[i] = __bfloat162float(vb16[i]); }
-      valid = p.key_valid[r % p.mask_mod] != 0.f;
-    } else if (key == S) {
-#pragma unroll
-      for (int i = 0; i < HD; ++i) { kf[i] = p.bias_k[h * HD + i]; vf[i] = p.bias_v[h * HD + i]; }
-      valid = true;
-    } else {
-#pragma unroll
-      for (int i = 0; i < HD; ++i) { kf[i] = 0.f; vf[i] = 0.f; }
-    }
-    if (p.cs && key <= S) {
-#pragma unroll
-      for (int i = 0; i < HD / 2; ++i) {
-        const float c = p.cs[key * (HD / 2) + i], s = p.sn[key * (HD / 2) + i];
-        const float a = kf[i], b = kf[i + HD / 2];
-        kf[i] = a * c - b * s;
-        kf[i + HD / 2] = b * c + a * s;
-      }
-    }
-    uint8_t* krow = smem + OFF_K;
-#pragma unroll
-    for (int g = 0; g < 3; ++g) {
-      uint4 v = make_uint4(pack_bf16(kf[g * 8], kf[g * 8 + 1]), pack_bf16(kf[g * 8 + 2], kf[g * 8 + 3]),
-                           pack_bf16(kf[g * 8 + 4], kf[g * 8 + 5]), pack_bf16(kf[g * 8 + 6], kf[g * 8 + 7]));
-      *reinterpret_cast<uint4*>(krow + cm_off(key, g * 8, 512)) = v;
-    }
-    *reinterpret_cast<uint4*>(krow + cm_off(key, 24, 512)) = make_uint4(0, 0, 0, 0);
-    bf16* vt = reinterpret_cast<bf16*>(smem + OFF_VT);
-#pragma unroll
-    for (int d = 0; d < HD; ++d) vt[cm_off(d, key, 16384) >> 1] = __float2bfloat16_rn(vf[d]);
-#pragma unroll
-    for (int d = HD; d < DP; ++d) vt[cm_off(d, key, 16384) >> 1] = __float2bfloat16_rn(0.f);
-    kbias[key] = valid ? 0.f : -INFINITY;
+  // padding d-group (d = 24..31) of every operand block: zeros for K and Q, [1,0,...,0] for V (row-sum column)
+  for (int i = tid; i < NKB_MAX * KB; i += THREADS) {
+    const int b = i / KB, r = i % KB;
+    *reinterpret_cast<uint4*>(smem + OFF_K + b * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(0, 0, 0, 0);
+    *reinterpret_cast<uint4*>(smem + OFF_V + b * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(0x3F80u, 0, 0, 0);
+    if (b < 4) *reinterpret_cast<uint4*>(smem + OFF_Q + b * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(0, 0, 0, 0);
   }
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic smem writes -> visible to tcgen05.mma
+  fence_async_smem();
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem = bars->tmem_base;
-  const uint32_t sK = smem_u32(smem + OFF_K), sVT = smem_u32(smem + OFF_VT), sQ = smem_u32(smem + OFF_Q),
-                 sP = smem_u32(smem + OFF_P);
+  const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V), sQ = smem_u32(smem + OFF_Q);
 
-  if (warp == 4) {
+  if (warp == 0) {
     // =============================== MMA issuer ===============================
     if (lane == 0) {
-      constexpr uint32_t idesc_s = tc::make_idesc_bf16(QT, KB);   // S[128 x 128] = Q[128x32] K[128x32]^T
-      constexpr uint32_t idesc_o = tc::make_idesc_bf16(QT, DP);   // O[128 x 32] += P[128x128] V^T[32x128]^T
-      uint32_t s_it = 0, p_it = 0;
-      auto issue_s = [&](int kb) {
-        const int b = s_it & 1;
-        mbar_wait(&bars->s_empty[b], ((s_it >> 1) & 1) ^ 1);
+      uint32_t qk_cnt[2] = {0, 0}, pv_cnt[2] = {0, 0};
+      auto issue_qk = [&](int w, int buf, int kb) {
+        mbar_wait(&bars->s_empty[w], (qk_cnt[w] & 1) ^ 1);       // softmax has pulled the previous S block
         tcgen05_fence_after();
-        const uint32_t d = tmem + (b ? TM_S1 : TM_S0);
+        const int n = (kb == nkb - 1) ? last_cols : KB;
+        const uint32_t id = idesc(QT, n, false);
+        const uint32_t d = tmem + w * TM_WG + TM_S;
+        const uint32_t qa = sQ + (w * 2 + buf) * BLK_BYTES, ka = sK + kb * BLK_BYTES;
 #pragma unroll
-        for (int k = 0; k < DP / 16; ++k)
-          umma_bf16(d, desc_nosw(sQ + k * 256, 128, 512), desc_nosw(sK + kb * (KB / 8) * 512 + k * 256, 128, 512), idesc_s, k);
-        tcgen05_commit(&bars->s_full[b]);
-        ++s_it;
+        for (int j = 0; j < DP / 16; ++j)
+          umma_bf16(d, desc_nosw(qa + j * 2 * GRP_BYTES, GRP_BYTES, 128), desc_nosw(ka + j * 2 * GRP_BYTES, GRP_BYTES, 128), id, j);
+        tcgen05_commit(&bars->s_full[w]);
+        ++qk_cnt[w];
       };
-      auto issue_pv = [&](int kb, bool first) {
-        const int b = p_it & 1;
-        mbar_wait(&bars->p_full[b], (p_it >> 1) & 1);
+      auto issue_pv = [&](int w, int kb) {
+        mbar_wait(&bars->p_full[w], pv_cnt[w] & 1);
         tcgen05_fence_after();
-#pragma unroll
-        for (int k = 0; k < KB / 16; ++k)
-          umma_bf16(tmem + TM_O, desc_nosw(sP + b * P_BYTES + k * 256, 128, 2048),
-                    desc_nosw(sVT + (kb * (KB / 8) + k * 2) * 128, 128, 16384), idesc_o, (first && k == 0) ? 0u : 1u);
-        tcgen05_commit(&bars->p_empty[b]);
-        ++p_it;
+        const int n = (kb == nkb - 1) ? last_cols : KB;
+        const uint32_t id = idesc(QT, DP, true);
+        const uint32_t d = tmem + w * TM_WG + TM_O, pa = tmem + w * TM_WG + TM_P;
+        const uint32_t va = sV + kb * BLK_BYTES;
+        for (int j = 0; j < n / 16; ++j)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
+          umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (kb == 0 && j == 0) ? 0u : 1u);
+        tcgen05_commit(&bars->pv_done[w]);
+        ++pv_cnt[w];
       };
-      for (int t = 0; t < ntiles; ++t) {
-        mbar_wait(&bars->q_full, t & 1);
-        tcgen05_fence_after();
-        for (int kb = 0; kb < nkb; ++kb) issue_s(kb);                 // pass 1: row maxima
-        mbar_wait(&bars->o_empty, (t & 1) ^ 1);                       // previous tile's O drained
-        tcgen05_fence_after();
-        for (int kb = 0; kb < nkb; ++kb) {                            // pass 2: probabilities and P.V
-          issue_s(kb);
-          if (kb > 0) issue_pv(kb - 1, kb == 1);
+      for (int pr = 0; pr < npairs; ++pr) {
+        const int buf = pr & 1;
+        const int nw = (2 * pr + 1 < ntiles) ? 2 : 1;
+        for (int w = 0; w < nw; ++w) mbar_wait(&bars->q_ready[w][buf], (pr >> 1) & 1);
+        if (pr == 0) mbar_wait(&bars->kv_ready[0], 0);
+        for (int w = 0; w < nw; ++w) {
+          issue_qk(w, buf, 0);
+          if (nkb == 1) tcgen05_commit(&bars->q_free[w][buf]);
         }
-        issue_pv(nkb - 1, nkb == 1);
-        tcgen05_commit(&bars->o_full);
+        for (int kb = 0; kb < nkb; ++kb) {
+          if (kb + 1 < nkb) {
+            if (pr == 0) mbar_wait(&bars->kv_ready[kb + 1], 0);
+            for (int w = 0; w < nw; ++w) {
+              issue_qk(w, buf, kb + 1);
+              if (kb + 1 == nkb - 1) tcgen05_commit(&bars->q_free[w][buf]);
+            }
+          }
+          for (int w = 0; w < nw; ++w) issue_pv(w, kb);
+        }
       }
     }
   } else if (warp < 4) {
-    // =============================== softmax / epilogue ===============================
-    const int r = tid;                                   // query row in tile = TMEM lane
-    const uint32_t lane_addr = ((uint32_t)(warp * 32) << 16);
-    const float LOG2E = 1.4426950408889634f;
-    uint32_t s_it = 0, p_it = 0;
-    for (int t = 0; t < ntiles; ++t) {
-      const int q = q_begin + t * QT + r;
-      // ---- Q row: global -> RoPE -> bf16 -> smem (padded to 32)
-      {
-        float qf[HD];
-        if (q < S) {
-          const uint4* src = reinterpret_cast<const uint4*>(p.qkv + attn_row(nbi, q, S, p.inner) * p.ld + h * HD);
-          uint4 qr[3] = {src[0], src[1], src[2]};
-          const bf16* q16 = reinterpret_cast<const bf16*>(qr);
+    // =============================== staging warps ===============================
+    const int pt = tid - 32, pw = warp - 1;
+    const bf16* qkv_h = p.qkv + h * HD;
+    auto stage_q = [&](int pr) {
+      const int buf = pr & 1;
+      for (int w = 0; w < 2; ++w) {
+        const int t = 2 * pr + w;
+        if (t >= ntiles) break;
+        mbar_wait(&bars->q_free[w][buf], ((pr >> 1) & 1) ^ 1);
+        uint8_t* qb = smem + OFF_Q + (w * 2 + buf) * BLK_BYTES;
+        for (int r = pt; r < QT; r += PREP_THREADS) {
+          const int q = q_begin + t * QT + r;
+          uint4 g[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+          if (q < S) {
+            const uint4* src = reinterpret_cast<const uint4*>(qkv_h + attn_row(nbi, q, S, p.inner) * p.ld);
+            g[0] = __ldg(src);
+            g[1] = __ldg(src + 1);
+            g[2] = __ldg(src + 2);
+            if (p.cs) rope_row(g, p.cs + q * (HD / 2), p.sn + q * (HD / 2));
+          }
 #pragma unroll
-          for (int i = 0; i < HD; ++i) qf[i] = __bfloat162float(q16[i]);
-          if (p.cs) {
+          for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(qb + j * GRP_BYTES + r * 16) = g[j];
+        }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->q_ready[w][buf]);
+      }
+    };
+    // ---- cp.async of K and V, one commit group per key block (always NKB_MAX groups)
 #pragma unroll
-            for (int i = 0; i < HD / 2; ++i) {
-              const float c = p.cs[q * (HD / 2) + i], s = p.sn[q * (HD / 2) + i];
-              const float a = qf[i], b = qf[i + HD / 2];
-              qf[i] = a * c - b * s;
-              qf[i + HD / 2] = b * c + a * s;
+    for (int b = 0; b < NKB_MAX; ++b) {
+      if (b < nkb) {
+        for (int i = pt; i < KB * 6; i += PREP_THREADS) {
+          const int kl = i / 6, c = i % 6, key = b * KB + kl;
+          const bool in = key < S;
+          const size_t row = in ? attn_row(nbi, key, S, p.inner) : 0;
+          const bf16* src = qkv_h + row * p.ld + (c < 3 ? C + c * 8 : 2 * C + (c - 3) * 8);
+          const uint32_t dst = (c < 3 ? sK : sV) + b * BLK_BYTES + (c % 3) * GRP_BYTES + kl * 16;
+          cp_async16(dst, src, in ? 16u : 0u);
+        }
+      }
+      cp_async_commit();
+    }
+    // ---- attendable-key bit masks
+    for (int wi = pw; wi < nkb * 4; wi += 3) {
+      const int key = wi * 32 + lane;
+      bool ok = key == S;
+      if (key < S) ok = p.key_valid[attn_row(nbi, key, S, p.inner) % p.mask_mod] != 0.f;
+      const uint32_t bits = __ballot_sync(0xffffffffu, ok);
+      if (lane == 0) kmask[wi] = bits;
+    }
+    stage_q(0);
+    // ---- per key block: wait for its cp.async group, RoPE K in place, bias token, publish
+    auto finish_block = [&](int b) {
+      prep_bar();
+      for (int kl = pt; kl < KB; kl += PREP_THREADS) {
+        const int key = b * KB + kl;
+        uint8_t* kr = smem + OFF_K + b * BLK_BYTES + kl * 16;
+        uint4 g[3];
+        if (key < S) {
+          if (!p.cs) continue;
+#pragma unroll
+          for (int j = 0; j < 3; ++j) g[j] = *reinterpret_cast<uint4*>(kr + j * GRP_BYTES);
+        } else if (key == S) {
+          uint32_t* gw = reinterpret_cast<uint32_t*>(g);
+          uint8_t* vr = smem + OFF_V + b * BLK_BYTES + kl * 16;
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            uint4 v;
+            uint32_t* vw = reinterpret_cast<uint32_t*>(&v);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int d = j * 8 + e * 2;
+              gw[j * 4 + e] = pack_bf16(p.bias_k[h * HD + d], p.bias_k[h * HD + d + 1]);
+              vw[e] = pack_bf16(p.bias_v[h * HD + d], p.bias_v[h * HD + d + 1]);
             }
+            *reinterpret_cast<uint4*>(vr + j * GRP_BYTES) = v;
           }
         } else {
-#pragma unroll
-          for (int i = 0; i < HD; ++i) qf[i] = 0.f;
+          continue;
         }
-        uint8_t* qrow = smem + OFF_Q;
+        if (p.cs) rope_row(g, p.cs + key * (HD / 2), p.sn + key * (HD / 2));
 #pragma unroll
-        for (int g = 0; g < 3; ++g)
-          *reinterpret_cast<uint4*>(qrow + cm_off(r, g * 8, 512)) =
-              make_uint4(pack_bf16(qf[g * 8], qf[g * 8 + 1]), pack_bf16(qf[g * 8 + 2], qf[g * 8 + 3]),
-                         pack_bf16(qf[g * 8 + 4], qf[g * 8 + 5]), pack_bf16(qf[g * 8 + 6], qf[g * 8 + 7]));
-        *reinterpret_cast<uint4*>(qrow + cm_off(r, 24, 512)) = make_uint4(0, 0, 0, 0);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->q_full);
+        for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * GRP_BYTES) = g[j];
       }
-      // ---- pass 1: row max
-      float mrow = -INFINITY;
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int b = s_it & 1;
-        mbar_wait(&bars->s_full[b], (s_it >> 1) & 1);
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->kv_ready[b]);
+    };
+#define MD_ATC_BLOCK(b)            \
+  if ((b) < nkb) {                 \
+    cp_async_wait<NKB_MAX - 1 - (b)>(); \
+    finish_block(b);               \
+  }
+    MD_ATC_BLOCK(0) MD_ATC_BLOCK(1) MD_ATC_BLOCK(2) MD_ATC_BLOCK(3)
+    MD_ATC_BLOCK(4) MD_ATC_BLOCK(5) MD_ATC_BLOCK(6) MD_ATC_BLOCK(7)
+#undef MD_ATC_BLOCK
+    cp_async_wait<0>();
+    for (int pr = 1; pr < npairs; ++pr) stage_q(pr);
+  } else {
+    // =============================== softmax warpgroups ===============================
+    const int w = (warp - 4) >> 2, quarter = warp & 3;
+    const int r = quarter * 32 + lane;                       // query row in tile = TMEM lane
+    const uint32_t tbase = tmem + w * TM_WG + ((uint32_t)(quarter * 32) << 16);
+    const float LOG2E = 1.4426950408889634f;
+    uint32_t it = 0;                                         // S blocks consumed by this warpgroup
+    for (int pr = 0; pr < npairs; ++pr) {
+      const int t = 2 * pr + w;
+      if (t >= ntiles) break;
+      const int q = q_begin + t * QT + r;
+      float m_used = -INFINITY;
+      for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int nch = (kb == nkb - 1) ? (last_keys + 31) >> 5 : 4;   // 32-column chunks holding keys
+        mbar_wait(&bars->s_full[w], it & 1);
         tcgen05_fence_after();
-        const uint32_t ta = tmem + lane_addr + (b ? TM_S1 : TM_S0);
+        uint32_t v[128];
 #pragma unroll
-        for (int c = 0; c < KB / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(ta + c * 32, v);
-          tmem_ld_wait();
-          const float* kbp = kbias + kb * KB + c * 32;
-#pragma unroll
-          for (int j = 0; j < 32; ++j) mrow = fmaxf(mrow, __uint_as_float(v[j]) + kbp[j]);
-        }
-        tcgen05_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->s_empty[b]);
-        ++s_it;
-      }
-      const float mneg = -mrow * LOG2E;
-      // ---- pass 2: P = exp2(S log2e - m log2e), row sum, P -> smem
-      float lsum = 0.f;
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int b = s_it & 1, pb = p_it & 1;
-        mbar_wait(&bars->s_full[b], (s_it >> 1) & 1);
-        mbar_wait(&bars->p_empty[pb], ((p_it >> 1) & 1) ^ 1);
-        tcgen05_fence_after();
-        const uint32_t ta = tmem + lane_addr + (b ? TM_S1 : TM_S0);
-        uint8_t* prow = smem + OFF_P + pb * P_BYTES + (r >> 3) * 2048 + (r & 7) * 16;
-#pragma unroll
-        for (int c = 0; c < KB / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(ta + c * 32, v);
-          tmem_ld_wait();
-          const float* kbp = kbias + kb * KB + c * 32;
-          float e[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            e[j] = ex2(fmaf(__uint_as_float(v[j]) + kbp[j], LOG2E, mneg));
-            lsum += e[j];
-          }
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            *reinterpret_cast<uint4*>(prow + (c * 4 + g) * 128) =
-                make_uint4(pack_bf16(e[g * 8], e[g * 8 + 1]), pack_bf16(e[g * 8 + 2], e[g * 8 + 3]),
-                           pack_bf16(e[g * 8 + 4], e[g * 8 + 5]), pack_bf16(e[g * 8 + 6], e[g * 8 + 7]));
-        }
-        tcgen05_fence_before();
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(&bars->s_empty[b]);
-          mbar_arrive(&bars->p_full[pb]);
-        }
-        ++s_it;
-        ++p_it;
-      }
-      // ---- epilogue: O / rowsum -> bf16 -> global
-      mbar_wait(&bars->o_full, t & 1);
-      tcgen05_fence_after();
-      {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem + lane_addr + TM_O, v);
+        for (int c = 0; c < 4; ++c)
+          if (c < nch) tmem_ld_32x32b_x32(tbase + TM_S + c * 32, v + c * 32);
         tmem_ld_wait();
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->o_empty);
-        if (q < S) {
-          const float inv = 1.0f / lsum;
-          uint4* dst = reinterpret_cast<uint4*>(p.out + attn_row(nbi, q, S, p.inner) * p.ldo + h * HD);
+        if (lane == 0) mbar_arrive(&bars->s_empty[w]);       // the next Q.K^T block may overwrite S
+        // ---- key padding / tail mask and block row max
+        float bmax = -INFINITY;
 #pragma unroll
-          for (int g = 0; g < 3; ++g)
-            dst[g] = make_uint4(pack_bf16(__uint_as_float(v[g * 8]) * inv, __uint_as_float(v[g * 8 + 1]) * inv),
-                                pack_bf16(__uint_as_float(v[g * 8 + 2]) * inv, __uint_as_float(v[g * 8 + 3]) * inv),
-                                pack_bf16(__uint_as_float(v[g * 8 + 4]) * inv, __uint_as_float(v[g * 8 + 5]) * inv),
-                                pack_bf16(__uint_as_float(v[g * 8 + 6]) * inv, __uint_as_float(v[g * 8 + 7]) * inv));
+        for (int c = 0; c < 4; ++c) {
+          if (c < nch) {
+            const uint32_t bits = kmask[kb * 4 + c];
+            if (bits != 0xffffffffu) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (!((bits >> j) & 1u)) v[c * 32 + j] = 0xff800000u;   // -inf
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) bmax = fmaxf(bmax, __uint_as_float(v[c * 32 + j]));
+          }
         }
+        const float mb = bmax * LOG2E;
+        const bool grow = mb > m_used + RESCALE_TAU;         // false when both are -inf
+        bool waited_pv = false;
+        if (kb > 0 && __any_sync(0xffffffffu, grow)) {
+          // lazy rescale of the running O (and of the row sum in its column 24)
+          mbar_wait(&bars->pv_done[w], (it - 1) & 1);
+          waited_pv = true;
+          tcgen05_fence_after();
+          uint32_t o[32];
+          tmem_ld_32x32b_x32(tbase + TM_O, o);
+          tmem_ld_wait();
+          const float sc = grow ? ex2(m_used - mb) : 1.0f;   // m_used = -inf -> 0 (O is still all zero)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * sc);
+          tmem_st_32x32b_x32(tbase + TM_O, o);
+          tmem_st_wait();
+        }
+        if (grow) m_used = mb;
+        const float mneg = (m_used == -INFINITY) ? 0.f : -m_used;
+        if (kb > 0 || pr > 0) {
+          if (!waited_pv && it > 0) mbar_wait(&bars->pv_done[w], (it - 1) & 1);   // P.V of the previous block has read P
+          tcgen05_fence_after();
+        }
+        // ---- P = exp2(S log2e - m) -> packed bf16 -> TMEM
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (c < nch) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float e0 = ex2(fmaf(__uint_as_float(v[c * 32 + 2 * j]), LOG2E, mneg));
+              const float e1 = ex2(fmaf(__uint_as_float(v[c * 32 + 2 * j + 1]), LOG2E, mneg));
+              pk[j] = pack_bf16(e0, e1);
+            }
+            tmem_st_32x32b_x16(tbase + TM_P + c * 16, pk);
+          }
+        }
+        tmem_st_wait();
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->p_full[w]);
+      }
+      // ---- epilogue: O / rowsum -> bf16 -> global
+      mbar_wait(&bars->pv_done[w], (it - 1) & 1);
+      tcgen05_fence_after();
+      uint32_t o[32];
+      tmem_ld_32x32b_x32(tbase + TM_O, o);
+      tmem_ld_wait();
+      tcgen05_fence_before();
+      if (q < S) {
+        const float inv = 1.0f / __uint_as_float(o[HD]);
+        uint4* dst = reinterpret_cast<uint4*>(p.out + attn_row(nbi, q, S, p.inner) * p.ldo + h * HD);
+#pragma unroll
+        for (int g = 0; g < 3; ++g)
+          dst[g] = make_uint4(pack_bf16(__uint_as_float(o[g * 8]) * inv, __uint_as_float(o[g * 8 + 1]) * inv),
+                              pack_bf16(__uint_as_float(o[g * 8 + 2]) * inv, __uint_as_float(o[g * 8 + 3]) * inv),
+                              pack_bf16(__uint_as_float(o[g * 8 + 4]) * inv, __uint_as_float(o[g * 8 + 5]) * inv),
+                              pack_bf16(__uint_as_float(o[g * 8 + 6]) * inv, __uint_as_float(o[g * 8 + 7]) * inv));
       }
     }
   }
   tcgen05_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 0) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
   }
@@ -331,6 +441,8 @@ inline bool attention_tc_supported(const AttnParams<bf16>& p, int head_dim) {
   return head_dim == atc::HD && p.S + 1 <= atc::MAX_KEYS && p.S >= 64 && (p.ld % 8) == 0 && (p.ldo % 8) == 0;
 }
 
+int num_sms();
+
 inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStream_t st) {
   MD_CHECK(attention_tc_supported(p, head_dim), "attention_tc: unsupported shape");
   static bool configured = false;
@@ -338,9 +450,14 @@ inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStre
     MD_CUDA(cudaFuncSetAttribute(atc::attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
     configured = true;
   }
-  const int chunks = (p.S + atc::QT_PER_ITEM * atc::QT - 1) / (atc::QT_PER_ITEM * atc::QT);
+  // query tiles per CTA: as many as possible (K/V staging is per CTA) while keeping >= 4 CTAs per SM of work
+  const int qtiles = (p.S + atc::QT - 1) / atc::QT;
+  int per = 8;
+  while (per > 2 && (long)p.nb * p.H * ((qtiles + per - 1) / per) < 4L * num_sms()) per >>= 1;
+  if (per > qtiles) per = (qtiles + 1) & ~1;
+  const int chunks = (qtiles + per - 1) / per;
   ProfScope ps(PC_ATTN_TC, st);
-  atc::attention_tc_kernel<<<p.nb * p.H * chunks, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks);
+  atc::attention_tc_kernel<<<p.nb * p.H * chunks, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, per);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;

@@ -60,7 +60,7 @@ static int make_tmap_2d(CUtensorMap* m, const bf16* ptr, int rows, int cols, int
 }
 
 static int g_num_sms = 0;
-static int num_sms() {
+int num_sms() {
   if (!g_num_sms) {
     int dev = 0;
     cudaGetDevice(&dev);
