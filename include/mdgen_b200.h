@@ -123,6 +123,10 @@ int mdgen_profile_begin(void);
 int mdgen_profile_end(float* ms_by_cat, int32_t* launches_by_cat, int32_t ncat);
 const char* mdgen_profile_category_name(int32_t i);
 
+/* Kernel-developer hook: when device_buf != NULL, the attention kernel's CTA `cta` writes per-role
+ * clock64() stamps into device_buf[0..95] (tools/attn_probe.py).  NULL (default) disables it. */
+int mdgen_debug_set_buffer(long long* device_buf, int32_t cta);
+
 /* unit-test entry points (tests/ only): run one kernel family on caller buffers --------- */
 /* C[M,N] = A[M,K] . W[N,K]^T + bias, A/W fp32 on device (converted to bf16 inside when
  * use_tc != 0 -> tcgen05 path; fp32 SIMT path otherwise). */

@@ -21,7 +21,7 @@ PREC_BF16, PREC_FP32_CHECK = 0, 1
 EXPORTS = ["mdgen_create", "mdgen_destroy", "mdgen_last_error", "mdgen_abi_version", "mdgen_load_weight",
            "mdgen_finalize_weights", "mdgen_set_conditioning", "mdgen_forward", "mdgen_euler_rollout",
            "mdgen_launches_per_forward", "mdgen_launch_count", "mdgen_workspace_bytes", "mdgen_profile_begin", "mdgen_profile_end",
-           "mdgen_profile_category_name", "mdgen_test_gemm", "mdgen_test_attention"]
+           "mdgen_profile_category_name", "mdgen_debug_set_buffer", "mdgen_test_gemm", "mdgen_test_attention"]
 
 
 class MdgenConfig(ctypes.Structure):
@@ -84,6 +84,7 @@ def lib():
     L.mdgen_launch_count.restype = ctypes.c_int64
     L.mdgen_test_gemm.argtypes = [i32, i32, i32, fp, fp, fp, fp, i32, i32, vp]
     L.mdgen_test_attention.argtypes = [i32] * 5 + [fp] * 5 + [i32, i32, vp]
+    L.mdgen_debug_set_buffer.argtypes = [vp, i32]
     L.mdgen_profile_end.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int32), i32]
     L.mdgen_profile_category_name.argtypes = [i32]
     L.mdgen_profile_category_name.restype = ctypes.c_char_p

@@ -35,19 +35,21 @@ constexpr int HD = 24, DP = 32;          // head dim and its MMA-padded width
 constexpr int QT = 128, KB = 128;        // query tile rows, key block width
 constexpr int MAX_KEYS = 1024;           // S + 1 <= 1024
 constexpr int NKB_MAX = MAX_KEYS / KB;
-constexpr int THREADS = 384, PREP_THREADS = 96;
+constexpr int SM_WARPS = 16;             // softmax warps: 2 warpgroups x 2 column halves x 4 lane quarters
+constexpr int THREADS = 128 + 32 * SM_WARPS, PREP_THREADS = 96;
 constexpr int BLK_BYTES = 4 * KB * 16;   // one 128-row operand block: [4 d-groups][128 rows][8 bf16] = 8 KB
 constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups (K-major LBO / MN-major SBO)
+constexpr int XO = 25;                   // floats per row in the half-combine exchange (24 outputs + row sum)
 constexpr int OFF_K = 0, OFF_V = OFF_K + NKB_MAX * BLK_BYTES, OFF_Q = OFF_V + NKB_MAX * BLK_BYTES,
-              OFF_MASK = OFF_Q + 4 * BLK_BYTES, OFF_BAR = OFF_MASK + NKB_MAX * 4 * 4,
-              SMEM_BYTES = OFF_BAR + 256 + 128;
+              OFF_XM = OFF_Q + 4 * BLK_BYTES, OFF_XO = OFF_XM + 2 * 2 * QT * 4, OFF_MASK = OFF_XO + 2 * QT * XO * 4,
+              OFF_BAR = OFF_MASK + NKB_MAX * 4 * 4, SMEM_BYTES = OFF_BAR + 256 + 128;
 constexpr uint32_t TMEM_COLS = 512;
-// per-warpgroup TMEM columns: S fp32 [128], P packed bf16 [64], O fp32 [32]
-constexpr uint32_t TM_WG = 224, TM_S = 0, TM_P = 128, TM_O = 192;
+// per-warpgroup TMEM columns: S fp32 [128], P packed bf16 [64], O fp32 [32] for each column half
+constexpr uint32_t TM_WG = 256, TM_S = 0, TM_P = 128, TM_O = 192;
 constexpr float RESCALE_TAU = 8.0f;      // log2 units: P <= 2^8 between rescales
 
 struct Bars {
-  uint64_t s_full[2], s_empty[2], p_full[2], pv_done[2], q_ready[2][2], q_free[2][2], kv_ready[NKB_MAX];
+  uint64_t s_full[2], s_empty[2], p_full[2], pv_done[2], q_ready[2][2], q_free[2][2];
   uint32_t tmem_base;
 };
 
@@ -86,6 +88,11 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+__device__ __forceinline__ float max3(float a, float b, float c) {   // one FMNMX3
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -97,6 +104,12 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void prep_bar() { asm volatile("bar.sync 1, %0;" ::"n"(PREP_THREADS) : "memory"); }
+
+// optional per-role cycle stamps of one CTA (tools/attn_probe.py); dbg == nullptr in production
+constexpr int DBG_SLOTS = 96;
+__device__ __forceinline__ void dbg_stamp(long long* dbg, int slot) {
+  if (dbg) dbg[slot] = clock64();
+}
 
 // rotate one 24-wide row held as 3 x (8 bf16) groups: pairs (i, i+12), fair-esm rotate_half
 __device__ __forceinline__ void rope_row(uint4* g, const float* __restrict__ cs, const float* __restrict__ sn) {
@@ -127,14 +140,31 @@ __device__ __forceinline__ void rope_row(uint4* g, const float* __restrict__ cs,
   for (int i = 0; i < HD / 2; ++i) o[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
 }
 
+// one Q row: global -> RoPE -> [d group][row][8] operand block
+__device__ __forceinline__ void stage_q_row(const AttnParams<bf16>& p, const bf16* qkv_h, uint8_t* qb, int r, int q,
+                                            uint32_t seq_row0) {
+  uint4 g[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+  if (q < p.S) {
+    const uint4* src = reinterpret_cast<const uint4*>(qkv_h + (size_t)(seq_row0 + (uint32_t)q * p.inner) * p.ld);
+    g[0] = __ldg(src);
+    g[1] = __ldg(src + 1);
+    g[2] = __ldg(src + 2);
+    if (p.cs) rope_row(g, p.cs + q * (HD / 2), p.sn + q * (HD / 2));
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(qb + j * GRP_BYTES + r * 16) = g[j];
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
-attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item) {
+attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, long long* dbg_buf, int dbg_cta) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
   uint32_t* kmask = reinterpret_cast<uint32_t*>(smem + OFF_MASK);   // bit j of word w: key 32 w + j is attendable
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
   const int item = blockIdx.x;
+  long long* dbg = (dbg_buf && item == dbg_cta) ? dbg_buf : nullptr;
+  if (tid == 0) dbg_stamp(dbg, 0);
   const int chunk = item % chunks_per_seq, h = (item / chunks_per_seq) % p.H, nbi = item / (chunks_per_seq * p.H);
   const int C = p.H * HD, S = p.S, nkeys = S + 1;
   const int nkb = (nkeys + KB - 1) / KB;
@@ -144,37 +174,96 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item) 
   const int q_end = min(S, q_begin + tiles_per_item * QT);
   const int ntiles = (q_end - q_begin + QT - 1) / QT;
   const int npairs = (ntiles + 1) >> 1;
+  const uint32_t seq_row0 = (uint32_t)(nbi / p.inner) * S * p.inner + (nbi % p.inner);   // row of key/query 0
+  const bf16* qkv_h = p.qkv + h * HD;
 
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars->s_full[i], 1);
-      mbar_init(&bars->s_empty[i], 4);
-      mbar_init(&bars->p_full[i], 4);
+      mbar_init(&bars->s_empty[i], SM_WARPS / 2);
+      mbar_init(&bars->p_full[i], SM_WARPS / 2);
       mbar_init(&bars->pv_done[i], 1);
       for (int j = 0; j < 2; ++j) {
         mbar_init(&bars->q_ready[i][j], 3);
         mbar_init(&bars->q_free[i][j], 1);
       }
     }
-    for (int i = 0; i < NKB_MAX; ++i) mbar_init(&bars->kv_ready[i], 3);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // padding d-group (d = 24..31) of every operand block: zeros for K and Q, [1,0,...,0] for V (row-sum column)
-  for (int i = tid; i < NKB_MAX * KB; i += THREADS) {
-    const int b = i / KB, r = i % KB;
-    *reinterpret_cast<uint4*>(smem + OFF_K + b * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(0, 0, 0, 0);
-    *reinterpret_cast<uint4*>(smem + OFF_V + b * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(0x3F80u, 0, 0, 0);
-    if (b < 4) *reinterpret_cast<uint4*>(smem + OFF_Q + b * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(0, 0, 0, 0);
+  // =============================== prologue: every thread stages K / V / Q(pair 0) ===============================
+  {
+    const uint32_t sV = smem_u32(smem + OFF_V);
+    // V: cp.async 16-byte pieces straight into the MN-major operand layout (rows >= S zero-filled)
+    for (int i = tid; i < nkb * KB * 3; i += THREADS) {
+      const int key = i / 3, c = i - key * 3;
+      const bool in = key < S;
+      const bf16* src = qkv_h + (size_t)(seq_row0 + (uint32_t)(in ? key : 0) * p.inner) * p.ld + 2 * C + c * 8;
+      cp_async16(sV + (key >> 7) * BLK_BYTES + c * GRP_BYTES + (key & 127) * 16, src, in ? 16u : 0u);
+    }
+    cp_async_commit();
+    if (tid == 0) dbg_stamp(dbg, 2);
+    // K: global -> registers -> RoPE -> K-major operand layout; key S = learned bias token (mha.py:265-268)
+    for (int key = tid; key < nkb * KB; key += THREADS) {
+      uint4 g[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+      if (key < S) {
+        const uint4* src = reinterpret_cast<const uint4*>(qkv_h + (size_t)(seq_row0 + (uint32_t)key * p.inner) * p.ld + C);
+        g[0] = __ldg(src);
+        g[1] = __ldg(src + 1);
+        g[2] = __ldg(src + 2);
+      } else if (key == S) {
+        uint32_t* gw = reinterpret_cast<uint32_t*>(g);
+#pragma unroll
+        for (int e = 0; e < HD / 2; ++e) gw[e] = pack_bf16(p.bias_k[h * HD + 2 * e], p.bias_k[h * HD + 2 * e + 1]);
+      }
+      if (p.cs && key <= S) rope_row(g, p.cs + key * (HD / 2), p.sn + key * (HD / 2));
+      uint8_t* kr = smem + OFF_K + (key >> 7) * BLK_BYTES + (key & 127) * 16;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * GRP_BYTES) = g[j];
+      // padding d-group (d = 24..31): zeros for K, [1, 0, ..] for V (row-sum column)
+      *reinterpret_cast<uint4*>(kr + 3 * GRP_BYTES) = make_uint4(0, 0, 0, 0);
+      *reinterpret_cast<uint4*>(smem + OFF_V + (key >> 7) * BLK_BYTES + 3 * GRP_BYTES + (key & 127) * 16) = make_uint4(0x3F80u, 0, 0, 0);
+    }
+    if (tid == 0) dbg_stamp(dbg, 3);
+    // Q tiles of pair 0 and the zero padding group of all four Q buffers
+    for (int i = tid; i < 4 * QT; i += THREADS)
+      *reinterpret_cast<uint4*>(smem + OFF_Q + (i >> 7) * BLK_BYTES + 3 * GRP_BYTES + (i & 127) * 16) = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < 2 * QT; i += THREADS) {
+      const int w = i >> 7, r = i & 127;
+      if (w < ntiles) stage_q_row(p, qkv_h, smem + OFF_Q + (w * 2) * BLK_BYTES, r, q_begin + w * QT + r, seq_row0);
+    }
+    if (tid == 0) dbg_stamp(dbg, 4);
+    // attendable-key bit masks
+    for (int wi = warp; wi < nkb * 4; wi += THREADS / 32) {
+      const int key = wi * 32 + lane;
+      bool ok = key == S;
+      if (key < S) ok = p.key_valid[(seq_row0 + (uint32_t)key * p.inner) % (uint32_t)p.mask_mod] != 0.f;
+      const uint32_t bits = __ballot_sync(0xffffffffu, ok);
+      if (lane == 0) kmask[wi] = bits;
+    }
+    if (tid == 0) dbg_stamp(dbg, 5);
+    cp_async_wait<0>();
+    if (tid == 0) dbg_stamp(dbg, 6);
+  }
+  __syncthreads();
+  if (tid == 0) dbg_stamp(dbg, 7);
+  // bias_v row (after the zero-filling cp.async of key S has landed)
+  if (tid < 3) {
+    uint4 v;
+    uint32_t* vw = reinterpret_cast<uint32_t*>(&v);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) vw[e] = pack_bf16(p.bias_v[h * HD + tid * 8 + 2 * e], p.bias_v[h * HD + tid * 8 + 2 * e + 1]);
+    *reinterpret_cast<uint4*>(smem + OFF_V + (S >> 7) * BLK_BYTES + tid * GRP_BYTES + (S & 127) * 16) = v;
   }
   fence_async_smem();
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem = bars->tmem_base;
+  if (tid == 0) dbg_stamp(dbg, 1);
   const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V), sQ = smem_u32(smem + OFF_Q);
 
   if (warp == 0) {
@@ -199,25 +288,30 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item) 
         tcgen05_fence_after();
         const int n = (kb == nkb - 1) ? last_cols : KB;
         const uint32_t id = idesc(QT, DP, true);
-        const uint32_t d = tmem + w * TM_WG + TM_O, pa = tmem + w * TM_WG + TM_P;
+        const uint32_t pa = tmem + w * TM_WG + TM_P;
         const uint32_t va = sV + kb * BLK_BYTES;
-        for (int j = 0; j < n / 16; ++j)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
-          umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (kb == 0 && j == 0) ? 0u : 1u);
+        for (int j = 0; j < n / 16; ++j) {    // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
+          const uint32_t d = tmem + w * TM_WG + TM_O + (j >> 2) * DP;       // keys 0-63 -> O half 0, 64-127 -> half 1
+          umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (kb == 0 && (j & 3) == 0) ? 0u : 1u);
+        }
         tcgen05_commit(&bars->pv_done[w]);
         ++pv_cnt[w];
       };
+      dbg_stamp(dbg, 14);
       for (int pr = 0; pr < npairs; ++pr) {
         const int buf = pr & 1;
         const int nw = (2 * pr + 1 < ntiles) ? 2 : 1;
-        for (int w = 0; w < nw; ++w) mbar_wait(&bars->q_ready[w][buf], (pr >> 1) & 1);
-        if (pr == 0) mbar_wait(&bars->kv_ready[0], 0);
+        if (pr > 0)
+          for (int w = 0; w < nw; ++w) mbar_wait(&bars->q_ready[w][buf], ((pr - 1) >> 1) & 1);
         for (int w = 0; w < nw; ++w) {
+          // stagger the warpgroups: WG1's first block is released only when WG0 has pulled its S into registers,
+          // so that one group's TMEM-read / max phase overlaps the other's MUFU phase for the rest of the tile
+          if (w == 1) mbar_wait(&bars->s_empty[0], (qk_cnt[0] - 1) & 1);
           issue_qk(w, buf, 0);
           if (nkb == 1) tcgen05_commit(&bars->q_free[w][buf]);
         }
         for (int kb = 0; kb < nkb; ++kb) {
           if (kb + 1 < nkb) {
-            if (pr == 0) mbar_wait(&bars->kv_ready[kb + 1], 0);
             for (int w = 0; w < nw; ++w) {
               issue_qk(w, buf, kb + 1);
               if (kb + 1 == nkb - 1) tcgen05_commit(&bars->q_free[w][buf]);
@@ -226,113 +320,37 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item) 
           for (int w = 0; w < nw; ++w) issue_pv(w, kb);
         }
       }
+      dbg_stamp(dbg, 15);
     }
   } else if (warp < 4) {
-    // =============================== staging warps ===============================
-    const int pt = tid - 32, pw = warp - 1;
-    const bf16* qkv_h = p.qkv + h * HD;
-    auto stage_q = [&](int pr) {
+    // =============================== Q staging warps (pairs >= 1) ===============================
+    const int pt = tid - 32;
+    for (int pr = 1; pr < npairs; ++pr) {
       const int buf = pr & 1;
       for (int w = 0; w < 2; ++w) {
         const int t = 2 * pr + w;
         if (t >= ntiles) break;
-        mbar_wait(&bars->q_free[w][buf], ((pr >> 1) & 1) ^ 1);
+        // q_ready[.][buf] / q_free[.][buf] phases count the staged uses of the buffer; pair 0 was staged by the prologue
+        if (pr >= 2) mbar_wait(&bars->q_free[w][buf], ((pr >> 1) & 1) ^ 1);
         uint8_t* qb = smem + OFF_Q + (w * 2 + buf) * BLK_BYTES;
-        for (int r = pt; r < QT; r += PREP_THREADS) {
-          const int q = q_begin + t * QT + r;
-          uint4 g[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-          if (q < S) {
-            const uint4* src = reinterpret_cast<const uint4*>(qkv_h + attn_row(nbi, q, S, p.inner) * p.ld);
-            g[0] = __ldg(src);
-            g[1] = __ldg(src + 1);
-            g[2] = __ldg(src + 2);
-            if (p.cs) rope_row(g, p.cs + q * (HD / 2), p.sn + q * (HD / 2));
-          }
-#pragma unroll
-          for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(qb + j * GRP_BYTES + r * 16) = g[j];
-        }
+        for (int r = pt; r < QT; r += PREP_THREADS) stage_q_row(p, qkv_h, qb, r, q_begin + t * QT + r, seq_row0);
         fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->q_ready[w][buf]);
       }
-    };
-    // ---- cp.async of K and V, one commit group per key block (always NKB_MAX groups)
-#pragma unroll
-    for (int b = 0; b < NKB_MAX; ++b) {
-      if (b < nkb) {
-        for (int i = pt; i < KB * 6; i += PREP_THREADS) {
-          const int kl = i / 6, c = i % 6, key = b * KB + kl;
-          const bool in = key < S;
-          const size_t row = in ? attn_row(nbi, key, S, p.inner) : 0;
-          const bf16* src = qkv_h + row * p.ld + (c < 3 ? C + c * 8 : 2 * C + (c - 3) * 8);
-          const uint32_t dst = (c < 3 ? sK : sV) + b * BLK_BYTES + (c % 3) * GRP_BYTES + kl * 16;
-          cp_async16(dst, src, in ? 16u : 0u);
-        }
-      }
-      cp_async_commit();
     }
-    // ---- attendable-key bit masks
-    for (int wi = pw; wi < nkb * 4; wi += 3) {
-      const int key = wi * 32 + lane;
-      bool ok = key == S;
-      if (key < S) ok = p.key_valid[attn_row(nbi, key, S, p.inner) % p.mask_mod] != 0.f;
-      const uint32_t bits = __ballot_sync(0xffffffffu, ok);
-      if (lane == 0) kmask[wi] = bits;
-    }
-    stage_q(0);
-    // ---- per key block: wait for its cp.async group, RoPE K in place, bias token, publish
-    auto finish_block = [&](int b) {
-      prep_bar();
-      for (int kl = pt; kl < KB; kl += PREP_THREADS) {
-        const int key = b * KB + kl;
-        uint8_t* kr = smem + OFF_K + b * BLK_BYTES + kl * 16;
-        uint4 g[3];
-        if (key < S) {
-          if (!p.cs) continue;
-#pragma unroll
-          for (int j = 0; j < 3; ++j) g[j] = *reinterpret_cast<uint4*>(kr + j * GRP_BYTES);
-        } else if (key == S) {
-          uint32_t* gw = reinterpret_cast<uint32_t*>(g);
-          uint8_t* vr = smem + OFF_V + b * BLK_BYTES + kl * 16;
-#pragma unroll
-          for (int j = 0; j < 3; ++j) {
-            uint4 v;
-            uint32_t* vw = reinterpret_cast<uint32_t*>(&v);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int d = j * 8 + e * 2;
-              gw[j * 4 + e] = pack_bf16(p.bias_k[h * HD + d], p.bias_k[h * HD + d + 1]);
-              vw[e] = pack_bf16(p.bias_v[h * HD + d], p.bias_v[h * HD + d + 1]);
-            }
-            *reinterpret_cast<uint4*>(vr + j * GRP_BYTES) = v;
-          }
-        } else {
-          continue;
-        }
-        if (p.cs) rope_row(g, p.cs + key * (HD / 2), p.sn + key * (HD / 2));
-#pragma unroll
-        for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * GRP_BYTES) = g[j];
-      }
-      fence_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->kv_ready[b]);
-    };
-#define MD_ATC_BLOCK(b)            \
-  if ((b) < nkb) {                 \
-    cp_async_wait<NKB_MAX - 1 - (b)>(); \
-    finish_block(b);               \
-  }
-    MD_ATC_BLOCK(0) MD_ATC_BLOCK(1) MD_ATC_BLOCK(2) MD_ATC_BLOCK(3)
-    MD_ATC_BLOCK(4) MD_ATC_BLOCK(5) MD_ATC_BLOCK(6) MD_ATC_BLOCK(7)
-#undef MD_ATC_BLOCK
-    cp_async_wait<0>();
-    for (int pr = 1; pr < npairs; ++pr) stage_q(pr);
+    if (pt == 0) dbg_stamp(dbg, 13);
   } else {
-    // =============================== softmax warpgroups ===============================
-    const int w = (warp - 4) >> 2, quarter = warp & 3;
+    // =============================== softmax warps ===============================
+    const int sw = warp - 4;
+    const int w = sw >> 3, hf = (sw >> 2) & 1, quarter = warp & 3;
     const int r = quarter * 32 + lane;                       // query row in tile = TMEM lane
     const uint32_t tbase = tmem + w * TM_WG + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t tS = tbase + TM_S + hf * 64, tP = tbase + TM_P + hf * 32, tO = tbase + TM_O + hf * DP;
+    float* xm = reinterpret_cast<float*>(smem + OFF_XM) + w * 2 * QT;
+    float* xo = reinterpret_cast<float*>(smem + OFF_XO) + w * QT * XO;
     const float LOG2E = 1.4426950408889634f;
+    const bool stamp = (r == 0 && hf == 0);
     uint32_t it = 0;                                         // S blocks consumed by this warpgroup
     for (int pr = 0; pr < npairs; ++pr) {
       const int t = 2 * pr + w;
@@ -340,90 +358,117 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item) 
       const int q = q_begin + t * QT + r;
       float m_used = -INFINITY;
       for (int kb = 0; kb < nkb; ++kb, ++it) {
-        const int nch = (kb == nkb - 1) ? (last_keys + 31) >> 5 : 4;   // 32-column chunks holding keys
+        // 32-column chunks of this half that hold keys
+        const int nch = (kb == nkb - 1) ? min(2, max(0, (last_keys - hf * 64 + 31) >> 5)) : 2;
         mbar_wait(&bars->s_full[w], it & 1);
         tcgen05_fence_after();
-        uint32_t v[128];
+        if (stamp && it < 16) dbg_stamp(dbg, 16 + w * 40 + 2 * it);
+        uint32_t v[64];
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
-          if (c < nch) tmem_ld_32x32b_x32(tbase + TM_S + c * 32, v + c * 32);
+        for (int c = 0; c < 2; ++c)
+          if (c < nch) tmem_ld_32x32b_x32(tS + c * 32, v + c * 32);
         tmem_ld_wait();
+        if (stamp && it == 2) dbg_stamp(dbg, 90);
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->s_empty[w]);       // the next Q.K^T block may overwrite S
-        // ---- key padding / tail mask and block row max
-        float bmax = -INFINITY;
+        if (stamp && it == 2) dbg_stamp(dbg, 91);
+        if (nch > 0) {
+          // ---- key padding / tail mask and block row max
+          float bm[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          if (c < nch) {
-            const uint32_t bits = kmask[kb * 4 + c];
-            if (bits != 0xffffffffu) {
+          for (int c = 0; c < 2; ++c) {
+            if (c < nch) {
+              const uint32_t bits = kmask[kb * 4 + hf * 2 + c];
+              if (bits != 0xffffffffu) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (!((bits >> j) & 1u)) v[c * 32 + j] = 0xff800000u;   // -inf
+                for (int j = 0; j < 32; ++j)
+                  if (!((bits >> j) & 1u)) v[c * 32 + j] = 0xff800000u;   // -inf
+              }
+#pragma unroll
+              for (int j = 0; j < 32; j += 2)
+                bm[(j >> 1) & 3] = max3(bm[(j >> 1) & 3], __uint_as_float(v[c * 32 + j]), __uint_as_float(v[c * 32 + j + 1]));
             }
-#pragma unroll
-            for (int j = 0; j < 32; ++j) bmax = fmaxf(bmax, __uint_as_float(v[c * 32 + j]));
           }
-        }
-        const float mb = bmax * LOG2E;
-        const bool grow = mb > m_used + RESCALE_TAU;         // false when both are -inf
-        bool waited_pv = false;
-        if (kb > 0 && __any_sync(0xffffffffu, grow)) {
-          // lazy rescale of the running O (and of the row sum in its column 24)
-          mbar_wait(&bars->pv_done[w], (it - 1) & 1);
-          waited_pv = true;
-          tcgen05_fence_after();
-          uint32_t o[32];
-          tmem_ld_32x32b_x32(tbase + TM_O, o);
-          tmem_ld_wait();
-          const float sc = grow ? ex2(m_used - mb) : 1.0f;   // m_used = -inf -> 0 (O is still all zero)
+          const float mb = fmaxf(fmaxf(bm[0], bm[1]), fmaxf(bm[2], bm[3])) * LOG2E;
+          if (stamp && it == 2 && dbg) dbg[92] = clock64() + (long long)(mb == 12345.f);
+          const bool grow = mb > m_used + RESCALE_TAU;         // false when both are -inf
+          bool waited_pv = false;
+          if (kb > 0 && __any_sync(0xffffffffu, grow)) {
+            // lazy rescale of this half's running O (and of its row sum in column 24)
+            mbar_wait(&bars->pv_done[w], (it - 1) & 1);
+            waited_pv = true;
+            tcgen05_fence_after();
+            uint32_t o[32];
+            tmem_ld_32x32b_x32(tO, o);
+            tmem_ld_wait();
+            const float sc = grow ? ex2(m_used - mb) : 1.0f;   // m_used = -inf -> 0 (O is still all zero)
 #pragma unroll
-          for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * sc);
-          tmem_st_32x32b_x32(tbase + TM_O, o);
+            for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * sc);
+            tmem_st_32x32b_x32(tO, o);
+            tmem_st_wait();
+          }
+          if (grow) m_used = mb;
+          const float mneg = (m_used == -INFINITY) ? 0.f : -m_used;
+          if (it > 0 && !waited_pv) {
+            mbar_wait(&bars->pv_done[w], (it - 1) & 1);        // P.V of the previous block has read P
+            tcgen05_fence_after();
+          }
+          if (stamp && it == 2) dbg_stamp(dbg, 93);
+          // ---- P = exp2(S log2e - m) -> packed bf16 -> TMEM
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            if (c < nch) {
+              uint32_t pk[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const float e0 = ex2(fmaf(__uint_as_float(v[c * 32 + 2 * j]), LOG2E, mneg));
+                const float e1 = ex2(fmaf(__uint_as_float(v[c * 32 + 2 * j + 1]), LOG2E, mneg));
+                pk[j] = pack_bf16(e0, e1);
+              }
+              tmem_st_32x32b_x16(tP + c * 16, pk);
+            }
+          }
+          if (stamp && it == 2) dbg_stamp(dbg, 94);
           tmem_st_wait();
+          if (stamp && it == 2) dbg_stamp(dbg, 95);
+        } else if (it > 0) {
+          // nothing to do for this half in a short last block, but every pv_done phase must be observed in
+          // order: a skipped phase would let the parity wait of the epilogue pass one phase early
+          mbar_wait(&bars->pv_done[w], (it - 1) & 1);
         }
-        if (grow) m_used = mb;
-        const float mneg = (m_used == -INFINITY) ? 0.f : -m_used;
-        if (kb > 0 || pr > 0) {
-          if (!waited_pv && it > 0) mbar_wait(&bars->pv_done[w], (it - 1) & 1);   // P.V of the previous block has read P
-          tcgen05_fence_after();
-        }
-        // ---- P = exp2(S log2e - m) -> packed bf16 -> TMEM
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          if (c < nch) {
-            uint32_t pk[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const float e0 = ex2(fmaf(__uint_as_float(v[c * 32 + 2 * j]), LOG2E, mneg));
-              const float e1 = ex2(fmaf(__uint_as_float(v[c * 32 + 2 * j + 1]), LOG2E, mneg));
-              pk[j] = pack_bf16(e0, e1);
-            }
-            tmem_st_32x32b_x16(tbase + TM_P + c * 16, pk);
-          }
-        }
-        tmem_st_wait();
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->p_full[w]);
+        if (stamp && it < 16) dbg_stamp(dbg, 17 + w * 40 + 2 * it);
       }
-      // ---- epilogue: O / rowsum -> bf16 -> global
+      // ---- epilogue: merge the two column halves, O / rowsum -> bf16 -> global
       mbar_wait(&bars->pv_done[w], (it - 1) & 1);
       tcgen05_fence_after();
       uint32_t o[32];
-      tmem_ld_32x32b_x32(tbase + TM_O, o);
+      tmem_ld_32x32b_x32(tO, o);
       tmem_ld_wait();
       tcgen05_fence_before();
-      if (q < S) {
-        const float inv = 1.0f / __uint_as_float(o[HD]);
-        uint4* dst = reinterpret_cast<uint4*>(p.out + attn_row(nbi, q, S, p.inner) * p.ldo + h * HD);
+      xm[hf * QT + r] = m_used;
+      asm volatile("bar.sync %0, 256;" ::"r"(2 + w) : "memory");
+      const float mo = xm[(hf ^ 1) * QT + r];
+      const float wself = ex2(m_used - fmaxf(m_used, mo));     // m_used = -inf -> 0
+      if (hf == 1) {
+#pragma unroll
+        for (int j = 0; j < XO; ++j) xo[r * XO + j] = __uint_as_float(o[j]) * wself;
+      }
+      asm volatile("bar.sync %0, 256;" ::"r"(2 + w) : "memory");
+      if (stamp && pr == 0) dbg_stamp(dbg, 48 + w * 40);
+      if (hf == 0 && q < S) {
+        float f[XO];
+#pragma unroll
+        for (int j = 0; j < XO; ++j) f[j] = fmaf(__uint_as_float(o[j]), wself, xo[r * XO + j]);
+        const float inv = 1.0f / f[HD];
+        uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(seq_row0 + (uint32_t)q * p.inner) * p.ldo + h * HD);
 #pragma unroll
         for (int g = 0; g < 3; ++g)
-          dst[g] = make_uint4(pack_bf16(__uint_as_float(o[g * 8]) * inv, __uint_as_float(o[g * 8 + 1]) * inv),
-                              pack_bf16(__uint_as_float(o[g * 8 + 2]) * inv, __uint_as_float(o[g * 8 + 3]) * inv),
-                              pack_bf16(__uint_as_float(o[g * 8 + 4]) * inv, __uint_as_float(o[g * 8 + 5]) * inv),
-                              pack_bf16(__uint_as_float(o[g * 8 + 6]) * inv, __uint_as_float(o[g * 8 + 7]) * inv));
+          dst[g] = make_uint4(pack_bf16(f[g * 8] * inv, f[g * 8 + 1] * inv), pack_bf16(f[g * 8 + 2] * inv, f[g * 8 + 3] * inv),
+                              pack_bf16(f[g * 8 + 4] * inv, f[g * 8 + 5] * inv), pack_bf16(f[g * 8 + 6] * inv, f[g * 8 + 7] * inv));
       }
     }
   }
@@ -442,6 +487,8 @@ inline bool attention_tc_supported(const AttnParams<bf16>& p, int head_dim) {
 }
 
 int num_sms();
+extern long long* g_dbg_buf;   // device buffer for dbg_stamp (mdgen_debug_set_buffer), normally null
+extern int g_dbg_cta;
 
 inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStream_t st) {
   MD_CHECK(attention_tc_supported(p, head_dim), "attention_tc: unsupported shape");
@@ -457,7 +504,7 @@ inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStre
   if (per > qtiles) per = (qtiles + 1) & ~1;
   const int chunks = (qtiles + per - 1) / per;
   ProfScope ps(PC_ATTN_TC, st);
-  atc::attention_tc_kernel<<<p.nb * p.H * chunks, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, per);
+  atc::attention_tc_kernel<<<p.nb * p.H * chunks, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, per, g_dbg_buf, g_dbg_cta);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;

@@ -25,6 +25,8 @@ namespace mdgen {
 static thread_local std::string g_err;
 thread_local long long g_launches = 0;
 Profiler g_prof;
+long long* g_dbg_buf = nullptr;
+int g_dbg_cta = 0;
 void set_error(const std::string& msg) { g_err = msg; }
 
 // ---- driver entry point for TMA descriptors (no link-time dependency on libcuda) ----------
@@ -1130,6 +1132,11 @@ const char* mdgen_profile_category_name(int32_t i) {
   return (i >= 0 && i < PC_COUNT) ? names[i] : "";
 }
 
+int mdgen_debug_set_buffer(long long* device_buf, int32_t cta) {
+  g_dbg_buf = device_buf;
+  g_dbg_cta = cta;
+  return MDGEN_OK;
+}
 long long mdgen_launch_count(void) { return g_launches; }
 int mdgen_launches_per_forward(MdgenHandle* h) { return h ? h->launches_last_forward : 0; }
 int64_t mdgen_workspace_bytes(MdgenHandle* h) { return h ? (int64_t)h->ws_bytes : 0; }
