@@ -2,17 +2,20 @@
 // configs, 257 / 251 keys of ATLAS).  Semantics = attention_simt.cuh (mha.py:258-397): bias-KV token as
 // key S, RoPE on q/k, key-padding -> -inf, fp32 softmax statistics, P.V.
 //
-// head_dim = 24 makes this kernel MUFU(ex2)-bound, not tensor-bound (one exp per 96 MMA FLOPs), so the
-// design minimises per-score instruction count and keeps two softmax warps resident per SM sub-partition:
+// head_dim = 24 makes this kernel MUFU(ex2)- and TMEM-read-bound, not tensor-bound: one exp and one 4-byte
+// TMEM read per 96 MMA FLOPs; B200 does 16 ex2/clk/SM and reads TMEM at ~64-100 B/clk/SM against 8192 bf16
+// FLOP/clk/SM.  The design therefore keeps the MUFU pipe, the TMEM read port and the ALU busy AT THE SAME TIME:
 //   * one CTA = one (sequence, head, chunk of query tiles); K (RoPE'd) and V of the head are staged ONCE in
-//     shared memory as no-swizzle UMMA operands [key block][d group of 8][128 keys][8] (cp.async, 16 B units);
-//     V is consumed MN-major, so no transpose is ever materialised; d is zero-padded 24 -> 32 and padding
-//     column 24 of V is set to 1, which makes O[:, 24] the softmax row sum for free.
-//   * single pass, online softmax with lazy rescaling: S = Q.K^T block (128x128, fp32 in TMEM) -> registers
-//     -> P = exp2(S log2e - m) as packed bf16 back into TMEM -> O += P.V with P as the TMEM A operand.  O is
-//     rescaled only when the running max grows by more than 2^8.
-//   * two softmax warpgroups (warps 4-7, 8-11) work on two query tiles at once (own S/P/O TMEM columns);
-//     warp 0 lane 0 issues every tcgen05.mma; warps 1-3 stage K/V/Q (cp.async, RoPE in shared memory).
+//     shared memory as no-swizzle UMMA operands [128-key block][d group of 8][128 keys][8]; V is consumed
+//     MN-major, so no transpose is ever materialised; d is zero-padded 24 -> 32 and padding column 24 of V is
+//     set to 1, which makes O[:, 24] the softmax row sum for free.
+//   * single pass over key blocks of 64: S = Q.K^T (128x64 fp32, double-buffered in TMEM) -> registers in
+//     32-column chunks -> P = exp2(S log2e - m) as packed bf16 back into TMEM -> O += P.V with P as the TMEM A
+//     operand.  The TMEM load of the next chunk is in flight while the current chunk is exponentiated.
+//     Online softmax at chunk granularity with lazy rescaling: O (and the not yet stored P chunk) are rescaled
+//     only when the running max grows by more than 2^8.
+//   * two softmax warpgroups (warps 4-7, 8-11; thread = query row) work on two query tiles at once;
+//     warp 0 lane 0 issues every tcgen05.mma; every thread helps staging K/V, warps 1-3 stage later Q tiles.
 #pragma once
 #include "attention_simt.cuh"
 #include "gemm_tc.cuh"
@@ -32,24 +35,22 @@ using tc::tmem_ld_wait;
 using tc::umma_bf16;
 
 constexpr int HD = 24, DP = 32;          // head dim and its MMA-padded width
-constexpr int QT = 128, KB = 128;        // query tile rows, key block width
+constexpr int QT = 128, KB = 128;        // query tile rows, rows of one staged operand block
+constexpr int SB = 64;                   // keys per MMA / softmax block (half an operand block)
 constexpr int MAX_KEYS = 1024;           // S + 1 <= 1024
 constexpr int NKB_MAX = MAX_KEYS / KB;
-constexpr int SM_WARPS = 16;             // softmax warps: 2 warpgroups x 2 column halves x 4 lane quarters
-constexpr int THREADS = 128 + 32 * SM_WARPS, PREP_THREADS = 96;
+constexpr int THREADS = 384, PREP_THREADS = 96;
 constexpr int BLK_BYTES = 4 * KB * 16;   // one 128-row operand block: [4 d-groups][128 rows][8 bf16] = 8 KB
 constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups (K-major LBO / MN-major SBO)
-constexpr int XO = 25;                   // floats per row in the half-combine exchange (24 outputs + row sum)
 constexpr int OFF_K = 0, OFF_V = OFF_K + NKB_MAX * BLK_BYTES, OFF_Q = OFF_V + NKB_MAX * BLK_BYTES,
-              OFF_XM = OFF_Q + 4 * BLK_BYTES, OFF_XO = OFF_XM + 2 * 2 * QT * 4, OFF_MASK = OFF_XO + 2 * QT * XO * 4,
-              OFF_BAR = OFF_MASK + NKB_MAX * 4 * 4, SMEM_BYTES = OFF_BAR + 256 + 128;
+              OFF_MASK = OFF_Q + 4 * BLK_BYTES, OFF_BAR = OFF_MASK + NKB_MAX * 4 * 4, SMEM_BYTES = OFF_BAR + 256 + 128;
 constexpr uint32_t TMEM_COLS = 512;
-// per-warpgroup TMEM columns: S fp32 [128], P packed bf16 [64], O fp32 [32] for each column half
-constexpr uint32_t TM_WG = 256, TM_S = 0, TM_P = 128, TM_O = 192;
+// per-warpgroup TMEM columns: S fp32 2 x [64], P packed bf16 [32], O fp32 [32]
+constexpr uint32_t TM_WG = 256, TM_S = 0, TM_P = 128, TM_O = 160;
 constexpr float RESCALE_TAU = 8.0f;      // log2 units: P <= 2^8 between rescales
 
 struct Bars {
-  uint64_t s_full[2], s_empty[2], p_full[2], pv_done[2], q_ready[2][2], q_free[2][2];
+  uint64_t s_full[2][2], s_empty[2][2], p_full[2], pv_done[2], q_ready[2][2], q_free[2][2];
   uint32_t tmem_base;
 };
 
@@ -155,6 +156,49 @@ __device__ __forceinline__ void stage_q_row(const AttnParams<bf16>& p, const bf1
   for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(qb + j * GRP_BYTES + r * 16) = g[j];
 }
 
+// One 32-column chunk of scores of one query row: key mask, running-max update with lazy rescale of O (TMEM)
+// and of the previous, not yet stored P chunk (registers), then P = exp2(x log2e - m) packed to bf16.
+__device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16], uint32_t* pk_prev, uint32_t bits,
+                                           bool have_o, float& m_used, uint32_t tO, uint64_t* pv_done, uint32_t pv_parity) {
+  const float LOG2E = 1.4426950408889634f;
+  if (bits != 0xffffffffu) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (!((bits >> j) & 1u)) x[j] = 0xff800000u;   // -inf
+  }
+  float bm[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+  for (int j = 0; j < 32; j += 2) bm[(j >> 1) & 3] = max3(bm[(j >> 1) & 3], __uint_as_float(x[j]), __uint_as_float(x[j + 1]));
+  const float mb = fmaxf(fmaxf(bm[0], bm[1]), fmaxf(bm[2], bm[3])) * LOG2E;
+  const bool grow = mb > m_used + RESCALE_TAU;           // false when both are -inf
+  if (__any_sync(0xffffffffu, grow)) {
+    const float sc = grow ? ex2(m_used - mb) : 1.0f;     // m_used = -inf -> 0 (nothing accumulated yet)
+    if (have_o) {
+      mbar_wait(pv_done, pv_parity);                     // every P.V issued so far has landed in O
+      tcgen05_fence_after();
+      uint32_t o[32];
+      tmem_ld_32x32b_x32(tO, o);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * sc);
+      tmem_st_32x32b_x32(tO, o);
+      tmem_st_wait();
+    }
+    if (pk_prev) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pk_prev[j]));
+        pk_prev[j] = pack_bf16(f.x * sc, f.y * sc);
+      }
+    }
+    if (grow) m_used = mb;
+  }
+  const float mneg = (m_used == -INFINITY) ? 0.f : -m_used;
+#pragma unroll
+  for (int j = 0; j < 16; ++j)
+    pk[j] = pack_bf16(ex2(fmaf(__uint_as_float(x[2 * j]), LOG2E, mneg)), ex2(fmaf(__uint_as_float(x[2 * j + 1]), LOG2E, mneg)));
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
 attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, long long* dbg_buf, int dbg_cta) {
   extern __shared__ uint8_t smem_raw[];
@@ -168,7 +212,8 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
   const int chunk = item % chunks_per_seq, h = (item / chunks_per_seq) % p.H, nbi = item / (chunks_per_seq * p.H);
   const int C = p.H * HD, S = p.S, nkeys = S + 1;
   const int nkb = (nkeys + KB - 1) / KB;
-  const int last_keys = nkeys - (nkb - 1) * KB;              // keys in the last block (1..128)
+  const int nsb = (nkeys + SB - 1) / SB;                     // MMA / softmax blocks of 64 keys
+  const int last_keys = nkeys - (nsb - 1) * SB;              // keys in the last block (1..64)
   const int last_cols = (last_keys + 15) & ~15;              // MMA N / K extent of the last block
   const int q_begin = chunk * tiles_per_item * QT;
   const int q_end = min(S, q_begin + tiles_per_item * QT);
@@ -179,11 +224,11 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
 
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&bars->s_full[i], 1);
-      mbar_init(&bars->s_empty[i], SM_WARPS / 2);
-      mbar_init(&bars->p_full[i], SM_WARPS / 2);
+      mbar_init(&bars->p_full[i], 4);
       mbar_init(&bars->pv_done[i], 1);
       for (int j = 0; j < 2; ++j) {
+        mbar_init(&bars->s_full[i][j], 1);
+        mbar_init(&bars->s_empty[i][j], 4);
         mbar_init(&bars->q_ready[i][j], 3);
         mbar_init(&bars->q_free[i][j], 1);
       }
@@ -269,31 +314,31 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
   if (warp == 0) {
     // =============================== MMA issuer ===============================
     if (lane == 0) {
-      uint32_t qk_cnt[2] = {0, 0}, pv_cnt[2] = {0, 0};
+      uint32_t qk_cnt[2] = {0, 0}, pv_cnt[2] = {0, 0};     // blocks issued per warpgroup (S buffer = count & 1)
       auto issue_qk = [&](int w, int buf, int kb) {
-        mbar_wait(&bars->s_empty[w], (qk_cnt[w] & 1) ^ 1);       // softmax has pulled the previous S block
+        const uint32_t n_ = qk_cnt[w], sb = n_ & 1;
+        mbar_wait(&bars->s_empty[w][sb], ((n_ >> 1) & 1) ^ 1);   // softmax has pulled the block that used this S buffer
         tcgen05_fence_after();
-        const int n = (kb == nkb - 1) ? last_cols : KB;
+        const int n = (kb == nsb - 1) ? last_cols : SB;
         const uint32_t id = idesc(QT, n, false);
-        const uint32_t d = tmem + w * TM_WG + TM_S;
-        const uint32_t qa = sQ + (w * 2 + buf) * BLK_BYTES, ka = sK + kb * BLK_BYTES;
+        const uint32_t d = tmem + w * TM_WG + TM_S + sb * SB;
+        const uint32_t qa = sQ + (w * 2 + buf) * BLK_BYTES, ka = sK + (kb >> 1) * BLK_BYTES + (kb & 1) * (SB * 16);
 #pragma unroll
         for (int j = 0; j < DP / 16; ++j)
           umma_bf16(d, desc_nosw(qa + j * 2 * GRP_BYTES, GRP_BYTES, 128), desc_nosw(ka + j * 2 * GRP_BYTES, GRP_BYTES, 128), id, j);
-        tcgen05_commit(&bars->s_full[w]);
+        tcgen05_commit(&bars->s_full[w][sb]);
         ++qk_cnt[w];
+        if (kb == nsb - 1) tcgen05_commit(&bars->q_free[w][buf]);   // last use of this Q tile
       };
       auto issue_pv = [&](int w, int kb) {
         mbar_wait(&bars->p_full[w], pv_cnt[w] & 1);
         tcgen05_fence_after();
-        const int n = (kb == nkb - 1) ? last_cols : KB;
+        const int n = (kb == nsb - 1) ? last_cols : SB;
         const uint32_t id = idesc(QT, DP, true);
-        const uint32_t pa = tmem + w * TM_WG + TM_P;
-        const uint32_t va = sV + kb * BLK_BYTES;
-        for (int j = 0; j < n / 16; ++j) {    // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
-          const uint32_t d = tmem + w * TM_WG + TM_O + (j >> 2) * DP;       // keys 0-63 -> O half 0, 64-127 -> half 1
-          umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (kb == 0 && (j & 3) == 0) ? 0u : 1u);
-        }
+        const uint32_t d = tmem + w * TM_WG + TM_O, pa = tmem + w * TM_WG + TM_P;
+        const uint32_t va = sV + (kb >> 1) * BLK_BYTES + (kb & 1) * (SB * 16);
+        for (int j = 0; j < n / 16; ++j)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
+          umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (kb == 0 && j == 0) ? 0u : 1u);
         tcgen05_commit(&bars->pv_done[w]);
         ++pv_cnt[w];
       };
@@ -303,21 +348,13 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
         const int nw = (2 * pr + 1 < ntiles) ? 2 : 1;
         if (pr > 0)
           for (int w = 0; w < nw; ++w) mbar_wait(&bars->q_ready[w][buf], ((pr - 1) >> 1) & 1);
-        for (int w = 0; w < nw; ++w) {
-          // stagger the warpgroups: WG1's first block is released only when WG0 has pulled its S into registers,
-          // so that one group's TMEM-read / max phase overlaps the other's MUFU phase for the rest of the tile
-          if (w == 1) mbar_wait(&bars->s_empty[0], (qk_cnt[0] - 1) & 1);
-          issue_qk(w, buf, 0);
-          if (nkb == 1) tcgen05_commit(&bars->q_free[w][buf]);
-        }
-        for (int kb = 0; kb < nkb; ++kb) {
-          if (kb + 1 < nkb) {
-            for (int w = 0; w < nw; ++w) {
-              issue_qk(w, buf, kb + 1);
-              if (kb + 1 == nkb - 1) tcgen05_commit(&bars->q_free[w][buf]);
-            }
+        for (int kb = 0; kb < 2 && kb < nsb; ++kb)
+          for (int w = 0; w < nw; ++w) issue_qk(w, buf, kb);
+        for (int kb = 0; kb < nsb; ++kb) {
+          for (int w = 0; w < nw; ++w) {
+            issue_pv(w, kb);
+            if (kb + 2 < nsb) issue_qk(w, buf, kb + 2);
           }
-          for (int w = 0; w < nw; ++w) issue_pv(w, kb);
         }
       }
       dbg_stamp(dbg, 15);
@@ -342,133 +379,74 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
     if (pt == 0) dbg_stamp(dbg, 13);
   } else {
     // =============================== softmax warps ===============================
-    const int sw = warp - 4;
-    const int w = sw >> 3, hf = (sw >> 2) & 1, quarter = warp & 3;
+    const int w = (warp - 4) >> 2, quarter = warp & 3;
     const int r = quarter * 32 + lane;                       // query row in tile = TMEM lane
     const uint32_t tbase = tmem + w * TM_WG + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t tS = tbase + TM_S + hf * 64, tP = tbase + TM_P + hf * 32, tO = tbase + TM_O + hf * DP;
-    float* xm = reinterpret_cast<float*>(smem + OFF_XM) + w * 2 * QT;
-    float* xo = reinterpret_cast<float*>(smem + OFF_XO) + w * QT * XO;
-    const float LOG2E = 1.4426950408889634f;
-    const bool stamp = (r == 0 && hf == 0);
+    const uint32_t tP = tbase + TM_P, tO = tbase + TM_O;
+    const bool stamp = (r == 0);
     uint32_t it = 0;                                         // S blocks consumed by this warpgroup
     for (int pr = 0; pr < npairs; ++pr) {
       const int t = 2 * pr + w;
       if (t >= ntiles) break;
       const int q = q_begin + t * QT + r;
       float m_used = -INFINITY;
-      for (int kb = 0; kb < nkb; ++kb, ++it) {
-        // 32-column chunks of this half that hold keys
-        const int nch = (kb == nkb - 1) ? min(2, max(0, (last_keys - hf * 64 + 31) >> 5)) : 2;
-        mbar_wait(&bars->s_full[w], it & 1);
-        tcgen05_fence_after();
+      uint32_t xa[32], xb[32];
+      mbar_wait(&bars->s_full[w][it & 1], (it >> 1) & 1);
+      tcgen05_fence_after();
+      tmem_ld_32x32b_x32(tbase + TM_S + (it & 1) * SB, xa);
+      for (int kb = 0; kb < nsb; ++kb, ++it) {
+        const bool two = (kb < nsb - 1) || last_keys > 32;     // second 32-column chunk holds keys
         if (stamp && it < 16) dbg_stamp(dbg, 16 + w * 40 + 2 * it);
-        uint32_t v[64];
-#pragma unroll
-        for (int c = 0; c < 2; ++c)
-          if (c < nch) tmem_ld_32x32b_x32(tS + c * 32, v + c * 32);
-        tmem_ld_wait();
-        if (stamp && it == 2) dbg_stamp(dbg, 90);
+        tmem_ld_wait();                                        // chunk A in registers
+        if (stamp && it == 4) dbg_stamp(dbg, 88);
+        if (two) tmem_ld_32x32b_x32(tbase + TM_S + (it & 1) * SB + 32, xb);
+        uint32_t pka[16], pkb[16];
+        soft_chunk(xa, pka, nullptr, kmask[kb * 2], kb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1);
+        if (stamp && it == 4) dbg_stamp(dbg, 89);
+        tmem_ld_wait();                                        // chunk B in registers: S buffer is free
+        if (stamp && it == 4) dbg_stamp(dbg, 90);
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->s_empty[w]);       // the next Q.K^T block may overwrite S
-        if (stamp && it == 2) dbg_stamp(dbg, 91);
-        if (nch > 0) {
-          // ---- key padding / tail mask and block row max
-          float bm[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            if (c < nch) {
-              const uint32_t bits = kmask[kb * 4 + hf * 2 + c];
-              if (bits != 0xffffffffu) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                  if (!((bits >> j) & 1u)) v[c * 32 + j] = 0xff800000u;   // -inf
-              }
-#pragma unroll
-              for (int j = 0; j < 32; j += 2)
-                bm[(j >> 1) & 3] = max3(bm[(j >> 1) & 3], __uint_as_float(v[c * 32 + j]), __uint_as_float(v[c * 32 + j + 1]));
-            }
-          }
-          const float mb = fmaxf(fmaxf(bm[0], bm[1]), fmaxf(bm[2], bm[3])) * LOG2E;
-          if (stamp && it == 2 && dbg) dbg[92] = clock64() + (long long)(mb == 12345.f);
-          const bool grow = mb > m_used + RESCALE_TAU;         // false when both are -inf
-          bool waited_pv = false;
-          if (kb > 0 && __any_sync(0xffffffffu, grow)) {
-            // lazy rescale of this half's running O (and of its row sum in column 24)
-            mbar_wait(&bars->pv_done[w], (it - 1) & 1);
-            waited_pv = true;
-            tcgen05_fence_after();
-            uint32_t o[32];
-            tmem_ld_32x32b_x32(tO, o);
-            tmem_ld_wait();
-            const float sc = grow ? ex2(m_used - mb) : 1.0f;   // m_used = -inf -> 0 (O is still all zero)
-#pragma unroll
-            for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * sc);
-            tmem_st_32x32b_x32(tO, o);
-            tmem_st_wait();
-          }
-          if (grow) m_used = mb;
-          const float mneg = (m_used == -INFINITY) ? 0.f : -m_used;
-          if (it > 0 && !waited_pv) {
-            mbar_wait(&bars->pv_done[w], (it - 1) & 1);        // P.V of the previous block has read P
-            tcgen05_fence_after();
-          }
-          if (stamp && it == 2) dbg_stamp(dbg, 93);
-          // ---- P = exp2(S log2e - m) -> packed bf16 -> TMEM
-#pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            if (c < nch) {
-              uint32_t pk[16];
-#pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const float e0 = ex2(fmaf(__uint_as_float(v[c * 32 + 2 * j]), LOG2E, mneg));
-                const float e1 = ex2(fmaf(__uint_as_float(v[c * 32 + 2 * j + 1]), LOG2E, mneg));
-                pk[j] = pack_bf16(e0, e1);
-              }
-              tmem_st_32x32b_x16(tP + c * 16, pk);
-            }
-          }
-          if (stamp && it == 2) dbg_stamp(dbg, 94);
-          tmem_st_wait();
-          if (stamp && it == 2) dbg_stamp(dbg, 95);
-        } else if (it > 0) {
-          // nothing to do for this half in a short last block, but every pv_done phase must be observed in
-          // order: a skipped phase would let the parity wait of the epilogue pass one phase early
-          mbar_wait(&bars->pv_done[w], (it - 1) & 1);
+        if (lane == 0) mbar_arrive(&bars->s_empty[w][it & 1]);
+        if (kb + 1 < nsb) {                                    // prefetch chunk A of the next block
+          mbar_wait(&bars->s_full[w][(it + 1) & 1], ((it + 1) >> 1) & 1);
+          tcgen05_fence_after();
+          tmem_ld_32x32b_x32(tbase + TM_S + ((it + 1) & 1) * SB, xa);
         }
+        if (stamp && it == 4) dbg_stamp(dbg, 91);
+        if (two) soft_chunk(xb, pkb, pka, kmask[kb * 2 + 1], kb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1);
+        if (stamp && it == 4) dbg_stamp(dbg, 92);
+        if (it > 0) {
+          mbar_wait(&bars->pv_done[w], (it - 1) & 1);          // P.V of the previous block has read P
+          tcgen05_fence_after();
+        }
+        if (stamp && it == 4) dbg_stamp(dbg, 93);
+        tmem_st_32x32b_x16(tP, pka);
+        if (two) tmem_st_32x32b_x16(tP + 16, pkb);
+        tmem_st_wait();
+        if (stamp && it == 4) dbg_stamp(dbg, 94);
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->p_full[w]);
         if (stamp && it < 16) dbg_stamp(dbg, 17 + w * 40 + 2 * it);
       }
-      // ---- epilogue: merge the two column halves, O / rowsum -> bf16 -> global
+      // ---- epilogue: O / rowsum -> bf16 -> global
       mbar_wait(&bars->pv_done[w], (it - 1) & 1);
       tcgen05_fence_after();
       uint32_t o[32];
       tmem_ld_32x32b_x32(tO, o);
       tmem_ld_wait();
       tcgen05_fence_before();
-      xm[hf * QT + r] = m_used;
-      asm volatile("bar.sync %0, 256;" ::"r"(2 + w) : "memory");
-      const float mo = xm[(hf ^ 1) * QT + r];
-      const float wself = ex2(m_used - fmaxf(m_used, mo));     // m_used = -inf -> 0
-      if (hf == 1) {
-#pragma unroll
-        for (int j = 0; j < XO; ++j) xo[r * XO + j] = __uint_as_float(o[j]) * wself;
-      }
-      asm volatile("bar.sync %0, 256;" ::"r"(2 + w) : "memory");
       if (stamp && pr == 0) dbg_stamp(dbg, 48 + w * 40);
-      if (hf == 0 && q < S) {
-        float f[XO];
-#pragma unroll
-        for (int j = 0; j < XO; ++j) f[j] = fmaf(__uint_as_float(o[j]), wself, xo[r * XO + j]);
-        const float inv = 1.0f / f[HD];
+      if (q < S) {
+        const float inv = 1.0f / __uint_as_float(o[HD]);
         uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(seq_row0 + (uint32_t)q * p.inner) * p.ldo + h * HD);
 #pragma unroll
         for (int g = 0; g < 3; ++g)
-          dst[g] = make_uint4(pack_bf16(f[g * 8] * inv, f[g * 8 + 1] * inv), pack_bf16(f[g * 8 + 2] * inv, f[g * 8 + 3] * inv),
-                              pack_bf16(f[g * 8 + 4] * inv, f[g * 8 + 5] * inv), pack_bf16(f[g * 8 + 6] * inv, f[g * 8 + 7] * inv));
+          dst[g] = make_uint4(pack_bf16(__uint_as_float(o[g * 8]) * inv, __uint_as_float(o[g * 8 + 1]) * inv),
+                              pack_bf16(__uint_as_float(o[g * 8 + 2]) * inv, __uint_as_float(o[g * 8 + 3]) * inv),
+                              pack_bf16(__uint_as_float(o[g * 8 + 4]) * inv, __uint_as_float(o[g * 8 + 5]) * inv),
+                              pack_bf16(__uint_as_float(o[g * 8 + 6]) * inv, __uint_as_float(o[g * 8 + 7]) * inv));
       }
     }
   }

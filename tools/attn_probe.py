@@ -40,7 +40,7 @@ for w in range(2):
         names[16 + w * 40 + 2 * i] = f"wg{w} blk{i} S ready"
         names[17 + w * 40 + 2 * i] = f"wg{w} blk{i} P done"
     names[48 + w * 40] = f"wg{w} tile0 epilogue"
-names.update({90: "  blk2: ld done", 91: "  blk2: s_empty arrived", 92: "  blk2: max done", 93: "  blk2: pv waited", 94: "  blk2: exps+st issued", 95: "  blk2: st done"})
+names.update({88: "  blk4: A loaded", 89: "  blk4: chunk A done", 90: "  blk4: B loaded", 91: "  blk4: s_empty+prefetch issued", 92: "  blk4: chunk B done", 93: "  blk4: pv waited", 94: "  blk4: P stored"})
 ev = sorted((d[i] - t0, names.get(i, str(i))) for i in range(96) if d[i])
 for t, n in ev:
     print(f"{t:8d} clk  {t / 1.965e3:8.2f} us  {n}")
