@@ -9,13 +9,15 @@
 //     shared memory as no-swizzle UMMA operands [128-key block][d group of 8][128 keys][8]; V is consumed
 //     MN-major, so no transpose is ever materialised; d is zero-padded 24 -> 32 and padding column 24 of V is
 //     set to 1, which makes O[:, 24] the softmax row sum for free.
-//   * single pass over key blocks of 64: S = Q.K^T (128x64 fp32, double-buffered in TMEM) -> registers in
-//     32-column chunks -> P = exp2(S log2e - m) as packed bf16 back into TMEM -> O += P.V with P as the TMEM A
-//     operand.  The TMEM load of the next chunk is in flight while the current chunk is exponentiated.
-//     Online softmax at chunk granularity with lazy rescaling: O (and the not yet stored P chunk) are rescaled
-//     only when the running max grows by more than 2^8.
-//   * two softmax warpgroups (warps 4-7, 8-11; thread = query row) work on two query tiles at once;
-//     warp 0 lane 0 issues every tcgen05.mma; every thread helps staging K/V, warps 1-3 stage later Q tiles.
+//   * single pass over key blocks of 64: S = Q.K^T (128x64 fp32 in TMEM) -> registers in two 32-column chunks
+//     -> P = exp2(S log2e - m) as packed bf16 back into TMEM -> O += P.V with P as the TMEM A operand.
+//     Online softmax at chunk granularity with lazy rescaling: O (and the P chunk already stored for the block)
+//     are rescaled only when the running max grows by more than 2^8.
+//   * FOUR softmax warpgroups (warps 4-19; thread = query row) work on four query tiles at once with their own
+//     S / P / O TMEM columns (4 x 128 = all 512), i.e. four warps per SM sub-partition, so that one warp's MUFU
+//     phase overlaps the others' TMEM-read / max / store phases.  Lane 0 of warp w (w < 4) issues the
+//     tcgen05.mma of warpgroup w in that group's natural order (blocking mbarrier waits, no polling).
+//     Every thread helps staging K/V and the first Q tiles; later Q tiles are restaged by their own warpgroup.
 #pragma once
 #include "attention_simt.cuh"
 #include "gemm_tc.cuh"
@@ -39,18 +41,19 @@ constexpr int QT = 128, KB = 128;        // query tile rows, rows of one staged 
 constexpr int SB = 64;                   // keys per MMA / softmax block (half an operand block)
 constexpr int MAX_KEYS = 1024;           // S + 1 <= 1024
 constexpr int NKB_MAX = MAX_KEYS / KB;
-constexpr int THREADS = 384, PREP_THREADS = 96;
+constexpr int NWG = 4;                   // softmax warpgroups = query tiles in flight per CTA
+constexpr int THREADS = 128 + NWG * 128, PREP_THREADS = 96;
 constexpr int BLK_BYTES = 4 * KB * 16;   // one 128-row operand block: [4 d-groups][128 rows][8 bf16] = 8 KB
 constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups (K-major LBO / MN-major SBO)
 constexpr int OFF_K = 0, OFF_V = OFF_K + NKB_MAX * BLK_BYTES, OFF_Q = OFF_V + NKB_MAX * BLK_BYTES,
-              OFF_MASK = OFF_Q + 4 * BLK_BYTES, OFF_BAR = OFF_MASK + NKB_MAX * 4 * 4, SMEM_BYTES = OFF_BAR + 256 + 128;
+              OFF_MASK = OFF_Q + NWG * BLK_BYTES, OFF_BAR = OFF_MASK + NKB_MAX * 4 * 4, SMEM_BYTES = OFF_BAR + 256 + 128;
 constexpr uint32_t TMEM_COLS = 512;
-// per-warpgroup TMEM columns: S fp32 2 x [64], P packed bf16 [32], O fp32 [32]
-constexpr uint32_t TM_WG = 256, TM_S = 0, TM_P = 128, TM_O = 160;
+// per-warpgroup TMEM columns: S fp32 [64], P packed bf16 [32], O fp32 [32]
+constexpr uint32_t TM_WG = 128, TM_S = 0, TM_P = 64, TM_O = 96;
 constexpr float RESCALE_TAU = 8.0f;      // log2 units: P <= 2^8 between rescales
 
 struct Bars {
-  uint64_t s_full[2][2], s_empty[2][2], p_full[2], pv_done[2], q_ready[2][2], q_free[2][2];
+  uint64_t s_full[NWG], s_empty[NWG], p_full[NWG], pv_done[NWG], q_ready[NWG];
   uint32_t tmem_base;
 };
 
@@ -82,6 +85,25 @@ __device__ __forceinline__ void tmem_st_32x32b_x16(uint32_t taddr, const uint32_
 __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t* r) {
   tmem_st_32x32b_x16(taddr, r);
   tmem_st_32x32b_x16(taddr + 16, r + 16);
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+// non-blocking phase test (the MMA issuer polls several warpgroups)
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float ex2(float x) {
@@ -141,6 +163,33 @@ __device__ __forceinline__ void rope_row(uint4* g, const float* __restrict__ cs,
   for (int i = 0; i < HD / 2; ++i) o[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
 }
 
+// same rotation with the cos (cst[0..2]) / sin (cst[3..5]) rows already in registers
+__device__ __forceinline__ void rope_row_regs(uint4* g, const float4* cst) {
+  float f[HD];
+  const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(g);
+#pragma unroll
+  for (int i = 0; i < HD / 2; ++i) {
+    const float2 v = __bfloat1622float2(h2[i]);
+    f[2 * i] = v.x;
+    f[2 * i + 1] = v.y;
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float cc[4] = {cst[j].x, cst[j].y, cst[j].z, cst[j].w};
+    const float ss[4] = {cst[3 + j].x, cst[3 + j].y, cst[3 + j].z, cst[3 + j].w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int i = 4 * j + e;
+      const float a = f[i], b = f[i + HD / 2];
+      f[i] = a * cc[e] - b * ss[e];
+      f[i + HD / 2] = b * cc[e] + a * ss[e];
+    }
+  }
+  uint32_t* o = reinterpret_cast<uint32_t*>(g);
+#pragma unroll
+  for (int i = 0; i < HD / 2; ++i) o[i] = pack_bf16(f[2 * i], f[2 * i + 1]);
+}
+
 // one Q row: global -> RoPE -> [d group][row][8] operand block
 __device__ __forceinline__ void stage_q_row(const AttnParams<bf16>& p, const bf16* qkv_h, uint8_t* qb, int r, int q,
                                             uint32_t seq_row0) {
@@ -156,9 +205,10 @@ __device__ __forceinline__ void stage_q_row(const AttnParams<bf16>& p, const bf1
   for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(qb + j * GRP_BYTES + r * 16) = g[j];
 }
 
-// One 32-column chunk of scores of one query row: key mask, running-max update with lazy rescale of O (TMEM)
-// and of the previous, not yet stored P chunk (registers), then P = exp2(x log2e - m) packed to bf16.
-__device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16], uint32_t* pk_prev, uint32_t bits,
+// One 32-column chunk of scores of one query row: key mask, running-max update with lazy rescale of O and of
+// the P chunk already stored for this block (both in TMEM, `tP_prev` = 0 if none), then P = exp2(x log2e - m)
+// packed to bf16.
+__device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16], uint32_t tP_prev, uint32_t bits,
                                            bool have_o, float& m_used, uint32_t tO, uint64_t* pv_done, uint32_t pv_parity) {
   const float LOG2E = 1.4426950408889634f;
   if (bits != 0xffffffffu) {
@@ -171,26 +221,34 @@ __device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16]
   for (int j = 0; j < 32; j += 2) bm[(j >> 1) & 3] = max3(bm[(j >> 1) & 3], __uint_as_float(x[j]), __uint_as_float(x[j + 1]));
   const float mb = fmaxf(fmaxf(bm[0], bm[1]), fmaxf(bm[2], bm[3])) * LOG2E;
   const bool grow = mb > m_used + RESCALE_TAU;           // false when both are -inf
-  if (__any_sync(0xffffffffu, grow)) {
+  if (__any_sync(0xffffffffu, grow)) {                   // rare after the first chunks of a tile
     const float sc = grow ? ex2(m_used - mb) : 1.0f;     // m_used = -inf -> 0 (nothing accumulated yet)
     if (have_o) {
       mbar_wait(pv_done, pv_parity);                     // every P.V issued so far has landed in O
       tcgen05_fence_after();
-      uint32_t o[32];
-      tmem_ld_32x32b_x32(tO, o);
-      tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * sc);
-      tmem_st_32x32b_x32(tO, o);
-      tmem_st_wait();
-    }
-    if (pk_prev) {
+      for (int hh = 0; hh < 2; ++hh) {
+        uint32_t o[16];
+        tmem_ld_32x32b_x16(tO + hh * 16, o);
+        tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pk_prev[j]));
-        pk_prev[j] = pack_bf16(f.x * sc, f.y * sc);
+        for (int j = 0; j < 16; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * sc);
+        tmem_st_32x32b_x16(tO + hh * 16, o);
       }
     }
+    if (tP_prev) {
+      uint32_t pp[16];
+      tmem_st_wait();                                    // the chunk was stored just before
+      tmem_ld_32x32b_x16(tP_prev, pp);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pp[j]));
+        pp[j] = pack_bf16(f.x * sc, f.y * sc);
+      }
+      tmem_st_32x32b_x16(tP_prev, pp);
+    }
+    tmem_st_wait();
     if (grow) m_used = mb;
   }
   const float mneg = (m_used == -INFINITY) ? 0.f : -m_used;
@@ -217,21 +275,17 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
   const int last_cols = (last_keys + 15) & ~15;              // MMA N / K extent of the last block
   const int q_begin = chunk * tiles_per_item * QT;
   const int q_end = min(S, q_begin + tiles_per_item * QT);
-  const int ntiles = (q_end - q_begin + QT - 1) / QT;
-  const int npairs = (ntiles + 1) >> 1;
+  const int ntiles = (q_end - q_begin + QT - 1) / QT;        // tile t is handled by warpgroup t % NWG in round t / NWG
   const uint32_t seq_row0 = (uint32_t)(nbi / p.inner) * S * p.inner + (nbi % p.inner);   // row of key/query 0
   const bf16* qkv_h = p.qkv + h * HD;
 
   if (tid == 0) {
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NWG; ++i) {
+      mbar_init(&bars->s_full[i], 1);
+      mbar_init(&bars->s_empty[i], 4);
       mbar_init(&bars->p_full[i], 4);
       mbar_init(&bars->pv_done[i], 1);
-      for (int j = 0; j < 2; ++j) {
-        mbar_init(&bars->s_full[i][j], 1);
-        mbar_init(&bars->s_empty[i][j], 4);
-        mbar_init(&bars->q_ready[i][j], 3);
-        mbar_init(&bars->q_free[i][j], 1);
-      }
+      mbar_init(&bars->q_ready[i], 4);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -239,7 +293,7 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // =============================== prologue: every thread stages K / V / Q(pair 0) ===============================
+  // =============================== prologue: every thread stages K / V / Q(round 0) ===============================
   {
     const uint32_t sV = smem_u32(smem + OFF_V);
     // V: cp.async 16-byte pieces straight into the MN-major operand layout (rows >= S zero-filled)
@@ -251,45 +305,63 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
     }
     cp_async_commit();
     if (tid == 0) dbg_stamp(dbg, 2);
-    // K: global -> registers -> RoPE -> K-major operand layout; key S = learned bias token (mha.py:265-268)
-    for (int key = tid; key < nkb * KB; key += THREADS) {
-      uint4 g[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-      if (key < S) {
-        const uint4* src = reinterpret_cast<const uint4*>(qkv_h + (size_t)(seq_row0 + (uint32_t)key * p.inner) * p.ld + C);
-        g[0] = __ldg(src);
-        g[1] = __ldg(src + 1);
-        g[2] = __ldg(src + 2);
-      } else if (key == S) {
-        uint32_t* gw = reinterpret_cast<uint32_t*>(g);
+    // K: global -> registers -> RoPE -> K-major operand layout; key S = learned bias token (mha.py:265-268).
+    // Two keys per thread with every load issued before the first use; the attendable-key bit masks come
+    // from the same pass (a warp holds 32 consecutive keys).
+    {
+      uint4 g[2][3];
+      float4 cst[2][6];
+      float valid[2];
 #pragma unroll
-        for (int e = 0; e < HD / 2; ++e) gw[e] = pack_bf16(p.bias_k[h * HD + 2 * e], p.bias_k[h * HD + 2 * e + 1]);
+      for (int u = 0; u < 2; ++u) {
+        const int key = tid + u * THREADS;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) g[u][j] = make_uint4(0, 0, 0, 0);
+        valid[u] = (key == S) ? 1.f : 0.f;
+        if (key < S) {
+          const uint32_t row = seq_row0 + (uint32_t)key * p.inner;
+          const uint4* src = reinterpret_cast<const uint4*>(qkv_h + (size_t)row * p.ld + C);
+#pragma unroll
+          for (int j = 0; j < 3; ++j) g[u][j] = __ldg(src + j);
+          valid[u] = __ldg(p.key_valid + row % (uint32_t)p.mask_mod);
+        }
+        if (p.cs && key <= S) {
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            cst[u][j] = __ldg(reinterpret_cast<const float4*>(p.cs + key * (HD / 2)) + j);
+            cst[u][3 + j] = __ldg(reinterpret_cast<const float4*>(p.sn + key * (HD / 2)) + j);
+          }
+        }
       }
-      if (p.cs && key <= S) rope_row(g, p.cs + key * (HD / 2), p.sn + key * (HD / 2));
-      uint8_t* kr = smem + OFF_K + (key >> 7) * BLK_BYTES + (key & 127) * 16;
 #pragma unroll
-      for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * GRP_BYTES) = g[j];
-      // padding d-group (d = 24..31): zeros for K, [1, 0, ..] for V (row-sum column)
-      *reinterpret_cast<uint4*>(kr + 3 * GRP_BYTES) = make_uint4(0, 0, 0, 0);
-      *reinterpret_cast<uint4*>(smem + OFF_V + (key >> 7) * BLK_BYTES + 3 * GRP_BYTES + (key & 127) * 16) = make_uint4(0x3F80u, 0, 0, 0);
+      for (int u = 0; u < 2; ++u) {
+        const int key = tid + u * THREADS;
+        if (key < nkb * KB) {                               // warp-uniform: nkb * KB and THREADS are multiples of 32
+          if (key == S) {
+            uint32_t* gw = reinterpret_cast<uint32_t*>(g[u]);
+#pragma unroll
+            for (int e = 0; e < HD / 2; ++e) gw[e] = pack_bf16(p.bias_k[h * HD + 2 * e], p.bias_k[h * HD + 2 * e + 1]);
+          }
+          if (p.cs && key <= S) rope_row_regs(g[u], cst[u]);
+          uint8_t* kr = smem + OFF_K + (key >> 7) * BLK_BYTES + (key & 127) * 16;
+#pragma unroll
+          for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * GRP_BYTES) = g[u][j];
+          // padding d-group (d = 24..31): zeros for K, [1, 0, ..] for V (row-sum column)
+          *reinterpret_cast<uint4*>(kr + 3 * GRP_BYTES) = make_uint4(0, 0, 0, 0);
+          *reinterpret_cast<uint4*>(smem + OFF_V + (key >> 7) * BLK_BYTES + 3 * GRP_BYTES + (key & 127) * 16) = make_uint4(0x3F80u, 0, 0, 0);
+          const uint32_t bits = __ballot_sync(0xffffffffu, valid[u] != 0.f);
+          if (lane == 0) kmask[key >> 5] = bits;
+        }
+      }
     }
     if (tid == 0) dbg_stamp(dbg, 3);
-    // Q tiles of pair 0 and the zero padding group of all four Q buffers
-    for (int i = tid; i < 4 * QT; i += THREADS)
-      *reinterpret_cast<uint4*>(smem + OFF_Q + (i >> 7) * BLK_BYTES + 3 * GRP_BYTES + (i & 127) * 16) = make_uint4(0, 0, 0, 0);
-    for (int i = tid; i < 2 * QT; i += THREADS) {
-      const int w = i >> 7, r = i & 127;
-      if (w < ntiles) stage_q_row(p, qkv_h, smem + OFF_Q + (w * 2) * BLK_BYTES, r, q_begin + w * QT + r, seq_row0);
+    // Q tiles of round 0 (one row per thread) and the zero padding group of the Q buffers
+    if (tid < NWG * QT) {
+      const int w = tid >> 7, r = tid & 127;
+      *reinterpret_cast<uint4*>(smem + OFF_Q + w * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(0, 0, 0, 0);
+      if (w < ntiles) stage_q_row(p, qkv_h, smem + OFF_Q + w * BLK_BYTES, r, q_begin + w * QT + r, seq_row0);
     }
     if (tid == 0) dbg_stamp(dbg, 4);
-    // attendable-key bit masks
-    for (int wi = warp; wi < nkb * 4; wi += THREADS / 32) {
-      const int key = wi * 32 + lane;
-      bool ok = key == S;
-      if (key < S) ok = p.key_valid[(seq_row0 + (uint32_t)key * p.inner) % (uint32_t)p.mask_mod] != 0.f;
-      const uint32_t bits = __ballot_sync(0xffffffffu, ok);
-      if (lane == 0) kmask[wi] = bits;
-    }
-    if (tid == 0) dbg_stamp(dbg, 5);
     cp_async_wait<0>();
     if (tid == 0) dbg_stamp(dbg, 6);
   }
@@ -311,124 +383,96 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
   if (tid == 0) dbg_stamp(dbg, 1);
   const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V), sQ = smem_u32(smem + OFF_Q);
 
-  if (warp == 0) {
-    // =============================== MMA issuer ===============================
+  if (warp < NWG) {
+    // =============================== MMA issuers ===============================
+    // Lane 0 of warp w issues every tcgen05.mma of warpgroup w, in that group's natural order: Q.K^T of block
+    // k+1 as soon as the softmax warps have pulled S(k) into registers, then P.V of block k once P(k) is in TMEM.
+    const int w = warp;
     if (lane == 0) {
-      uint32_t qk_cnt[2] = {0, 0}, pv_cnt[2] = {0, 0};     // blocks issued per warpgroup (S buffer = count & 1)
-      auto issue_qk = [&](int w, int buf, int kb) {
-        const uint32_t n_ = qk_cnt[w], sb = n_ & 1;
-        mbar_wait(&bars->s_empty[w][sb], ((n_ >> 1) & 1) ^ 1);   // softmax has pulled the block that used this S buffer
+      uint32_t nq = 0, np = 0;            // blocks issued so far (barrier phases)
+      auto issue_qk = [&](int kb) {
+        mbar_wait(&bars->s_empty[w], (nq & 1) ^ 1);              // S of the previous block is in registers
         tcgen05_fence_after();
         const int n = (kb == nsb - 1) ? last_cols : SB;
         const uint32_t id = idesc(QT, n, false);
-        const uint32_t d = tmem + w * TM_WG + TM_S + sb * SB;
-        const uint32_t qa = sQ + (w * 2 + buf) * BLK_BYTES, ka = sK + (kb >> 1) * BLK_BYTES + (kb & 1) * (SB * 16);
+        const uint32_t d = tmem + w * TM_WG + TM_S;
+        const uint32_t qa = sQ + w * BLK_BYTES, ka = sK + (kb >> 1) * BLK_BYTES + (kb & 1) * (SB * 16);
 #pragma unroll
         for (int j = 0; j < DP / 16; ++j)
           umma_bf16(d, desc_nosw(qa + j * 2 * GRP_BYTES, GRP_BYTES, 128), desc_nosw(ka + j * 2 * GRP_BYTES, GRP_BYTES, 128), id, j);
-        tcgen05_commit(&bars->s_full[w][sb]);
-        ++qk_cnt[w];
-        if (kb == nsb - 1) tcgen05_commit(&bars->q_free[w][buf]);   // last use of this Q tile
+        tcgen05_commit(&bars->s_full[w]);
+        ++nq;
       };
-      auto issue_pv = [&](int w, int kb) {
-        mbar_wait(&bars->p_full[w], pv_cnt[w] & 1);
-        tcgen05_fence_after();
-        const int n = (kb == nsb - 1) ? last_cols : SB;
-        const uint32_t id = idesc(QT, DP, true);
-        const uint32_t d = tmem + w * TM_WG + TM_O, pa = tmem + w * TM_WG + TM_P;
-        const uint32_t va = sV + (kb >> 1) * BLK_BYTES + (kb & 1) * (SB * 16);
-        for (int j = 0; j < n / 16; ++j)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
-          umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (kb == 0 && j == 0) ? 0u : 1u);
-        tcgen05_commit(&bars->pv_done[w]);
-        ++pv_cnt[w];
-      };
-      dbg_stamp(dbg, 14);
-      for (int pr = 0; pr < npairs; ++pr) {
-        const int buf = pr & 1;
-        const int nw = (2 * pr + 1 < ntiles) ? 2 : 1;
-        if (pr > 0)
-          for (int w = 0; w < nw; ++w) mbar_wait(&bars->q_ready[w][buf], ((pr - 1) >> 1) & 1);
-        for (int kb = 0; kb < 2 && kb < nsb; ++kb)
-          for (int w = 0; w < nw; ++w) issue_qk(w, buf, kb);
+      if (w == 0) dbg_stamp(dbg, 14);
+      int rd = 0;
+      for (int t = w; t < ntiles; t += NWG, ++rd) {
+        if (rd > 0) {
+          mbar_wait(&bars->q_ready[w], (rd - 1) & 1);            // the warpgroup has restaged its Q buffer
+          tcgen05_fence_after();
+        }
+        issue_qk(0);
         for (int kb = 0; kb < nsb; ++kb) {
-          for (int w = 0; w < nw; ++w) {
-            issue_pv(w, kb);
-            if (kb + 2 < nsb) issue_qk(w, buf, kb + 2);
-          }
+          if (kb + 1 < nsb) issue_qk(kb + 1);
+          mbar_wait(&bars->p_full[w], np & 1);
+          tcgen05_fence_after();
+          const int n = (kb == nsb - 1) ? last_cols : SB;
+          const uint32_t id = idesc(QT, DP, true);
+          const uint32_t d = tmem + w * TM_WG + TM_O, pa = tmem + w * TM_WG + TM_P;
+          const uint32_t va = sV + (kb >> 1) * BLK_BYTES + (kb & 1) * (SB * 16);
+          for (int j = 0; j < n / 16; ++j)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
+            umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (kb == 0 && j == 0) ? 0u : 1u);
+          tcgen05_commit(&bars->pv_done[w]);
+          ++np;
         }
       }
-      dbg_stamp(dbg, 15);
+      if (w == 0) dbg_stamp(dbg, 15);
     }
-  } else if (warp < 4) {
-    // =============================== Q staging warps (pairs >= 1) ===============================
-    const int pt = tid - 32;
-    for (int pr = 1; pr < npairs; ++pr) {
-      const int buf = pr & 1;
-      for (int w = 0; w < 2; ++w) {
-        const int t = 2 * pr + w;
-        if (t >= ntiles) break;
-        // q_ready[.][buf] / q_free[.][buf] phases count the staged uses of the buffer; pair 0 was staged by the prologue
-        if (pr >= 2) mbar_wait(&bars->q_free[w][buf], ((pr >> 1) & 1) ^ 1);
-        uint8_t* qb = smem + OFF_Q + (w * 2 + buf) * BLK_BYTES;
-        for (int r = pt; r < QT; r += PREP_THREADS) stage_q_row(p, qkv_h, qb, r, q_begin + t * QT + r, seq_row0);
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->q_ready[w][buf]);
-      }
-    }
-    if (pt == 0) dbg_stamp(dbg, 13);
   } else {
     // =============================== softmax warps ===============================
     const int w = (warp - 4) >> 2, quarter = warp & 3;
     const int r = quarter * 32 + lane;                       // query row in tile = TMEM lane
     const uint32_t tbase = tmem + w * TM_WG + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t tP = tbase + TM_P, tO = tbase + TM_O;
-    const bool stamp = (r == 0);
+    const uint32_t tS = tbase + TM_S, tP = tbase + TM_P, tO = tbase + TM_O;
+    const bool stamp = (r == 0 && w < 2);
     uint32_t it = 0;                                         // S blocks consumed by this warpgroup
-    for (int pr = 0; pr < npairs; ++pr) {
-      const int t = 2 * pr + w;
-      if (t >= ntiles) break;
+    for (int t = w; t < ntiles; t += NWG) {
       const int q = q_begin + t * QT + r;
       float m_used = -INFINITY;
-      uint32_t xa[32], xb[32];
-      mbar_wait(&bars->s_full[w][it & 1], (it >> 1) & 1);
-      tcgen05_fence_after();
-      tmem_ld_32x32b_x32(tbase + TM_S + (it & 1) * SB, xa);
       for (int kb = 0; kb < nsb; ++kb, ++it) {
         const bool two = (kb < nsb - 1) || last_keys > 32;     // second 32-column chunk holds keys
+        uint32_t xa[32], xb[32], pk[16];
+        mbar_wait(&bars->s_full[w], it & 1);
+        tcgen05_fence_after();
         if (stamp && it < 16) dbg_stamp(dbg, 16 + w * 40 + 2 * it);
-        tmem_ld_wait();                                        // chunk A in registers
-        if (stamp && it == 4) dbg_stamp(dbg, 88);
-        if (two) tmem_ld_32x32b_x32(tbase + TM_S + (it & 1) * SB + 32, xb);
-        uint32_t pka[16], pkb[16];
-        soft_chunk(xa, pka, nullptr, kmask[kb * 2], kb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1);
-        if (stamp && it == 4) dbg_stamp(dbg, 89);
-        tmem_ld_wait();                                        // chunk B in registers: S buffer is free
-        if (stamp && it == 4) dbg_stamp(dbg, 90);
+        tmem_ld_32x32b_x32(tS, xa);
+        if (two) tmem_ld_32x32b_x32(tS + 32, xb);
+        tmem_ld_wait();
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->s_empty[w][it & 1]);
-        if (kb + 1 < nsb) {                                    // prefetch chunk A of the next block
-          mbar_wait(&bars->s_full[w][(it + 1) & 1], ((it + 1) >> 1) & 1);
-          tcgen05_fence_after();
-          tmem_ld_32x32b_x32(tbase + TM_S + ((it + 1) & 1) * SB, xa);
-        }
-        if (stamp && it == 4) dbg_stamp(dbg, 91);
-        if (two) soft_chunk(xb, pkb, pka, kmask[kb * 2 + 1], kb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1);
-        if (stamp && it == 4) dbg_stamp(dbg, 92);
+        if (lane == 0) mbar_arrive(&bars->s_empty[w]);         // the next Q.K^T block may overwrite S
+        soft_chunk(xa, pk, 0u, kmask[kb * 2], kb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1);
         if (it > 0) {
           mbar_wait(&bars->pv_done[w], (it - 1) & 1);          // P.V of the previous block has read P
           tcgen05_fence_after();
         }
-        if (stamp && it == 4) dbg_stamp(dbg, 93);
-        tmem_st_32x32b_x16(tP, pka);
-        if (two) tmem_st_32x32b_x16(tP + 16, pkb);
+        tmem_st_32x32b_x16(tP, pk);
+        if (two) {
+          soft_chunk(xb, pk, tP, kmask[kb * 2 + 1], kb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1);
+          tmem_st_32x32b_x16(tP + 16, pk);
+        }
         tmem_st_wait();
-        if (stamp && it == 4) dbg_stamp(dbg, 94);
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->p_full[w]);
         if (stamp && it < 16) dbg_stamp(dbg, 17 + w * 40 + 2 * it);
+      }
+      // ---- next round's Q tile: every Q.K^T of this tile has completed (its last S block was consumed above),
+      // so the warpgroup restages its own buffer, one row per thread
+      if (t + NWG < ntiles) {
+        stage_q_row(p, qkv_h, smem + OFF_Q + w * BLK_BYTES, r, q + NWG * QT, seq_row0);
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->q_ready[w]);
       }
       // ---- epilogue: O / rowsum -> bf16 -> global
       mbar_wait(&bars->pv_done[w], (it - 1) & 1);
@@ -437,7 +481,7 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
       tmem_ld_32x32b_x32(tO, o);
       tmem_ld_wait();
       tcgen05_fence_before();
-      if (stamp && pr == 0) dbg_stamp(dbg, 48 + w * 40);
+      if (stamp && t == w) dbg_stamp(dbg, 48 + w * 40);
       if (q < S) {
         const float inv = 1.0f / __uint_as_float(o[HD]);
         uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(seq_row0 + (uint32_t)q * p.inner) * p.ldo + h * HD);
@@ -475,11 +519,11 @@ inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStre
     MD_CUDA(cudaFuncSetAttribute(atc::attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
     configured = true;
   }
-  // query tiles per CTA: as many as possible (K/V staging is per CTA) while keeping >= 4 CTAs per SM of work
+  // query tiles per CTA: NWG are in flight at once; take two rounds (K/V staged once for 8 tiles) only while
+  // that still leaves >= 4 CTAs of work per SM
   const int qtiles = (p.S + atc::QT - 1) / atc::QT;
-  int per = 8;
-  while (per > 2 && (long)p.nb * p.H * ((qtiles + per - 1) / per) < 4L * num_sms()) per >>= 1;
-  if (per > qtiles) per = (qtiles + 1) & ~1;
+  int per = 2 * atc::NWG;
+  if ((long)p.nb * p.H * ((qtiles + per - 1) / per) < 4L * num_sms()) per = atc::NWG;
   const int chunks = (qtiles + per - 1) / per;
   ProfScope ps(PC_ATTN_TC, st);
   atc::attention_tc_kernel<<<p.nb * p.H * chunks, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, per, g_dbg_buf, g_dbg_cta);
