@@ -129,7 +129,9 @@ int mdgen_debug_set_buffer(long long* device_buf, int32_t cta);
 
 /* unit-test entry points (tests/ only): run one kernel family on caller buffers --------- */
 /* C[M,N] = A[M,K] . W[N,K]^T + bias, A/W fp32 on device (converted to bf16 inside when
- * use_tc != 0 -> tcgen05 path; fp32 SIMT path otherwise). */
+ * use_tc != 0 -> tcgen05 path; fp32 SIMT path otherwise).  tcgen05 epilogue variants: use_tc = 1 fp32 store,
+ * 2 bf16 store, 3 bf16 erf-GELU (both converted back to fp32 into C), 4 C[m,n] += bias[n] * (acc + bias[n])
+ * (the gated-residual epilogue with gate = bias). */
 int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float* W,
                     const float* bias, float* C, int32_t use_tc, int32_t block_n,
                     mdgen_stream_t stream);

@@ -110,6 +110,7 @@ struct EpiParams {
   int rows_per_batch = 1;        // batch(m) = (m / rows_per_batch) % nbatch
   int nbatch = 1;
   float dt = 0.f;
+  int staged = 0;                // set by launch_gemm_tc: pointers / pitches allow the coalesced 128-bit epilogue
 };
 
 }  // namespace mdgen

@@ -238,4 +238,11 @@ __global__ void bf16_to_f32_kernel(const bf16* __restrict__ x, float* __restrict
   if (i < n) y[i] = __bfloat162float(x[i]);
 }
 
+__global__ void bf16_rows_to_f32_kernel(const bf16* __restrict__ x, int ldx, float* __restrict__ y, int ldy, int M, int N) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)M * N) return;
+  const int m = (int)(i / N), n = (int)(i % N);
+  y[(size_t)m * ldy + n] = __bfloat162float(x[(size_t)m * ldx + n]);
+}
+
 }  // namespace mdgen

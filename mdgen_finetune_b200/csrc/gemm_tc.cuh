@@ -22,9 +22,13 @@ constexpr int NUM_THREADS = 64 + 32 * NUM_EPI_WARPS;
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
 
 __host__ __device__ constexpr int stage_bytes(int bn) { return A_STAGE_BYTES + bn * BLOCK_K * 2; }
-__host__ __device__ constexpr int num_stages(int bn) { return bn >= 192 ? 5 : (bn >= 128 ? 6 : 8); }
+__host__ __device__ constexpr int num_stages(int bn) { return bn >= 128 ? 5 : (bn >= 64 ? 6 : 8); }
+// per-epilogue-warp staging tile: 32 rows x 128 B (+16 B pad per row: conflict-free 128-bit rows both ways)
+constexpr int STG_PITCH = 144, STG_BYTES = 32 * STG_PITCH;
 __host__ __device__ constexpr int tmem_cols(int bn) { return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512; }
-__host__ __device__ constexpr int smem_bytes(int bn) { return num_stages(bn) * stage_bytes(bn) + 1024 + 256; }
+__host__ __device__ constexpr int smem_bytes(int bn) { return num_stages(bn) * stage_bytes(bn) + NUM_EPI_WARPS * STG_BYTES + 1024 + 256; }
+
+static_assert(smem_bytes(128) <= 227 * 1024 && smem_bytes(64) <= 227 * 1024 && smem_bytes(32) <= 227 * 1024, "shared memory budget");
 
 // ---- PTX wrappers ----------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -150,7 +154,9 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& p, int m, int n0
     float* x = p.resid + (size_t)m * p.ldr + n0;
     const float* g = nullptr;
     if constexpr (EPI == EPI_GATE_RESID) g = p.gate + (size_t)((m / p.rows_per_batch) % p.nbatch) * p.gate_stride + n0;
-    if (full) {
+    const bool vec = full && (p.ldr % 4 == 0) && (((uintptr_t)p.resid & 15) == 0) &&
+                     (EPI != EPI_GATE_RESID || ((p.gate_stride % 4 == 0) && (((uintptr_t)p.gate & 15) == 0)));
+    if (vec) {
 #pragma unroll
       for (int j = 0; j < 32; j += 4) {
         float4 xv = *reinterpret_cast<float4*>(x + j);
@@ -176,6 +182,112 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& p, int m, int n0
         o[j] = v[j];
         if (s) s[j] = fmaf(p.dt, v[j], s[j]);
       }
+  }
+}
+
+// ---- staged epilogues: registers (thread = row) -> per-warp shared tile -> coalesced 128-bit global accesses ----
+// The row-per-thread layout that tcgen05.ld delivers makes every direct global access touch 32 different
+// cache lines per instruction; transposing through shared memory turns them into full 128-byte lines.
+
+// bf16 output of W32 = 32 * PER consecutive columns of 32 rows (EPI_STORE / EPI_GELU)
+template <int EPI, int PER>
+__device__ __forceinline__ void epilogue_staged_bf16(const EpiParams& p, uint8_t* stg, int lane, int mrow0, int n0, int M,
+                                                     int N, uint32_t (&r)[PER][32]) {
+  constexpr int PIECES = PER * 4;               // 16-byte pieces per row
+  constexpr int ROWS_PER = 32 / PIECES;         // rows covered by one warp-wide access
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int n = n0 + i * 32 + j + e;
+        v[e] = __uint_as_float(r[i][j + e]) + ((p.bias && n < N) ? __ldg(p.bias + n) : 0.f);
+        if constexpr (EPI == EPI_GELU) v[e] = gelu_erf_fast(v[e]);
+      }
+      __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+      __nv_bfloat162 c = __floats2bfloat162_rn(v[4], v[5]), d = __floats2bfloat162_rn(v[6], v[7]);
+      *reinterpret_cast<uint4*>(stg + lane * STG_PITCH + (i * 4 + j / 8) * 16) =
+          make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b), *reinterpret_cast<uint32_t*>(&c),
+                     *reinterpret_cast<uint32_t*>(&d));
+    }
+  }
+  __syncwarp();
+  bf16* out = reinterpret_cast<bf16*>(p.out);
+  const int piece = lane % PIECES, rsub = lane / PIECES;
+  const int n = n0 + piece * 8;
+#pragma unroll
+  for (int it = 0; it < 32 / ROWS_PER; ++it) {
+    const int row = it * ROWS_PER + rsub, m = mrow0 + row;
+    const uint4 v = *reinterpret_cast<const uint4*>(stg + row * STG_PITCH + piece * 16);
+    if (m < M) {
+      bf16* o = out + (size_t)m * p.ldo + n;
+      if (n + 8 <= N) {
+        *reinterpret_cast<uint4*>(o) = v;
+      } else {
+        const bf16* e = reinterpret_cast<const bf16*>(&v);
+        for (int k = 0; k < 8; ++k)
+          if (n + k < N) o[k] = e[k];
+      }
+    }
+  }
+  __syncwarp();
+}
+
+// fp32 residual read-modify-write of 32 columns x 32 rows: x += gate * (acc + bias)   (EPI_GATE_RESID / EPI_RESID)
+// xv = the 8 residual float4 of this lane, prefetched by residual_prefetch() before the accumulator was ready.
+template <int EPI>
+__device__ __forceinline__ void epilogue_staged_resid(const EpiParams& p, uint8_t* stg, int lane, int mrow0, int n0, int M,
+                                                      int N, const uint32_t (&r)[32], const float4 (&xv)[8]) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    float v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int n = n0 + j + e;
+      v[e] = __uint_as_float(r[j + e]) + ((p.bias && n < N) ? __ldg(p.bias + n) : 0.f);
+    }
+    *reinterpret_cast<float4*>(stg + lane * STG_PITCH + j * 4) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  __syncwarp();
+  const int c4 = lane & 7, rsub = lane >> 3;
+  const int n = n0 + c4 * 4;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int row = it * 4 + rsub, m = mrow0 + row;
+    const float4 v = *reinterpret_cast<const float4*>(stg + row * STG_PITCH + c4 * 16);
+    if (m < M && n < N) {
+      float* x = p.resid + (size_t)m * p.ldr + n;
+      float4 g = make_float4(1.f, 1.f, 1.f, 1.f);
+      const float* gp = nullptr;
+      if constexpr (EPI == EPI_GATE_RESID) gp = p.gate + (size_t)((m / p.rows_per_batch) % p.nbatch) * p.gate_stride + n;
+      if (n + 4 <= N) {
+        if constexpr (EPI == EPI_GATE_RESID) g = __ldg(reinterpret_cast<const float4*>(gp));
+        float4 o = xv[it];
+        o.x = fmaf(g.x, v.x, o.x);
+        o.y = fmaf(g.y, v.y, o.y);
+        o.z = fmaf(g.z, v.z, o.z);
+        o.w = fmaf(g.w, v.w, o.w);
+        *reinterpret_cast<float4*>(x) = o;
+      } else {
+        const float vv[4] = {v.x, v.y, v.z, v.w};
+        for (int k = 0; k < 4; ++k)
+          if (n + k < N) x[k] += (gp ? gp[k] : 1.f) * vv[k];
+      }
+    }
+  }
+  __syncwarp();
+}
+// the residual values epilogue_staged_resid() will update (issued early: their latency hides behind the MMAs)
+__device__ __forceinline__ void residual_prefetch(const EpiParams& p, int lane, int mrow0, int n0, int M, int N, float4 (&xv)[8]) {
+  const int c4 = lane & 7, rsub = lane >> 3;
+  const int n = n0 + c4 * 4;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int m = mrow0 + it * 4 + rsub;
+    xv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (m < M && n + 4 <= N) xv[it] = *reinterpret_cast<const float4*>(p.resid + (size_t)m * p.ldr + n);
   }
 }
 
@@ -285,13 +397,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     const int quarter = warp & 3, half = (warp - 2) >> 2;
     constexpr int CHUNKS = BN / 32;                      // 32-column chunks per tile
     constexpr int PER = (CHUNKS + 1) / 2;                // chunks per warp
+    constexpr bool kResid = (EPI == EPI_GATE_RESID || EPI == EPI_RESID);
+    constexpr bool kBf16 = (EPI == EPI_STORE || EPI == EPI_GELU) && sizeof(OT) == 2;
+    uint8_t* stg = smem + STAGES * STAGE_BYTES + 256 + (warp - 2) * STG_BYTES;
+    const bool active = half * PER < CHUNKS;             // BN = 32: only the first column half has work
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int mb = tile / num_n, nb = tile % num_n;
+      const int mrow0 = mb * BLOCK_M + quarter * 32;
+      const int ncol0 = nb * BN + half * PER * 32;
+      float4 xv[kResid ? PER : 1][8];
+      if constexpr (kResid) {
+        if (ep.staged && active) {
+#pragma unroll
+          for (int i = 0; i < PER; ++i) residual_prefetch(ep, lane, mrow0, ncol0 + i * 32, M, N, xv[i]);
+        }
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
-      const int m = mb * BLOCK_M + quarter * 32 + lane;
+      const int m = mrow0 + lane;
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
       uint32_t r[PER][32];
 #pragma unroll
@@ -304,11 +429,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (active && ncol0 < N) {
+        if (kBf16 && ep.staged) {
+          if constexpr (kBf16) epilogue_staged_bf16<EPI, PER>(ep, stg, lane, mrow0, ncol0, M, N, r);
+        } else if (kResid && ep.staged) {
+          if constexpr (kResid) {
 #pragma unroll
-      for (int i = 0; i < PER; ++i) {
-        const int c = half * PER + i;
-        const int n0 = nb * BN + c * 32;
-        if (c < CHUNKS && m < M && n0 < N) epilogue_chunk<EPI, OT>(ep, m, n0, N, r[i]);
+            for (int i = 0; i < PER; ++i)
+              if (ncol0 + i * 32 < N) epilogue_staged_resid<EPI>(ep, stg, lane, mrow0, ncol0 + i * 32, M, N, r[i], xv[i]);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < PER; ++i) {
+            const int n0 = ncol0 + i * 32;
+            if (half * PER + i < CHUNKS && m < M && n0 < N) epilogue_chunk<EPI, OT>(ep, m, n0, N, r[i]);
+          }
+        }
       }
       if (++acc == 2) {
         acc = 0;

@@ -122,13 +122,18 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
       block_n = t128 >= num_sms() ? 128 : 64;
     }
   }
+  EpiParams epp = ep;
+  auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
+  if ((epi == EPI_STORE || epi == EPI_GELU) && out_bf16) epp.staged = al16(ep.out) && ep.ldo % 8 == 0;
+  else if (epi == EPI_RESID) epp.staged = al16(ep.resid) && ep.ldr % 4 == 0;
+  else if (epi == EPI_GATE_RESID) epp.staged = al16(ep.resid) && ep.ldr % 4 == 0 && al16(ep.gate) && ep.gate_stride % 4 == 0;
   CUtensorMap ta, tw;
   MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
   MD_TRY(make_tmap_2d(&tw, W, N, K, ldw, block_n));
   switch (block_n) {
-    case 32: return launch_tc_bn<32>(ta, tw, M, N, K, epi, out_bf16, ep, st);
-    case 64: return launch_tc_bn<64>(ta, tw, M, N, K, epi, out_bf16, ep, st);
-    case 128: return launch_tc_bn<128>(ta, tw, M, N, K, epi, out_bf16, ep, st);
+    case 32: return launch_tc_bn<32>(ta, tw, M, N, K, epi, out_bf16, epp, st);
+    case 64: return launch_tc_bn<64>(ta, tw, M, N, K, epi, out_bf16, epp, st);
+    case 128: return launch_tc_bn<128>(ta, tw, M, N, K, epi, out_bf16, epp, st);
   }
   set_error("launch_gemm_tc: block_n must be 32, 64 or 128");
   return -1;
@@ -1159,10 +1164,32 @@ int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float
   MD_CUDA(cudaMalloc((void**)&Wb, (size_t)N * K * 2));
   f32_to_bf16_kernel<<<(unsigned)(((size_t)M * K + 255) / 256), 256, 0, st>>>(A, Ab, (size_t)M * K, 1.f);
   f32_to_bf16_kernel<<<(unsigned)(((size_t)N * K + 255) / 256), 256, 0, st>>>(W, Wb, (size_t)N * K, 1.f);
-  int r = launch_gemm_tc(Ab, K, Wb, K, M, N, K, EPI_STORE, false, ep, block_n, st);
+  // use_tc: 1 fp32 store | 2 bf16 store | 3 bf16 erf-GELU | 4 C += bias[n] * (acc + bias[n])  (gate = bias, one batch)
+  bf16* Cb = nullptr;
+  int r = 0;
+  if (use_tc == 2 || use_tc == 3) {
+    const int ldo = (N + 7) & ~7;
+    MD_CUDA(cudaMalloc((void**)&Cb, (size_t)M * ldo * 2));
+    ep.out = Cb;
+    ep.ldo = ldo;
+    r = launch_gemm_tc(Ab, K, Wb, K, M, N, K, use_tc == 2 ? EPI_STORE : EPI_GELU, true, ep, block_n, st);
+    if (r == 0) bf16_rows_to_f32_kernel<<<(unsigned)(((size_t)M * N + 255) / 256), 256, 0, st>>>(Cb, ldo, Cout, N, M, N);
+  } else if (use_tc == 4) {
+    ep.out = nullptr;
+    ep.resid = Cout;
+    ep.ldr = N;
+    ep.gate = bias;
+    ep.gate_stride = 0;
+    ep.rows_per_batch = M;
+    ep.nbatch = 1;
+    r = launch_gemm_tc(Ab, K, Wb, K, M, N, K, EPI_GATE_RESID, false, ep, block_n, st);
+  } else {
+    r = launch_gemm_tc(Ab, K, Wb, K, M, N, K, EPI_STORE, false, ep, block_n, st);
+  }
   cudaError_t e = cudaStreamSynchronize(st);
   cudaFree(Ab);
   cudaFree(Wb);
+  cudaFree(Cb);
   if (r == 0 && e != cudaSuccess) {
     set_error(std::string("gemm_tc kernel: ") + cudaGetErrorString(e));
     return MDGEN_ECUDA;

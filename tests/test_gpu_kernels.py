@@ -45,6 +45,38 @@ def test_gemm_tcgen05_bf16(M, N, K, bn):
     assert err < 1e-5, err          # fp32 accumulation of identical bf16 products
 
 
+@pytest.mark.parametrize("M,N,K,bn", [(4000, 1152, 384, 0), (777, 1536, 384, 128), (1000, 384, 384, 64), (129, 48, 384, 64),
+                                      (300, 72, 64, 0), (64, 24, 384, 32)])
+@pytest.mark.parametrize("mode", [2, 3])
+def test_gemm_tcgen05_bf16_out_staged_epilogue(M, N, K, bn, mode):
+    g = torch.Generator().manual_seed(M + N + K)
+    A, W, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5, torch.randn(N, generator=g)
+    C = _gemm(A.cuda(), W.cuda(), b.cuda(), mode, bn).cpu()
+    ref = A.bfloat16().double() @ W.bfloat16().double().T + b.double()
+    if mode == 3:
+        ref = ref * 0.5 * (1.0 + torch.erf(ref / 2 ** 0.5))          # layers.py:78-85
+    assert torch.isfinite(C).all()
+    err = float((C - ref.float()).norm() / ref.norm())
+    assert err < 4e-3, err          # one bf16 rounding of the output
+
+
+@pytest.mark.parametrize("M,N,K,bn", [(4000, 384, 1536, 0), (4000, 384, 384, 0), (777, 384, 384, 128), (129, 48, 384, 64),
+                                      (300, 21, 384, 0), (100, 70, 64, 64)])
+def test_gemm_tcgen05_gated_residual_epilogue(M, N, K, bn):
+    g = torch.Generator().manual_seed(M + N + K)
+    A, W, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5, torch.randn(N, generator=g)
+    x0 = torch.randn(M, N, generator=g)
+    M_, K_ = A.shape
+    C = x0.clone().cuda()
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    dA, dW, db = A.cuda(), W.cuda(), b.cuda()
+    _lib.check(_lib.lib().mdgen_test_gemm(M, N, K, _p(dA), _p(dW), _p(db), _p(C), 4, bn, st), "test_gemm")
+    torch.cuda.synchronize()
+    acc = A.bfloat16().double() @ W.bfloat16().double().T + b.double()
+    ref = (x0.double() + b.double() * acc).float()
+    assert float((C.cpu() - ref).norm() / ref.norm()) < 1e-5
+
+
 def _attn_ref(qkv, bk, bv, valid, nb, S, inner, H, hd, rope):
     from oracle import mdgen_oracle as O
     C = H * hd
