@@ -110,6 +110,8 @@ struct EpiParams {
   int rows_per_batch = 1;        // batch(m) = (m / rows_per_batch) % nbatch
   int nbatch = 1;
   float dt = 0.f;
+  long long* dbg = nullptr;      // kernel-developer clock stamps of CTA dbg_cta (mdgen_debug_set_buffer), normally null
+  int dbg_cta = 0;
   int staged = 0;                // set by launch_gemm_tc: pointers / pitches allow the coalesced 128-bit epilogue
 };
 

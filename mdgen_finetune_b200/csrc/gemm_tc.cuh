@@ -23,6 +23,13 @@ constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
 
 __host__ __device__ constexpr int stage_bytes(int bn) { return A_STAGE_BYTES + bn * BLOCK_K * 2; }
 __host__ __device__ constexpr int num_stages(int bn) { return bn >= 128 ? 5 : (bn >= 64 ? 6 : 8); }
+// W-stationary variant (K <= WS_MAX_KB * 64): the CTA keeps its whole [BN, K] weight slice in shared memory and
+// streams only A tiles.  At 128x128 tiles a streamed-operand GEMM needs (128 + 128) * 2 B per 2 * 128 * 128 FLOP =
+// 128 B/clk/SM at tensor peak, ~3x what the L2 -> SM fabric delivers (~6300 B/clk chip-wide); W-stationary halves it.
+constexpr int WS_MAX_KB = 6, WS_STAGES = 5;
+__host__ __device__ constexpr int ws_smem_bytes(int bn) {
+  return WS_MAX_KB * bn * BLOCK_K * 2 + WS_STAGES * A_STAGE_BYTES + 8 * 32 * 144 + 1024 + 256;
+}
 // per-epilogue-warp staging tile: 32 rows x 128 B (+16 B pad per row: conflict-free 128-bit rows both ways)
 constexpr int STG_PITCH = 144, STG_BYTES = 32 * STG_PITCH;
 __host__ __device__ constexpr int tmem_cols(int bn) { return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512; }
@@ -235,82 +242,132 @@ __device__ __forceinline__ void epilogue_staged_bf16(const EpiParams& p, uint8_t
   __syncwarp();
 }
 
-// fp32 residual read-modify-write of 32 columns x 32 rows: x += gate * (acc + bias)   (EPI_GATE_RESID / EPI_RESID)
-// xv = the 8 residual float4 of this lane, prefetched by residual_prefetch() before the accumulator was ready.
+// fp32 residual read-modify-write of 32 columns x 32 rows: x += gate * (acc + bias)   (EPI_GATE_RESID / EPI_RESID).
+// Everything the inner loops need is precomputed per tile into registers (ResidLane): kernel parameters live in
+// the constant bank and re-reading them inside the loops (LDC, long-scoreboard latency) dominated this epilogue.
+struct ResidLane {
+  float* x;            // this lane's first residual element: row rsub, columns n .. n+3 of the chunk
+  size_t row_step;     // 4 rows, in floats
+  const float* g0;     // gate row for rows < split, already offset to column n (or null)
+  const float* g1;     // gate row for rows >= split
+  int split;           // first row (0..32) that belongs to the next batch element
+  int rows;            // valid rows of the 32 (M tail)
+  int n;               // first of the lane's 4 columns in chunk 0 of the warp
+};
 template <int EPI>
-__device__ __forceinline__ void epilogue_staged_resid(const EpiParams& p, uint8_t* stg, int lane, int mrow0, int n0, int M,
-                                                      int N, const uint32_t (&r)[32], const float4 (&xv)[8]) {
-#pragma unroll
-  for (int j = 0; j < 32; j += 4) {
-    float v[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int n = n0 + j + e;
-      v[e] = __uint_as_float(r[j + e]) + ((p.bias && n < N) ? __ldg(p.bias + n) : 0.f);
-    }
-    *reinterpret_cast<float4*>(stg + lane * STG_PITCH + j * 4) = make_float4(v[0], v[1], v[2], v[3]);
+__device__ __forceinline__ ResidLane resid_lane(const EpiParams& p, int lane, int mrow0, int n0, int M, int N) {
+  ResidLane L;
+  const int c4 = lane & 7, rsub = lane >> 3, n = n0 + c4 * 4;
+  L.x = p.resid + (size_t)(mrow0 + rsub) * p.ldr + n;
+  L.row_step = (size_t)4 * p.ldr;
+  L.rows = M - mrow0;
+  L.n = n;
+  L.g0 = L.g1 = nullptr;
+  L.split = 32;
+  if constexpr (EPI == EPI_GATE_RESID) {
+    const int q = mrow0 / p.rows_per_batch;
+    L.g0 = p.gate + (size_t)(q % p.nbatch) * p.gate_stride + n;
+    L.g1 = p.gate + (size_t)((q + 1) % p.nbatch) * p.gate_stride + n;
+    L.split = (q + 1) * p.rows_per_batch - mrow0;        // >= 1; a 32-row slab crosses at most one boundary
   }
-  __syncwarp();
-  const int c4 = lane & 7, rsub = lane >> 3;
-  const int n = n0 + c4 * 4;
+  return L;
+}
+// coff = column offset of the chunk inside the warp's span (0, 32, ..)
+__device__ __forceinline__ void residual_prefetch(const ResidLane& L, int lane, int coff, int N, float4 (&xv)[8]) {
+  const int rsub = lane >> 3;
+  const float* x = L.x + coff;
+  const bool vec = L.n + coff + 4 <= N;
 #pragma unroll
   for (int it = 0; it < 8; ++it) {
-    const int row = it * 4 + rsub, m = mrow0 + row;
+    xv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (it * 4 + rsub < L.rows && vec) xv[it] = *reinterpret_cast<const float4*>(x);
+    x += L.row_step;
+  }
+}
+template <int EPI>
+__device__ __forceinline__ void epilogue_staged_resid(const ResidLane& L, const float* bias, uint8_t* stg, int lane, int coff,
+                                                      int N, const uint32_t (&r)[32], const float4 (&xv)[8]) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4)
+    *reinterpret_cast<uint4*>(stg + lane * STG_PITCH + j * 4) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+  __syncwarp();
+  const int c4 = lane & 7, rsub = lane >> 3;
+  const int n = L.n + coff;
+  const bool vec = n + 4 <= N;
+  // in the transposed phase a lane owns 4 fixed columns: its bias and gate values are loop invariants
+  float4 bz = make_float4(0.f, 0.f, 0.f, 0.f), g0 = make_float4(1.f, 1.f, 1.f, 1.f), g1 = g0;
+  if (vec) {
+    if (bias) bz = __ldg(reinterpret_cast<const float4*>(bias + n));
+    if constexpr (EPI == EPI_GATE_RESID) {
+      g0 = __ldg(reinterpret_cast<const float4*>(L.g0 + coff));
+      g1 = __ldg(reinterpret_cast<const float4*>(L.g1 + coff));
+    }
+  }
+  float* x = L.x + coff;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int row = it * 4 + rsub;
     const float4 v = *reinterpret_cast<const float4*>(stg + row * STG_PITCH + c4 * 16);
-    if (m < M && n < N) {
-      float* x = p.resid + (size_t)m * p.ldr + n;
-      float4 g = make_float4(1.f, 1.f, 1.f, 1.f);
-      const float* gp = nullptr;
-      if constexpr (EPI == EPI_GATE_RESID) gp = p.gate + (size_t)((m / p.rows_per_batch) % p.nbatch) * p.gate_stride + n;
-      if (n + 4 <= N) {
-        if constexpr (EPI == EPI_GATE_RESID) g = __ldg(reinterpret_cast<const float4*>(gp));
+    if (row < L.rows) {
+      if (vec) {
+        const float4 g = row < L.split ? g0 : g1;
         float4 o = xv[it];
-        o.x = fmaf(g.x, v.x, o.x);
-        o.y = fmaf(g.y, v.y, o.y);
-        o.z = fmaf(g.z, v.z, o.z);
-        o.w = fmaf(g.w, v.w, o.w);
+        o.x = fmaf(g.x, v.x + bz.x, o.x);
+        o.y = fmaf(g.y, v.y + bz.y, o.y);
+        o.z = fmaf(g.z, v.z + bz.z, o.z);
+        o.w = fmaf(g.w, v.w + bz.w, o.w);
         *reinterpret_cast<float4*>(x) = o;
       } else {
         const float vv[4] = {v.x, v.y, v.z, v.w};
+        const float* gp = (row < L.split ? L.g0 : L.g1);
         for (int k = 0; k < 4; ++k)
-          if (n + k < N) x[k] += (gp ? gp[k] : 1.f) * vv[k];
+          if (n + k < N) x[k] += (gp ? gp[coff + k] : 1.f) * (vv[k] + (bias ? bias[n + k] : 0.f));
       }
     }
+    x += L.row_step;
   }
   __syncwarp();
 }
-// the residual values epilogue_staged_resid() will update (issued early: their latency hides behind the MMAs)
-__device__ __forceinline__ void residual_prefetch(const EpiParams& p, int lane, int mrow0, int n0, int M, int N, float4 (&xv)[8]) {
-  const int c4 = lane & 7, rsub = lane >> 3;
-  const int n = n0 + c4 * 4;
-#pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const int m = mrow0 + it * 4 + rsub;
-    xv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (m < M && n + 4 <= N) xv[it] = *reinterpret_cast<const float4*>(p.resid + (size_t)m * p.ldr + n);
-  }
-}
 
 // ---- the kernel ----------------------------------------------------------------------------
-template <int BN, int EPI, typename OT>
+template <int BN, int EPI, typename OT, int WS, int STG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW, int M, int N,
                int K, EpiParams ep) {
-  constexpr int STAGES = num_stages(BN);
-  constexpr int STAGE_BYTES = stage_bytes(BN);
+  constexpr int STAGES = WS ? WS_STAGES : num_stages(BN);
+  constexpr int STAGE_BYTES = WS ? A_STAGE_BYTES : stage_bytes(BN);
+  constexpr int W_KB_BYTES = BN * BLOCK_K * 2;                 // one 64-wide K block of the weight slice
+  constexpr int W_BYTES = WS ? WS_MAX_KB * W_KB_BYTES : 0;     // resident weight slice (WS only), in front of the ring
   constexpr uint32_t TMEM_COLS = tmem_cols(BN);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint8_t* ring = smem + W_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + STAGES * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* w_bar = tmem_empty + 2;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_m = (M + BLOCK_M - 1) / BLOCK_M, num_n = (N + BN - 1) / BN;
   const int num_tiles = num_m * num_n;
   const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  // tile schedule: streamed-W = round robin over all tiles; W-stationary = fixed n tile, strided m tiles
+  const int ws_nb = blockIdx.x % num_n, ws_ci = blockIdx.x / num_n;
+  const int ws_cn = ((int)gridDim.x - ws_nb + num_n - 1) / num_n;
+  auto get_tile = [&](int i, int& mb, int& nb) -> bool {
+    if constexpr (WS) {
+      mb = ws_ci + i * ws_cn;
+      nb = ws_nb;
+      return mb < num_m;
+    } else {
+      const int tile = blockIdx.x + i * (int)gridDim.x;
+      mb = tile / num_n;
+      nb = tile % num_n;
+      return tile < num_tiles;
+    }
+  };
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapA) : "memory");
@@ -323,6 +380,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       mbar_init(&tmem_full[s], 1);
       mbar_init(&tmem_empty[s], NUM_EPI_WARPS);
     }
+    mbar_init(w_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -341,14 +399,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int mb = tile / num_n, nb = tile % num_n;
+      int mb, nb;
+      if constexpr (WS) {
+        if (get_tile(0, mb, nb)) {
+          mbar_expect_tx(w_bar, num_kb * W_KB_BYTES);
+          for (int kb = 0; kb < num_kb; ++kb) tma_load_2d(&tmapW, w_bar, smem + kb * W_KB_BYTES, kb * BLOCK_K, nb * BN);
+        }
+      }
+      for (int i = 0; get_tile(i, mb, nb); ++i) {
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sa = ring + stage * STAGE_BYTES;
           mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
           tma_load_2d(&tmapA, &full_bar[stage], sa, kb * BLOCK_K, mb * BLOCK_M);
-          tma_load_2d(&tmapW, &full_bar[stage], sa + A_STAGE_BYTES, kb * BLOCK_K, nb * BN);
+          if constexpr (!WS) tma_load_2d(&tmapW, &full_bar[stage], sa + A_STAGE_BYTES, kb * BLOCK_K, nb * BN);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -364,16 +428,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int mb, nb;
+      if constexpr (WS) {
+        if (get_tile(0, mb, nb)) mbar_wait(w_bar, 0);          // the resident weight slice has landed
+      }
+      for (int i = 0; get_tile(i, mb, nb); ++i) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tcgen05_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tcgen05_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sa = smem_u32(ring + stage * STAGE_BYTES);
           const uint64_t adesc = make_smem_desc_sw128(sa);
-          const uint64_t bdesc = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+          const uint64_t bdesc = make_smem_desc_sw128(WS ? smem_u32(smem + kb * W_KB_BYTES) : sa + A_STAGE_BYTES);
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
             // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
@@ -397,52 +465,69 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     const int quarter = warp & 3, half = (warp - 2) >> 2;
     constexpr int CHUNKS = BN / 32;                      // 32-column chunks per tile
     constexpr int PER = (CHUNKS + 1) / 2;                // chunks per warp
-    constexpr bool kResid = (EPI == EPI_GATE_RESID || EPI == EPI_RESID);
-    constexpr bool kBf16 = (EPI == EPI_STORE || EPI == EPI_GELU) && sizeof(OT) == 2;
-    uint8_t* stg = smem + STAGES * STAGE_BYTES + 256 + (warp - 2) * STG_BYTES;
+    // STG = coalesced shared-memory-staged epilogue (host guarantees the alignment it needs); else row-per-thread
+    constexpr bool kResid = STG && (EPI == EPI_GATE_RESID || EPI == EPI_RESID);
+    constexpr bool kBf16 = STG && (EPI == EPI_STORE || EPI == EPI_GELU) && sizeof(OT) == 2;
+    static_assert(!STG || kResid || kBf16, "no staged epilogue for this combination");
+    uint8_t* stg = ring + STAGES * STAGE_BYTES + 256 + (warp - 2) * STG_BYTES;
     const bool active = half * PER < CHUNKS;             // BN = 32: only the first column half has work
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int mb = tile / num_n, nb = tile % num_n;
+    int mb, nb;
+    for (int i = 0; get_tile(i, mb, nb); ++i) {
       const int mrow0 = mb * BLOCK_M + quarter * 32;
       const int ncol0 = nb * BN + half * PER * 32;
       float4 xv[kResid ? PER : 1][8];
+      ResidLane rl;
       if constexpr (kResid) {
-        if (ep.staged && active) {
+        if (active) {
+          rl = resid_lane<EPI>(ep, lane, mrow0, ncol0, M, N);
 #pragma unroll
-          for (int i = 0; i < PER; ++i) residual_prefetch(ep, lane, mrow0, ncol0 + i * 32, M, N, xv[i]);
+          for (int i = 0; i < PER; ++i) residual_prefetch(rl, lane, i * 32, N, xv[i]);
         }
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
       const int m = mrow0 + lane;
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
-      uint32_t r[PER][32];
-#pragma unroll
-      for (int i = 0; i < PER; ++i) {
-        const int c = half * PER + i;
-        if (c < CHUNKS) tmem_ld_32x32b_x32(taddr + c * 32, r[i]);
-      }
-      tmem_ld_wait();
-      // accumulator is in registers: hand the TMEM stage back before the math / stores
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
-      if (active && ncol0 < N) {
-        if (kBf16 && ep.staged) {
-          if constexpr (kBf16) epilogue_staged_bf16<EPI, PER>(ep, stg, lane, mrow0, ncol0, M, N, r);
-        } else if (kResid && ep.staged) {
-          if constexpr (kResid) {
-#pragma unroll
-            for (int i = 0; i < PER; ++i)
-              if (ncol0 + i * 32 < N) epilogue_staged_resid<EPI>(ep, stg, lane, mrow0, ncol0 + i * 32, M, N, r[i], xv[i]);
-          }
-        } else {
+      if constexpr (kResid) {
+        // one 32-column chunk at a time (keeps a single chunk of accumulators live next to the prefetched residual)
+        {
 #pragma unroll
           for (int i = 0; i < PER; ++i) {
-            const int n0 = ncol0 + i * 32;
-            if (half * PER + i < CHUNKS && m < M && n0 < N) epilogue_chunk<EPI, OT>(ep, m, n0, N, r[i]);
+            uint32_t rr[32];
+            const int c = half * PER + i;
+            if (c < CHUNKS) tmem_ld_32x32b_x32(taddr + c * 32, rr);
+            tmem_ld_wait();
+            if (i == PER - 1) {                     // accumulator fully read: hand the TMEM stage back
+              tcgen05_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+            }
+            if (active && ncol0 + i * 32 < N) epilogue_staged_resid<EPI>(rl, ep.bias, stg, lane, i * 32, N, rr, xv[i]);
+          }
+        }
+      } else {
+        uint32_t r[PER][32];
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+          const int c = half * PER + i;
+          if (c < CHUNKS) tmem_ld_32x32b_x32(taddr + c * 32, r[i]);
+        }
+        tmem_ld_wait();
+        // accumulator is in registers: hand the TMEM stage back before the math / stores
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (active && ncol0 < N) {
+          if constexpr (kBf16) {
+            epilogue_staged_bf16<EPI, PER>(ep, stg, lane, mrow0, ncol0, M, N, r);
+          } else {
+#pragma unroll
+            for (int i2 = 0; i2 < PER; ++i2) {
+              const int n0 = ncol0 + i2 * 32;
+              if (half * PER + i2 < CHUNKS && m < M && n0 < N) epilogue_chunk<EPI, OT>(ep, m, n0, N, r[i2]);
+            }
           }
         }
       }

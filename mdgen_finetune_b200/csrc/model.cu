@@ -72,22 +72,41 @@ int num_sms() {
   return g_num_sms;
 }
 
-template <int BN, int EPI, typename OT>
-static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, const EpiParams& ep,
-                          cudaStream_t st) {
+template <int BN, int EPI, typename OT, int WS, int STG>
+static int launch_tc_ws(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, const EpiParams& ep,
+                        cudaStream_t st) {
   static bool configured = false;
-  auto kern = tc::gemm_tc_kernel<BN, EPI, OT>;
+  auto kern = tc::gemm_tc_kernel<BN, EPI, OT, WS, STG>;
+  constexpr int smem = WS ? tc::ws_smem_bytes(BN) : tc::smem_bytes(BN);
   if (!configured) {
-    MD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::smem_bytes(BN)));
+    MD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
   int tiles = ((M + tc::BLOCK_M - 1) / tc::BLOCK_M) * ((N + BN - 1) / BN);
   int grid = tiles < num_sms() ? tiles : num_sms();
   ProfScope ps(PC_GEMM_TC, st);
-  kern<<<grid, tc::NUM_THREADS, tc::smem_bytes(BN), st>>>(ta, tw, M, N, K, ep);
+  kern<<<grid, tc::NUM_THREADS, smem, st>>>(ta, tw, M, N, K, ep);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
+}
+template <int BN, int EPI, typename OT>
+static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, const EpiParams& ep,
+                          cudaStream_t st) {
+  constexpr bool can_stage = BN >= 64 && ((sizeof(OT) == 2 && (EPI == EPI_STORE || EPI == EPI_GELU)) ||
+                                          EPI == EPI_GATE_RESID || EPI == EPI_RESID);
+  if constexpr (can_stage) {
+    if (ep.staged) {
+      // weight-stationary when the [BN, K] slice fits and every CTA gets a tile of its fixed n tile
+      if constexpr (BN == 128) {
+        const int num_n = (N + BN - 1) / BN, num_m = (M + tc::BLOCK_M - 1) / tc::BLOCK_M;
+        if (K <= tc::WS_MAX_KB * tc::BLOCK_K && num_n <= num_sms() && num_m >= 2 && !getenv("MDGEN_NO_GEMM_WS"))
+          return launch_tc_ws<BN, EPI, OT, 1, 1>(ta, tw, M, N, K, ep, st);
+      }
+      return launch_tc_ws<BN, EPI, OT, 0, 1>(ta, tw, M, N, K, ep, st);
+    }
+  }
+  return launch_tc_ws<BN, EPI, OT, 0, 0>(ta, tw, M, N, K, ep, st);
 }
 
 template <int BN>
@@ -126,7 +145,9 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
   auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
   if ((epi == EPI_STORE || epi == EPI_GELU) && out_bf16) epp.staged = al16(ep.out) && ep.ldo % 8 == 0;
   else if (epi == EPI_RESID) epp.staged = al16(ep.resid) && ep.ldr % 4 == 0;
-  else if (epi == EPI_GATE_RESID) epp.staged = al16(ep.resid) && ep.ldr % 4 == 0 && al16(ep.gate) && ep.gate_stride % 4 == 0;
+  else if (epi == EPI_GATE_RESID)   // the staged path assumes at most one batch boundary inside a 32-row slab
+    epp.staged = al16(ep.resid) && ep.ldr % 4 == 0 && al16(ep.gate) && ep.gate_stride % 4 == 0 && ep.rows_per_batch >= 32;
+  if ((epi == EPI_RESID || epi == EPI_GATE_RESID) && ep.bias && !al16(ep.bias)) epp.staged = 0;
   CUtensorMap ta, tw;
   MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
   MD_TRY(make_tmap_2d(&tw, W, N, K, ldw, block_n));
