@@ -168,62 +168,103 @@ attention_simt_kernel(AttnParams<AT> p) {
 }
 
 // Short sequences (residue axis of the tetrapeptide configs: S = L = 4, 5 keys): one thread per
-// (token, head); the S+1 keys are read straight from global/L1 -- no shared memory, no idle lanes.
-template <typename AT, int HD>
-__global__ void __launch_bounds__(256)
-attention_short_kernel(AttnParams<AT> p, long long total) {
-  constexpr int HALF = HD / 2;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  const int h = (int)(idx % p.H);
-  const long long tok = idx / p.H;           // (nbi, qi) with qi fastest
-  const int qi = (int)(tok % p.S), nbi = (int)(tok / p.S);
+// (sequence, head, query).  Each thread loads and rotates ITS OWN token's q, k, v once; the S threads of a
+// (sequence, head) group exchange the rotated keys / values through shared memory (layout [key][float4][group],
+// conflict-free), so every K/V element is read from HBM and rotated exactly once.
+constexpr int ASH_THREADS = 128;
+template <typename AT, int HD, int S_>
+__global__ void __launch_bounds__(ASH_THREADS, 6)
+attention_short_kernel(AttnParams<AT> p, long long total_groups) {
+  constexpr int HALF = HD / 2, G = ASH_THREADS / S_, F4 = HD / 4;
+  __shared__ float4 ks[S_][F4][G], vs[S_][F4][G];
+  __shared__ float kvalid[S_][G];
+  __shared__ __align__(16) float bks[16][HD + 4], bvs[16][HD + 4];   // bias token per head, key rotated to position S
+  const int g = threadIdx.x / S_, qi = threadIdx.x % S_;
+  const long long grp = (long long)blockIdx.x * G + g;     // (sequence, head) with head fastest
+  const bool live = g < G && grp < total_groups;
+  const int h = live ? (int)(grp % p.H) : 0;
+  const int nbi = live ? (int)(grp / p.H) : 0;
   const int C = p.H * HD;
-  float q[HD], acc[HD];
-  {
-    float raw[HD];
-    load24(p.qkv + attn_row(nbi, qi, p.S, p.inner) * p.ld + h * HD, raw);
-#pragma unroll
-    for (int i = 0; i < HALF; ++i) {
-      float a = raw[i], b = raw[i + HALF];
-      float c = 1.f, s = 0.f;
-      if (p.cs) { c = p.cs[qi * HALF + i]; s = p.sn[qi * HALF + i]; }
-      q[i] = a * c - b * s;
-      q[i + HALF] = b * c + a * s;
-    }
+  for (int i = threadIdx.x; i < p.H * HALF; i += ASH_THREADS) {
+    const int hh = i / HALF, ii = i % HALF;
+    const float a = p.bias_k[hh * HD + ii], b = p.bias_k[hh * HD + ii + HALF];
+    const float c = p.cs ? p.cs[S_ * HALF + ii] : 1.f, sn = p.cs ? p.sn[S_ * HALF + ii] : 0.f;
+    bks[hh][ii] = a * c - b * sn;
+    bks[hh][ii + HALF] = b * c + a * sn;
+    bvs[hh][ii] = p.bias_v[hh * HD + ii];
+    bvs[hh][ii + HALF] = p.bias_v[hh * HD + ii + HALF];
   }
+  float q[HD];
+  if (live) {
+    const size_t r = attn_row(nbi, qi, S_, p.inner);
+    const AT* row = p.qkv + r * p.ld + h * HD;
+    float k[HD], v[HD];
+    load24(row, q);
+    load24(row + C, k);
+    load24(row + 2 * C, v);
+    if (p.cs) {
+      float cc[HALF], ss[HALF];
+#pragma unroll
+      for (int j = 0; j < HALF / 4; ++j) {
+        const float4 c4 = __ldg(reinterpret_cast<const float4*>(p.cs + qi * HALF) + j);
+        const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.sn + qi * HALF) + j);
+        cc[4 * j] = c4.x; cc[4 * j + 1] = c4.y; cc[4 * j + 2] = c4.z; cc[4 * j + 3] = c4.w;
+        ss[4 * j] = s4.x; ss[4 * j + 1] = s4.y; ss[4 * j + 2] = s4.z; ss[4 * j + 3] = s4.w;
+      }
+#pragma unroll
+      for (int i = 0; i < HALF; ++i) {
+        const float c = cc[i], sn = ss[i];
+        const float a = q[i], b = q[i + HALF], ka = k[i], kb = k[i + HALF];
+        q[i] = a * c - b * sn;
+        q[i + HALF] = b * c + a * sn;
+        k[i] = ka * c - kb * sn;
+        k[i + HALF] = kb * c + ka * sn;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < F4; ++j) {
+      ks[qi][j][g] = make_float4(k[4 * j], k[4 * j + 1], k[4 * j + 2], k[4 * j + 3]);
+      vs[qi][j][g] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    kvalid[qi][g] = p.key_valid[r % p.mask_mod];
+  }
+  __syncthreads();
+  if (!live) return;
+  float acc[HD];
 #pragma unroll
   for (int i = 0; i < HD; ++i) acc[i] = 0.f;
   float mrun = -INFINITY, lrun = 0.f;
-  for (int key = 0; key <= p.S; ++key) {
-    float kv[HD], vv[HD];
-    if (key < p.S) {
-      const size_t r = attn_row(nbi, key, p.S, p.inner);
-      if (p.key_valid[r % p.mask_mod] == 0.f) continue;
-      const AT* kr = p.qkv + r * p.ld + C + h * HD;
-      load24(kr, kv);
-      load24(kr + C, vv);
-    } else {
 #pragma unroll
-      for (int i = 0; i < HD; ++i) { kv[i] = p.bias_k[h * HD + i]; vv[i] = p.bias_v[h * HD + i]; }
+  for (int key = 0; key <= S_; ++key) {
+    float kv[HD], vv[HD];
+    if (key < S_) {
+      if (kvalid[key][g] == 0.f) continue;
+#pragma unroll
+      for (int j = 0; j < F4; ++j) {
+        const float4 a = ks[key][j][g], b = vs[key][j][g];
+        kv[4 * j] = a.x; kv[4 * j + 1] = a.y; kv[4 * j + 2] = a.z; kv[4 * j + 3] = a.w;
+        vv[4 * j] = b.x; vv[4 * j + 1] = b.y; vv[4 * j + 2] = b.z; vv[4 * j + 3] = b.w;
+      }
+    } else {   // learned bias token at position S (mha.py:265-268), rotated like any key
+#pragma unroll
+      for (int j = 0; j < F4; ++j) {
+        const float4 a = *reinterpret_cast<const float4*>(&bks[h][4 * j]);
+        const float4 b = *reinterpret_cast<const float4*>(&bvs[h][4 * j]);
+        kv[4 * j] = a.x; kv[4 * j + 1] = a.y; kv[4 * j + 2] = a.z; kv[4 * j + 3] = a.w;
+        vv[4 * j] = b.x; vv[4 * j + 1] = b.y; vv[4 * j + 2] = b.z; vv[4 * j + 3] = b.w;
+      }
     }
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < HALF; ++i) {
-      float c = 1.f, sn = 0.f;
-      if (p.cs) { c = p.cs[key * HALF + i]; sn = p.sn[key * HALF + i]; }
-      float a = kv[i] * c - kv[i + HALF] * sn, b = kv[i + HALF] * c + kv[i] * sn;
-      s = fmaf(q[i], a, s);
-      s = fmaf(q[i + HALF], b, s);
-    }
+    for (int i = 0; i < HD; ++i) s = fmaf(q[i], kv[i], s);
     if (s > mrun) {
-      float corr = expf(mrun - s);
+      const float corr = __expf(mrun - s);
       lrun *= corr;
 #pragma unroll
       for (int i = 0; i < HD; ++i) acc[i] *= corr;
       mrun = s;
     }
-    float pr = expf(s - mrun);
+    const float pr = __expf(s - mrun);
     lrun += pr;
 #pragma unroll
     for (int i = 0; i < HD; ++i) acc[i] = fmaf(pr, vv[i], acc[i]);
@@ -231,18 +272,26 @@ attention_short_kernel(AttnParams<AT> p, long long total) {
   const float inv = 1.0f / lrun;
 #pragma unroll
   for (int i = 0; i < HD; ++i) acc[i] *= inv;
-  store24(p.out + attn_row(nbi, qi, p.S, p.inner) * p.ldo + h * HD, acc);
+  store24(p.out + attn_row(nbi, qi, S_, p.inner) * p.ldo + h * HD, acc);
+}
+
+template <typename AT, int S_>
+inline void launch_attention_short(const AttnParams<AT>& p, cudaStream_t st) {
+  const long long groups = (long long)p.nb * p.H;
+  const int G = ASH_THREADS / S_;
+  attention_short_kernel<AT, 24, S_><<<(unsigned)((groups + G - 1) / G), ASH_THREADS, 0, st>>>(p, groups);
 }
 
 template <typename AT>
 inline int launch_attention_simt(const AttnParams<AT>& p, int head_dim, cudaStream_t st) {
   MD_CHECK(head_dim == 24, "attention_simt: head_dim must be 24");
   if (p.nb <= 0 || p.S <= 0) return 0;
-  ProfScope ps(p.S <= 16 ? PC_ATTN_SHORT : PC_ATTN_SIMT, st);
-  if (p.S <= 16) {
-    long long total = (long long)p.nb * p.S * p.H;
-    attention_short_kernel<AT, 24><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(p, total);
-  } else {
+  const bool is_short = (p.S == 4 || p.S == 8 || p.S == 16) && p.H <= 16;
+  ProfScope ps(is_short ? PC_ATTN_SHORT : PC_ATTN_SIMT, st);
+  if (is_short && p.S == 4) launch_attention_short<AT, 4>(p, st);
+  else if (is_short && p.S == 8) launch_attention_short<AT, 8>(p, st);
+  else if (is_short) launch_attention_short<AT, 16>(p, st);
+  else {
     dim3 grid(p.nb * p.H, (p.S + AS_THREADS - 1) / AS_THREADS);
     attention_simt_kernel<AT, 24><<<grid, AS_THREADS, 0, st>>>(p);
   }

@@ -259,8 +259,11 @@ __device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16]
 
 __global__ void __launch_bounds__(THREADS, 1)
 attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, long long* dbg_buf, int dbg_cta) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  // No integer round trip on this pointer: the compiler must keep seeing a shared-space address, otherwise every
+  // staging access becomes a generic LD.E / ST.E (long-scoreboard latency instead of LDS / STS).
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 127u) != 0) __trap();     // dynamic shared memory starts at the window base (no static shared)
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
   uint32_t* kmask = reinterpret_cast<uint32_t*>(smem + OFF_MASK);   // bit j of word w: key 32 w + j is attendable
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;

@@ -81,6 +81,7 @@ embed_kernel(const float* __restrict__ x, int D, const float* __restrict__ xc, i
              const float* __restrict__ mask_emb, const float* __restrict__ pos, const float* __restrict__ time_emb,
              const float* __restrict__ ipa, float* __restrict__ out, int N, int T, int L) {
   __shared__ __align__(16) float sm[EMB_TOK][DDP];
+  __shared__ int4 meta[EMB_TOK];   // per token: mask_emb row, pos row, time row, ipa row (element offsets / C)
   const int c = threadIdx.x;
   const int m0 = blockIdx.x * EMB_TOK;
   const int DD = D + Dc;
@@ -93,26 +94,37 @@ embed_kernel(const float* __restrict__ x, int D, const float* __restrict__ xc, i
     if (m < N && d < DD) v = d < D ? x[(size_t)m * D + d] : xc[(size_t)m * Dc + (d - D)];
     sm[tk][d] = v;
   }
+  if (threadIdx.x < EMB_TOK) {
+    const int m = min(m0 + (int)threadIdx.x, N - 1);
+    const int l = m % L, t = (m / L) % T, b = m / (L * T);
+    meta[threadIdx.x] = make_int4(cm ? (int)cm[m] : 0, l, t, b * L + l);
+  }
   __syncthreads();
   const float base = bsum[c];
-  for (int tk = 0; tk < EMB_TOK; ++tk) {
-    const int m = m0 + tk;
-    if (m >= N) break;
-    float acc = base;
+  const int ntk = min(EMB_TOK, N - m0);
+#pragma unroll 4
+  for (int tk = 0; tk < ntk; ++tk) {
+    const int4 mt = meta[tk];
+    float add = 0.f;
+    if (cm) add += __ldg(mask_emb + (size_t)mt.x * C + c);
+    if (pos) add += __ldg(pos + (size_t)mt.y * C + c);
+    if (time_emb) add += __ldg(time_emb + (size_t)mt.z * C + c);
+    if (ipa) add += __ldg(ipa + (size_t)mt.w * C + c);
+    float a0 = base, a1 = 0.f;
 #pragma unroll
-    for (int d = 0; d < DDP; d += 4) {
+    for (int d = 0; d < DDP; d += 8) {
       const float4 xv = *reinterpret_cast<const float4*>(&sm[tk][d]);
-      acc = fmaf(w[d], xv.x, acc);
-      acc = fmaf(w[d + 1], xv.y, acc);
-      acc = fmaf(w[d + 2], xv.z, acc);
-      acc = fmaf(w[d + 3], xv.w, acc);
+      const float4 yv = *reinterpret_cast<const float4*>(&sm[tk][d + 4]);
+      a0 = fmaf(w[d], xv.x, a0);
+      a1 = fmaf(w[d + 4], yv.x, a1);
+      a0 = fmaf(w[d + 1], xv.y, a0);
+      a1 = fmaf(w[d + 5], yv.y, a1);
+      a0 = fmaf(w[d + 2], xv.z, a0);
+      a1 = fmaf(w[d + 6], yv.z, a1);
+      a0 = fmaf(w[d + 3], xv.w, a0);
+      a1 = fmaf(w[d + 7], yv.w, a1);
     }
-    const int l = m % L, t = (m / L) % T, b = m / (L * T);
-    if (cm) acc += mask_emb[(size_t)cm[m] * C + c];
-    if (pos) acc += pos[(size_t)l * C + c];
-    if (time_emb) acc += time_emb[(size_t)t * C + c];
-    if (ipa) acc += ipa[((size_t)b * L + l) * C + c];
-    out[(size_t)m * C + c] = acc;
+    out[(size_t)(m0 + tk) * C + c] = (a0 + a1) + add;
   }
 }
 
@@ -223,6 +235,10 @@ __global__ void broadcast_rows_kernel(const float* __restrict__ src, float* __re
 __global__ void axpy_kernel(float* __restrict__ y, const float* __restrict__ x, float a, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) y[i] += a * x[i];
+}
+__global__ void silu_kernel(const float* __restrict__ x, float* __restrict__ y, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = silu(x[i]);
 }
 __global__ void fill_kernel(float* __restrict__ y, float v, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

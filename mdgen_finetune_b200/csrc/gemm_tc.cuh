@@ -28,14 +28,20 @@ __host__ __device__ constexpr int num_stages(int bn) { return bn >= 128 ? 5 : (b
 // 128 B/clk/SM at tensor peak, ~3x what the L2 -> SM fabric delivers (~6300 B/clk chip-wide); W-stationary halves it.
 constexpr int WS_MAX_KB = 6, WS_STAGES = 5;
 __host__ __device__ constexpr int ws_smem_bytes(int bn) {
-  return WS_MAX_KB * bn * BLOCK_K * 2 + WS_STAGES * A_STAGE_BYTES + 8 * 32 * 144 + 1024 + 256;
+  return WS_MAX_KB * bn * BLOCK_K * 2 + WS_STAGES * A_STAGE_BYTES + 8 * (32 * 144 + 3 * 128 * 4) + 1024 + 256;
 }
 // per-epilogue-warp staging tile: 32 rows x 128 B (+16 B pad per row: conflict-free 128-bit rows both ways)
 constexpr int STG_PITCH = 144, STG_BYTES = 32 * STG_PITCH;
+// per-epilogue-warp column vectors (bias, gate of the two batch elements a 32-row slab can touch) for up to 128 columns.
+// With the shared-memory carve-out at its maximum the L1 keeps almost nothing: reading bias / gate straight from
+// global inside the epilogue loops cost an L2 round trip (~700 clk) per use and dominated the tile time.
+constexpr int CV_FLOATS = 128, CV_BYTES_PER_WARP = 3 * CV_FLOATS * 4;
+constexpr int EPI_SMEM_BYTES = 8 * (STG_BYTES + CV_BYTES_PER_WARP);
 __host__ __device__ constexpr int tmem_cols(int bn) { return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512; }
-__host__ __device__ constexpr int smem_bytes(int bn) { return num_stages(bn) * stage_bytes(bn) + NUM_EPI_WARPS * STG_BYTES + 1024 + 256; }
+__host__ __device__ constexpr int smem_bytes(int bn) { return num_stages(bn) * stage_bytes(bn) + EPI_SMEM_BYTES + 1024 + 256; }
 
-static_assert(smem_bytes(128) <= 227 * 1024 && smem_bytes(64) <= 227 * 1024 && smem_bytes(32) <= 227 * 1024, "shared memory budget");
+static_assert(smem_bytes(128) <= 227 * 1024 && smem_bytes(64) <= 227 * 1024 && smem_bytes(32) <= 227 * 1024 &&
+                  ws_smem_bytes(128) <= 227 * 1024, "shared memory budget");
 
 // ---- PTX wrappers ----------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -110,19 +116,22 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-// erf-GELU (layers.py:78-85) with erf from Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7) on the MUFU
-// ex2/rcp units: the exact erff costs ~3x more issue slots than the tile's MMA time allows.
+// erf-GELU (layers.py:78-85) = x * Phi(x) with one MUFU op: Phi(-|x|) = 2^-q(|x|), q a degree-5 polynomial fitted
+// (weighted minimax of the GELU error, tools/fit_gelu.py) to -log2(erfc(|x|/sqrt 2)/2) on [0, 7]; beyond 7 the
+// polynomial keeps growing so 2^-q underflows to 0 like the exact tail.  Max |error| 6.4e-7 in fp32 over [-30, 30]
+// (the exact erff costs ~3x the issue slots and the rcp + ex2 formulation two MUFU ops per element, which made the
+// fc1 epilogue slower than its tile's MMAs).
 __device__ __forceinline__ float gelu_erf_fast(float x) {
-  const float z = fabsf(x) * 0.70710678118654752440f;
-  float t, e;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-z * z * 1.4426950408889634f));
-  float poly = fmaf(t, 1.061405429f, -1.453152027f);
-  poly = fmaf(t, poly, 1.421413741f);
-  poly = fmaf(t, poly, -0.284496736f);
-  poly = fmaf(t, poly, 0.254829592f);
-  const float erf_abs = fmaf(-poly * t, e, 1.0f);
-  return 0.5f * x * (1.0f + copysignf(erf_abs, x));
+  const float a = fabsf(x);
+  float q = fmaf(a, 0.0004733167006634176f, -0.007084609474986792f);
+  q = fmaf(a, q, 0.05182751268148422f);
+  q = fmaf(a, q, 0.45999228954315186f);
+  q = fmaf(a, q, 1.1507879495620728f);
+  q = fmaf(a, q, 1.000037670135498f);
+  float h;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(h) : "f"(-q));
+  const float t = x * h;              // x * Phi(-|x|)
+  return x > 0.f ? x - t : t;
 }
 
 // ---- epilogue on 32 consecutive accumulator columns of one row --------------------------
@@ -196,47 +205,83 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& p, int m, int n0
 // The row-per-thread layout that tcgen05.ld delivers makes every direct global access touch 32 different
 // cache lines per instruction; transposing through shared memory turns them into full 128-byte lines.
 
-// bf16 output of W32 = 32 * PER consecutive columns of 32 rows (EPI_STORE / EPI_GELU)
+// dst[0..128) = src[n0 .. n0+128) (columns >= N and a null src read as `fill`); one float4 per lane, warp-private
+__device__ __forceinline__ void stage_colvec(float* dst, const float* src, int n0, int N, int lane, float fill) {
+  float4 v = make_float4(fill, fill, fill, fill);
+  const int n = n0 + lane * 4;
+  if (src) {
+    if (n + 4 <= N) {
+      v = __ldg(reinterpret_cast<const float4*>(src + n));
+    } else {
+      if (n < N) v.x = src[n];
+      if (n + 1 < N) v.y = src[n + 1];
+      if (n + 2 < N) v.z = src[n + 2];
+    }
+  }
+  *reinterpret_cast<float4*>(dst + lane * 4) = v;
+}
+
+// bf16 output of W32 = 32 * PER consecutive columns of 32 rows (EPI_STORE / EPI_GELU); sbias = staged bias of column n0
 template <int EPI, int PER>
-__device__ __forceinline__ void epilogue_staged_bf16(const EpiParams& p, uint8_t* stg, int lane, int mrow0, int n0, int M,
-                                                     int N, uint32_t (&r)[PER][32]) {
+__device__ __forceinline__ void epilogue_staged_bf16(const EpiParams& p, uint8_t* stg, const float* sbias, int lane, int mrow0,
+                                                     int n0, int M, int N, uint32_t (&r)[PER][32]) {
   constexpr int PIECES = PER * 4;               // 16-byte pieces per row
   constexpr int ROWS_PER = 32 / PIECES;         // rows covered by one warp-wide access
+  constexpr int ITERS = 32 / ROWS_PER;
+  // Loads are batched ahead of their uses by hand (bias quads, then the staged rows): interleaved load/use pairs on one
+  // recycled register quad left every shared-memory latency exposed (short-scoreboard stalls on each FADD / STG).
 #pragma unroll
   for (int i = 0; i < PER; ++i) {
+    float4 b4[8];
 #pragma unroll
-    for (int j = 0; j < 32; j += 8) {
-      float v[8];
+    for (int k = 0; k < 8; ++k) b4[k] = *reinterpret_cast<const float4*>(sbias + i * 32 + k * 4);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const int n = n0 + i * 32 + j + e;
-        v[e] = __uint_as_float(r[i][j + e]) + ((p.bias && n < N) ? __ldg(p.bias + n) : 0.f);
-        if constexpr (EPI == EPI_GELU) v[e] = gelu_erf_fast(v[e]);
+    for (int k = 0; k < 8; ++k) {
+      float v0 = __uint_as_float(r[i][4 * k]) + b4[k].x, v1 = __uint_as_float(r[i][4 * k + 1]) + b4[k].y;
+      float v2 = __uint_as_float(r[i][4 * k + 2]) + b4[k].z, v3 = __uint_as_float(r[i][4 * k + 3]) + b4[k].w;
+      if constexpr (EPI == EPI_GELU) {
+        v0 = gelu_erf_fast(v0);
+        v1 = gelu_erf_fast(v1);
+        v2 = gelu_erf_fast(v2);
+        v3 = gelu_erf_fast(v3);
       }
-      __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
-      __nv_bfloat162 c = __floats2bfloat162_rn(v[4], v[5]), d = __floats2bfloat162_rn(v[6], v[7]);
-      *reinterpret_cast<uint4*>(stg + lane * STG_PITCH + (i * 4 + j / 8) * 16) =
-          make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b), *reinterpret_cast<uint32_t*>(&c),
-                     *reinterpret_cast<uint32_t*>(&d));
+      const __nv_bfloat162 lo = __floats2bfloat162_rn(v0, v1), hi = __floats2bfloat162_rn(v2, v3);
+      r[i][2 * k] = *reinterpret_cast<const uint32_t*>(&lo);       // packed in place: r[i][0..15] = 32 bf16
+      r[i][2 * k + 1] = *reinterpret_cast<const uint32_t*>(&hi);
     }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      *reinterpret_cast<uint4*>(stg + lane * STG_PITCH + (i * 4 + k) * 16) =
+          make_uint4(r[i][4 * k], r[i][4 * k + 1], r[i][4 * k + 2], r[i][4 * k + 3]);
   }
   __syncwarp();
   bf16* out = reinterpret_cast<bf16*>(p.out);
   const int piece = lane % PIECES, rsub = lane / PIECES;
   const int n = n0 + piece * 8;
+  uint4 v[ITERS];
 #pragma unroll
-  for (int it = 0; it < 32 / ROWS_PER; ++it) {
-    const int row = it * ROWS_PER + rsub, m = mrow0 + row;
-    const uint4 v = *reinterpret_cast<const uint4*>(stg + row * STG_PITCH + piece * 16);
-    if (m < M) {
-      bf16* o = out + (size_t)m * p.ldo + n;
-      if (n + 8 <= N) {
-        *reinterpret_cast<uint4*>(o) = v;
-      } else {
-        const bf16* e = reinterpret_cast<const bf16*>(&v);
-        for (int k = 0; k < 8; ++k)
-          if (n + k < N) o[k] = e[k];
+  for (int it = 0; it < ITERS; ++it) v[it] = *reinterpret_cast<const uint4*>(stg + (it * ROWS_PER + rsub) * STG_PITCH + piece * 16);
+  bf16* o = out + (size_t)(mrow0 + rsub) * p.ldo + n;
+  const size_t step = (size_t)ROWS_PER * p.ldo;
+  if (mrow0 + 32 <= M && n0 + PER * 32 <= N) {       // interior slab: unpredicated 128-bit stores
+#pragma unroll
+    for (int it = 0; it < ITERS; ++it) {
+      *reinterpret_cast<uint4*>(o) = v[it];
+      o += step;
+    }
+  } else {
+#pragma unroll
+    for (int it = 0; it < ITERS; ++it) {
+      if (mrow0 + it * ROWS_PER + rsub < M) {
+        if (n + 8 <= N) {
+          *reinterpret_cast<uint4*>(o) = v[it];
+        } else {
+          const bf16* e = reinterpret_cast<const bf16*>(&v[it]);
+          for (int k = 0; k < 8; ++k)
+            if (n + k < N) o[k] = e[k];
+        }
       }
+      o += step;
     }
   }
   __syncwarp();
@@ -248,8 +293,6 @@ __device__ __forceinline__ void epilogue_staged_bf16(const EpiParams& p, uint8_t
 struct ResidLane {
   float* x;            // this lane's first residual element: row rsub, columns n .. n+3 of the chunk
   size_t row_step;     // 4 rows, in floats
-  const float* g0;     // gate row for rows < split, already offset to column n (or null)
-  const float* g1;     // gate row for rows >= split
   int split;           // first row (0..32) that belongs to the next batch element
   int rows;            // valid rows of the 32 (M tail)
   int n;               // first of the lane's 4 columns in chunk 0 of the warp
@@ -262,15 +305,22 @@ __device__ __forceinline__ ResidLane resid_lane(const EpiParams& p, int lane, in
   L.row_step = (size_t)4 * p.ldr;
   L.rows = M - mrow0;
   L.n = n;
-  L.g0 = L.g1 = nullptr;
   L.split = 32;
   if constexpr (EPI == EPI_GATE_RESID) {
     const int q = mrow0 / p.rows_per_batch;
-    L.g0 = p.gate + (size_t)(q % p.nbatch) * p.gate_stride + n;
-    L.g1 = p.gate + (size_t)((q + 1) % p.nbatch) * p.gate_stride + n;
     L.split = (q + 1) * p.rows_per_batch - mrow0;        // >= 1; a 32-row slab crosses at most one boundary
   }
   return L;
+}
+// stage bias and the two gate rows of the slab's 128 columns starting at n0 into the warp's column-vector buffer
+template <int EPI>
+__device__ __forceinline__ void stage_resid_colvecs(const EpiParams& p, float* cv, int lane, int mrow0, int n0, int N) {
+  stage_colvec(cv, p.bias, n0, N, lane, 0.f);
+  if constexpr (EPI == EPI_GATE_RESID) {
+    const int q = mrow0 / p.rows_per_batch;
+    stage_colvec(cv + CV_FLOATS, p.gate + (size_t)(q % p.nbatch) * p.gate_stride, n0, N, lane, 1.f);
+    stage_colvec(cv + 2 * CV_FLOATS, p.gate + (size_t)((q + 1) % p.nbatch) * p.gate_stride, n0, N, lane, 1.f);
+  }
 }
 // coff = column offset of the chunk inside the warp's span (0, 32, ..)
 __device__ __forceinline__ void residual_prefetch(const ResidLane& L, int lane, int coff, int N, float4 (&xv)[8]) {
@@ -285,7 +335,7 @@ __device__ __forceinline__ void residual_prefetch(const ResidLane& L, int lane, 
   }
 }
 template <int EPI>
-__device__ __forceinline__ void epilogue_staged_resid(const ResidLane& L, const float* bias, uint8_t* stg, int lane, int coff,
+__device__ __forceinline__ void epilogue_staged_resid(const ResidLane& L, const float* cv, uint8_t* stg, int lane, int coff,
                                                       int N, const uint32_t (&r)[32], const float4 (&xv)[8]) {
 #pragma unroll
   for (int j = 0; j < 32; j += 4)
@@ -294,37 +344,50 @@ __device__ __forceinline__ void epilogue_staged_resid(const ResidLane& L, const 
   const int c4 = lane & 7, rsub = lane >> 3;
   const int n = L.n + coff;
   const bool vec = n + 4 <= N;
-  // in the transposed phase a lane owns 4 fixed columns: its bias and gate values are loop invariants
-  float4 bz = make_float4(0.f, 0.f, 0.f, 0.f), g0 = make_float4(1.f, 1.f, 1.f, 1.f), g1 = g0;
-  if (vec) {
-    if (bias) bz = __ldg(reinterpret_cast<const float4*>(bias + n));
-    if constexpr (EPI == EPI_GATE_RESID) {
-      g0 = __ldg(reinterpret_cast<const float4*>(L.g0 + coff));
-      g1 = __ldg(reinterpret_cast<const float4*>(L.g1 + coff));
-    }
+  // in the transposed phase a lane owns 4 fixed columns: its bias and gate values are loop invariants (from shared memory)
+  const float4 bz = *reinterpret_cast<const float4*>(cv + coff + c4 * 4);
+  float4 g0 = make_float4(1.f, 1.f, 1.f, 1.f), g1 = g0;
+  if constexpr (EPI == EPI_GATE_RESID) {
+    g0 = *reinterpret_cast<const float4*>(cv + CV_FLOATS + coff + c4 * 4);
+    g1 = *reinterpret_cast<const float4*>(cv + 2 * CV_FLOATS + coff + c4 * 4);
   }
   float* x = L.x + coff;
+  float4 v[8];
 #pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const int row = it * 4 + rsub;
-    const float4 v = *reinterpret_cast<const float4*>(stg + row * STG_PITCH + c4 * 16);
-    if (row < L.rows) {
-      if (vec) {
-        const float4 g = row < L.split ? g0 : g1;
-        float4 o = xv[it];
-        o.x = fmaf(g.x, v.x + bz.x, o.x);
-        o.y = fmaf(g.y, v.y + bz.y, o.y);
-        o.z = fmaf(g.z, v.z + bz.z, o.z);
-        o.w = fmaf(g.w, v.w + bz.w, o.w);
-        *reinterpret_cast<float4*>(x) = o;
-      } else {
-        const float vv[4] = {v.x, v.y, v.z, v.w};
-        const float* gp = (row < L.split ? L.g0 : L.g1);
-        for (int k = 0; k < 4; ++k)
-          if (n + k < N) x[k] += (gp ? gp[coff + k] : 1.f) * (vv[k] + (bias ? bias[n + k] : 0.f));
-      }
+  for (int it = 0; it < 8; ++it) v[it] = *reinterpret_cast<const float4*>(stg + (it * 4 + rsub) * STG_PITCH + c4 * 16);
+  if (L.rows >= 32 && vec) {            // interior slab: unpredicated read-modify-write
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const float4 g = it * 4 + rsub < L.split ? g0 : g1;
+      float4 o = xv[it];
+      o.x = fmaf(g.x, v[it].x + bz.x, o.x);
+      o.y = fmaf(g.y, v[it].y + bz.y, o.y);
+      o.z = fmaf(g.z, v[it].z + bz.z, o.z);
+      o.w = fmaf(g.w, v[it].w + bz.w, o.w);
+      *reinterpret_cast<float4*>(x) = o;
+      x += L.row_step;
     }
-    x += L.row_step;
+  } else {
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int row = it * 4 + rsub;
+      if (row < L.rows) {
+        const float4 g = row < L.split ? g0 : g1;
+        const float vv[4] = {v[it].x, v[it].y, v[it].z, v[it].w}, gg[4] = {g.x, g.y, g.z, g.w}, bb[4] = {bz.x, bz.y, bz.z, bz.w};
+        if (vec) {
+          float4 o = xv[it];
+          o.x = fmaf(gg[0], vv[0] + bb[0], o.x);
+          o.y = fmaf(gg[1], vv[1] + bb[1], o.y);
+          o.z = fmaf(gg[2], vv[2] + bb[2], o.z);
+          o.w = fmaf(gg[3], vv[3] + bb[3], o.w);
+          *reinterpret_cast<float4*>(x) = o;
+        } else {
+          for (int k = 0; k < 4; ++k)
+            if (n + k < N) x[k] += gg[k] * (vv[k] + bb[k]);
+        }
+      }
+      x += L.row_step;
+    }
   }
   __syncwarp();
 }
@@ -339,8 +402,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   constexpr int W_KB_BYTES = BN * BLOCK_K * 2;                 // one 64-wide K block of the weight slice
   constexpr int W_BYTES = WS ? WS_MAX_KB * W_KB_BYTES : 0;     // resident weight slice (WS only), in front of the ring
   constexpr uint32_t TMEM_COLS = tmem_cols(BN);
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  // No integer round trip on this pointer: the compiler must keep seeing a shared-space address, otherwise every
+  // staging access becomes a generic LD.E / ST.E (long-scoreboard latency instead of LDS / STS).
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();     // dynamic shared memory starts at the window base (no static shared)
   uint8_t* ring = smem + W_BYTES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(ring + STAGES * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
@@ -470,6 +536,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     constexpr bool kBf16 = STG && (EPI == EPI_STORE || EPI == EPI_GELU) && sizeof(OT) == 2;
     static_assert(!STG || kResid || kBf16, "no staged epilogue for this combination");
     uint8_t* stg = ring + STAGES * STAGE_BYTES + 256 + (warp - 2) * STG_BYTES;
+    float* cv = reinterpret_cast<float*>(ring + STAGES * STAGE_BYTES + 256 + NUM_EPI_WARPS * STG_BYTES + (warp - 2) * CV_BYTES_PER_WARP);
     const bool active = half * PER < CHUNKS;             // BN = 32: only the first column half has work
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -482,9 +549,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       if constexpr (kResid) {
         if (active) {
           rl = resid_lane<EPI>(ep, lane, mrow0, ncol0, M, N);
+          stage_resid_colvecs<EPI>(ep, cv, lane, mrow0, ncol0, N);
+          __syncwarp();
 #pragma unroll
           for (int i = 0; i < PER; ++i) residual_prefetch(rl, lane, i * 32, N, xv[i]);
         }
+      }
+      if constexpr (kBf16) {
+        if (active) stage_colvec(cv, ep.bias, ncol0, N, lane, 0.f);
+        __syncwarp();
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
@@ -504,7 +577,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
               __syncwarp();
               if (lane == 0) mbar_arrive(&tmem_empty[acc]);
             }
-            if (active && ncol0 + i * 32 < N) epilogue_staged_resid<EPI>(rl, ep.bias, stg, lane, i * 32, N, rr, xv[i]);
+            if (active && ncol0 + i * 32 < N) epilogue_staged_resid<EPI>(rl, cv, stg, lane, i * 32, N, rr, xv[i]);
           }
         }
       } else {
@@ -521,7 +594,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
         if (active && ncol0 < N) {
           if constexpr (kBf16) {
-            epilogue_staged_bf16<EPI, PER>(ep, stg, lane, mrow0, ncol0, M, N, r);
+            epilogue_staged_bf16<EPI, PER>(ep, stg, cv, lane, mrow0, ncol0, M, N, r);
           } else {
 #pragma unroll
             for (int i2 = 0; i2 < PER; ++i2) {

@@ -1,0 +1,287 @@
+// gemm_tc2.cuh -- the CTA-pair (tcgen05 cta_group::2) variant of gemm_tc.cuh for the large projections.
+//   C[M,N] = A[M,K] . W[N,K]^T (+ fused epilogue), 256 x 256 output tiles owned by a cluster of two CTAs.
+// A single CTA issuing 128 x 128 MMAs has to pull (128 + 128) * 32 B of operands out of shared memory per 64-clock
+// MMA while TMA writes the same amount in: the mainloop saturates at ~50 % of the tensor peak (measured 690 TFLOP/s).
+// In a pair each CTA stages only its own 128 rows of A and its own half (128 rows) of the W tile, the leader's
+// MMA (M = 256, N = 256) reads both CTAs' shared memory, and each CTA's TMEM receives its own 128 accumulator rows:
+// operand traffic per SM halves.
+// Roles per CTA (320 threads): warp 0 = TMA producer (both CTAs), warp 1 = MMA issuer (leader CTA only),
+// warps 2..9 = epilogue (both CTAs, own TMEM).  Barrier protocol:
+//   full[s]      lives in the leader; leader's producer arms it with the bytes of BOTH CTAs, both CTAs' TMA complete on it
+//   empty[s]     one per CTA; the leader's tcgen05.commit multicasts the arrival to both
+//   tmem_full[a] one per CTA; multicast commit after the last MMA of a tile
+//   tmem_empty[a] lives in the leader; the 8 epilogue warps of both CTAs arrive on it (remote arrive from the peer)
+// Only the staged (shared-memory transposed, coalesced) epilogues of gemm_tc.cuh are instantiated here.
+#pragma once
+#include "gemm_tc.cuh"
+
+namespace mdgen {
+namespace tc2 {
+
+using namespace tc;
+
+constexpr int TILE_M = 256, TILE_N = 256;
+constexpr int HALF_N = TILE_N / 2;                       // W rows staged per CTA
+constexpr int STAGES2 = 5;
+constexpr int STAGE2_BYTES = A_STAGE_BYTES + HALF_N * BLOCK_K * 2;   // 32 KB per CTA per stage
+constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + EPI_SMEM_BYTES + 1024 + 256;
+static_assert(SMEM2_BYTES <= 227 * 1024, "shared memory budget");
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `local` (a shared::cta address) inside CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+// Relaxed on purpose: the arrival only hands a TMEM accumulator stage back (ordered by tcgen05.wait::ld +
+// tcgen05.fence::before_thread_sync).  A release at cluster scope would first drain the warp's outstanding global
+// stores -- measured as the dominant epilogue stall (ERRBAR / membar) in the first version of this kernel.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load into this CTA's shared memory, completion bytes signalled on a barrier that may live in the peer CTA
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* map, uint32_t bar_cluster_addr, void* dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at the same shared-memory offset in both CTAs of the pair once all prior MMAs retire
+__device__ __forceinline__ void tcgen05_commit_pair(uint64_t* bar) {
+  const uint16_t mask = 3;
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"(mask)
+               : "memory");
+}
+
+// kernel-developer timeline (tools/gemm_trace.py): 16 slots per tile for the first 16 tiles of CTA ep.dbg_cta
+__device__ __forceinline__ void stamp(const EpiParams& ep, int tile_i, int slot) {
+  if (ep.dbg && (int)blockIdx.x == ep.dbg_cta && tile_i < 16) ep.dbg[tile_i * 16 + slot] = clock64();
+}
+
+template <int EPI, typename OT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW, int M, int N,
+                int K, EpiParams ep) {
+  constexpr bool kResid = (EPI == EPI_GATE_RESID || EPI == EPI_RESID);
+  constexpr bool kBf16 = (EPI == EPI_STORE || EPI == EPI_GELU) && sizeof(OT) == 2;
+  static_assert(kResid || kBf16, "gemm_tc2: only the staged epilogues exist");
+  // No integer round trip on this pointer: the compiler must keep seeing a shared-space address, otherwise every
+  // staging access becomes a generic LD.E / ST.E (long-scoreboard latency instead of LDS / STS).
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();     // dynamic shared memory starts at the window base (no static shared)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES2 * STAGE2_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES2;
+  uint64_t* tmem_full = empty_bar + STAGES2;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  const int num_m = (M + TILE_M - 1) / TILE_M, num_n = (N + TILE_N - 1) / TILE_N;
+  const int num_tiles = num_m * num_n;
+  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  // n fastest: the clusters running at the same time share A rows through L2
+  auto get_tile = [&](int i, int& mb, int& nb, int& n_cur) -> bool {
+    const int tile = cluster_id + i * num_clusters;
+    mb = tile / num_n;
+    nb = tile % num_n;
+    n_cur = min(TILE_N, N - nb * TILE_N);       // host guarantees N % 128 == 0: 128 or 256
+    return tile < num_tiles;
+  };
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapW) : "memory");
+    for (int s = 0; s < STAGES2; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 2 * NUM_EPI_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {   // the same warp of both CTAs allocates the pair's tensor memory (all 512 columns)
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_slot)), "r"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  cluster_sync_all();       // the peer's barriers are initialised before anything is signalled across the pair
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: own 128 rows of A, own half of the W tile =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int mb, nb, n_cur;
+      for (int i = 0; get_tile(i, mb, nb, n_cur); ++i) {
+        const int arow = mb * TILE_M + (int)rank * BLOCK_M;
+        const int wrow = nb * TILE_N + (int)rank * (n_cur >> 1);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (kb == 0) stamp(ep, i, 12);
+          uint8_t* sa = smem + stage * STAGE2_BYTES;
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * STAGE2_BYTES);
+          const uint32_t fb = map_to_rank(smem_u32(&full_bar[stage]), 0);
+          tma_load_2d_pair(&tmapA, fb, sa, kb * BLOCK_K, arow);
+          tma_load_2d_pair(&tmapW, fb, sa + A_STAGE_BYTES, kb * BLOCK_K, wrow);
+          if (kb == num_kb - 1) stamp(ep, i, 13);
+          if (++stage == STAGES2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: one thread of the leader CTA drives both tensor cores =====
+    if (lane == 0 && rank == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      int mb, nb, n_cur;
+      for (int i = 0; get_tile(i, mb, nb, n_cur); ++i) {
+        const uint32_t idesc = make_idesc_bf16(TILE_M, n_cur);
+        stamp(ep, i, 0);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tcgen05_fence_after();
+        stamp(ep, i, 1);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TILE_N);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tcgen05_fence_after();
+          if (kb < 6) stamp(ep, i, 2 + kb);
+          const uint32_t sa = smem_u32(smem + stage * STAGE2_BYTES);
+          const uint64_t adesc = make_smem_desc_sw128(sa);
+          const uint64_t bdesc = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+            umma_bf16_pair(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+          tcgen05_commit_pair(&empty_bar[stage]);   // frees this stage in both CTAs
+          if (++stage == STAGES2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        tcgen05_commit_pair(&tmem_full[acc]);
+        stamp(ep, i, 8);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ===== epilogue warps 2..9: TMEM lane quarter = warp % 4, column half = (warp - 2) / 4 =====
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    uint8_t* stg = smem + STAGES2 * STAGE2_BYTES + 256 + (warp - 2) * STG_BYTES;
+    float* cv = reinterpret_cast<float*>(smem + STAGES2 * STAGE2_BYTES + 256 + NUM_EPI_WARPS * STG_BYTES + (warp - 2) * CV_BYTES_PER_WARP);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int mb, nb, n_cur;
+    for (int i = 0; get_tile(i, mb, nb, n_cur); ++i) {
+      const int cpw = n_cur >> 6;                         // 32-column chunks per warp: 4 (n_cur 256) or 2 (128)
+      const int mrow0 = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32;
+      const int col_in_tile = half * cpw * 32;
+      const int ncol0 = nb * TILE_N + col_in_tile;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * TILE_N + col_in_tile);
+      const uint32_t te = map_to_rank(smem_u32(&tmem_empty[acc]), 0);
+      if constexpr (kResid) {
+        // rolling residual prefetch: chunks c and c+1 are in flight while chunk c is combined and written back
+        const ResidLane rl = resid_lane<EPI>(ep, lane, mrow0, ncol0, M, N);
+        stage_resid_colvecs<EPI>(ep, cv, lane, mrow0, ncol0, N);
+        __syncwarp();
+        float4 xv[2][8];
+        residual_prefetch(rl, lane, 0, N, xv[0]);
+        residual_prefetch(rl, lane, 32, N, xv[1]);
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tcgen05_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < cpw; c += 2) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            uint32_t rr[32];
+            tmem_ld_32x32b_x32(taddr + (c + u) * 32, rr);
+            tmem_ld_wait();
+            if (c + u == cpw - 1) {                 // accumulator fully read: hand the TMEM stage back to the leader
+              tcgen05_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_cluster(te);
+            }
+            epilogue_staged_resid<EPI>(rl, cv, stg, lane, (c + u) * 32, N, rr, xv[u]);
+            if (c + u + 2 < cpw) residual_prefetch(rl, lane, (c + u + 2) * 32, N, xv[u]);
+          }
+        }
+      } else {
+        stage_colvec(cv, ep.bias, ncol0, N, lane, 0.f);
+        __syncwarp();
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tcgen05_fence_after();
+        if (warp == 2 && lane == 0) stamp(ep, i, 9);
+        // one 32-column chunk at a time, the next chunk's tcgen05.ld in flight while this one is converted and stored
+        uint32_t r[2][1][32];
+        tmem_ld_32x32b_x32(taddr, r[0][0]);
+#pragma unroll 1
+        for (int c = 0; c < cpw; c += 2) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            tmem_ld_wait();
+            if (c + u + 1 < cpw) {
+              tmem_ld_32x32b_x32(taddr + (c + u + 1) * 32, r[u ^ 1][0]);
+            } else {                                  // accumulator fully read: hand the TMEM stage back to the leader
+              tcgen05_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_cluster(te);
+              if (warp == 2 && lane == 0) stamp(ep, i, 10);
+            }
+            epilogue_staged_bf16<EPI, 1>(ep, stg, cv + (c + u) * 32, lane, mrow0, ncol0 + (c + u) * 32, M, N, r[u]);
+          }
+        }
+      }
+      if (warp == 2 && lane == 0) stamp(ep, i, 11);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  cluster_sync_all();       // the peer's shared memory and barriers stay valid until both CTAs are done
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
+}  // namespace tc2
+}  // namespace mdgen

@@ -18,6 +18,7 @@
 #include "elementwise.cuh"
 #include "gemm_simt.cuh"
 #include "gemm_tc.cuh"
+#include "gemm_tc2.cuh"
 #include "ipa.cuh"
 
 namespace mdgen {
@@ -109,6 +110,37 @@ static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, int M, i
   return launch_tc_ws<BN, EPI, OT, 0, 0>(ta, tw, M, N, K, ep, st);
 }
 
+// CTA-pair kernel (gemm_tc2.cuh): 256 x 256 tiles, one cluster of two CTAs per tile
+template <int EPI, typename OT>
+static int launch_tc2_inst(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, const EpiParams& ep,
+                           cudaStream_t st) {
+  static bool configured = false;
+  auto kern = tc2::gemm_tc2_kernel<EPI, OT>;
+  if (!configured) {
+    MD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc2::SMEM2_BYTES));
+    configured = true;
+  }
+  const int tiles = ((M + tc2::TILE_M - 1) / tc2::TILE_M) * ((N + tc2::TILE_N - 1) / tc2::TILE_N);
+  const int pairs = num_sms() / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  ProfScope ps(PC_GEMM_TC, st);
+  kern<<<grid, tc::NUM_THREADS, tc2::SMEM2_BYTES, st>>>(ta, tw, M, N, K, ep);
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+static int launch_tc2(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, int epi, const EpiParams& ep,
+                      cudaStream_t st) {
+  switch (epi) {
+    case EPI_STORE: return launch_tc2_inst<EPI_STORE, bf16>(ta, tw, M, N, K, ep, st);
+    case EPI_GELU: return launch_tc2_inst<EPI_GELU, bf16>(ta, tw, M, N, K, ep, st);
+    case EPI_GATE_RESID: return launch_tc2_inst<EPI_GATE_RESID, float>(ta, tw, M, N, K, ep, st);
+    case EPI_RESID: return launch_tc2_inst<EPI_RESID, float>(ta, tw, M, N, K, ep, st);
+  }
+  set_error("launch_gemm_tc: epilogue not available in the CTA-pair kernel");
+  return -1;
+}
+
 template <int BN>
 static int launch_tc_bn(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, int epi, bool out_bf16,
                         const EpiParams& ep, cudaStream_t st) {
@@ -132,6 +164,7 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
                    const EpiParams& ep, int block_n, cudaStream_t st) {
   if (M <= 0 || N <= 0) return 0;
   MD_CHECK(K % 8 == 0, "gemm_tc: K must be a multiple of 8");
+  const bool auto_bn = block_n == 0;
   if (block_n == 0) {
     if (N <= 32) block_n = 32;
     else if (N <= 64) block_n = 64;
@@ -142,21 +175,33 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
     }
   }
   EpiParams epp = ep;
+  epp.dbg = g_dbg_buf;
+  epp.dbg_cta = g_dbg_cta;
   auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
   if ((epi == EPI_STORE || epi == EPI_GELU) && out_bf16) epp.staged = al16(ep.out) && ep.ldo % 8 == 0;
   else if (epi == EPI_RESID) epp.staged = al16(ep.resid) && ep.ldr % 4 == 0;
   else if (epi == EPI_GATE_RESID)   // the staged path assumes at most one batch boundary inside a 32-row slab
     epp.staged = al16(ep.resid) && ep.ldr % 4 == 0 && al16(ep.gate) && ep.gate_stride % 4 == 0 && ep.rows_per_batch >= 32;
-  if ((epi == EPI_RESID || epi == EPI_GATE_RESID) && ep.bias && !al16(ep.bias)) epp.staged = 0;
+  if (ep.bias && !al16(ep.bias)) epp.staged = 0;
+  // CTA-pair kernel: staged epilogues only, N in whole 128-column halves, enough 256 x 256 tiles to fill the pairs
+  const bool pair_ok = epp.staged && N % 128 == 0 && epi != EPI_EULER && (epi == EPI_GATE_RESID || epi == EPI_RESID || out_bf16);
+  if (block_n == 256) MD_CHECK(pair_ok, "launch_gemm_tc: shape / epilogue not supported by the CTA-pair kernel");
+  if (auto_bn && pair_ok && !getenv("MDGEN_NO_GEMM_2CTA")) {
+    const long t256 = (long)((M + 255) / 256) * ((N + 255) / 256);
+    // measured on config 3 (tools/gemm_probe.py): the pair kernel wins for the K = 1536 projection (fc2) and the plain
+    // bf16 stores of wide N; the K = 384 residual / GELU epilogues are shared-memory-bandwidth bound either way
+    if (t256 >= num_sms() / 2 && (K >= 1024 || (epi == EPI_STORE && N >= 1024))) block_n = 256;
+  }
   CUtensorMap ta, tw;
   MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
-  MD_TRY(make_tmap_2d(&tw, W, N, K, ldw, block_n));
+  MD_TRY(make_tmap_2d(&tw, W, N, K, ldw, block_n == 256 ? tc2::HALF_N : block_n));
+  if (block_n == 256) return launch_tc2(ta, tw, M, N, K, epi, epp, st);
   switch (block_n) {
     case 32: return launch_tc_bn<32>(ta, tw, M, N, K, epi, out_bf16, epp, st);
     case 64: return launch_tc_bn<64>(ta, tw, M, N, K, epi, out_bf16, epp, st);
     case 128: return launch_tc_bn<128>(ta, tw, M, N, K, epi, out_bf16, epp, st);
   }
-  set_error("launch_gemm_tc: block_n must be 32, 64 or 128");
+  set_error("launch_gemm_tc: block_n must be 32, 64, 128 or 256 (CTA pair)");
   return -1;
 }
 
@@ -807,9 +852,29 @@ static int time_tables(Fwd<AT>& f, const float* t, int nt, const float* x_for_de
   MD_CHECK(w0 && b0 && w2 && b2, "missing t_embedder weights");
   timestep_features_kernel<<<(R * 128 + 127) / 128, 128, 0, st>>>(t, h->cfg.time_multiplier, R, h->tfeat);
   MD_LAUNCHED();
-  MD_TRY(rowvec(st, h->tfeat, 256, R, w0->d, 256, b0->d, C, h->th1, C, 0, 0, 0));
-  MD_TRY(rowvec(st, h->th1, C, R, w2->d, C, b2->d, C, h->temb, C, 1, 0, 0));
-  MD_TRY(rowvec(st, h->temb, C, R, h->ada_w, C, h->ada_b, h->ada_cols, h->ada, h->ada_cols, 1, 0, 0));
+  if (R <= 16) {
+    MD_TRY(rowvec(st, h->tfeat, 256, R, w0->d, 256, b0->d, C, h->th1, C, 0, 0, 0));
+    MD_TRY(rowvec(st, h->th1, C, R, w2->d, C, b2->d, C, h->temb, C, 1, 0, 0));
+    MD_TRY(rowvec(st, h->temb, C, R, h->ada_w, C, h->ada_b, h->ada_cols, h->ada, h->ada_cols, 1, 0, 0));
+  } else {  // a sampler's whole time grid: tiled fp32 GEMMs, SiLU applied once per element in between
+    const unsigned nblk = (unsigned)(((size_t)R * C + 255) / 256);
+    EpiParams e;
+    e.bias = b0->d;
+    e.out = h->th1;
+    e.ldo = C;
+    MD_TRY((launch_gemm_simt<float, float>(h->tfeat, 256, w0->d, 256, R, C, 256, EPI_STORE, e, st)));
+    silu_kernel<<<nblk, 256, 0, st>>>(h->th1, h->th1, (size_t)R * C);
+    MD_LAUNCHED();
+    e.bias = b2->d;
+    e.out = h->temb;
+    MD_TRY((launch_gemm_simt<float, float>(h->th1, C, w2->d, C, R, C, C, EPI_STORE, e, st)));
+    silu_kernel<<<nblk, 256, 0, st>>>(h->temb, h->th1, (size_t)R * C);
+    MD_LAUNCHED();
+    e.bias = h->ada_b;
+    e.out = h->ada;
+    e.ldo = h->ada_cols;
+    MD_TRY((launch_gemm_simt<float, float>(h->th1, C, h->ada_w, C, R, h->ada_cols, C, EPI_STORE, e, st)));
+  }
   h->nt_cur = nt;
   if (!h->flag(MDGEN_F_PREPEND_IPA)) return 0;
   const int ntBL = nt * BL, M = h->streams * ntBL;

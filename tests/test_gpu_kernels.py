@@ -46,7 +46,10 @@ def test_gemm_tcgen05_bf16(M, N, K, bn):
 
 
 @pytest.mark.parametrize("M,N,K,bn", [(4000, 1152, 384, 0), (777, 1536, 384, 128), (1000, 384, 384, 64), (129, 48, 384, 64),
-                                      (300, 72, 64, 0), (64, 24, 384, 32)])
+                                      (300, 72, 64, 0), (64, 24, 384, 32),
+                                      # block_n 256 = the CTA-pair (cta_group::2) kernel, 256 x 256 tiles
+                                      (256, 256, 64, 256), (4000, 1152, 384, 256), (777, 1536, 384, 256), (300, 128, 64, 256),
+                                      (20000, 384, 384, 256)])
 @pytest.mark.parametrize("mode", [2, 3])
 def test_gemm_tcgen05_bf16_out_staged_epilogue(M, N, K, bn, mode):
     g = torch.Generator().manual_seed(M + N + K)
@@ -61,7 +64,8 @@ def test_gemm_tcgen05_bf16_out_staged_epilogue(M, N, K, bn, mode):
 
 
 @pytest.mark.parametrize("M,N,K,bn", [(4000, 384, 1536, 0), (4000, 384, 384, 0), (777, 384, 384, 128), (129, 48, 384, 64),
-                                      (300, 21, 384, 0), (100, 70, 64, 64)])
+                                      (300, 21, 384, 0), (100, 70, 64, 64),
+                                      (256, 256, 384, 256), (4000, 384, 1536, 256), (777, 384, 384, 256), (20000, 1152, 384, 256)])
 def test_gemm_tcgen05_gated_residual_epilogue(M, N, K, bn):
     g = torch.Generator().manual_seed(M + N + K)
     A, W, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5, torch.randn(N, generator=g)
