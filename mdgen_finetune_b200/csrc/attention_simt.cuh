@@ -275,6 +275,112 @@ attention_short_kernel(AttnParams<AT> p, long long total_groups) {
   store24(p.out + attn_row(nbi, qi, S_, p.inner) * p.ldo + h * HD, acc);
 }
 
+// S <= 4 (the tetrapeptide residue axis): one thread per (sequence, head) owns ALL S queries.  Nothing is exchanged
+// between threads, every q/k/v element is loaded, converted and rotated once, scores for the S x (S+1) pairs are kept in
+// registers and the softmax is taken without running-max rescaling.  ~2.4x fewer instructions per query than the
+// thread-per-query kernel above, and consecutive lanes read consecutive 48-byte head slices of the same token row.
+// rotate one 24-wide head vector to position pos (rotate_half pairing i, i+12); tables read as 6 float4
+__device__ __forceinline__ void rope24(float* x, const float* cs, const float* sn, int pos) {
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float4 c4 = __ldg(reinterpret_cast<const float4*>(cs + pos * 12) + j);
+    const float4 s4 = __ldg(reinterpret_cast<const float4*>(sn + pos * 12) + j);
+    const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int i = 4 * j + e;
+      const float a = x[i], b = x[i + 12];
+      x[i] = a * cc[e] - b * ss[e];
+      x[i + 12] = b * cc[e] + a * ss[e];
+    }
+  }
+}
+constexpr int ASQ_THREADS = 128;
+template <typename AT, int HD, int S_>
+__global__ void __launch_bounds__(ASQ_THREADS)
+attention_seq_kernel(AttnParams<AT> p, long long total_groups) {
+  constexpr int HALF = HD / 2;
+  const long long grp = (long long)blockIdx.x * ASQ_THREADS + threadIdx.x;   // (sequence, head), head fastest
+  if (grp >= total_groups) return;
+  const int h = (int)(grp % p.H), nbi = (int)(grp / p.H);
+  const int C = p.H * HD;
+  float q[S_][HD];
+  float sc[S_][S_ + 1];
+  const AT* rows[S_];
+  bool valid[S_];
+#pragma unroll
+  for (int t = 0; t < S_; ++t) {
+    const size_t r = attn_row(nbi, t, S_, p.inner);
+    rows[t] = p.qkv + r * p.ld + h * HD;
+    valid[t] = p.key_valid[r % p.mask_mod] != 0.f;
+    load24(rows[t], q[t]);
+  }
+  static_assert(HD == 24, "rope24 is written for head_dim 24");
+  if (p.cs) {
+#pragma unroll
+    for (int t = 0; t < S_; ++t) rope24(q[t], p.cs, p.sn, t);
+  }
+  // ---- scores: keys 0..S-1 from the tokens, key S = learned bias token (mha.py:265-268), all rotated by position
+#pragma unroll
+  for (int j = 0; j <= S_; ++j) {
+    float k[HD];
+    if (j < S_) {
+      load24(rows[j] + C, k);
+    } else {
+#pragma unroll
+      for (int i = 0; i < HD; ++i) k[i] = __ldg(p.bias_k + h * HD + i);
+    }
+    if (p.cs) rope24(k, p.cs, p.sn, j);
+#pragma unroll
+    for (int t = 0; t < S_; ++t) {
+      float s0 = 0.f, s1 = 0.f;       // two partial sums: halves the dependent FMA chain
+#pragma unroll
+      for (int i = 0; i < HALF; ++i) {
+        s0 = fmaf(q[t][i], k[i], s0);
+        s1 = fmaf(q[t][i + HALF], k[i + HALF], s1);
+      }
+      sc[t][j] = (j < S_ && !valid[j]) ? -INFINITY : s0 + s1;
+    }
+  }
+  // ---- softmax over the S+1 keys (the bias key is never masked, so the maximum is finite)
+#pragma unroll
+  for (int t = 0; t < S_; ++t) {
+    float m = sc[t][S_];
+#pragma unroll
+    for (int j = 0; j < S_; ++j) m = fmaxf(m, sc[t][j]);
+    float l = 0.f;
+#pragma unroll
+    for (int j = 0; j <= S_; ++j) {
+      sc[t][j] = __expf(sc[t][j] - m);
+      l += sc[t][j];
+    }
+    const float inv = 1.0f / l;
+#pragma unroll
+    for (int j = 0; j <= S_; ++j) sc[t][j] *= inv;
+  }
+  // ---- P.V (q's registers are dead: the accumulators take their place)
+#pragma unroll
+  for (int t = 0; t < S_; ++t)
+#pragma unroll
+    for (int i = 0; i < HD; ++i) q[t][i] = 0.f;
+#pragma unroll
+  for (int j = 0; j <= S_; ++j) {
+    float v[HD];
+    if (j < S_) {
+      load24(rows[j] + 2 * C, v);
+    } else {
+#pragma unroll
+      for (int i = 0; i < HD; ++i) v[i] = __ldg(p.bias_v + h * HD + i);
+    }
+#pragma unroll
+    for (int t = 0; t < S_; ++t)
+#pragma unroll
+      for (int i = 0; i < HD; ++i) q[t][i] = fmaf(sc[t][j], v[i], q[t][i]);
+  }
+#pragma unroll
+  for (int t = 0; t < S_; ++t) store24(p.out + attn_row(nbi, t, S_, p.inner) * p.ldo + h * HD, q[t]);
+}
+
 template <typename AT, int S_>
 inline void launch_attention_short(const AttnParams<AT>& p, cudaStream_t st) {
   const long long groups = (long long)p.nb * p.H;
@@ -286,9 +392,16 @@ template <typename AT>
 inline int launch_attention_simt(const AttnParams<AT>& p, int head_dim, cudaStream_t st) {
   MD_CHECK(head_dim == 24, "attention_simt: head_dim must be 24");
   if (p.nb <= 0 || p.S <= 0) return 0;
-  const bool is_short = (p.S == 4 || p.S == 8 || p.S == 16) && p.H <= 16;
+  const bool is_short = (p.S <= 4 && p.S >= 2) || ((p.S == 8 || p.S == 16) && p.H <= 16);
   ProfScope ps(is_short ? PC_ATTN_SHORT : PC_ATTN_SIMT, st);
-  if (is_short && p.S == 4) launch_attention_short<AT, 4>(p, st);
+  if (p.S == 4 || p.S == 2 || p.S == 3) {
+    const long long groups = (long long)p.nb * p.H;
+    const unsigned grid = (unsigned)((groups + ASQ_THREADS - 1) / ASQ_THREADS);
+    if (p.S == 4) attention_seq_kernel<AT, 24, 4><<<grid, ASQ_THREADS, 0, st>>>(p, groups);
+    else if (p.S == 3) attention_seq_kernel<AT, 24, 3><<<grid, ASQ_THREADS, 0, st>>>(p, groups);
+    else attention_seq_kernel<AT, 24, 2><<<grid, ASQ_THREADS, 0, st>>>(p, groups);
+  }
+  else if (is_short && p.S == 4) launch_attention_short<AT, 4>(p, st);
   else if (is_short && p.S == 8) launch_attention_short<AT, 8>(p, st);
   else if (is_short) launch_attention_short<AT, 16>(p, st);
   else {

@@ -9,6 +9,9 @@ namespace mdgen {
 // out[m,:] = LN(x[m,:]) * (1 + scale[b]) + shift[b],  b = (m / rows_per_batch) % nbatch.
 // latent_model.py:385,390,467,475,489 + layers.py:14-15,73.  If shift == nullptr: affine
 // LayerNorm with weight/bias (ipa_norm, latent_model.py:360,382; eps 1e-5).
+// LN_ROWS consecutive rows per warp: all their loads are issued before the first reduction (memory-level parallelism
+// per warp), and the batch-index division plus the shift / scale loads are shared when the rows fall in one batch element.
+constexpr int LN_ROWS = 2;
 template <typename OT, int C>
 __global__ void __launch_bounds__(256)
 ln_modulate_kernel(const float* __restrict__ x, OT* __restrict__ out, int M, const float* __restrict__ shift,
@@ -17,54 +20,91 @@ ln_modulate_kernel(const float* __restrict__ x, OT* __restrict__ out, int M, con
   static_assert(C % 128 == 0, "C must be a multiple of 128");
   constexpr int V = C / 128;  // float4 per lane
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= M) return;
-  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)warp * C);
-  float4 v[V];
-  float s = 0.f;
+  const int row0 = warp * LN_ROWS;
+  if (row0 >= M) return;
+  float4 v[LN_ROWS][V];
 #pragma unroll
-  for (int i = 0; i < V; ++i) {
-    v[i] = xr[lane + 32 * i];
-    s += v[i].x + v[i].y + v[i].z + v[i].w;
-  }
-  const float mean = warp_sum(s) * (1.0f / C);
-  float q = 0.f;
+  for (int r = 0; r < LN_ROWS; ++r) {
+    const int row = min(row0 + r, M - 1);
+    const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * C);
 #pragma unroll
-  for (int i = 0; i < V; ++i) {
-    float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
-    q += a * a + b * b + c * c + d * d;
+    for (int i = 0; i < V; ++i) v[r][i] = xr[lane + 32 * i];
   }
-  const float rstd = rsqrtf(warp_sum(q) * (1.0f / C) + eps);
-  const int b = (warp / rows_per_batch) % nbatch;
+  // per-channel multiplier / offset of the first row's batch element (or the affine LayerNorm weights)
+  const int q0 = row0 / rows_per_batch;
+  const int b0 = q0 % nbatch;
+  const int split = (q0 + 1) * rows_per_batch - row0;      // rows >= split belong to the next batch element
+  float4 mul[V], add[V];
 #pragma unroll
   for (int i = 0; i < V; ++i) {
     const int c0 = (lane + 32 * i) * 4;
-    float r[4] = {(v[i].x - mean) * rstd, (v[i].y - mean) * rstd, (v[i].z - mean) * rstd,
-                  (v[i].w - mean) * rstd};
     if (shift) {
-      const float4 sh = *reinterpret_cast<const float4*>(shift + (size_t)b * mod_stride + c0);
-      const float4 sc = *reinterpret_cast<const float4*>(scale + (size_t)b * mod_stride + c0);
-      r[0] = r[0] * (1.f + sc.x) + sh.x;
-      r[1] = r[1] * (1.f + sc.y) + sh.y;
-      r[2] = r[2] * (1.f + sc.z) + sh.z;
-      r[3] = r[3] * (1.f + sc.w) + sh.w;
+      const float4 sc = *reinterpret_cast<const float4*>(scale + (size_t)b0 * mod_stride + c0);
+      mul[i] = make_float4(1.f + sc.x, 1.f + sc.y, 1.f + sc.z, 1.f + sc.w);
+      add[i] = *reinterpret_cast<const float4*>(shift + (size_t)b0 * mod_stride + c0);
     } else if (w) {
-      const float4 ww = *reinterpret_cast<const float4*>(w + c0);
-      const float4 bb = *reinterpret_cast<const float4*>(bvec + c0);
-      r[0] = r[0] * ww.x + bb.x;
-      r[1] = r[1] * ww.y + bb.y;
-      r[2] = r[2] * ww.z + bb.z;
-      r[3] = r[3] * ww.w + bb.w;
-    }
-    OT* o = out + (size_t)warp * C + c0;
-    if constexpr (sizeof(OT) == 4) {
-      *reinterpret_cast<float4*>(o) = make_float4(r[0], r[1], r[2], r[3]);
+      mul[i] = *reinterpret_cast<const float4*>(w + c0);
+      add[i] = *reinterpret_cast<const float4*>(bvec + c0);
     } else {
-      __nv_bfloat162 p0 = __floats2bfloat162_rn(r[0], r[1]);
-      __nv_bfloat162 p1 = __floats2bfloat162_rn(r[2], r[3]);
-      uint2 pk;
-      pk.x = *reinterpret_cast<uint32_t*>(&p0);
-      pk.y = *reinterpret_cast<uint32_t*>(&p1);
-      *reinterpret_cast<uint2*>(o) = pk;
+      mul[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+      add[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  float mean[LN_ROWS], rstd[LN_ROWS];
+#pragma unroll
+  for (int r = 0; r < LN_ROWS; ++r) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < V; ++i) s += (v[r][i].x + v[r][i].y) + (v[r][i].z + v[r][i].w);
+    mean[r] = s;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+    for (int r = 0; r < LN_ROWS; ++r) mean[r] += __shfl_xor_sync(0xffffffffu, mean[r], o);
+#pragma unroll
+  for (int r = 0; r < LN_ROWS; ++r) {
+    mean[r] *= (1.0f / C);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const float a = v[r][i].x - mean[r], b = v[r][i].y - mean[r], c = v[r][i].z - mean[r], d = v[r][i].w - mean[r];
+      q += (a * a + b * b) + (c * c + d * d);
+    }
+    rstd[r] = q;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+    for (int r = 0; r < LN_ROWS; ++r) rstd[r] += __shfl_xor_sync(0xffffffffu, rstd[r], o);
+#pragma unroll
+  for (int r = 0; r < LN_ROWS; ++r) {
+    const int row = row0 + r;
+    if (row >= M) break;
+    const float rs = rsqrtf(rstd[r] * (1.0f / C) + eps), mu = mean[r];
+    const bool next = shift && r >= split;                  // crossed into the next batch element: reload its vectors
+    const int b1 = (q0 + 1) % nbatch;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const int c0 = (lane + 32 * i) * 4;
+      float4 m4 = mul[i], a4 = add[i];
+      if (next) {
+        const float4 sc = *reinterpret_cast<const float4*>(scale + (size_t)b1 * mod_stride + c0);
+        m4 = make_float4(1.f + sc.x, 1.f + sc.y, 1.f + sc.z, 1.f + sc.w);
+        a4 = *reinterpret_cast<const float4*>(shift + (size_t)b1 * mod_stride + c0);
+      }
+      const float o0 = fmaf((v[r][i].x - mu) * rs, m4.x, a4.x), o1 = fmaf((v[r][i].y - mu) * rs, m4.y, a4.y);
+      const float o2 = fmaf((v[r][i].z - mu) * rs, m4.z, a4.z), o3 = fmaf((v[r][i].w - mu) * rs, m4.w, a4.w);
+      OT* o = out + (size_t)row * C + c0;
+      if constexpr (sizeof(OT) == 4) {
+        *reinterpret_cast<float4*>(o) = make_float4(o0, o1, o2, o3);
+      } else {
+        const __nv_bfloat162 p0 = __floats2bfloat162_rn(o0, o1), p1 = __floats2bfloat162_rn(o2, o3);
+        uint2 pk;
+        pk.x = *reinterpret_cast<const uint32_t*>(&p0);
+        pk.y = *reinterpret_cast<const uint32_t*>(&p1);
+        *reinterpret_cast<uint2*>(o) = pk;
+      }
     }
   }
 }

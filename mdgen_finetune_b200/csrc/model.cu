@@ -727,7 +727,7 @@ struct Fwd {
   int lnmod(const float* x, AT* out, int M, const float* shift, const float* scale, int rows_per_batch, int nbatch) {
     if (M <= 0) return 0;
     ProfScope ps(PC_LN, st);
-    ln_modulate_kernel<AT, 384><<<(M * 32 + 255) / 256, 256, 0, st>>>(x, out, M, shift, scale, h->ada_cols,
+    ln_modulate_kernel<AT, 384><<<((M + LN_ROWS - 1) / LN_ROWS * 32 + 255) / 256, 256, 0, st>>>(x, out, M, shift, scale, h->ada_cols,
                                                                        rows_per_batch, nbatch, nullptr, nullptr, 1e-6f);
     MD_LAUNCHED();
     MD_CUDA(cudaGetLastError());
@@ -903,7 +903,7 @@ static int time_tables(Fwd<AT>& f, const float* t, int nt, const float* x_for_de
     const float* ada_row = h->ada + Lw.ada_off;
     {
       ProfScope ps(PC_LN, st);
-      ln_modulate_kernel<float, 384><<<(M * 32 + 255) / 256, 256, 0, st>>>(h->ipa_s, h->ipa_n, M, nullptr, nullptr, 0, 1, 1,
+      ln_modulate_kernel<float, 384><<<((M + LN_ROWS - 1) / LN_ROWS * 32 + 255) / 256, 256, 0, st>>>(h->ipa_s, h->ipa_n, M, nullptr, nullptr, 0, 1, 1,
                                                                            Lw.norm_w, Lw.norm_b, 1e-5f);
       MD_LAUNCHED();
     }
