@@ -1,0 +1,400 @@
+// gemm_ln.cuh -- output projection fused with the residual update AND the next block's LayerNorm + adaLN modulate:
+//   x[m,:]  += gate[b] * (A[m,:] . W^T + bias)                        (latent_model.py:387,392,486,491)
+//   h[m,:]   = LN(x[m,:]) * (1 + scale'[b]) + shift'[b]   as bf16      (the NEXT block's latent_model.py:385,390,467,475,489)
+// for the C = 384 wide residual stream (N = 384 = one full row per tile, K = 384 or 1536).
+// Why: the stand-alone LayerNorm kernel re-reads the fp32 stream the projection has just written (49 MB in, 24.5 MB out,
+// 14-17 us) and costs a kernel boundary; here the new row is still on chip when it is normalised.
+// Structure: the CTA-pair machinery of gemm_tc2.cuh (cluster of 2, tcgen05 cta_group::2, M = 256 rows per pair), but a
+// tile spans the whole row: two MMAs per k-step (N = 256 into TMEM columns 0..255, N = 128 into 256..383).  The 384
+// accumulator columns leave no room for a second accumulator stage, so the epilogue does not overlap the next tile's
+// MMAs -- the TMA producer keeps prefetching the next tile's operands meanwhile.
+// Epilogue (warps 2..9, thread = row, two warps per TMEM lane quarter each owning 6 of the 12 32-column chunks):
+//   pass 1  acc -> x_new = x + gate * (acc + bias) -> global x, x_new written back over the accumulator in TMEM, row sum
+//   pass 2  sum of (x_new - mean)^2 from TMEM            (two-pass variance, like ln_modulate_kernel)
+//   pass 3  normalise, modulate, bf16 -> global h
+// (global x / h accesses are transposed through a per-warp shared-memory tile so that they are coalesced)
+// Row statistics of the two column halves are combined through shared memory (one named barrier per lane quarter).
+#pragma once
+#include "gemm_tc2.cuh"
+
+namespace mdgen {
+namespace tcln {
+
+using namespace tc;
+using tc2::cluster_ctarank;
+using tc2::cluster_sync_all;
+using tc2::map_to_rank;
+using tc2::mbar_arrive_cluster;
+using tc2::tcgen05_commit_pair;
+using tc2::tma_load_2d_pair;
+using tc2::umma_bf16_pair;
+using tc2::stamp;
+
+constexpr int LN_N = 384, TILE_M = 256;
+constexpr int W1_ROWS = 128, W2_ROWS = 64;      // W rows staged per CTA for the N = 256 and the N = 128 MMA
+constexpr int STAGE_BYTES = A_STAGE_BYTES + (W1_ROWS + W2_ROWS) * BLOCK_K * 2;   // 40 KB
+constexpr int STAGES = 4;
+constexpr int NVEC = 7;                          // bias, gate[2], 1 + scale[2], shift[2]   (two batch elements per slab)
+constexpr int CV_BYTES = NVEC * LN_N * 4;
+constexpr int STATS_BYTES = 2 * 2 * 128 * 4;     // [sum | centred square][column half][row] partial statistics
+constexpr int OFF_STG = STAGES * STAGE_BYTES + CV_BYTES + STATS_BYTES + 256;      // per-epilogue-warp 32 x 32 fp32 staging tiles
+constexpr int SMEM_BYTES = OFF_STG + NUM_EPI_WARPS * STG_BYTES + 1024;
+static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+static_assert(STAGE_BYTES % 1024 == 0, "SWIZZLE_128B tiles need 1024-byte aligned bases");
+
+struct LnFuse {
+  bf16* out;            // [M, 384] normalised + modulated rows for the next block
+  const float* shift;   // next block's adaLN shift / scale rows, indexed like the gate: + b * gate_stride
+  const float* scale;
+  float eps;
+};
+
+__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+      "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]),
+      "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]),
+      "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW1,
+               const __grid_constant__ CUtensorMap tmapW2, int M, int K, EpiParams ep, LnFuse ln) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  float* cv = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES);          // [NVEC][384]
+  float* stats = cv + NVEC * LN_N;                                            // row sums [2][128]
+  float* stats2 = stats + 2 * 128;                                            // centred squares [2][128]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + CV_BYTES + STATS_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full = empty_bar + STAGES;
+  uint64_t* tmem_empty = tmem_full + 1;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  const int num_tiles = (M + TILE_M - 1) / TILE_M;
+  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapW1) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapW2) : "memory");
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    mbar_init(tmem_empty, 2 * NUM_EPI_WARPS);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_slot)), "r"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: own 128 rows of A, own halves of the two W slices =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const int arow = tile * TILE_M + (int)rank * BLOCK_M;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+          const uint32_t fb = map_to_rank(smem_u32(&full_bar[stage]), 0);
+          tma_load_2d_pair(&tmapA, fb, sa, kb * BLOCK_K, arow);
+          tma_load_2d_pair(&tmapW1, fb, sa + A_STAGE_BYTES, kb * BLOCK_K, (int)rank * W1_ROWS);
+          tma_load_2d_pair(&tmapW2, fb, sa + A_STAGE_BYTES + W1_ROWS * BLOCK_K * 2, kb * BLOCK_K, 256 + (int)rank * W2_ROWS);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA): per k-step one N = 256 and one N = 128 MMA =====
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc1 = make_idesc_bf16(TILE_M, 256), idesc2 = make_idesc_bf16(TILE_M, 128);
+      int stage = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      int ti = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
+        mbar_wait(tmem_empty, acc_phase ^ 1);
+        tcgen05_fence_after();
+        stamp(ep, ti, 0);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint64_t adesc = make_smem_desc_sw128(sa);
+          const uint64_t b1desc = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+          const uint64_t b2desc = make_smem_desc_sw128(sa + A_STAGE_BYTES + W1_ROWS * BLOCK_K * 2);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            const uint32_t accum = (kb | k) != 0 ? 1u : 0u;
+            umma_bf16_pair(tmem_base, adesc + (uint64_t)(k * 2), b1desc + (uint64_t)(k * 2), idesc1, accum);
+            umma_bf16_pair(tmem_base + 256, adesc + (uint64_t)(k * 2), b2desc + (uint64_t)(k * 2), idesc2, accum);
+          }
+          tcgen05_commit_pair(&empty_bar[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        tcgen05_commit_pair(tmem_full);
+        stamp(ep, ti, 1);
+        acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===== epilogue warps 2..9 =====
+    // All arithmetic happens in the TMEM row layout (thread = row: per-row statistics need no shuffles, x_new can live
+    // in TMEM between the passes); every global access goes through a per-warp 32 x 32 staging tile so that it is
+    // coalesced (lane = 4 columns x 8 rows).  Row-per-thread global accesses were measured 10x slower here: with the
+    // shared-memory carve-out at its maximum there is no L1 left to merge the 16-byte pieces of a line.
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    const int et = threadIdx.x - 64;                       // 0..255 among the epilogue threads
+    const int row_in_cta = quarter * 32 + lane;
+    const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t te = map_to_rank(smem_u32(tmem_empty), 0);
+    uint8_t* stg = smem + OFF_STG + (warp - 2) * STG_BYTES;
+    constexpr int CH = 6;                                  // 32-column chunks per warp
+    const int col0 = half * CH * 32;
+    const int c4 = lane & 7, rsub = lane >> 3;             // transposed phase: 4 columns c4*4.., rows rsub + 4*it
+    int staged_q = -1;
+    uint32_t acc_phase = 0;
+    int ti = 0;
+    const bool st0 = (warp == 2 && lane == 0);
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
+      const int cta_row0 = tile * TILE_M + (int)rank * BLOCK_M;
+      const int slab_row0 = cta_row0 + quarter * 32;
+      const int rows_live = M - slab_row0;                 // rows of this warp's 32-row slab that exist (may be <= 0)
+      // ---- per-column vectors of the (at most two) batch elements this CTA's 128 rows touch
+      const int q0 = cta_row0 / ep.rows_per_batch;
+      const int split = (q0 + 1) * ep.rows_per_batch - cta_row0;        // rows >= split belong to the next batch element
+      if (q0 != staged_q) {
+        named_bar_sync(5, 32 * NUM_EPI_WARPS);                          // everyone is done with the previous vectors
+        const int b0 = q0 % ep.nbatch, b1 = (q0 + 1) % ep.nbatch;
+        for (int i = et; i < NVEC * (LN_N / 4); i += 32 * NUM_EPI_WARPS) {
+          const int v = i / (LN_N / 4), cc = (i % (LN_N / 4)) * 4;
+          float4 val;
+          if (v == 0) {
+            val = ep.bias ? __ldg(reinterpret_cast<const float4*>(ep.bias + cc)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          } else if (v <= 2) {
+            val = ep.gate ? __ldg(reinterpret_cast<const float4*>(ep.gate + (size_t)(v == 1 ? b0 : b1) * ep.gate_stride + cc))
+                          : make_float4(1.f, 1.f, 1.f, 1.f);
+          } else if (v <= 4) {
+            val = __ldg(reinterpret_cast<const float4*>(ln.scale + (size_t)(v == 3 ? b0 : b1) * ep.gate_stride + cc));
+            val = make_float4(1.f + val.x, 1.f + val.y, 1.f + val.z, 1.f + val.w);
+          } else {
+            val = __ldg(reinterpret_cast<const float4*>(ln.shift + (size_t)(v == 5 ? b0 : b1) * ep.gate_stride + cc));
+          }
+          *reinterpret_cast<float4*>(cv + v * LN_N + cc) = val;
+        }
+        named_bar_sync(5, 32 * NUM_EPI_WARPS);
+        staged_q = q0;
+      }
+      const int sel = row_in_cta < split ? 0 : 1;
+      const float* cbias = cv + col0;
+      const float* cgate = cv + (1 + sel) * LN_N + col0;
+      const float* cmul = cv + (3 + sel) * LN_N + col0;
+      const float* cadd = cv + (5 + sel) * LN_N + col0;
+      // transposed-phase pointers: this lane's first row / 4 columns of chunk 0
+      float* xt = ep.resid + (size_t)(slab_row0 + rsub) * ep.ldr + col0 + c4 * 4;
+      const size_t xstep = (size_t)4 * ep.ldr;
+      // the first two chunks of x are in flight while the MMAs finish; each chunk then prefetches two chunks ahead
+      float4 xv[2][8];
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+          xv[u][it] = (it * 4 + rsub < rows_live) ? *reinterpret_cast<const float4*>(xt + u * 32 + it * xstep)
+                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (st0) stamp(ep, ti, 2);
+      mbar_wait(tmem_full, acc_phase);
+      tcgen05_fence_after();
+      if (st0) stamp(ep, ti, 3);
+      // ---- pass 1: residual update, row sum, x_new back into TMEM and out to global
+      float sum = 0.f;
+#pragma unroll 1
+      for (int c2 = 0; c2 < CH; c2 += 2) {
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int c = c2 + u;
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(trow + col0 + c * 32, r);
+          // x: coalesced registers -> staging (transposed) -> this thread's row
+#pragma unroll
+          for (int it = 0; it < 8; ++it) *reinterpret_cast<float4*>(stg + (it * 4 + rsub) * STG_PITCH + c4 * 16) = xv[u][it];
+          __syncwarp();
+          if (c + 2 < CH) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+              xv[u][it] = (it * 4 + rsub < rows_live) ? *reinterpret_cast<const float4*>(xt + (c + 2) * 32 + it * xstep)
+                                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          float4 xr[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) xr[j] = *reinterpret_cast<const float4*>(stg + lane * STG_PITCH + j * 16);
+          float4 bb[8], gg[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            bb[j] = *reinterpret_cast<const float4*>(cbias + c * 32 + j * 4);
+            gg[j] = *reinterpret_cast<const float4*>(cgate + c * 32 + j * 4);
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float o0 = fmaf(gg[j].x, __uint_as_float(r[4 * j]) + bb[j].x, xr[j].x);
+            const float o1 = fmaf(gg[j].y, __uint_as_float(r[4 * j + 1]) + bb[j].y, xr[j].y);
+            const float o2 = fmaf(gg[j].z, __uint_as_float(r[4 * j + 2]) + bb[j].z, xr[j].z);
+            const float o3 = fmaf(gg[j].w, __uint_as_float(r[4 * j + 3]) + bb[j].w, xr[j].w);
+            sum += (o0 + o1) + (o2 + o3);
+            r[4 * j] = __float_as_uint(o0);
+            r[4 * j + 1] = __float_as_uint(o1);
+            r[4 * j + 2] = __float_as_uint(o2);
+            r[4 * j + 3] = __float_as_uint(o3);
+          }
+          tmem_st_32x32b_x32(trow + col0 + c * 32, r);
+          // x_new: this thread's row -> staging -> coalesced global stores (everyone has read its x row above)
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(stg + lane * STG_PITCH + j * 16) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+          __syncwarp();
+          float4 xo[8];
+#pragma unroll
+          for (int it = 0; it < 8; ++it) xo[it] = *reinterpret_cast<const float4*>(stg + (it * 4 + rsub) * STG_PITCH + c4 * 16);
+          if (rows_live >= 32) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) *reinterpret_cast<float4*>(xt + c * 32 + it * xstep) = xo[it];
+          } else {
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+              if (it * 4 + rsub < rows_live) *reinterpret_cast<float4*>(xt + c * 32 + it * xstep) = xo[it];
+          }
+          __syncwarp();
+        }
+      }
+      tmem_st_wait();
+      if (st0) stamp(ep, ti, 4);
+      stats[half * 128 + row_in_cta] = sum;
+      named_bar_sync(1 + quarter, 64);
+      const float mean = (sum + stats[(half ^ 1) * 128 + row_in_cta]) * (1.0f / LN_N);
+      named_bar_sync(1 + quarter, 64);                      // both partial sums consumed before the slots are reused
+      // ---- pass 2: centred second moment
+      float sq = 0.f;
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32b_x32(trow + col0, ra);
+#pragma unroll 1
+        for (int c = 0; c < CH; c += 2) {
+          tmem_ld_wait();
+          tmem_ld_32x32b_x32(trow + col0 + (c + 1) * 32, rb);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float d = __uint_as_float(ra[j]) - mean;
+            sq = fmaf(d, d, sq);
+          }
+          tmem_ld_wait();
+          if (c + 2 < CH) tmem_ld_32x32b_x32(trow + col0 + (c + 2) * 32, ra);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float d = __uint_as_float(rb[j]) - mean;
+            sq = fmaf(d, d, sq);
+          }
+        }
+      }
+      if (st0) stamp(ep, ti, 5);
+      stats2[half * 128 + row_in_cta] = sq;
+      named_bar_sync(1 + quarter, 64);
+      const float rstd = rsqrtf((sq + stats2[(half ^ 1) * 128 + row_in_cta]) * (1.0f / LN_N) + ln.eps);
+      // ---- pass 3: normalise + modulate -> bf16 -> staging -> coalesced h (lane = 16-byte piece of rows p8 + 8*it)
+      // two chunks (64 columns = one 128-byte bf16 row segment) per staging round
+      auto pack_h = [&](int c, int pbase, const uint32_t (&r)[32]) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t pk[4];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const float4 mu = *reinterpret_cast<const float4*>(cmul + c * 32 + j * 8 + e * 4);
+            const float4 ad = *reinterpret_cast<const float4*>(cadd + c * 32 + j * 8 + e * 4);
+            const float y0 = fmaf((__uint_as_float(r[8 * j + 4 * e]) - mean) * rstd, mu.x, ad.x);
+            const float y1 = fmaf((__uint_as_float(r[8 * j + 4 * e + 1]) - mean) * rstd, mu.y, ad.y);
+            const float y2 = fmaf((__uint_as_float(r[8 * j + 4 * e + 2]) - mean) * rstd, mu.z, ad.z);
+            const float y3 = fmaf((__uint_as_float(r[8 * j + 4 * e + 3]) - mean) * rstd, mu.w, ad.w);
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
+            pk[2 * e] = *reinterpret_cast<const uint32_t*>(&lo);
+            pk[2 * e + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+          }
+          *reinterpret_cast<uint4*>(stg + lane * STG_PITCH + (pbase + j) * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
+      };
+      bf16* ht8 = ln.out + (size_t)(slab_row0 + rsub) * LN_N + col0 + c4 * 8;     // lane = 16-byte piece c4 of rows rsub + 4*it
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32b_x32(trow + col0, ra);
+        tmem_ld_32x32b_x32(trow + col0 + 32, rb);
+#pragma unroll 1
+        for (int c = 0; c < CH; c += 2) {
+          tmem_ld_wait();
+          pack_h(c, 0, ra);
+          pack_h(c + 1, 4, rb);
+          if (c + 2 < CH) {
+            tmem_ld_32x32b_x32(trow + col0 + (c + 2) * 32, ra);
+            tmem_ld_32x32b_x32(trow + col0 + (c + 3) * 32, rb);
+          } else {                                            // every accumulator column has been read: free the stage
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(te);
+          }
+          __syncwarp();
+          uint4 hv[8];
+#pragma unroll
+          for (int it = 0; it < 8; ++it) hv[it] = *reinterpret_cast<const uint4*>(stg + (it * 4 + rsub) * STG_PITCH + c4 * 16);
+          if (rows_live >= 32) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) *reinterpret_cast<uint4*>(ht8 + c * 32 + (size_t)it * 4 * LN_N) = hv[it];
+          } else {
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+              if (it * 4 + rsub < rows_live) *reinterpret_cast<uint4*>(ht8 + c * 32 + (size_t)it * 4 * LN_N) = hv[it];
+          }
+          __syncwarp();
+        }
+      }
+      if (st0) stamp(ep, ti, 6);
+      acc_phase ^= 1;
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
+}  // namespace tcln
+}  // namespace mdgen

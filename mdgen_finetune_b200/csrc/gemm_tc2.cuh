@@ -77,6 +77,13 @@ __device__ __forceinline__ void tcgen05_commit_pair(uint64_t* bar) {
 __device__ __forceinline__ void stamp(const EpiParams& ep, int tile_i, int slot) {
   if (ep.dbg && (int)blockIdx.x == ep.dbg_cta && tile_i < 16) ep.dbg[tile_i * 16 + slot] = clock64();
 }
+__device__ __forceinline__ void stamp_ns(const EpiParams& ep, int tile_i, int slot) {     // wall clock (globaltimer)
+  if (ep.dbg && (int)blockIdx.x == ep.dbg_cta) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    ep.dbg[tile_i * 16 + slot] = (long long)t;
+  }
+}
 
 template <int EPI, typename OT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
@@ -97,6 +104,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
   uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) { stamp(ep, 15, 0); stamp_ns(ep, 15, 3); }      // kernel entry
+  if (threadIdx.x == 0 && ep.dbg) {       // every CTA: wall-clock entry (exit below) at dbg[256 + 2 * blockIdx.x]
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    ep.dbg[256 + 2 * blockIdx.x] = (long long)t;
+  }
   const uint32_t rank = cluster_ctarank();
   const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
   const int num_m = (M + TILE_M - 1) / TILE_M, num_n = (N + TILE_N - 1) / TILE_N;
@@ -135,6 +148,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
   cluster_sync_all();       // the peer's barriers are initialised before anything is signalled across the pair
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
+  if (threadIdx.x == 0) stamp(ep, 15, 1);      // setup done
 
   if (warp == 0) {
     // ===== TMA producer: own 128 rows of A, own half of the W tile =====
@@ -277,6 +291,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
   tcgen05_fence_before();
   __syncthreads();
   cluster_sync_all();       // the peer's shared memory and barriers stay valid until both CTAs are done
+  if (threadIdx.x == 0) { stamp(ep, 15, 2); stamp_ns(ep, 15, 4); }      // kernel exit
+  if (threadIdx.x == 0 && ep.dbg) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    ep.dbg[256 + 2 * blockIdx.x + 1] = (long long)t;
+  }
   if (warp == 1) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");

@@ -19,6 +19,7 @@
 #include "gemm_simt.cuh"
 #include "gemm_tc.cuh"
 #include "gemm_tc2.cuh"
+#include "gemm_ln.cuh"
 #include "ipa.cuh"
 
 namespace mdgen {
@@ -139,6 +140,37 @@ static int launch_tc2(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N
   }
   set_error("launch_gemm_tc: epilogue not available in the CTA-pair kernel");
   return -1;
+}
+
+// out_proj / fc2 fused with the residual update and the next block's LayerNorm + modulate (gemm_ln.cuh).
+// Returns 1 when the shape / alignment is not supported (caller falls back to GEMM + stand-alone LayerNorm).
+int launch_gemm_resid_ln(const bf16* A, int lda, const bf16* W, int ldw, int M, int N, int K, const EpiParams& ep,
+                         const tcln::LnFuse& ln, cudaStream_t st) {
+  auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
+  if (getenv("MDGEN_NO_GEMM_LN")) return 1;
+  if (N != tcln::LN_N || K % tc::BLOCK_K != 0 || M < tcln::TILE_M || ep.rows_per_batch < tc::BLOCK_M) return 1;
+  if (!al16(ep.resid) || ep.ldr % 4 != 0 || (ep.bias && !al16(ep.bias)) || (ep.gate && !al16(ep.gate)) || ep.gate_stride % 4 != 0 ||
+      !al16(ln.shift) || !al16(ln.scale) || !al16(ln.out))
+    return 1;
+  static bool configured = false;
+  if (!configured) {
+    MD_CUDA(cudaFuncSetAttribute(tcln::gemm_ln_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcln::SMEM_BYTES));
+    configured = true;
+  }
+  CUtensorMap ta, tw1, tw2;
+  MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
+  MD_TRY(make_tmap_2d(&tw1, W, N, K, ldw, tcln::W1_ROWS));
+  MD_TRY(make_tmap_2d(&tw2, W, N, K, ldw, tcln::W2_ROWS));
+  const int tiles = (M + tcln::TILE_M - 1) / tcln::TILE_M, pairs = num_sms() / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  ProfScope ps(PC_GEMM_TC, st);
+  EpiParams epp = ep;
+  epp.dbg = g_dbg_buf;
+  epp.dbg_cta = g_dbg_cta;
+  tcln::gemm_ln_kernel<<<grid, tc::NUM_THREADS, tcln::SMEM_BYTES, st>>>(ta, tw1, tw2, M, K, epp, ln);
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return 0;
 }
 
 template <int BN>
@@ -710,6 +742,29 @@ struct Fwd {
   MdgenHandle* h;
   cudaStream_t st;
   int C, H, hd;
+  bool h_ready = false;   // hbuf already holds modulate(LN(x)) for the next block (written by the fused projection epilogue)
+
+  // x += gate * (A . W^T + b); when the next block's adaLN rows are known and the shape allows, the same kernel also
+  // writes that block's modulate(LN(x)) into hbuf (gemm_ln.cuh) and the block skips its stand-alone LayerNorm.
+  int resid_gemm(const AT* A, int lda, const LinearW& w, int M, EpiParams ep, const float* nshift, const float* nscale) {
+    h_ready = false;
+    if constexpr (sizeof(AT) == 2) {
+      if (nshift && nscale && ep.resid == h->xres) {
+        ep.bias = w.b;
+        tcln::LnFuse ln;
+        ln.out = (bf16*)h->hbuf;
+        ln.shift = nshift;
+        ln.scale = nscale;
+        ln.eps = 1e-6f;
+        const int r = launch_gemm_resid_ln((const bf16*)A, lda, w.wb, w.K, M, w.N, w.K, ep, ln, st);
+        if (r <= 0) {
+          h_ready = (r == 0);
+          return r;
+        }
+      }
+    }
+    return gemm(A, lda, w, M, EPI_GATE_RESID, ep, false);
+  }
 
   // y = A . W^T with epilogue; A is the AT activation buffer
   int gemm(const AT* A, int lda, const LinearW& w, int M, int epi, EpiParams ep, bool out_act) {
@@ -757,11 +812,12 @@ struct Fwd {
   }
   // x += gate * MHA(modulate(LN(x)))      (latent_model.py:384-387, 466-486)
   int attn_block(float* x, int M, const MhaW& m, const float* ada_row, int chunk0, int rows_per_batch, int nbatch,
-                 int nb, int S, int inner, const float* key_valid, int mask_mod, bool frame_axis) {
+                 int nb, int S, int inner, const float* key_valid, int mask_mod, bool frame_axis,
+                 const float* nshift = nullptr, const float* nscale = nullptr) {
     const float* shift = ada_row + (size_t)chunk0 * C;
     const float* scale = ada_row + (size_t)(chunk0 + 1) * C;
     const float* gate = ada_row + (size_t)(chunk0 + 2) * C;
-    MD_TRY(lnmod(x, (AT*)h->hbuf, M, shift, scale, rows_per_batch, nbatch));
+    if (!h_ready) MD_TRY(lnmod(x, (AT*)h->hbuf, M, shift, scale, rows_per_batch, nbatch));
     EpiParams e1;
     e1.out = h->qkv;
     e1.ldo = 3 * C;
@@ -774,15 +830,15 @@ struct Fwd {
     e2.gate_stride = h->ada_cols;
     e2.rows_per_batch = rows_per_batch;
     e2.nbatch = nbatch;
-    return gemm((const AT*)h->att, C, m.out, M, EPI_GATE_RESID, e2, false);
+    return resid_gemm((const AT*)h->att, C, m.out, M, e2, nshift, nscale);
   }
   // x += gate * fc2(gelu(fc1(modulate(LN(x)))))   (latent_model.py:389-392, 488-491)
   int mlp_block(float* x, int M, const LinearW& fc1, const LinearW& fc2, const float* ada_row, int chunk0,
-                int rows_per_batch, int nbatch) {
+                int rows_per_batch, int nbatch, const float* nshift = nullptr, const float* nscale = nullptr) {
     const float* shift = ada_row + (size_t)chunk0 * C;
     const float* scale = ada_row + (size_t)(chunk0 + 1) * C;
     const float* gate = ada_row + (size_t)(chunk0 + 2) * C;
-    MD_TRY(lnmod(x, (AT*)h->hbuf, M, shift, scale, rows_per_batch, nbatch));
+    if (!h_ready) MD_TRY(lnmod(x, (AT*)h->hbuf, M, shift, scale, rows_per_batch, nbatch));
     EpiParams e1;
     e1.out = h->mlp;
     e1.ldo = fc1.N;
@@ -794,7 +850,7 @@ struct Fwd {
     e2.gate_stride = h->ada_cols;
     e2.rows_per_batch = rows_per_batch;
     e2.nbatch = nbatch;
-    return gemm((const AT*)h->mlp, fc1.N, fc2, M, EPI_GATE_RESID, e2, false);
+    return resid_gemm((const AT*)h->mlp, fc1.N, fc2, M, e2, nshift, nscale);
   }
 };
 
@@ -977,15 +1033,18 @@ static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state,
   for (size_t i = 0; i < h->layers.size(); ++i) {
     const MainLayerW& Lw = h->layers[i];
     const float* ada_row = ada + Lw.ada_off;
-    MD_TRY(f.attn_block(h->xres, N, Lw.mha_l, ada_row, 0, T * L, B, B * T, L, 1, h->mask, N, false));
-    MD_TRY(f.attn_block(h->xres, N, Lw.mha_t, ada_row, 3, T * L, B, B * L, T, L, h->mask, N, true));
-    MD_TRY(f.mlp_block(h->xres, N, Lw.fc1, Lw.fc2, ada_row, 6, T * L, B));
+    // the LayerNorm after this layer's MLP: the next layer's first block, or the final layer's (layers.py:73)
+    const float* after = i + 1 < h->layers.size() ? ada + h->layers[i + 1].ada_off : ada + h->ada_final_off;
+    MD_TRY(f.attn_block(h->xres, N, Lw.mha_l, ada_row, 0, T * L, B, B * T, L, 1, h->mask, N, false, ada_row + 3 * C, ada_row + 4 * C));
+    MD_TRY(f.attn_block(h->xres, N, Lw.mha_t, ada_row, 3, T * L, B, B * L, T, L, h->mask, N, true, ada_row + 6 * C, ada_row + 7 * C));
+    MD_TRY(f.mlp_block(h->xres, N, Lw.fc1, Lw.fc2, ada_row, 6, T * L, B, after, after + C));
   }
   // ---- final layer (layers.py:71-75) with optional fused Euler update
   const bool design = h->flag(MDGEN_F_DESIGN);
   {
     const float* ada_row = ada + h->ada_final_off;
-    MD_TRY(f.lnmod(h->xres, (AT*)h->hbuf, N, ada_row, ada_row + C, T * L, B));
+    if (!f.h_ready) MD_TRY(f.lnmod(h->xres, (AT*)h->hbuf, N, ada_row, ada_row + C, T * L, B));
+    f.h_ready = false;
     EpiParams e;
     e.out = out;
     e.ldo = D;
@@ -1174,6 +1233,41 @@ int mdgen_forward(MdgenHandle* h, const float* x, const float* t, float* out, md
   return forward_dispatch(h, x, t, out, (cudaStream_t)stream);
 }
 
+// Keeps the fp32 residual stream (xres, 49 MB on config 3) resident in the 126 MB L2 for the duration of a call: every
+// block reads and rewrites it (LayerNorm read, out_proj / fc2 read-modify-write) while the activations in between
+// (h, qkv, mlp hidden) stream through once.  Scoped: the stream's access-policy window is cleared again on exit.
+struct L2Residency {
+  cudaStream_t st;
+  bool on = false;
+  L2Residency(cudaStream_t s, void* ptr, size_t bytes) : st(s) {
+    if (getenv("MDGEN_NO_L2_PERSIST") || !ptr || bytes == 0) return;
+    int dev = 0, max_persist = 0, max_win = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+    cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+    if (max_persist <= 0 || max_win <= 0) return;
+    const size_t carve = bytes < (size_t)max_persist ? bytes : (size_t)max_persist;
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) != cudaSuccess) {
+      cudaGetLastError();
+      return;
+    }
+    cudaStreamAttrValue v = {};
+    v.accessPolicyWindow.base_ptr = ptr;
+    v.accessPolicyWindow.num_bytes = bytes < (size_t)max_win ? bytes : (size_t)max_win;
+    v.accessPolicyWindow.hitRatio = (float)((double)carve / (double)v.accessPolicyWindow.num_bytes);
+    v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess) on = true;
+    else cudaGetLastError();
+  }
+  ~L2Residency() {
+    if (!on) return;
+    cudaStreamAttrValue v = {};
+    v.accessPolicyWindow.num_bytes = 0;
+    cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v);
+  }
+};
+
 int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, float* traj, float* out_final,
                         mdgen_stream_t stream) {
   MD_CHECK(h && x0 && out_final && num_steps >= 2, "bad argument");
@@ -1188,6 +1282,7 @@ int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, floa
   if (out_final != x0) MD_CUDA(cudaMemcpyAsync(out_final, x0, n * 4, cudaMemcpyDeviceToDevice, st));
   if (traj) MD_CUDA(cudaMemcpyAsync(traj, x0, n * 4, cudaMemcpyDeviceToDevice, st));
   MD_TRY(ensure_scratch(h, num_steps - 1));
+  L2Residency keep(st, h->xres, (size_t)h->B * h->T * h->L * h->C() * sizeof(float));
   return h->bf16_mode() ? rollout_impl<bf16>(h, out_final, num_steps, traj, st)
                         : rollout_impl<float>(h, out_final, num_steps, traj, st);
 }
@@ -1269,6 +1364,29 @@ int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float
     ep.rows_per_batch = M;
     ep.nbatch = 1;
     r = launch_gemm_tc(Ab, K, Wb, K, M, N, K, EPI_GATE_RESID, false, ep, block_n, st);
+  } else if (use_tc == 5) {
+    // fused residual + next LayerNorm/modulate (gemm_ln.cuh).  bias holds 2 * N floats: batch element b = (m / 200) % 2
+    // uses bias[b * N ..] as gate, shift and scale; the linear bias is bias[0 .. N).  Cout is [2 * M, N]: rows [0, M) are
+    // the residual stream (in / out), rows [M, 2 M) receive the normalised bf16 rows (as fp32).
+    ep.out = nullptr;
+    ep.resid = Cout;
+    ep.ldr = N;
+    ep.gate = bias;
+    ep.gate_stride = N;
+    ep.rows_per_batch = 200;
+    ep.nbatch = 2;
+    MD_CUDA(cudaMalloc((void**)&Cb, (size_t)M * N * 2));
+    tcln::LnFuse ln;
+    ln.out = Cb;
+    ln.shift = bias;
+    ln.scale = bias;
+    ln.eps = 1e-6f;
+    r = launch_gemm_resid_ln(Ab, K, Wb, K, M, N, K, ep, ln, st);
+    if (r == 1) {
+      set_error("mdgen_test_gemm: shape not supported by the fused residual + LayerNorm kernel");
+      r = MDGEN_EINVAL;
+    }
+    if (r == 0) bf16_rows_to_f32_kernel<<<(unsigned)(((size_t)M * N + 255) / 256), 256, 0, st>>>(Cb, N, Cout + (size_t)M * N, N, M, N);
   } else {
     r = launch_gemm_tc(Ab, K, Wb, K, M, N, K, EPI_STORE, false, ep, block_n, st);
   }

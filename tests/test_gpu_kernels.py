@@ -81,6 +81,29 @@ def test_gemm_tcgen05_gated_residual_epilogue(M, N, K, bn):
     assert float((C.cpu() - ref).norm() / ref.norm()) < 1e-5
 
 
+@pytest.mark.parametrize("M,K", [(256, 384), (1000, 384), (4000, 384), (4000, 1536), (20000, 384), (777, 64)])
+def test_gemm_tcgen05_fused_residual_layernorm(M, K):
+    """gemm_ln.cuh: x += gate * (A W^T + b); h = LN(x) * (1 + scale) + shift, batch element switching every 200 rows."""
+    N = 384
+    g = torch.Generator().manual_seed(M + K)
+    A, W = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5
+    vec = torch.randn(2, N, generator=g) * 0.5          # row b: gate = shift = scale of batch element b; row 0 also the bias
+    x0 = torch.randn(M, N, generator=g) * 2.0 + 0.3
+    C = torch.cat([x0, torch.zeros(M, N)]).cuda()
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    dA, dW, dv = A.cuda(), W.cuda(), vec.cuda()
+    _lib.check(_lib.lib().mdgen_test_gemm(M, N, K, _p(dA), _p(dW), _p(dv), _p(C), 5, 0, st), "test_gemm")
+    torch.cuda.synchronize()
+    b = (torch.arange(M) // 200) % 2
+    acc = A.bfloat16().double() @ W.bfloat16().double().T + vec[0].double()
+    x = x0.double() + vec[b].double() * acc
+    h = torch.nn.functional.layer_norm(x, (N,), eps=1e-6) * (1 + vec[b].double()) + vec[b].double()
+    out = C.cpu()
+    assert torch.isfinite(out).all()
+    assert float((out[:M] - x.float()).norm() / x.norm()) < 1e-5
+    assert float((out[M:] - h.float()).norm() / h.norm()) < 4e-3      # one bf16 rounding
+
+
 def _attn_ref(qkv, bk, bv, valid, nb, S, inner, H, hd, rope):
     from oracle import mdgen_oracle as O
     C = H * hd

@@ -15,17 +15,30 @@ C = torch.zeros(M, N, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 for _ in range(2):
     _lib.check(L.mdgen_test_gemm(M, N, K, p(A), p(W), p(b), p(C), mode, 256, st))
-dbg = torch.zeros(256, dtype=torch.int64, device="cuda")
+dbg = torch.zeros(1024, dtype=torch.int64, device="cuda")
 flush.zero_()
 L.mdgen_debug_set_buffer(p(dbg), cta)
+_lib.profile_begin()
 _lib.check(L.mdgen_test_gemm(M, N, K, p(A), p(W), p(b), p(C), mode, 256, st))
+prof = _lib.profile_end()
 L.mdgen_debug_set_buffer(None, 0)
 torch.cuda.synchronize()
-d = dbg.cpu().view(16, 16).tolist()
+allc = dbg.cpu()[256:256 + 2 * 148].view(148, 2)
+ent, ext = allc[:, 0], allc[:, 1]
+g0 = int(ent[ent > 0].min())
+print("CTA entry  (us after first): min %.1f median %.1f max %.1f" % (0.0, float((ent[ent > 0] - g0).double().median()) / 1e3, float((ent[ent > 0] - g0).max()) / 1e3))
+print("CTA exit   (us after first entry): min %.1f median %.1f max %.1f" % (float((ext[ext > 0] - g0).min()) / 1e3, float((ext[ext > 0] - g0).double().median()) / 1e3, float((ext[ext > 0] - g0).max()) / 1e3))
+d = dbg.cpu()[:256].view(16, 16).tolist()
+ns = d[15][4] - d[15][3]
+d[15][3] = d[15][4] = 0
 t0 = min(v for r in d for v in r if v)
+print(f"in-kernel wall time {ns / 1e3:.1f} us for {d[15][2] - d[15][0]} clk -> SM clock {(d[15][2] - d[15][0]) / ns * 1e3:.0f} MHz")
 names = ["mma top", "acc free", "kb0", "kb1", "kb2", "kb3", "kb4", "kb5", "mma issued", "epi acc ready", "epi tmem read", "epi done",
          "prod kb0 slot free", "prod issued"]
 print("tile " + " ".join(f"{n[:9]:>9s}" for n in names))
+print(f"entry {d[15][0] - t0}, setup done {d[15][1] - t0}, exit {d[15][2] - t0} clk; profile-scope kernel time:", end=" ")
+print(f"{prof['gemm_tcgen05'][0] * 1e3:.1f} us")
+d[15] = [0] * 16
 for i, r in enumerate(d):
     if not any(r):
         continue
