@@ -85,6 +85,24 @@ def oracle_time_forward(cfg_id, nfwd=3):
     return ts[len(ts) // 2], c, torch.get_num_threads()
 
 
+def ncu_traffic(category, cfg_id):
+    """DRAM bytes (read + write) per launch of the dominant kernel family from the committed `ncu --set full` capture
+    (profiles/r01/traffic_cfg<id>.json, written by tools/ncu_traffic.py); None when no capture exists for this config."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01", f"traffic_cfg{cfg_id}.json")
+    names = {"gemm_tcgen05": ("gemm_tc_kernel", "gemm_tc2_kernel", "gemm_ln_kernel"), "attention_tcgen05": ("attention_tc_kernel",),
+             "attention_short": ("attention_seq_kernel", "attention_short_kernel"), "layernorm_modulate": ("ln_modulate_kernel",)}
+    try:
+        t = json.load(open(path))
+    except (OSError, ValueError):
+        return None
+    tot = n = 0
+    for k in names.get(category, ()):
+        if k in t:
+            tot += t[k]["dram_bytes_per_launch"] * t[k]["launches"]
+            n += t[k]["launches"]
+    return tot / n if n else None
+
+
 def algorithmic_flops(c):
     """Per-category algorithmic FLOPs of ONE velocity evaluation (BASELINE.md section 3 formula)."""
     B, T, L, D = c["B"], c["T"], c["L"], c["D"]
@@ -222,7 +240,7 @@ def run_gpu(a, rank, world, local_rank):
     flop_of = {"gemm_tcgen05": fl["gemm_tcgen05"], "attention_tcgen05": fl["attention_frame"],
                "attention_simt": fl["attention_frame"], "attention_short": fl["attention_residue"]}
     roof = {"bound": "tensor", "kernel": dom, "unit": "TFLOP/s", "peak": pk["tflops"], "peak_source": pk["src"] + " (sustained cuBLAS bf16)",
-            "traffic": None}
+            "traffic": ncu_traffic(dom, a.config)}
     if dom in flop_of:
         t_ms, n = prof[dom]
         ach = flop_of[dom] * nev / (t_ms * 1e-3) / 1e12

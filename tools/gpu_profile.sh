@@ -13,4 +13,7 @@ echo "ncu launches rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:"${KREGEX:-attention_tc_kernel|gemm_tc_kernel}" -s ${KSKIP:-60} -c ${KCOUNT:-8} \
     -o gpurun_out/prof -f $CMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
+# the raw page as CSV travels back (gpurun_out is capped at 64 MiB); the report itself only when small or KEEP_REP=1
+ncu -i gpurun_out/prof.ncu-rep --page raw --csv > gpurun_out/prof_raw.csv 2>/dev/null
+if [ "${KEEP_REP:-0}" != "1" ]; then rm -f gpurun_out/prof.ncu-rep; fi
 ls -la gpurun_out
