@@ -241,6 +241,9 @@ def run_gpu(a, rank, world, local_rank):
                "attention_simt": fl["attention_frame"], "attention_short": fl["attention_residue"]}
     roof = {"bound": "tensor", "kernel": dom, "unit": "TFLOP/s", "peak": pk["tflops"], "peak_source": pk["src"] + " (sustained cuBLAS bf16)",
             "traffic": ncu_traffic(dom, a.config)}
+    if dom.startswith("attention"):
+        roof["note"] = ("head_dim 24: 96 FLOP per (query, key) pair but one ex2 -- the kernel is bounded by the MUFU unit (16 ex2/clk/SM, "
+                        "2048 clk per 4 x 128 x 64 block round; measured 2900), not by the tensor pipe; DESIGN.md section 4")
     if dom in flop_of:
         t_ms, n = prof[dom]
         ach = flop_of[dom] * nev / (t_ms * 1e-3) / 1e12

@@ -33,12 +33,15 @@ using tc2::stamp;
 constexpr int LN_N = 384, TILE_M = 256;
 constexpr int W1_ROWS = 128, W2_ROWS = 64;      // W rows staged per CTA for the N = 256 and the N = 128 MMA
 constexpr int STAGE_BYTES = A_STAGE_BYTES + (W1_ROWS + W2_ROWS) * BLOCK_K * 2;   // 40 KB
-constexpr int STAGES = 4;
+constexpr int STAGES = 3;
 constexpr int NVEC = 7;                          // bias, gate[2], 1 + scale[2], shift[2]   (two batch elements per slab)
 constexpr int CV_BYTES = NVEC * LN_N * 4;
 constexpr int STATS_BYTES = 2 * 2 * 128 * 4;     // [sum | centred square][column half][row] partial statistics
-constexpr int OFF_STG = STAGES * STAGE_BYTES + CV_BYTES + STATS_BYTES + 256;      // per-epilogue-warp 32 x 32 fp32 staging tiles
-constexpr int SMEM_BYTES = OFF_STG + NUM_EPI_WARPS * STG_BYTES + 1024;
+constexpr int EBUF_BYTES = 4096;                 // one epilogue I/O tile: 32 rows x 128 B (32 fp32 or 64 bf16 columns), SWIZZLE_128B
+constexpr int OFF_EBUF = STAGES * STAGE_BYTES;   // [8 warps][2] tiles, 1024-byte aligned (TMA swizzle atom)
+constexpr int OFF_CV = OFF_EBUF + NUM_EPI_WARPS * 2 * EBUF_BYTES;
+constexpr int OFF_BAR = OFF_CV + CV_BYTES + STATS_BYTES;
+constexpr int SMEM_BYTES = OFF_BAR + 512;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 static_assert(STAGE_BYTES % 1024 == 0, "SWIZZLE_128B tiles need 1024-byte aligned bases");
 
@@ -60,24 +63,36 @@ __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// bulk tensor store shared -> global (OOB rows are clipped by the tensor map), bulk-group completion
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(smem_u32(src)), "r"(c0),
+               "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW1,
-               const __grid_constant__ CUtensorMap tmapW2, int M, int K, EpiParams ep, LnFuse ln) {
+               const __grid_constant__ CUtensorMap tmapW2, const __grid_constant__ CUtensorMap tmapX,
+               const __grid_constant__ CUtensorMap tmapH, int M, int K, EpiParams ep, LnFuse ln) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 1023u) != 0) __trap();
-  float* cv = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES);          // [NVEC][384]
+  float* cv = reinterpret_cast<float*>(smem + OFF_CV);                        // [NVEC][384]
   float* stats = cv + NVEC * LN_N;                                            // row sums [2][128]
   float* stats2 = stats + 2 * 128;                                            // centred squares [2][128]
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + CV_BYTES + STATS_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
   uint64_t* tmem_empty = tmem_full + 1;
-  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
+  uint64_t* xbar = tmem_empty + 1;                                            // [8 warps][2] residual-tile arrival barriers
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(xbar + 2 * NUM_EPI_WARPS);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -89,12 +104,15 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapW1) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapW2) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapX) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapH) : "memory");
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(tmem_full, 1);
     mbar_init(tmem_empty, 2 * NUM_EPI_WARPS);
+    for (int i = 0; i < 2 * NUM_EPI_WARPS; ++i) mbar_init(&xbar[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -177,18 +195,32 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     const int row_in_cta = quarter * 32 + lane;
     const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
     const uint32_t te = map_to_rank(smem_u32(tmem_empty), 0);
-    uint8_t* stg = smem + OFF_STG + (warp - 2) * STG_BYTES;
+    // Global I/O of the epilogue goes through TMA: per warp two 32 x 128 B tiles in the SWIZZLE_128B layout, which a
+    // thread = row reads / writes conflict-free (16-byte chunk j of row r sits at chunk j ^ (r & 7)).  The LSU path
+    // (LDG/STG + shared-memory transposition) moved only ~25 B/clk/SM here; the bulk path needs no registers, no L1.
+    uint8_t* ebuf = smem + OFF_EBUF + (warp - 2) * 2 * EBUF_BYTES;
+    uint64_t* xb = xbar + (warp - 2) * 2;
+    const uint32_t swz = (uint32_t)(lane & 7);
+    uint8_t* myrow0 = ebuf + lane * 128;
     constexpr int CH = 6;                                  // 32-column chunks per warp
     const int col0 = half * CH * 32;
-    const int c4 = lane & 7, rsub = lane >> 3;             // transposed phase: 4 columns c4*4.., rows rsub + 4*it
     int staged_q = -1;
-    uint32_t acc_phase = 0;
+    uint32_t acc_phase = 0, xph0 = 0, xph1 = 0;
     int ti = 0;
     const bool st0 = (warp == 2 && lane == 0);
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
       const int cta_row0 = tile * TILE_M + (int)rank * BLOCK_M;
       const int slab_row0 = cta_row0 + quarter * 32;
-      const int rows_live = M - slab_row0;                 // rows of this warp's 32-row slab that exist (may be <= 0)
+      // ---- the first two residual tiles of this slab start moving now (the previous tile's stores have left the buffers)
+      if (lane == 0) {
+        bulk_wait_read<0>();
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          mbar_expect_tx(&xb[u], EBUF_BYTES);
+          tma_load_2d(&tmapX, &xb[u], ebuf + u * EBUF_BYTES, col0 + u * 32, slab_row0);
+        }
+      }
+      __syncwarp();
       // ---- per-column vectors of the (at most two) batch elements this CTA's 128 rows touch
       const int q0 = cta_row0 / ep.rows_per_batch;
       const int split = (q0 + 1) * ep.rows_per_batch - cta_row0;        // rows >= split belong to the next batch element
@@ -219,49 +251,31 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       const float* cgate = cv + (1 + sel) * LN_N + col0;
       const float* cmul = cv + (3 + sel) * LN_N + col0;
       const float* cadd = cv + (5 + sel) * LN_N + col0;
-      // transposed-phase pointers: this lane's first row / 4 columns of chunk 0
-      float* xt = ep.resid + (size_t)(slab_row0 + rsub) * ep.ldr + col0 + c4 * 4;
-      const size_t xstep = (size_t)4 * ep.ldr;
-      // the first two chunks of x are in flight while the MMAs finish; each chunk then prefetches two chunks ahead
-      float4 xv[2][8];
-#pragma unroll
-      for (int u = 0; u < 2; ++u)
-#pragma unroll
-        for (int it = 0; it < 8; ++it)
-          xv[u][it] = (it * 4 + rsub < rows_live) ? *reinterpret_cast<const float4*>(xt + u * 32 + it * xstep)
-                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
       if (st0) stamp(ep, ti, 2);
       mbar_wait(tmem_full, acc_phase);
       tcgen05_fence_after();
       if (st0) stamp(ep, ti, 3);
-      // ---- pass 1: residual update, row sum, x_new back into TMEM and out to global
+      // ---- pass 1: residual update, row sum, x_new back into TMEM and (in place in the tile) out to global
       float sum = 0.f;
 #pragma unroll 1
       for (int c2 = 0; c2 < CH; c2 += 2) {
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           const int c = c2 + u;
+          uint8_t* row = myrow0 + u * EBUF_BYTES;
           uint32_t r[32];
           tmem_ld_32x32b_x32(trow + col0 + c * 32, r);
-          // x: coalesced registers -> staging (transposed) -> this thread's row
-#pragma unroll
-          for (int it = 0; it < 8; ++it) *reinterpret_cast<float4*>(stg + (it * 4 + rsub) * STG_PITCH + c4 * 16) = xv[u][it];
-          __syncwarp();
-          if (c + 2 < CH) {
-#pragma unroll
-            for (int it = 0; it < 8; ++it)
-              xv[u][it] = (it * 4 + rsub < rows_live) ? *reinterpret_cast<const float4*>(xt + (c + 2) * 32 + it * xstep)
-                                                      : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-          float4 xr[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) xr[j] = *reinterpret_cast<const float4*>(stg + lane * STG_PITCH + j * 16);
           float4 bb[8], gg[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             bb[j] = *reinterpret_cast<const float4*>(cbias + c * 32 + j * 4);
             gg[j] = *reinterpret_cast<const float4*>(cgate + c * 32 + j * 4);
           }
+          mbar_wait(&xb[u], u ? xph1 : xph0);               // this chunk's residual tile has landed
+          if (u) xph1 ^= 1; else xph0 ^= 1;
+          float4 xr[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) xr[j] = *reinterpret_cast<const float4*>(row + ((j ^ swz) << 4));
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -274,24 +288,19 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             r[4 * j + 1] = __float_as_uint(o1);
             r[4 * j + 2] = __float_as_uint(o2);
             r[4 * j + 3] = __float_as_uint(o3);
+            *reinterpret_cast<uint4*>(row + ((j ^ swz) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
           }
           tmem_st_32x32b_x32(trow + col0 + c * 32, r);
-          // x_new: this thread's row -> staging -> coalesced global stores (everyone has read its x row above)
+          fence_async_smem();                               // this thread's row is visible to the bulk-copy engine
           __syncwarp();
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<uint4*>(stg + lane * STG_PITCH + j * 16) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-          __syncwarp();
-          float4 xo[8];
-#pragma unroll
-          for (int it = 0; it < 8; ++it) xo[it] = *reinterpret_cast<const float4*>(stg + (it * 4 + rsub) * STG_PITCH + c4 * 16);
-          if (rows_live >= 32) {
-#pragma unroll
-            for (int it = 0; it < 8; ++it) *reinterpret_cast<float4*>(xt + c * 32 + it * xstep) = xo[it];
-          } else {
-#pragma unroll
-            for (int it = 0; it < 8; ++it)
-              if (it * 4 + rsub < rows_live) *reinterpret_cast<float4*>(xt + c * 32 + it * xstep) = xo[it];
+          if (lane == 0) {
+            tma_store_2d(&tmapX, ebuf + u * EBUF_BYTES, col0 + c * 32, slab_row0);
+            bulk_commit();
+            if (c + 2 < CH) {                               // refill the tile as soon as the store has read it
+              bulk_wait_read<0>();
+              mbar_expect_tx(&xb[u], EBUF_BYTES);
+              tma_load_2d(&tmapX, &xb[u], ebuf + u * EBUF_BYTES, col0 + (c + 2) * 32, slab_row0);
+            }
           }
           __syncwarp();
         }
@@ -329,9 +338,8 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       stats2[half * 128 + row_in_cta] = sq;
       named_bar_sync(1 + quarter, 64);
       const float rstd = rsqrtf((sq + stats2[(half ^ 1) * 128 + row_in_cta]) * (1.0f / LN_N) + ln.eps);
-      // ---- pass 3: normalise + modulate -> bf16 -> staging -> coalesced h (lane = 16-byte piece of rows p8 + 8*it)
-      // two chunks (64 columns = one 128-byte bf16 row segment) per staging round
-      auto pack_h = [&](int c, int pbase, const uint32_t (&r)[32]) {
+      // ---- pass 3: normalise + modulate -> bf16 tile (64 columns = 128 B per row) -> bulk store
+      auto pack_h = [&](int c, int pbase, uint8_t* row, const uint32_t (&r)[32]) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           uint32_t pk[4];
@@ -347,19 +355,24 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             pk[2 * e] = *reinterpret_cast<const uint32_t*>(&lo);
             pk[2 * e + 1] = *reinterpret_cast<const uint32_t*>(&hi);
           }
-          *reinterpret_cast<uint4*>(stg + lane * STG_PITCH + (pbase + j) * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          *reinterpret_cast<uint4*>(row + (((uint32_t)(pbase + j) ^ swz) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
         }
       };
-      bf16* ht8 = ln.out + (size_t)(slab_row0 + rsub) * LN_N + col0 + c4 * 8;     // lane = 16-byte piece c4 of rows rsub + 4*it
       {
         uint32_t ra[32], rb[32];
         tmem_ld_32x32b_x32(trow + col0, ra);
         tmem_ld_32x32b_x32(trow + col0 + 32, rb);
 #pragma unroll 1
         for (int c = 0; c < CH; c += 2) {
+          const int u = (c >> 1) & 1;
+          uint8_t* row = myrow0 + u * EBUF_BYTES;
+          if (lane == 0) {                                    // the tile's previous store (pass 1 / pair c - 4) has been read out
+            if (c == 0) bulk_wait_read<0>(); else bulk_wait_read<1>();
+          }
+          __syncwarp();
           tmem_ld_wait();
-          pack_h(c, 0, ra);
-          pack_h(c + 1, 4, rb);
+          pack_h(c, 0, row, ra);
+          pack_h(c + 1, 4, row, rb);
           if (c + 2 < CH) {
             tmem_ld_32x32b_x32(trow + col0 + (c + 2) * 32, ra);
             tmem_ld_32x32b_x32(trow + col0 + (c + 3) * 32, rb);
@@ -368,24 +381,18 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(te);
           }
+          fence_async_smem();
           __syncwarp();
-          uint4 hv[8];
-#pragma unroll
-          for (int it = 0; it < 8; ++it) hv[it] = *reinterpret_cast<const uint4*>(stg + (it * 4 + rsub) * STG_PITCH + c4 * 16);
-          if (rows_live >= 32) {
-#pragma unroll
-            for (int it = 0; it < 8; ++it) *reinterpret_cast<uint4*>(ht8 + c * 32 + (size_t)it * 4 * LN_N) = hv[it];
-          } else {
-#pragma unroll
-            for (int it = 0; it < 8; ++it)
-              if (it * 4 + rsub < rows_live) *reinterpret_cast<uint4*>(ht8 + c * 32 + (size_t)it * 4 * LN_N) = hv[it];
+          if (lane == 0) {
+            tma_store_2d(&tmapH, ebuf + u * EBUF_BYTES, col0 + c * 32, slab_row0);
+            bulk_commit();
           }
-          __syncwarp();
         }
       }
       if (st0) stamp(ep, ti, 6);
       acc_phase ^= 1;
     }
+    if (lane == 0) bulk_wait_read<0>();                       // shared memory must outlive the last bulk stores' reads
   }
   tcgen05_fence_before();
   __syncthreads();

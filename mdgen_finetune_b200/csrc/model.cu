@@ -63,6 +63,23 @@ static int make_tmap_2d(CUtensorMap* m, const bf16* ptr, int rows, int cols, int
   return 0;
 }
 
+// generic 2-D row-major tensor map with a [box_rows, box_cols] box whose inner extent is 128 bytes (SWIZZLE_128B)
+static int make_tmap_2d_box(CUtensorMap* m, const void* ptr, CUtensorMapDataType dt, int elem_bytes, int rows, int cols, int ld,
+                            int box_cols, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  MD_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  MD_CHECK(((uintptr_t)ptr & 15) == 0 && ((size_t)ld * elem_bytes) % 16 == 0 && box_cols * elem_bytes == 128,
+           "TMA operand must be 16-byte aligned with a 128-byte inner box");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * elem_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, dt, 2, (void*)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed");
+  return 0;
+}
+
 static int g_num_sms = 0;
 int num_sms() {
   if (!g_num_sms) {
@@ -157,17 +174,19 @@ int launch_gemm_resid_ln(const bf16* A, int lda, const bf16* W, int ldw, int M, 
     MD_CUDA(cudaFuncSetAttribute(tcln::gemm_ln_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcln::SMEM_BYTES));
     configured = true;
   }
-  CUtensorMap ta, tw1, tw2;
+  CUtensorMap ta, tw1, tw2, tx, th;
   MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
   MD_TRY(make_tmap_2d(&tw1, W, N, K, ldw, tcln::W1_ROWS));
   MD_TRY(make_tmap_2d(&tw2, W, N, K, ldw, tcln::W2_ROWS));
+  MD_TRY(make_tmap_2d_box(&tx, ep.resid, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, M, N, ep.ldr, 32, 32));
+  MD_TRY(make_tmap_2d_box(&th, ln.out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, M, N, N, 64, 32));
   const int tiles = (M + tcln::TILE_M - 1) / tcln::TILE_M, pairs = num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   ProfScope ps(PC_GEMM_TC, st);
   EpiParams epp = ep;
   epp.dbg = g_dbg_buf;
   epp.dbg_cta = g_dbg_cta;
-  tcln::gemm_ln_kernel<<<grid, tc::NUM_THREADS, tcln::SMEM_BYTES, st>>>(ta, tw1, tw2, M, K, epp, ln);
+  tcln::gemm_ln_kernel<<<grid, tc::NUM_THREADS, tcln::SMEM_BYTES, st>>>(ta, tw1, tw2, tx, th, M, K, epp, ln);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
