@@ -12,7 +12,8 @@
 //   pass 1  acc -> x_new = x + gate * (acc + bias) -> global x, x_new written back over the accumulator in TMEM, row sum
 //   pass 2  sum of (x_new - mean)^2 from TMEM            (two-pass variance, like ln_modulate_kernel)
 //   pass 3  normalise, modulate, bf16 -> global h
-// (global x / h accesses are transposed through a per-warp shared-memory tile so that they are coalesced)
+// Global x / h traffic of the epilogue moves by TMA: per warp two SWIZZLE_128B tiles (residual tile in, x_new in place and
+// the bf16 h tile out through bulk tensor stores) -- the LDG/STG path reached only ~25 B/clk/SM here.
 // Row statistics of the two column halves are combined through shared memory (one named barrier per lane quarter).
 #pragma once
 #include "gemm_tc2.cuh"
@@ -63,16 +64,6 @@ __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-// bulk tensor store shared -> global (OOB rows are clipped by the tensor map), bulk-group completion
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(smem_u32(src)), "r"(c0),
-               "r"(c1)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

@@ -98,6 +98,16 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t* r) 
       : "r"(taddr));
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// bulk tensor store shared -> global (rows / columns outside the tensor are clipped by the map), bulk-group completion
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(smem_u32(src)), "r"(c0),
+               "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor):
 // start>>4 [0,14) | LBO>>4 [16,30) = 1 | SBO>>4 [32,46) = 1024>>4 (8 rows x 128 B) | version=1 [46,48)
@@ -287,6 +297,49 @@ __device__ __forceinline__ void epilogue_staged_bf16(const EpiParams& p, uint8_t
   __syncwarp();
 }
 
+// bf16 output of 64 columns x 32 rows through the bulk-copy engine: each thread (= row) packs its 128 bytes into a
+// SWIZZLE_128B tile (16-byte chunk j of row r at chunk j ^ (r & 7): conflict-free), one lane issues the tensor store.
+// No LDS / STG, no L1: the LSU path moved only ~25 B/clk/SM in these epilogues (gemm_ln.cuh measurements).
+constexpr int TMA_TILE_BYTES = 4096;
+template <int EPI>
+__device__ __forceinline__ void epilogue_tma_bf16(const CUtensorMap* mapC, uint8_t* tile, const float* sbias, int lane, int mrow0,
+                                                  int n0, uint32_t (&r)[2][32]) {
+  if (lane == 0) bulk_wait_read<0>();              // the previous store from this tile has been read out
+  __syncwarp();
+  uint8_t* row = tile + lane * 128;
+  const uint32_t swz = (uint32_t)(lane & 7);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    float4 b4[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) b4[k] = *reinterpret_cast<const float4*>(sbias + i * 32 + k * 4);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float v0 = __uint_as_float(r[i][4 * k]) + b4[k].x, v1 = __uint_as_float(r[i][4 * k + 1]) + b4[k].y;
+      float v2 = __uint_as_float(r[i][4 * k + 2]) + b4[k].z, v3 = __uint_as_float(r[i][4 * k + 3]) + b4[k].w;
+      if constexpr (EPI == EPI_GELU) {
+        v0 = gelu_erf_fast(v0);
+        v1 = gelu_erf_fast(v1);
+        v2 = gelu_erf_fast(v2);
+        v3 = gelu_erf_fast(v3);
+      }
+      const __nv_bfloat162 lo = __floats2bfloat162_rn(v0, v1), hi = __floats2bfloat162_rn(v2, v3);
+      r[i][2 * k] = *reinterpret_cast<const uint32_t*>(&lo);
+      r[i][2 * k + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      *reinterpret_cast<uint4*>(row + (((uint32_t)(i * 4 + k) ^ swz) << 4)) =
+          make_uint4(r[i][4 * k], r[i][4 * k + 1], r[i][4 * k + 2], r[i][4 * k + 3]);
+  }
+  fence_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_2d(mapC, tile, n0, mrow0);
+    bulk_commit();
+  }
+}
+
 // fp32 residual read-modify-write of 32 columns x 32 rows: x += gate * (acc + bias)   (EPI_GATE_RESID / EPI_RESID).
 // Everything the inner loops need is precomputed per tile into registers (ResidLane): kernel parameters live in
 // the constant bank and re-reading them inside the loops (LDC, long-scoreboard latency) dominated this epilogue.
@@ -395,8 +448,8 @@ __device__ __forceinline__ void epilogue_staged_resid(const ResidLane& L, const 
 // ---- the kernel ----------------------------------------------------------------------------
 template <int BN, int EPI, typename OT, int WS, int STG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW, int M, int N,
-               int K, EpiParams ep) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
+               const __grid_constant__ CUtensorMap tmapC, int M, int N, int K, EpiParams ep) {
   constexpr int STAGES = WS ? WS_STAGES : num_stages(BN);
   constexpr int STAGE_BYTES = WS ? A_STAGE_BYTES : stage_bytes(BN);
   constexpr int W_KB_BYTES = BN * BLOCK_K * 2;                 // one 64-wide K block of the weight slice
@@ -438,6 +491,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapW) : "memory");
+    if constexpr (STG == 2) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapC) : "memory");
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -535,8 +589,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     constexpr bool kResid = STG && (EPI == EPI_GATE_RESID || EPI == EPI_RESID);
     constexpr bool kBf16 = STG && (EPI == EPI_STORE || EPI == EPI_GELU) && sizeof(OT) == 2;
     static_assert(!STG || kResid || kBf16, "no staged epilogue for this combination");
-    uint8_t* stg = ring + STAGES * STAGE_BYTES + 256 + (warp - 2) * STG_BYTES;
-    float* cv = reinterpret_cast<float*>(ring + STAGES * STAGE_BYTES + 256 + NUM_EPI_WARPS * STG_BYTES + (warp - 2) * CV_BYTES_PER_WARP);
+    // STG == 2: bf16 output leaves through TMA stores from 1024-byte aligned SWIZZLE_128B tiles (64 columns per warp)
+    constexpr bool kTma = STG == 2;
+    static_assert(!kTma || (kBf16 && PER == 2), "the TMA-store epilogue is the 128-column bf16 one");
+    uint8_t* epi = ring + STAGES * STAGE_BYTES + (kTma ? 1024 : 256);
+    uint8_t* stg = epi + (warp - 2) * (kTma ? TMA_TILE_BYTES : STG_BYTES);
+    float* cv = reinterpret_cast<float*>(epi + NUM_EPI_WARPS * (kTma ? TMA_TILE_BYTES : STG_BYTES) + (warp - 2) * CV_BYTES_PER_WARP);
     const bool active = half * PER < CHUNKS;             // BN = 32: only the first column half has work
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -593,7 +651,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
         if (active && ncol0 < N) {
-          if constexpr (kBf16) {
+          if constexpr (kTma) {
+            epilogue_tma_bf16<EPI>(&tmapC, stg, cv, lane, mrow0, ncol0, r);
+          } else if constexpr (kBf16) {
             epilogue_staged_bf16<EPI, PER>(ep, stg, cv, lane, mrow0, ncol0, M, N, r);
           } else {
 #pragma unroll
@@ -608,6 +668,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         acc = 0;
         acc_phase ^= 1;
       }
+    }
+    if constexpr (kTma) {
+      if (lane == 0) bulk_wait_read<0>();       // shared memory must outlive the last bulk store's read
     }
   }
   tcgen05_fence_before();

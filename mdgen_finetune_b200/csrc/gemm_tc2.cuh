@@ -87,8 +87,8 @@ __device__ __forceinline__ void stamp_ns(const EpiParams& ep, int tile_i, int sl
 
 template <int EPI, typename OT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
-gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW, int M, int N,
-                int K, EpiParams ep) {
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
+                const __grid_constant__ CUtensorMap tmapC, int M, int N, int K, EpiParams ep) {
   constexpr bool kResid = (EPI == EPI_GATE_RESID || EPI == EPI_RESID);
   constexpr bool kBf16 = (EPI == EPI_STORE || EPI == EPI_GELU) && sizeof(OT) == 2;
   static_assert(kResid || kBf16, "gemm_tc2: only the staged epilogues exist");
@@ -127,6 +127,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapW) : "memory");
+    if constexpr (kBf16) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmapC) : "memory");
     for (int s = 0; s < STAGES2; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -217,8 +218,11 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
   } else {
     // ===== epilogue warps 2..9: TMEM lane quarter = warp % 4, column half = (warp - 2) / 4 =====
     const int quarter = warp & 3, half = (warp - 2) >> 2;
-    uint8_t* stg = smem + STAGES2 * STAGE2_BYTES + 256 + (warp - 2) * STG_BYTES;
-    float* cv = reinterpret_cast<float*>(smem + STAGES2 * STAGE2_BYTES + 256 + NUM_EPI_WARPS * STG_BYTES + (warp - 2) * CV_BYTES_PER_WARP);
+    // bf16 outputs leave through TMA stores from 1024-byte aligned SWIZZLE_128B tiles; the residual epilogue keeps its
+    // padded transposition tiles
+    uint8_t* epi = smem + STAGES2 * STAGE2_BYTES + (kBf16 ? 1024 : 256);
+    uint8_t* stg = epi + (warp - 2) * (kBf16 ? TMA_TILE_BYTES : STG_BYTES);
+    float* cv = reinterpret_cast<float*>(epi + NUM_EPI_WARPS * (kBf16 ? TMA_TILE_BYTES : STG_BYTES) + (warp - 2) * CV_BYTES_PER_WARP);
     int acc = 0;
     uint32_t acc_phase = 0;
     int mb, nb, n_cur;
@@ -261,23 +265,35 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
         mbar_wait(&tmem_full[acc], acc_phase);
         tcgen05_fence_after();
         if (warp == 2 && lane == 0) stamp(ep, i, 9);
-        // one 32-column chunk at a time, the next chunk's tcgen05.ld in flight while this one is converted and stored
-        uint32_t r[2][1][32];
-        tmem_ld_32x32b_x32(taddr, r[0][0]);
+        // 64 columns (one 128-byte bf16 row segment) per round, the next pair's tcgen05.ld in flight meanwhile
+        uint32_t ra[2][32], rb[2][32];
+        tmem_ld_32x32b_x32(taddr, ra[0]);
+        tmem_ld_32x32b_x32(taddr + 32, ra[1]);
 #pragma unroll 1
-        for (int c = 0; c < cpw; c += 2) {
-#pragma unroll
-          for (int u = 0; u < 2; ++u) {
+        for (int c = 0; c < cpw; c += 4) {
+          tmem_ld_wait();
+          if (c + 2 < cpw) {
+            tmem_ld_32x32b_x32(taddr + (c + 2) * 32, rb[0]);
+            tmem_ld_32x32b_x32(taddr + (c + 3) * 32, rb[1]);
+          } else {                                    // accumulator fully read: hand the TMEM stage back to the leader
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(te);
+            if (warp == 2 && lane == 0) stamp(ep, i, 10);
+          }
+          epilogue_tma_bf16<EPI>(&tmapC, stg, cv + c * 32, lane, mrow0, ncol0 + c * 32, ra);
+          if (c + 2 < cpw) {
             tmem_ld_wait();
-            if (c + u + 1 < cpw) {
-              tmem_ld_32x32b_x32(taddr + (c + u + 1) * 32, r[u ^ 1][0]);
-            } else {                                  // accumulator fully read: hand the TMEM stage back to the leader
+            if (c + 4 < cpw) {
+              tmem_ld_32x32b_x32(taddr + (c + 4) * 32, ra[0]);
+              tmem_ld_32x32b_x32(taddr + (c + 5) * 32, ra[1]);
+            } else {
               tcgen05_fence_before();
               __syncwarp();
               if (lane == 0) mbar_arrive_cluster(te);
               if (warp == 2 && lane == 0) stamp(ep, i, 10);
             }
-            epilogue_staged_bf16<EPI, 1>(ep, stg, cv + (c + u) * 32, lane, mrow0, ncol0 + (c + u) * 32, M, N, r[u]);
+            epilogue_tma_bf16<EPI>(&tmapC, stg, cv + (c + 2) * 32, lane, mrow0, ncol0 + (c + 2) * 32, rb);
           }
         }
       }
@@ -286,6 +302,9 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
         acc = 0;
         acc_phase ^= 1;
       }
+    }
+    if constexpr (kBf16) {
+      if (lane == 0) bulk_wait_read<0>();       // shared memory must outlive the last bulk store's read
     }
   }
   tcgen05_fence_before();

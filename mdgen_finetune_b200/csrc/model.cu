@@ -92,8 +92,8 @@ int num_sms() {
 }
 
 template <int BN, int EPI, typename OT, int WS, int STG>
-static int launch_tc_ws(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, const EpiParams& ep,
-                        cudaStream_t st) {
+static int launch_tc_ws(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K,
+                        const EpiParams& ep, cudaStream_t st) {
   static bool configured = false;
   auto kern = tc::gemm_tc_kernel<BN, EPI, OT, WS, STG>;
   constexpr int smem = WS ? tc::ws_smem_bytes(BN) : tc::smem_bytes(BN);
@@ -104,34 +104,36 @@ static int launch_tc_ws(const CUtensorMap& ta, const CUtensorMap& tw, int M, int
   int tiles = ((M + tc::BLOCK_M - 1) / tc::BLOCK_M) * ((N + BN - 1) / BN);
   int grid = tiles < num_sms() ? tiles : num_sms();
   ProfScope ps(PC_GEMM_TC, st);
-  kern<<<grid, tc::NUM_THREADS, smem, st>>>(ta, tw, M, N, K, ep);
+  kern<<<grid, tc::NUM_THREADS, smem, st>>>(ta, tw, tcm, M, N, K, ep);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
 }
 template <int BN, int EPI, typename OT>
-static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, const EpiParams& ep,
-                          cudaStream_t st) {
-  constexpr bool can_stage = BN >= 64 && ((sizeof(OT) == 2 && (EPI == EPI_STORE || EPI == EPI_GELU)) ||
-                                          EPI == EPI_GATE_RESID || EPI == EPI_RESID);
+static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K,
+                          const EpiParams& ep, cudaStream_t st) {
+  constexpr bool bf16_out = sizeof(OT) == 2 && (EPI == EPI_STORE || EPI == EPI_GELU);
+  constexpr bool can_stage = BN >= 64 && (bf16_out || EPI == EPI_GATE_RESID || EPI == EPI_RESID);
   if constexpr (can_stage) {
     if (ep.staged) {
+      // bf16 outputs of 128-wide tiles leave through TMA stores (STG = 2); residual epilogues stay on the LSU path (STG = 1)
+      constexpr int STG = (bf16_out && BN == 128) ? 2 : 1;
       // weight-stationary when the [BN, K] slice fits and every CTA gets a tile of its fixed n tile
       if constexpr (BN == 128) {
         const int num_n = (N + BN - 1) / BN, num_m = (M + tc::BLOCK_M - 1) / tc::BLOCK_M;
         if (K <= tc::WS_MAX_KB * tc::BLOCK_K && num_n <= num_sms() && num_m >= 2 && !getenv("MDGEN_NO_GEMM_WS"))
-          return launch_tc_ws<BN, EPI, OT, 1, 1>(ta, tw, M, N, K, ep, st);
+          return launch_tc_ws<BN, EPI, OT, 1, STG>(ta, tw, tcm, M, N, K, ep, st);
       }
-      return launch_tc_ws<BN, EPI, OT, 0, 1>(ta, tw, M, N, K, ep, st);
+      return launch_tc_ws<BN, EPI, OT, 0, STG>(ta, tw, tcm, M, N, K, ep, st);
     }
   }
-  return launch_tc_ws<BN, EPI, OT, 0, 0>(ta, tw, M, N, K, ep, st);
+  return launch_tc_ws<BN, EPI, OT, 0, 0>(ta, tw, tcm, M, N, K, ep, st);
 }
 
 // CTA-pair kernel (gemm_tc2.cuh): 256 x 256 tiles, one cluster of two CTAs per tile
 template <int EPI, typename OT>
-static int launch_tc2_inst(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, const EpiParams& ep,
-                           cudaStream_t st) {
+static int launch_tc2_inst(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K,
+                           const EpiParams& ep, cudaStream_t st) {
   static bool configured = false;
   auto kern = tc2::gemm_tc2_kernel<EPI, OT>;
   if (!configured) {
@@ -142,18 +144,18 @@ static int launch_tc2_inst(const CUtensorMap& ta, const CUtensorMap& tw, int M, 
   const int pairs = num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   ProfScope ps(PC_GEMM_TC, st);
-  kern<<<grid, tc::NUM_THREADS, tc2::SMEM2_BYTES, st>>>(ta, tw, M, N, K, ep);
+  kern<<<grid, tc::NUM_THREADS, tc2::SMEM2_BYTES, st>>>(ta, tw, tcm, M, N, K, ep);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
 }
-static int launch_tc2(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, int epi, const EpiParams& ep,
-                      cudaStream_t st) {
+static int launch_tc2(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K, int epi,
+                      const EpiParams& ep, cudaStream_t st) {
   switch (epi) {
-    case EPI_STORE: return launch_tc2_inst<EPI_STORE, bf16>(ta, tw, M, N, K, ep, st);
-    case EPI_GELU: return launch_tc2_inst<EPI_GELU, bf16>(ta, tw, M, N, K, ep, st);
-    case EPI_GATE_RESID: return launch_tc2_inst<EPI_GATE_RESID, float>(ta, tw, M, N, K, ep, st);
-    case EPI_RESID: return launch_tc2_inst<EPI_RESID, float>(ta, tw, M, N, K, ep, st);
+    case EPI_STORE: return launch_tc2_inst<EPI_STORE, bf16>(ta, tw, tcm, M, N, K, ep, st);
+    case EPI_GELU: return launch_tc2_inst<EPI_GELU, bf16>(ta, tw, tcm, M, N, K, ep, st);
+    case EPI_GATE_RESID: return launch_tc2_inst<EPI_GATE_RESID, float>(ta, tw, tcm, M, N, K, ep, st);
+    case EPI_RESID: return launch_tc2_inst<EPI_RESID, float>(ta, tw, tcm, M, N, K, ep, st);
   }
   set_error("launch_gemm_tc: epilogue not available in the CTA-pair kernel");
   return -1;
@@ -193,18 +195,18 @@ int launch_gemm_resid_ln(const bf16* A, int lda, const bf16* W, int ldw, int M, 
 }
 
 template <int BN>
-static int launch_tc_bn(const CUtensorMap& ta, const CUtensorMap& tw, int M, int N, int K, int epi, bool out_bf16,
-                        const EpiParams& ep, cudaStream_t st) {
+static int launch_tc_bn(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K, int epi,
+                        bool out_bf16, const EpiParams& ep, cudaStream_t st) {
   switch (epi) {
     case EPI_STORE:
-      return out_bf16 ? launch_tc_inst<BN, EPI_STORE, bf16>(ta, tw, M, N, K, ep, st)
-                      : launch_tc_inst<BN, EPI_STORE, float>(ta, tw, M, N, K, ep, st);
+      return out_bf16 ? launch_tc_inst<BN, EPI_STORE, bf16>(ta, tw, tcm, M, N, K, ep, st)
+                      : launch_tc_inst<BN, EPI_STORE, float>(ta, tw, tcm, M, N, K, ep, st);
     case EPI_GELU:
-      return out_bf16 ? launch_tc_inst<BN, EPI_GELU, bf16>(ta, tw, M, N, K, ep, st)
-                      : launch_tc_inst<BN, EPI_GELU, float>(ta, tw, M, N, K, ep, st);
-    case EPI_GATE_RESID: return launch_tc_inst<BN, EPI_GATE_RESID, float>(ta, tw, M, N, K, ep, st);
-    case EPI_RESID: return launch_tc_inst<BN, EPI_RESID, float>(ta, tw, M, N, K, ep, st);
-    case EPI_EULER: return launch_tc_inst<BN, EPI_EULER, float>(ta, tw, M, N, K, ep, st);
+      return out_bf16 ? launch_tc_inst<BN, EPI_GELU, bf16>(ta, tw, tcm, M, N, K, ep, st)
+                      : launch_tc_inst<BN, EPI_GELU, float>(ta, tw, tcm, M, N, K, ep, st);
+    case EPI_GATE_RESID: return launch_tc_inst<BN, EPI_GATE_RESID, float>(ta, tw, tcm, M, N, K, ep, st);
+    case EPI_RESID: return launch_tc_inst<BN, EPI_RESID, float>(ta, tw, tcm, M, N, K, ep, st);
+    case EPI_EULER: return launch_tc_inst<BN, EPI_EULER, float>(ta, tw, tcm, M, N, K, ep, st);
   }
   set_error("launch_gemm_tc: bad epilogue");
   return -1;
@@ -246,11 +248,14 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
   CUtensorMap ta, tw;
   MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
   MD_TRY(make_tmap_2d(&tw, W, N, K, ldw, block_n == 256 ? tc2::HALF_N : block_n));
-  if (block_n == 256) return launch_tc2(ta, tw, M, N, K, epi, epp, st);
+  CUtensorMap tcm = ta;      // output map for the TMA-store epilogues (bf16 outputs, staged); unused otherwise
+  if (epp.staged && out_bf16 && (epi == EPI_STORE || epi == EPI_GELU) && block_n >= 128)
+    MD_TRY(make_tmap_2d_box(&tcm, ep.out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, M, N, ep.ldo, 64, 32));
+  if (block_n == 256) return launch_tc2(ta, tw, tcm, M, N, K, epi, epp, st);
   switch (block_n) {
-    case 32: return launch_tc_bn<32>(ta, tw, M, N, K, epi, out_bf16, epp, st);
-    case 64: return launch_tc_bn<64>(ta, tw, M, N, K, epi, out_bf16, epp, st);
-    case 128: return launch_tc_bn<128>(ta, tw, M, N, K, epi, out_bf16, epp, st);
+    case 32: return launch_tc_bn<32>(ta, tw, tcm, M, N, K, epi, out_bf16, epp, st);
+    case 64: return launch_tc_bn<64>(ta, tw, tcm, M, N, K, epi, out_bf16, epp, st);
+    case 128: return launch_tc_bn<128>(ta, tw, tcm, M, N, K, epi, out_bf16, epp, st);
   }
   set_error("launch_gemm_tc: block_n must be 32, 64, 128 or 256 (CTA pair)");
   return -1;
