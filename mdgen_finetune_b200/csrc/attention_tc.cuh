@@ -4,11 +4,15 @@
 //
 // head_dim = 24 makes this kernel MUFU(ex2)- and TMEM-read-bound, not tensor-bound: one exp and one 4-byte
 // TMEM read per 96 MMA FLOPs; B200 does 16 ex2/clk/SM and reads TMEM at ~64-100 B/clk/SM against 8192 bf16
-// FLOP/clk/SM.  The design therefore keeps the MUFU pipe, the TMEM read port and the ALU busy AT THE SAME TIME:
-//   * one CTA = one (sequence, head, chunk of query tiles); K (RoPE'd) and V of the head are staged ONCE in
-//     shared memory as no-swizzle UMMA operands [128-key block][d group of 8][128 keys][8]; V is consumed
-//     MN-major, so no transpose is ever materialised; d is zero-padded 24 -> 32 and padding column 24 of V is
-//     set to 1, which makes O[:, 24] the softmax row sum for free.
+// FLOP/clk/SM.  The design therefore keeps the MUFU pipe, the TMEM read port and the ALU busy AT THE SAME TIME
+// and never lets them wait for operand staging:
+//   * PERSISTENT CTAs (one per SM) walk a static list of work units; a unit = one (sequence, head, group of up
+//     to four 128-query tiles).  Four PRODUCER warps stream the unit's K (RoPE'd) and V through a ring of
+//     128-key operand blocks in shared memory (no-swizzle UMMA layout [d group of 8][128 keys][8]; V is
+//     consumed MN-major, so no transpose is ever materialised) and stage the Q tiles of the NEXT unit into the
+//     second Q buffer of each warpgroup -- staging is completely hidden behind the softmax of the current unit.
+//     d is zero-padded 24 -> 32; padding column 24 of V is 1, which makes O[:, 24] the softmax row sum for free.
+//     The padding groups are written once per CTA, never restaged.
 //   * single pass over key blocks of 64: S = Q.K^T (128x64 fp32 in TMEM) -> registers in two 32-column chunks
 //     -> P = exp2(S log2e - m) as packed bf16 back into TMEM -> O += P.V with P as the TMEM A operand.
 //     Online softmax at chunk granularity with lazy rescaling: O (and the P chunk already stored for the block)
@@ -16,8 +20,9 @@
 //   * FOUR softmax warpgroups (warps 4-19; thread = query row) work on four query tiles at once with their own
 //     S / P / O TMEM columns (4 x 128 = all 512), i.e. four warps per SM sub-partition, so that one warp's MUFU
 //     phase overlaps the others' TMEM-read / max / store phases.  Lane 0 of warp w (w < 4) issues the
-//     tcgen05.mma of warpgroup w in that group's natural order (blocking mbarrier waits, no polling).
-//     Every thread helps staging K/V and the first Q tiles; later Q tiles are restaged by their own warpgroup.
+//     tcgen05.mma of warpgroup w in that group's natural order (blocking mbarrier waits, no polling) and hands
+//     ring slots / Q buffers back to the producers with tcgen05.commit.
+//   * registers follow the roles (setmaxnreg): 24 for the MMA issuers, 72 for the producers, 96 for the softmax.
 #pragma once
 #include "attention_simt.cuh"
 #include "gemm_tc.cuh"
@@ -40,22 +45,30 @@ constexpr int HD = 24, DP = 32;          // head dim and its MMA-padded width
 constexpr int QT = 128, KB = 128;        // query tile rows, rows of one staged operand block
 constexpr int SB = 64;                   // keys per MMA / softmax block (half an operand block)
 constexpr int MAX_KEYS = 1024;           // S + 1 <= 1024
-constexpr int NKB_MAX = MAX_KEYS / KB;
 constexpr int NWG = 4;                   // softmax warpgroups = query tiles in flight per CTA
-constexpr int THREADS = 128 + NWG * 128, PREP_THREADS = 96;
+constexpr int NPW = 4;                   // producer warps (thread = one key row / one query row of a block)
+constexpr int NSLOT = 10;                // K/V ring: 128-key operand blocks in flight (a 1001-key unit uses 8)
+constexpr int MMA_WARP0 = 0, SOFT_WARP0 = 4, PROD_WARP0 = 4 + 4 * NWG;
+constexpr int THREADS = 32 * (PROD_WARP0 + NPW);
+constexpr int REGS_MMA = 40, REGS_SOFT = 96, REGS_PROD = 56;
+static_assert(128 * REGS_MMA + NWG * 128 * REGS_SOFT + NPW * 32 * REGS_PROD <= THREADS * 80, "register pool (launch bound: 80 / thread)");
 constexpr int BLK_BYTES = 4 * KB * 16;   // one 128-row operand block: [4 d-groups][128 rows][8 bf16] = 8 KB
 constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups (K-major LBO / MN-major SBO)
-constexpr int OFF_K = 0, OFF_V = OFF_K + NKB_MAX * BLK_BYTES, OFF_Q = OFF_V + NKB_MAX * BLK_BYTES,
-              OFF_MASK = OFF_Q + NWG * BLK_BYTES, OFF_BAR = OFF_MASK + NKB_MAX * 4 * 4, SMEM_BYTES = OFF_BAR + 256 + 128;
+constexpr int OFF_K = 0, OFF_V = OFF_K + NSLOT * BLK_BYTES, OFF_Q = OFF_V + NSLOT * BLK_BYTES,
+              OFF_MASK = OFF_Q + 2 * NWG * BLK_BYTES, OFF_BAR = OFF_MASK + NSLOT * 4 * 4, SMEM_BYTES = OFF_BAR + 512;
+static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 constexpr uint32_t TMEM_COLS = 512;
 // per-warpgroup TMEM columns: S fp32 [64], P packed bf16 [32], O fp32 [32]
 constexpr uint32_t TM_WG = 128, TM_S = 0, TM_P = 64, TM_O = 96;
 constexpr float RESCALE_TAU = 8.0f;      // log2 units: P <= 2^8 between rescales
 
 struct Bars {
-  uint64_t s_full[NWG], s_empty[NWG], p_full[NWG], pv_done[NWG], q_ready[NWG];
+  uint64_t s_full[NWG], s_empty[NWG], p_full[NWG], pv_done[NWG];
+  uint64_t q_full[2][NWG], q_empty[2][NWG];      // per warpgroup: two Q buffers
+  uint64_t kv_full[NSLOT], kv_empty[NSLOT];      // K/V ring
   uint32_t tmem_base;
 };
+static_assert(sizeof(Bars) <= 512, "barrier block");
 
 // no-swizzle descriptor: start>>4 | LBO>>4 << 16 | SBO>>4 << 32 | version 1 << 46 | layout 0
 __device__ __forceinline__ uint64_t desc_nosw(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
@@ -126,10 +139,9 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void prep_bar() { asm volatile("bar.sync 1, %0;" ::"n"(PREP_THREADS) : "memory"); }
 
 // optional per-role cycle stamps of one CTA (tools/attn_probe.py); dbg == nullptr in production
-constexpr int DBG_SLOTS = 96;
+constexpr int DBG_SLOTS = 256;
 __device__ __forceinline__ void dbg_stamp(long long* dbg, int slot) {
   if (dbg) dbg[slot] = clock64();
 }
@@ -209,7 +221,8 @@ __device__ __forceinline__ void stage_q_row(const AttnParams<bf16>& p, const bf1
 // the P chunk already stored for this block (both in TMEM, `tP_prev` = 0 if none), then P = exp2(x log2e - m)
 // packed to bf16.
 __device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16], uint32_t tP_prev, uint32_t bits,
-                                           bool have_o, float& m_used, uint32_t tO, uint64_t* pv_done, uint32_t pv_parity) {
+                                           bool have_o, float& m_used, uint32_t tO, uint64_t* pv_done, uint32_t pv_parity,
+                                           bool no_exp = false) {
   const float LOG2E = 1.4426950408889634f;
   if (bits != 0xffffffffu) {
 #pragma unroll
@@ -252,35 +265,53 @@ __device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16]
     if (grow) m_used = mb;
   }
   const float mneg = (m_used == -INFINITY) ? 0.f : -m_used;
+  if (no_exp) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      pk[j] = pack_bf16(fmaf(__uint_as_float(x[2 * j]), LOG2E, mneg), fmaf(__uint_as_float(x[2 * j + 1]), LOG2E, mneg));
+    return;
+  }
 #pragma unroll
   for (int j = 0; j < 16; ++j)
     pk[j] = pack_bf16(ex2(fmaf(__uint_as_float(x[2 * j]), LOG2E, mneg)), ex2(fmaf(__uint_as_float(x[2 * j + 1]), LOG2E, mneg)));
 }
 
+// work unit -> (sequence, head, query range)
+struct Unit {
+  int h, ntiles, q_begin;
+  uint32_t seq_row0;
+};
+__device__ __forceinline__ Unit decode_unit(const AttnParams<bf16>& p, int unit, int chunks_per_seq) {
+  Unit u;
+  const int chunk = unit % chunks_per_seq, nbi = unit / (chunks_per_seq * p.H);
+  u.h = (unit / chunks_per_seq) % p.H;
+  u.q_begin = chunk * NWG * QT;
+  u.ntiles = (min(p.S, u.q_begin + NWG * QT) - u.q_begin + QT - 1) / QT;
+  u.seq_row0 = (uint32_t)(nbi / p.inner) * p.S * p.inner + (nbi % p.inner);   // row of key/query 0
+  return u;
+}
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
+template <bool DBG>
 __global__ void __launch_bounds__(THREADS, 1)
-attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, long long* dbg_buf, int dbg_cta) {
+attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long long* dbg_buf, int dbg_cta, int dbg_var) {
+  const int var = DBG ? dbg_var : 0;   // timing experiments (tools/attn_probe.py); results are wrong when non-zero
   // No integer round trip on this pointer: the compiler must keep seeing a shared-space address, otherwise every
   // staging access becomes a generic LD.E / ST.E (long-scoreboard latency instead of LDS / STS).
   extern __shared__ __align__(128) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 127u) != 0) __trap();     // dynamic shared memory starts at the window base (no static shared)
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
-  uint32_t* kmask = reinterpret_cast<uint32_t*>(smem + OFF_MASK);   // bit j of word w: key 32 w + j is attendable
+  uint32_t* kmask = reinterpret_cast<uint32_t*>(smem + OFF_MASK);   // [slot][4]: bit j of word w: key 32 w + j of the block is attendable
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
-  const int item = blockIdx.x;
-  long long* dbg = (dbg_buf && item == dbg_cta) ? dbg_buf : nullptr;
+  long long* dbg = (DBG && dbg_buf && (int)blockIdx.x == dbg_cta) ? dbg_buf : nullptr;
   if (tid == 0) dbg_stamp(dbg, 0);
-  const int chunk = item % chunks_per_seq, h = (item / chunks_per_seq) % p.H, nbi = item / (chunks_per_seq * p.H);
   const int C = p.H * HD, S = p.S, nkeys = S + 1;
-  const int nkb = (nkeys + KB - 1) / KB;
+  const int nkb = (nkeys + KB - 1) / KB;                     // ring blocks per unit
   const int nsb = (nkeys + SB - 1) / SB;                     // MMA / softmax blocks of 64 keys
   const int last_keys = nkeys - (nsb - 1) * SB;              // keys in the last block (1..64)
   const int last_cols = (last_keys + 15) & ~15;              // MMA N / K extent of the last block
-  const int q_begin = chunk * tiles_per_item * QT;
-  const int q_end = min(S, q_begin + tiles_per_item * QT);
-  const int ntiles = (q_end - q_begin + QT - 1) / QT;        // tile t is handled by warpgroup t % NWG in round t / NWG
-  const uint32_t seq_row0 = (uint32_t)(nbi / p.inner) * S * p.inner + (nbi % p.inner);   // row of key/query 0
-  const bf16* qkv_h = p.qkv + h * HD;
 
   if (tid == 0) {
     for (int i = 0; i < NWG; ++i) {
@@ -288,7 +319,14 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
       mbar_init(&bars->s_empty[i], 4);
       mbar_init(&bars->p_full[i], 4);
       mbar_init(&bars->pv_done[i], 1);
-      mbar_init(&bars->q_ready[i], 4);
+      for (int b = 0; b < 2; ++b) {
+        mbar_init(&bars->q_full[b][i], NPW);
+        mbar_init(&bars->q_empty[b][i], 1);
+      }
+    }
+    for (int i = 0; i < NSLOT; ++i) {
+      mbar_init(&bars->kv_full[i], NPW);
+      mbar_init(&bars->kv_empty[i], NWG);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -296,87 +334,11 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // =============================== prologue: every thread stages K / V / Q(round 0) ===============================
-  {
-    const uint32_t sV = smem_u32(smem + OFF_V);
-    // V: cp.async 16-byte pieces straight into the MN-major operand layout (rows >= S zero-filled)
-    for (int i = tid; i < nkb * KB * 3; i += THREADS) {
-      const int key = i / 3, c = i - key * 3;
-      const bool in = key < S;
-      const bf16* src = qkv_h + (size_t)(seq_row0 + (uint32_t)(in ? key : 0) * p.inner) * p.ld + 2 * C + c * 8;
-      cp_async16(sV + (key >> 7) * BLK_BYTES + c * GRP_BYTES + (key & 127) * 16, src, in ? 16u : 0u);
-    }
-    cp_async_commit();
-    if (tid == 0) dbg_stamp(dbg, 2);
-    // K: global -> registers -> RoPE -> K-major operand layout; key S = learned bias token (mha.py:265-268).
-    // Two keys per thread with every load issued before the first use; the attendable-key bit masks come
-    // from the same pass (a warp holds 32 consecutive keys).
-    {
-      uint4 g[2][3];
-      float4 cst[2][6];
-      float valid[2];
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int key = tid + u * THREADS;
-#pragma unroll
-        for (int j = 0; j < 3; ++j) g[u][j] = make_uint4(0, 0, 0, 0);
-        valid[u] = (key == S) ? 1.f : 0.f;
-        if (key < S) {
-          const uint32_t row = seq_row0 + (uint32_t)key * p.inner;
-          const uint4* src = reinterpret_cast<const uint4*>(qkv_h + (size_t)row * p.ld + C);
-#pragma unroll
-          for (int j = 0; j < 3; ++j) g[u][j] = __ldg(src + j);
-          valid[u] = __ldg(p.key_valid + row % (uint32_t)p.mask_mod);
-        }
-        if (p.cs && key <= S) {
-#pragma unroll
-          for (int j = 0; j < 3; ++j) {
-            cst[u][j] = __ldg(reinterpret_cast<const float4*>(p.cs + key * (HD / 2)) + j);
-            cst[u][3 + j] = __ldg(reinterpret_cast<const float4*>(p.sn + key * (HD / 2)) + j);
-          }
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int key = tid + u * THREADS;
-        if (key < nkb * KB) {                               // warp-uniform: nkb * KB and THREADS are multiples of 32
-          if (key == S) {
-            uint32_t* gw = reinterpret_cast<uint32_t*>(g[u]);
-#pragma unroll
-            for (int e = 0; e < HD / 2; ++e) gw[e] = pack_bf16(p.bias_k[h * HD + 2 * e], p.bias_k[h * HD + 2 * e + 1]);
-          }
-          if (p.cs && key <= S) rope_row_regs(g[u], cst[u]);
-          uint8_t* kr = smem + OFF_K + (key >> 7) * BLK_BYTES + (key & 127) * 16;
-#pragma unroll
-          for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * GRP_BYTES) = g[u][j];
-          // padding d-group (d = 24..31): zeros for K, [1, 0, ..] for V (row-sum column)
-          *reinterpret_cast<uint4*>(kr + 3 * GRP_BYTES) = make_uint4(0, 0, 0, 0);
-          *reinterpret_cast<uint4*>(smem + OFF_V + (key >> 7) * BLK_BYTES + 3 * GRP_BYTES + (key & 127) * 16) = make_uint4(0x3F80u, 0, 0, 0);
-          const uint32_t bits = __ballot_sync(0xffffffffu, valid[u] != 0.f);
-          if (lane == 0) kmask[key >> 5] = bits;
-        }
-      }
-    }
-    if (tid == 0) dbg_stamp(dbg, 3);
-    // Q tiles of round 0 (one row per thread) and the zero padding group of the Q buffers
-    if (tid < NWG * QT) {
-      const int w = tid >> 7, r = tid & 127;
-      *reinterpret_cast<uint4*>(smem + OFF_Q + w * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(0, 0, 0, 0);
-      if (w < ntiles) stage_q_row(p, qkv_h, smem + OFF_Q + w * BLK_BYTES, r, q_begin + w * QT + r, seq_row0);
-    }
-    if (tid == 0) dbg_stamp(dbg, 4);
-    cp_async_wait<0>();
-    if (tid == 0) dbg_stamp(dbg, 6);
-  }
-  __syncthreads();
-  if (tid == 0) dbg_stamp(dbg, 7);
-  // bias_v row (after the zero-filling cp.async of key S has landed)
-  if (tid < 3) {
-    uint4 v;
-    uint32_t* vw = reinterpret_cast<uint32_t*>(&v);
-#pragma unroll
-    for (int e = 0; e < 4; ++e) vw[e] = pack_bf16(p.bias_v[h * HD + tid * 8 + 2 * e], p.bias_v[h * HD + tid * 8 + 2 * e + 1]);
-    *reinterpret_cast<uint4*>(smem + OFF_V + (S >> 7) * BLK_BYTES + tid * GRP_BYTES + (S & 127) * 16) = v;
+  // padding d-group (d = 24..31) of every operand block, written once: zeros for K and Q, [1, 0, ..] for V
+  for (int i = tid; i < (2 * NSLOT + 2 * NWG) * KB; i += THREADS) {
+    const int blk = i >> 7, r = i & 127;
+    const bool is_v = blk >= NSLOT && blk < 2 * NSLOT;
+    *reinterpret_cast<uint4*>(smem + OFF_K + blk * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(is_v ? 0x3F80u : 0u, 0, 0, 0);
   }
   fence_async_smem();
   tcgen05_fence_before();
@@ -386,82 +348,108 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
   if (tid == 0) dbg_stamp(dbg, 1);
   const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V), sQ = smem_u32(smem + OFF_Q);
 
-  if (warp < NWG) {
+  if (warp < SOFT_WARP0) {
     // =============================== MMA issuers ===============================
     // Lane 0 of warp w issues every tcgen05.mma of warpgroup w, in that group's natural order: Q.K^T of block
     // k+1 as soon as the softmax warps have pulled S(k) into registers, then P.V of block k once P(k) is in TMEM.
+    setmaxnreg_dec<REGS_MMA>();
     const int w = warp;
     if (lane == 0) {
       uint32_t nq = 0, np = 0;            // blocks issued so far (barrier phases)
-      auto issue_qk = [&](int kb) {
-        mbar_wait(&bars->s_empty[w], (nq & 1) ^ 1);              // S of the previous block is in registers
-        tcgen05_fence_after();
-        const int n = (kb == nsb - 1) ? last_cols : SB;
-        const uint32_t id = idesc(QT, n, false);
-        const uint32_t d = tmem + w * TM_WG + TM_S;
-        const uint32_t qa = sQ + w * BLK_BYTES, ka = sK + (kb >> 1) * BLK_BYTES + (kb & 1) * (SB * 16);
-#pragma unroll
-        for (int j = 0; j < DP / 16; ++j)
-          umma_bf16(d, desc_nosw(qa + j * 2 * GRP_BYTES, GRP_BYTES, 128), desc_nosw(ka + j * 2 * GRP_BYTES, GRP_BYTES, 128), id, j);
-        tcgen05_commit(&bars->s_full[w]);
-        ++nq;
-      };
+      uint32_t gblk = 0, quse = 0;        // ring blocks consumed by earlier units, units this warpgroup was active in
       if (w == 0) dbg_stamp(dbg, 14);
-      int rd = 0;
-      for (int t = w; t < ntiles; t += NWG, ++rd) {
-        if (rd > 0) {
-          mbar_wait(&bars->q_ready[w], (rd - 1) & 1);            // the warpgroup has restaged its Q buffer
-          tcgen05_fence_after();
+      for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, gblk += nkb) {
+        const Unit u = decode_unit(p, unit, chunks_per_seq);
+        if (w >= u.ntiles) {              // idle warpgroup: only hands the ring slots back
+          for (int kb = 0; kb < nkb; ++kb) {
+            const uint32_t g = gblk + kb, slot = g % NSLOT;
+            mbar_wait(&bars->kv_full[slot], (g / NSLOT) & 1);
+            mbar_arrive(&bars->kv_empty[slot]);
+          }
+          continue;
         }
+        const uint32_t qbuf = quse & 1;
+        mbar_wait(&bars->q_full[qbuf][w], (quse >> 1) & 1);
+        tcgen05_fence_after();
+        const uint32_t qa = sQ + (qbuf * NWG + w) * BLK_BYTES;
+        auto issue_qk = [&](int sb) {
+          const uint32_t g = gblk + (sb >> 1), slot = g % NSLOT;
+          if ((sb & 1) == 0) mbar_wait(&bars->kv_full[slot], (g / NSLOT) & 1);   // first use of the ring block
+          mbar_wait(&bars->s_empty[w], (nq & 1) ^ 1);              // S of the previous block is in registers
+          tcgen05_fence_after();
+          const int n = (sb == nsb - 1) ? last_cols : SB;
+          const uint32_t id = idesc(QT, n, false);
+          const uint32_t d = tmem + w * TM_WG + TM_S;
+          const uint32_t ka = sK + slot * BLK_BYTES + (sb & 1) * (SB * 16);
+#pragma unroll
+          for (int j = 0; j < DP / 16; ++j)
+            if (!(var & 8) || sb == 0) umma_bf16(d, desc_nosw(qa + j * 2 * GRP_BYTES, GRP_BYTES, 128), desc_nosw(ka + j * 2 * GRP_BYTES, GRP_BYTES, 128), id, j);
+          tcgen05_commit(&bars->s_full[w]);
+          ++nq;
+          if (sb == nsb - 1) tcgen05_commit(&bars->q_empty[qbuf][w]);   // every Q.K^T of the unit retired: Q buffer is free
+        };
         issue_qk(0);
-        for (int kb = 0; kb < nsb; ++kb) {
-          if (kb + 1 < nsb) issue_qk(kb + 1);
+        for (int sb = 0; sb < nsb; ++sb) {
+          if (sb + 1 < nsb) issue_qk(sb + 1);
           mbar_wait(&bars->p_full[w], np & 1);
           tcgen05_fence_after();
-          const int n = (kb == nsb - 1) ? last_cols : SB;
+          const int n = (sb == nsb - 1) ? last_cols : SB;
           const uint32_t id = idesc(QT, DP, true);
           const uint32_t d = tmem + w * TM_WG + TM_O, pa = tmem + w * TM_WG + TM_P;
-          const uint32_t va = sV + (kb >> 1) * BLK_BYTES + (kb & 1) * (SB * 16);
+          const uint32_t g = gblk + (sb >> 1), slot = g % NSLOT;
+          const uint32_t va = sV + slot * BLK_BYTES + (sb & 1) * (SB * 16);
           for (int j = 0; j < n / 16; ++j)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
-            umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (kb == 0 && j == 0) ? 0u : 1u);
+            if (!(var & 4)) umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (sb == 0 && j == 0) ? 0u : 1u);
           tcgen05_commit(&bars->pv_done[w]);
           ++np;
+          if ((sb & 1) || sb == nsb - 1) tcgen05_commit(&bars->kv_empty[slot]);   // this warpgroup is done with the ring block
         }
+        ++quse;
       }
       if (w == 0) dbg_stamp(dbg, 15);
     }
-  } else {
+  } else if (warp < PROD_WARP0) {
     // =============================== softmax warps ===============================
-    const int w = (warp - 4) >> 2, quarter = warp & 3;
+    setmaxnreg_inc<REGS_SOFT>();
+    const int w = (warp - SOFT_WARP0) >> 2, quarter = warp & 3;
     const int r = quarter * 32 + lane;                       // query row in tile = TMEM lane
     const uint32_t tbase = tmem + w * TM_WG + ((uint32_t)(quarter * 32) << 16);
     const uint32_t tS = tbase + TM_S, tP = tbase + TM_P, tO = tbase + TM_O;
-    const bool stamp = (r == 0 && w < 2);
-    uint32_t it = 0;                                         // S blocks consumed by this warpgroup
-    for (int t = w; t < ntiles; t += NWG) {
-      const int q = q_begin + t * QT + r;
+    const bool stamp = DBG && (r == 0 && w < 2);
+    uint32_t it = 0, gblk = 0;                               // S blocks consumed by this warpgroup; ring blocks of earlier units
+    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, gblk += nkb) {
+      const Unit u = decode_unit(p, unit, chunks_per_seq);
+      if (w >= u.ntiles) continue;
+      const int q = u.q_begin + w * QT + r;
       float m_used = -INFINITY;
-      for (int kb = 0; kb < nsb; ++kb, ++it) {
-        const bool two = (kb < nsb - 1) || last_keys > 32;     // second 32-column chunk holds keys
+      for (int sb = 0; sb < nsb; ++sb, ++it) {
+        const bool two = (sb < nsb - 1) || last_keys > 32;     // second 32-column chunk holds keys
+        const uint32_t g = gblk + (sb >> 1), slot = g % NSLOT;
         uint32_t xa[32], xb[32], pk[16];
+        if ((sb & 1) == 0) mbar_wait(&bars->kv_full[slot], (g / NSLOT) & 1);   // acquire the producers' key masks
         mbar_wait(&bars->s_full[w], it & 1);
         tcgen05_fence_after();
         if (stamp && it < 16) dbg_stamp(dbg, 16 + w * 40 + 2 * it);
         tmem_ld_32x32b_x32(tS, xa);
-        if (two) tmem_ld_32x32b_x32(tS + 32, xb);
+        if (two && !(var & 2)) tmem_ld_32x32b_x32(tS + 32, xb);
         tmem_ld_wait();
+        if (var & 2) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) xb[j] = xa[j];
+        }
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->s_empty[w]);         // the next Q.K^T block may overwrite S
-        soft_chunk(xa, pk, 0u, kmask[kb * 2], kb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1);
-        if (it > 0) {
+        const uint2 km = *reinterpret_cast<const uint2*>(kmask + slot * 4 + (sb & 1) * 2);
+        soft_chunk(xa, pk, 0u, km.x, sb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1, var & 1);
+        if (sb > 0) {
           mbar_wait(&bars->pv_done[w], (it - 1) & 1);          // P.V of the previous block has read P
           tcgen05_fence_after();
         }
-        tmem_st_32x32b_x16(tP, pk);
+        if (!(var & 16)) tmem_st_32x32b_x16(tP, pk);
         if (two) {
-          soft_chunk(xb, pk, tP, kmask[kb * 2 + 1], kb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1);
-          tmem_st_32x32b_x16(tP + 16, pk);
+          soft_chunk(xb, pk, tP, km.y, sb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1, var & 1);
+          if (!(var & 16)) tmem_st_32x32b_x16(tP + 16, pk);
         }
         tmem_st_wait();
         tcgen05_fence_before();
@@ -469,31 +457,101 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int tiles_per_item, 
         if (lane == 0) mbar_arrive(&bars->p_full[w]);
         if (stamp && it < 16) dbg_stamp(dbg, 17 + w * 40 + 2 * it);
       }
-      // ---- next round's Q tile: every Q.K^T of this tile has completed (its last S block was consumed above),
-      // so the warpgroup restages its own buffer, one row per thread
-      if (t + NWG < ntiles) {
-        stage_q_row(p, qkv_h, smem + OFF_Q + w * BLK_BYTES, r, q + NWG * QT, seq_row0);
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->q_ready[w]);
-      }
-      // ---- epilogue: O / rowsum -> bf16 -> global
+      // ---- epilogue: O / rowsum -> bf16 -> global.  The next unit's P.V cannot start before this warpgroup has
+      // stored P of its first block, i.e. after O has been read here.
       mbar_wait(&bars->pv_done[w], (it - 1) & 1);
       tcgen05_fence_after();
       uint32_t o[32];
       tmem_ld_32x32b_x32(tO, o);
       tmem_ld_wait();
       tcgen05_fence_before();
-      if (stamp && t == w) dbg_stamp(dbg, 48 + w * 40);
+      if (stamp && unit == (int)blockIdx.x) dbg_stamp(dbg, 48 + w * 40);
       if (q < S) {
         const float inv = 1.0f / __uint_as_float(o[HD]);
-        uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(seq_row0 + (uint32_t)q * p.inner) * p.ldo + h * HD);
+        uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(u.seq_row0 + (uint32_t)q * p.inner) * p.ldo + u.h * HD);
 #pragma unroll
-        for (int g = 0; g < 3; ++g)
-          dst[g] = make_uint4(pack_bf16(__uint_as_float(o[g * 8]) * inv, __uint_as_float(o[g * 8 + 1]) * inv),
-                              pack_bf16(__uint_as_float(o[g * 8 + 2]) * inv, __uint_as_float(o[g * 8 + 3]) * inv),
-                              pack_bf16(__uint_as_float(o[g * 8 + 4]) * inv, __uint_as_float(o[g * 8 + 5]) * inv),
-                              pack_bf16(__uint_as_float(o[g * 8 + 6]) * inv, __uint_as_float(o[g * 8 + 7]) * inv));
+        for (int g2 = 0; g2 < 3; ++g2)
+          dst[g2] = make_uint4(pack_bf16(__uint_as_float(o[g2 * 8]) * inv, __uint_as_float(o[g2 * 8 + 1]) * inv),
+                               pack_bf16(__uint_as_float(o[g2 * 8 + 2]) * inv, __uint_as_float(o[g2 * 8 + 3]) * inv),
+                               pack_bf16(__uint_as_float(o[g2 * 8 + 4]) * inv, __uint_as_float(o[g2 * 8 + 5]) * inv),
+                               pack_bf16(__uint_as_float(o[g2 * 8 + 6]) * inv, __uint_as_float(o[g2 * 8 + 7]) * inv));
+      }
+    }
+  } else {
+    // =============================== producers ===============================
+    // Thread r of the 128 stages row r of every operand block: Q tiles of the unit first (into the buffer the
+    // warpgroup is not reading), then the unit's K / V blocks through the ring.
+    setmaxnreg_dec<REGS_PROD>();
+    const int r = tid - PROD_WARP0 * 32, pw = r >> 5;
+    uint32_t gblk = 0;
+    int nbatch = 0;                       // DBG: producer batches (Q tiles and K/V blocks) stamped so far
+    uint32_t quse[NWG] = {0, 0, 0, 0};
+    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+      const Unit u = decode_unit(p, unit, chunks_per_seq);
+      const bf16* qkv_h = p.qkv + u.h * HD;
+#pragma unroll
+      for (int w = 0; w < NWG; ++w) {
+        if (w < u.ntiles) {
+          const uint32_t qbuf = quse[w] & 1;
+          mbar_wait(&bars->q_empty[qbuf][w], ((quse[w] >> 1) & 1) ^ 1);
+          if (DBG && r == 0 && nbatch < 48) dbg_stamp(dbg, 96 + 2 * nbatch);
+          stage_q_row(p, qkv_h, smem + OFF_Q + (qbuf * NWG + w) * BLK_BYTES, r, u.q_begin + w * QT + r, u.seq_row0);
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars->q_full[qbuf][w]);
+          if (DBG && r == 0 && nbatch < 48) dbg_stamp(dbg, 97 + 2 * nbatch);
+          if (DBG) ++nbatch;
+          ++quse[w];
+        }
+      }
+      for (int kb = 0; kb < nkb; ++kb, ++gblk) {
+        const uint32_t slot = gblk % NSLOT;
+        mbar_wait(&bars->kv_empty[slot], ((gblk / NSLOT) & 1) ^ 1);
+        if (DBG && r == 0 && nbatch < 48) dbg_stamp(dbg, 96 + 2 * nbatch);
+        const int key = kb * KB + r;
+        const uint32_t row = u.seq_row0 + (uint32_t)(key < S ? key : 0) * p.inner;
+        const bf16* src = qkv_h + (size_t)row * p.ld;
+        // V: cp.async 16-byte pieces straight into the MN-major operand layout (rows >= S zero-filled)
+        const uint32_t vrow = sV + slot * BLK_BYTES + r * 16;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) cp_async16(vrow + c * GRP_BYTES, src + 2 * C + c * 8, key < S ? 16u : 0u);
+        cp_async_commit();
+        // K: global -> registers -> RoPE -> K-major operand layout; key S = learned bias token (mha.py:265-268)
+        uint4 g[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+        float valid = (key == S) ? 1.f : 0.f;
+        if (key < S) {
+          const uint4* ks = reinterpret_cast<const uint4*>(src + C);
+#pragma unroll
+          for (int j = 0; j < 3; ++j) g[j] = __ldg(ks + j);
+          valid = __ldg(p.key_valid + row % (uint32_t)p.mask_mod);
+        } else if (key == S) {
+          uint32_t* gw = reinterpret_cast<uint32_t*>(g);
+#pragma unroll
+          for (int e = 0; e < HD / 2; ++e) gw[e] = pack_bf16(p.bias_k[u.h * HD + 2 * e], p.bias_k[u.h * HD + 2 * e + 1]);
+        }
+        if (p.cs && key <= S) rope_row(g, p.cs + key * (HD / 2), p.sn + key * (HD / 2));
+        uint8_t* kr = smem + OFF_K + slot * BLK_BYTES + r * 16;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * GRP_BYTES) = g[j];
+        const uint32_t bits = __ballot_sync(0xffffffffu, valid != 0.f);
+        if (lane == 0) kmask[slot * 4 + pw] = bits;
+        cp_async_wait<0>();
+        if (key == S) {                   // bias_v row, after this thread's zero-filling cp.async has landed
+          uint8_t* vr = smem + OFF_V + slot * BLK_BYTES + r * 16;
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            uint4 v;
+            uint32_t* vw = reinterpret_cast<uint32_t*>(&v);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) vw[e] = pack_bf16(p.bias_v[u.h * HD + c * 8 + 2 * e], p.bias_v[u.h * HD + c * 8 + 2 * e + 1]);
+            *reinterpret_cast<uint4*>(vr + c * GRP_BYTES) = v;
+          }
+        }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->kv_full[slot]);
+        if (DBG && r == 0 && nbatch < 48) dbg_stamp(dbg, 97 + 2 * nbatch);
+        if (DBG) ++nbatch;
       }
     }
   }
@@ -519,17 +577,22 @@ inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStre
   MD_CHECK(attention_tc_supported(p, head_dim), "attention_tc: unsupported shape");
   static bool configured = false;
   if (!configured) {
-    MD_CUDA(cudaFuncSetAttribute(atc::attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    MD_CUDA(cudaFuncSetAttribute(atc::attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    MD_CUDA(cudaFuncSetAttribute(atc::attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
     configured = true;
   }
-  // query tiles per CTA: NWG are in flight at once; take two rounds (K/V staged once for 8 tiles) only while
-  // that still leaves >= 4 CTAs of work per SM
+  // work units of up to NWG query tiles; unit id = (sequence, head, chunk) with the chunk fastest, so the CTAs
+  // that share a head's K / V run side by side (second reader hits L2)
   const int qtiles = (p.S + atc::QT - 1) / atc::QT;
-  int per = 2 * atc::NWG;
-  if ((long)p.nb * p.H * ((qtiles + per - 1) / per) < 4L * num_sms()) per = atc::NWG;
-  const int chunks = (qtiles + per - 1) / per;
+  const int chunks = (qtiles + atc::NWG - 1) / atc::NWG;
+  const long nunits = (long)p.nb * p.H * chunks;
+  const int grid = (int)(nunits < num_sms() ? nunits : num_sms());
   ProfScope ps(PC_ATTN_TC, st);
-  atc::attention_tc_kernel<<<p.nb * p.H * chunks, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, per, g_dbg_buf, g_dbg_cta);
+  static const int var = getenv("MDGEN_ATTN_VAR") ? atoi(getenv("MDGEN_ATTN_VAR")) : 0;
+  if (g_dbg_buf || var)
+    atc::attention_tc_kernel<true><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, (int)nunits, g_dbg_buf, g_dbg_cta, var);
+  else
+    atc::attention_tc_kernel<false><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, (int)nunits, nullptr, 0, 0);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;

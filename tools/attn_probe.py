@@ -17,8 +17,8 @@ valid = torch.ones(nb * S).cuda()
 out = torch.empty(nb * S, C, device="cuda")
 st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 p = lambda t: ctypes.c_void_p(t.data_ptr())
-dbg = torch.zeros(96, dtype=torch.int64, device="cuda")
-cta = int(os.environ.get("DBG_CTA", "300"))
+dbg = torch.zeros(256, dtype=torch.int64, device="cuda")
+cta = int(os.environ.get("DBG_CTA", "5"))
 def run():
     _lib.check(L.mdgen_test_attention(nb, S, inner, H, hd, p(qkv), p(bk), p(bv), p(valid), p(out), 1, 1, st))
 for _ in range(3):
@@ -28,6 +28,7 @@ for _ in range(5):
     run()
 prof = _lib.profile_end()
 print({k: (round(v[0] / v[1] * 1e3, 1), v[1]) for k, v in prof.items()}, "us/launch")
+if os.environ.get("NOSTAMP"): sys.exit(0)
 L.mdgen_debug_set_buffer(p(dbg), cta)
 run()
 L.mdgen_debug_set_buffer(None, 0)
@@ -41,6 +42,9 @@ for w in range(2):
         names[17 + w * 40 + 2 * i] = f"wg{w} blk{i} P done"
     names[48 + w * 40] = f"wg{w} tile0 epilogue"
 names.update({88: "  blk4: A loaded", 89: "  blk4: chunk A done", 90: "  blk4: B loaded", 91: "  blk4: s_empty+prefetch issued", 92: "  blk4: chunk B done", 93: "  blk4: pv waited", 94: "  blk4: P stored"})
-ev = sorted((d[i] - t0, names.get(i, str(i))) for i in range(96) if d[i])
+for i in range(48):
+    names[96 + 2 * i] = f"    producer batch {i} start"
+    names[97 + 2 * i] = f"    producer batch {i} published"
+ev = sorted((d[i] - t0, names.get(i, str(i))) for i in range(256) if d[i])
 for t, n in ev:
     print(f"{t:8d} clk  {t / 1.965e3:8.2f} us  {n}")
