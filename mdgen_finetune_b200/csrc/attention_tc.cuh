@@ -1,28 +1,32 @@
-// attention_tc.cuh -- tcgen05 attention core for the long axes (frame axis T <= 1023 keys of the 4AA
-// configs, 257 / 251 keys of ATLAS).  Semantics = attention_simt.cuh (mha.py:258-397): bias-KV token as
-// key S, RoPE on q/k, key-padding -> -inf, fp32 softmax statistics, P.V.
+// attention_tc.cuh -- tcgen05 attention core for the long axes (frame axis T of the 4AA configs, 257 / 251
+// keys of ATLAS).  Semantics = attention_simt.cuh (mha.py:258-397): bias-KV token as key S, RoPE on q/k,
+// key-padding -> -inf, fp32 softmax statistics, P.V.
 //
-// head_dim = 24 makes this kernel MUFU(ex2)- and TMEM-read-bound, not tensor-bound: one exp and one 4-byte
-// TMEM read per 96 MMA FLOPs; B200 does 16 ex2/clk/SM and reads TMEM at ~64-100 B/clk/SM against 8192 bf16
-// FLOP/clk/SM.  The design therefore keeps the MUFU pipe, the TMEM read port and the ALU busy AT THE SAME TIME
-// and never lets them wait for operand staging:
+// head_dim = 24 makes this kernel exp- and issue-bound, not tensor-bound: one ex2, one FFMA, half a bf16 pack and
+// one 4-byte TMEM read per 96 MMA FLOPs.  ncu on the previous versions showed no saturated pipe (XU 54 %, issue
+// 52 %) but softmax warps waiting on each other through per-block barriers, so the design minimises instructions
+// and synchronisation per key and never lets the softmax wait for operands:
 //   * PERSISTENT CTAs (one per SM) walk a static list of work units; a unit = one (sequence, head, group of up
 //     to four 128-query tiles).  Four PRODUCER warps stream the unit's K (RoPE'd) and V through a ring of
-//     128-key operand blocks in shared memory (no-swizzle UMMA layout [d group of 8][128 keys][8]; V is
-//     consumed MN-major, so no transpose is ever materialised) and stage the Q tiles of the NEXT unit into the
-//     second Q buffer of each warpgroup -- staging is completely hidden behind the softmax of the current unit.
+//     96-key operand blocks in shared memory (no-swizzle UMMA layout [d group of 8][96 keys][8]; V is consumed
+//     MN-major, so no transpose is ever materialised) and stage the Q tiles of the NEXT unit into the second Q
+//     buffer of each warpgroup -- staging is completely hidden behind the softmax of the current unit.
 //     d is zero-padded 24 -> 32; padding column 24 of V is 1, which makes O[:, 24] the softmax row sum for free.
 //     The padding groups are written once per CTA, never restaged.
-//   * single pass over key blocks of 64: S = Q.K^T (128x64 fp32 in TMEM) -> registers in two 32-column chunks
-//     -> P = exp2(S log2e - m) as packed bf16 back into TMEM -> O += P.V with P as the TMEM A operand.
-//     Online softmax at chunk granularity with lazy rescaling: O (and the P chunk already stored for the block)
-//     are rescaled only when the running max grows by more than 2^8.
+//   * single pass over key blocks of 48: S = Q.K^T (128x48 fp32 in TMEM) is DOUBLE-BUFFERED per warpgroup
+//     (2 x 48 columns) and P = exp2(S log2e - m), packed bf16, overwrites the first 24 columns of the S buffer it
+//     came from (a thread only ever touches its own TMEM lane, so no cross-warp hazard).  O += P.V takes P as the
+//     TMEM A operand.  The tensor pipe executes one thread's MMAs in order, so the issuer simply queues
+//     P.V(j) ; Q.K^T(j+2) behind each "P(j) ready": no S-empty / P-consumed barriers exist, the softmax does ONE
+//     wait (S ready) and ONE arrive (P ready) per block and S(j+1) is computed while it works on S(j).
+//     Online softmax at block granularity with lazy rescaling: O is rescaled only when the running max grows by
+//     more than 2^8.
 //   * FOUR softmax warpgroups (warps 4-19; thread = query row) work on four query tiles at once with their own
-//     S / P / O TMEM columns (4 x 128 = all 512), i.e. four warps per SM sub-partition, so that one warp's MUFU
-//     phase overlaps the others' TMEM-read / max / store phases.  Lane 0 of warp w (w < 4) issues the
-//     tcgen05.mma of warpgroup w in that group's natural order (blocking mbarrier waits, no polling) and hands
-//     ring slots / Q buffers back to the producers with tcgen05.commit.
-//   * registers follow the roles (setmaxnreg): 24 for the MMA issuers, 72 for the producers, 96 for the softmax.
+//     S0 / S1 / O TMEM columns (4 x (48 + 48 + 32) = all 512), i.e. four warps per SM sub-partition, so that one
+//     warp's MUFU phase overlaps the others' TMEM-read / max / store phases.  Lane 0 of warp w (w < 4) issues the
+//     tcgen05.mma of warpgroup w (blocking mbarrier waits, no polling) and hands ring slots / Q buffers back to
+//     the producers with tcgen05.commit.
+//   * registers follow the roles (setmaxnreg): 40 for the MMA issuers, 56 for the producers, 96 for the softmax.
 #pragma once
 #include "attention_simt.cuh"
 #include "gemm_tc.cuh"
@@ -42,30 +46,36 @@ using tc::tmem_ld_wait;
 using tc::umma_bf16;
 
 constexpr int HD = 24, DP = 32;          // head dim and its MMA-padded width
-constexpr int QT = 128, KB = 128;        // query tile rows, rows of one staged operand block
-constexpr int SB = 64;                   // keys per MMA / softmax block (half an operand block)
-constexpr int MAX_KEYS = 1024;           // S + 1 <= 1024
+constexpr int QT = 128;                  // query tile rows
+constexpr int KB = 128;                  // rows of a Q operand block
+constexpr int SB = 48;                   // keys per MMA / softmax block
+constexpr int RB = 2 * SB;               // keys (rows) per K/V ring block
+constexpr int MAX_KEYS = 2048;           // S + 1 <= MAX_KEYS (K/V are streamed; the limit only bounds what is tested)
 constexpr int NWG = 4;                   // softmax warpgroups = query tiles in flight per CTA
 constexpr int NPW = 4;                   // producer warps (thread = one key row / one query row of a block)
-constexpr int NSLOT = 10;                // K/V ring: 128-key operand blocks in flight (a 1001-key unit uses 8)
+constexpr int NSLOT = 12;                // K/V ring blocks in flight (a 1001-key unit uses 11)
 constexpr int MMA_WARP0 = 0, SOFT_WARP0 = 4, PROD_WARP0 = 4 + 4 * NWG;
 constexpr int THREADS = 32 * (PROD_WARP0 + NPW);
 constexpr int REGS_MMA = 40, REGS_SOFT = 96, REGS_PROD = 56;
 static_assert(128 * REGS_MMA + NWG * 128 * REGS_SOFT + NPW * 32 * REGS_PROD <= THREADS * 80, "register pool (launch bound: 80 / thread)");
-constexpr int BLK_BYTES = 4 * KB * 16;   // one 128-row operand block: [4 d-groups][128 rows][8 bf16] = 8 KB
-constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups (K-major LBO / MN-major SBO)
-constexpr int OFF_K = 0, OFF_V = OFF_K + NSLOT * BLK_BYTES, OFF_Q = OFF_V + NSLOT * BLK_BYTES,
+constexpr int BLK_BYTES = 4 * KB * 16;   // Q operand block: [4 d-groups][128 rows][8 bf16] = 8 KB
+constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups of a Q block (K-major LBO)
+constexpr int RGRP_BYTES = RB * 16;      // 1536: stride between d-groups of a K/V ring block (K-major LBO / MN-major SBO)
+constexpr int RBLK_BYTES = 4 * RGRP_BYTES;   // 6 KB
+constexpr int OFF_K = 0, OFF_V = OFF_K + NSLOT * RBLK_BYTES, OFF_Q = OFF_V + NSLOT * RBLK_BYTES,
               OFF_MASK = OFF_Q + 2 * NWG * BLK_BYTES, OFF_BAR = OFF_MASK + NSLOT * 4 * 4, SMEM_BYTES = OFF_BAR + 512;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 constexpr uint32_t TMEM_COLS = 512;
-// per-warpgroup TMEM columns: S fp32 [64], P packed bf16 [32], O fp32 [32]
-constexpr uint32_t TM_WG = 128, TM_S = 0, TM_P = 64, TM_O = 96;
+// per-warpgroup TMEM columns: S0 fp32 [48], S1 fp32 [48] (P packed bf16 overwrites the first 24 of its S), O fp32 [32]
+constexpr uint32_t TM_WG = 128, TM_S = 0, TM_O = 96;
 constexpr float RESCALE_TAU = 8.0f;      // log2 units: P <= 2^8 between rescales
 
 struct Bars {
-  uint64_t s_full[NWG], s_empty[NWG], p_full[NWG], pv_done[NWG];
+  uint64_t s_full[NWG][2];    // Q.K^T of a block has landed in S buffer b (and every MMA queued before it has retired)
+  uint64_t p_full[NWG][2];    // the warpgroup has written P over S buffer b
   uint64_t q_full[2][NWG], q_empty[2][NWG];      // per warpgroup: two Q buffers
   uint64_t kv_full[NSLOT], kv_empty[NSLOT];      // K/V ring
+  uint64_t o_free[NWG];       // the warpgroup has consumed the unit's last two s_full phases: the next unit may signal again
   uint32_t tmem_base;
 };
 static_assert(sizeof(Bars) <= 512, "barrier block");
@@ -217,27 +227,36 @@ __device__ __forceinline__ void stage_q_row(const AttnParams<bf16>& p, const bf1
   for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(qb + j * GRP_BYTES + r * 16) = g[j];
 }
 
-// One 32-column chunk of scores of one query row: key mask, running-max update with lazy rescale of O and of
-// the P chunk already stored for this block (both in TMEM, `tP_prev` = 0 if none), then P = exp2(x log2e - m)
-// packed to bf16.
-__device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16], uint32_t tP_prev, uint32_t bits,
-                                           bool have_o, float& m_used, uint32_t tO, uint64_t* pv_done, uint32_t pv_parity,
-                                           bool no_exp = false) {
+__device__ __forceinline__ void tmem_st_32x32b_x8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]),
+               "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+
+// One 48-key block of scores of one query row (x[0..47], fp32 bit patterns): key mask, running-max update with
+// lazy rescale of O (in TMEM; `pv_bar` / `pv_parity` = the barrier phase that tells every P.V issued so far has
+// retired), then P = exp2(x log2e - m) packed to bf16 (pk[0..23]).
+template <bool DBG>
+__device__ __forceinline__ void soft_block(uint32_t (&x)[SB], uint32_t (&pk)[SB / 2], uint32_t mlo, uint32_t mhi, bool have_o,
+                                           float& m_used, uint32_t tO, uint64_t* pv_bar, uint32_t pv_parity, int var) {
   const float LOG2E = 1.4426950408889634f;
-  if (bits != 0xffffffffu) {
+  if ((mlo & (mhi | 0xffff0000u)) != 0xffffffffu) {       // some key of the block is padding (or beyond the last key)
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-      if (!((bits >> j) & 1u)) x[j] = 0xff800000u;   // -inf
+      if (!((mlo >> j) & 1u)) x[j] = 0xff800000u;   // -inf
+#pragma unroll
+    for (int j = 0; j < SB - 32; ++j)
+      if (!((mhi >> j) & 1u)) x[32 + j] = 0xff800000u;
   }
   float bm[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-  for (int j = 0; j < 32; j += 2) bm[(j >> 1) & 3] = max3(bm[(j >> 1) & 3], __uint_as_float(x[j]), __uint_as_float(x[j + 1]));
+  for (int j = 0; j < SB; j += 2) bm[(j >> 1) & 3] = max3(bm[(j >> 1) & 3], __uint_as_float(x[j]), __uint_as_float(x[j + 1]));
   const float mb = fmaxf(fmaxf(bm[0], bm[1]), fmaxf(bm[2], bm[3])) * LOG2E;
   const bool grow = mb > m_used + RESCALE_TAU;           // false when both are -inf
-  if (__any_sync(0xffffffffu, grow)) {                   // rare after the first chunks of a tile
+  if (__any_sync(0xffffffffu, grow)) {                   // rare after the first blocks of a tile
     const float sc = grow ? ex2(m_used - mb) : 1.0f;     // m_used = -inf -> 0 (nothing accumulated yet)
     if (have_o) {
-      mbar_wait(pv_done, pv_parity);                     // every P.V issued so far has landed in O
+      mbar_wait(pv_bar, pv_parity);                      // every P.V issued so far has landed in O
       tcgen05_fence_after();
 #pragma unroll
       for (int hh = 0; hh < 2; ++hh) {
@@ -249,30 +268,17 @@ __device__ __forceinline__ void soft_chunk(uint32_t (&x)[32], uint32_t (&pk)[16]
         tmem_st_32x32b_x16(tO + hh * 16, o);
       }
     }
-    if (tP_prev) {
-      uint32_t pp[16];
-      tmem_st_wait();                                    // the chunk was stored just before
-      tmem_ld_32x32b_x16(tP_prev, pp);
-      tmem_ld_wait();
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pp[j]));
-        pp[j] = pack_bf16(f.x * sc, f.y * sc);
-      }
-      tmem_st_32x32b_x16(tP_prev, pp);
-    }
-    tmem_st_wait();
     if (grow) m_used = mb;
   }
   const float mneg = (m_used == -INFINITY) ? 0.f : -m_used;
-  if (no_exp) {
+  if (DBG && (var & 1)) {                                // timing experiment: no MUFU
 #pragma unroll
-    for (int j = 0; j < 16; ++j)
+    for (int j = 0; j < SB / 2; ++j)
       pk[j] = pack_bf16(fmaf(__uint_as_float(x[2 * j]), LOG2E, mneg), fmaf(__uint_as_float(x[2 * j + 1]), LOG2E, mneg));
     return;
   }
 #pragma unroll
-  for (int j = 0; j < 16; ++j)
+  for (int j = 0; j < SB / 2; ++j)
     pk[j] = pack_bf16(ex2(fmaf(__uint_as_float(x[2 * j]), LOG2E, mneg)), ex2(fmaf(__uint_as_float(x[2 * j + 1]), LOG2E, mneg)));
 }
 
@@ -293,6 +299,7 @@ __device__ __forceinline__ Unit decode_unit(const AttnParams<bf16>& p, int unit,
 template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
+
 template <bool DBG>
 __global__ void __launch_bounds__(THREADS, 1)
 attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long long* dbg_buf, int dbg_cta, int dbg_var) {
@@ -303,27 +310,23 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 127u) != 0) __trap();     // dynamic shared memory starts at the window base (no static shared)
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
-  uint32_t* kmask = reinterpret_cast<uint32_t*>(smem + OFF_MASK);   // [slot][4]: bit j of word w: key 32 w + j of the block is attendable
+  uint32_t* kmask = reinterpret_cast<uint32_t*>(smem + OFF_MASK);   // [slot][4]: bit j of word w: key 32 w + j of the ring block is attendable
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
   long long* dbg = (DBG && dbg_buf && (int)blockIdx.x == dbg_cta) ? dbg_buf : nullptr;
   if (tid == 0) dbg_stamp(dbg, 0);
   const int C = p.H * HD, S = p.S, nkeys = S + 1;
-  const int nkb = (nkeys + KB - 1) / KB;                     // ring blocks per unit
-  const int nsb = (nkeys + SB - 1) / SB;                     // MMA / softmax blocks of 64 keys
-  const int last_keys = nkeys - (nsb - 1) * SB;              // keys in the last block (1..64)
-  const int last_cols = (last_keys + 15) & ~15;              // MMA N / K extent of the last block
+  const int nkb = (nkeys + RB - 1) / RB;                     // ring blocks per unit
+  const int nsb = (nkeys + SB - 1) / SB;                     // MMA / softmax blocks of 48 keys (>= 2)
 
   if (tid == 0) {
-    for (int i = 0; i < NWG; ++i) {
-      mbar_init(&bars->s_full[i], 1);
-      mbar_init(&bars->s_empty[i], 4);
-      mbar_init(&bars->p_full[i], 4);
-      mbar_init(&bars->pv_done[i], 1);
+    for (int i = 0; i < NWG; ++i)
       for (int b = 0; b < 2; ++b) {
+        mbar_init(&bars->s_full[i][b], 1);
+        mbar_init(&bars->p_full[i][b], 4);
         mbar_init(&bars->q_full[b][i], NPW);
         mbar_init(&bars->q_empty[b][i], 1);
       }
-    }
+    for (int i = 0; i < NWG; ++i) mbar_init(&bars->o_free[i], 4);
     for (int i = 0; i < NSLOT; ++i) {
       mbar_init(&bars->kv_full[i], NPW);
       mbar_init(&bars->kv_empty[i], NWG);
@@ -335,11 +338,12 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   // padding d-group (d = 24..31) of every operand block, written once: zeros for K and Q, [1, 0, ..] for V
-  for (int i = tid; i < (2 * NSLOT + 2 * NWG) * KB; i += THREADS) {
-    const int blk = i >> 7, r = i & 127;
-    const bool is_v = blk >= NSLOT && blk < 2 * NSLOT;
-    *reinterpret_cast<uint4*>(smem + OFF_K + blk * BLK_BYTES + 3 * GRP_BYTES + r * 16) = make_uint4(is_v ? 0x3F80u : 0u, 0, 0, 0);
+  for (int i = tid; i < 2 * NSLOT * RB; i += THREADS) {
+    const int blk = i / RB, r = i - blk * RB;
+    *reinterpret_cast<uint4*>(smem + OFF_K + blk * RBLK_BYTES + 3 * RGRP_BYTES + r * 16) = make_uint4(blk >= NSLOT ? 0x3F80u : 0u, 0, 0, 0);
   }
+  for (int i = tid; i < 2 * NWG * KB; i += THREADS)
+    *reinterpret_cast<uint4*>(smem + OFF_Q + (i >> 7) * BLK_BYTES + 3 * GRP_BYTES + (i & 127) * 16) = make_uint4(0, 0, 0, 0);
   fence_async_smem();
   tcgen05_fence_before();
   __syncthreads();
@@ -350,13 +354,16 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
 
   if (warp < SOFT_WARP0) {
     // =============================== MMA issuers ===============================
-    // Lane 0 of warp w issues every tcgen05.mma of warpgroup w, in that group's natural order: Q.K^T of block
-    // k+1 as soon as the softmax warps have pulled S(k) into registers, then P.V of block k once P(k) is in TMEM.
+    // Lane 0 of warp w issues every tcgen05.mma of warpgroup w.  Queue order per unit:
+    //   QK(0) QK(1) | PV(0) QK(2) | PV(1) QK(3) | ... | PV(n-2) | PV(n-1)
+    // each group behind "P(j) ready" and followed by a commit on s_full[j & 1], which therefore means both
+    // "S(j+2) has landed" and "P.V(j) and everything before it has retired".
     setmaxnreg_dec<REGS_MMA>();
     const int w = warp;
     if (lane == 0) {
-      uint32_t nq = 0, np = 0;            // blocks issued so far (barrier phases)
+      uint32_t np0 = 0, np1 = 0;          // P-ready phases consumed per S buffer
       uint32_t gblk = 0, quse = 0;        // ring blocks consumed by earlier units, units this warpgroup was active in
+      const uint32_t id_qk = idesc(QT, SB, false), id_pv = idesc(QT, DP, true);
       if (w == 0) dbg_stamp(dbg, 14);
       for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, gblk += nkb) {
         const Unit u = decode_unit(p, unit, chunks_per_seq);
@@ -369,40 +376,48 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
           continue;
         }
         const uint32_t qbuf = quse & 1;
+        // an mbarrier phase must be consumed before the barrier completes again: the softmax warps have seen the
+        // previous unit's closing s_full phases
+        if (quse > 0) mbar_wait(&bars->o_free[w], (quse - 1) & 1);
         mbar_wait(&bars->q_full[qbuf][w], (quse >> 1) & 1);
         tcgen05_fence_after();
         const uint32_t qa = sQ + (qbuf * NWG + w) * BLK_BYTES;
-        auto issue_qk = [&](int sb) {
-          const uint32_t g = gblk + (sb >> 1), slot = g % NSLOT;
-          if ((sb & 1) == 0) mbar_wait(&bars->kv_full[slot], (g / NSLOT) & 1);   // first use of the ring block
-          mbar_wait(&bars->s_empty[w], (nq & 1) ^ 1);              // S of the previous block is in registers
-          tcgen05_fence_after();
-          const int n = (sb == nsb - 1) ? last_cols : SB;
-          const uint32_t id = idesc(QT, n, false);
-          const uint32_t d = tmem + w * TM_WG + TM_S;
-          const uint32_t ka = sK + slot * BLK_BYTES + (sb & 1) * (SB * 16);
+        const uint32_t tW = tmem + w * TM_WG;
+        auto issue_qk = [&](int j) {
+          const uint32_t g = gblk + (j >> 1), slot = g % NSLOT;
+          if ((j & 1) == 0) {                                      // first use of the ring block
+            mbar_wait(&bars->kv_full[slot], (g / NSLOT) & 1);
+            tcgen05_fence_after();
+          }
+          const uint32_t ka = sK + slot * RBLK_BYTES + (j & 1) * (SB * 16);
+          if (!(var & 8) || j < 2) {
 #pragma unroll
-          for (int j = 0; j < DP / 16; ++j)
-            if (!(var & 8) || sb == 0) umma_bf16(d, desc_nosw(qa + j * 2 * GRP_BYTES, GRP_BYTES, 128), desc_nosw(ka + j * 2 * GRP_BYTES, GRP_BYTES, 128), id, j);
-          tcgen05_commit(&bars->s_full[w]);
-          ++nq;
-          if (sb == nsb - 1) tcgen05_commit(&bars->q_empty[qbuf][w]);   // every Q.K^T of the unit retired: Q buffer is free
+            for (int jj = 0; jj < DP / 16; ++jj)
+              umma_bf16(tW + TM_S + (j & 1) * SB, desc_nosw(qa + jj * 2 * GRP_BYTES, GRP_BYTES, 128),
+                        desc_nosw(ka + jj * 2 * RGRP_BYTES, RGRP_BYTES, 128), id_qk, jj);
+          }
+          if (j == nsb - 1) tcgen05_commit(&bars->q_empty[qbuf][w]);   // every Q.K^T of the unit is queued: Q buffer free when they retire
         };
         issue_qk(0);
-        for (int sb = 0; sb < nsb; ++sb) {
-          if (sb + 1 < nsb) issue_qk(sb + 1);
-          mbar_wait(&bars->p_full[w], np & 1);
+        tcgen05_commit(&bars->s_full[w][0]);
+        issue_qk(1);
+        tcgen05_commit(&bars->s_full[w][1]);
+        for (int j = 0; j < nsb; ++j) {
+          const int b = j & 1;
+          mbar_wait(&bars->p_full[w][b], (b ? np1 : np0) & 1);
+          if (b) ++np1; else ++np0;
           tcgen05_fence_after();
-          const int n = (sb == nsb - 1) ? last_cols : SB;
-          const uint32_t id = idesc(QT, DP, true);
-          const uint32_t d = tmem + w * TM_WG + TM_O, pa = tmem + w * TM_WG + TM_P;
-          const uint32_t g = gblk + (sb >> 1), slot = g % NSLOT;
-          const uint32_t va = sV + slot * BLK_BYTES + (sb & 1) * (SB * 16);
-          for (int j = 0; j < n / 16; ++j)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
-            if (!(var & 4)) umma_bf16_ts(d, pa + j * 8, desc_nosw(va + j * 256, 128, GRP_BYTES), id, (sb == 0 && j == 0) ? 0u : 1u);
-          tcgen05_commit(&bars->pv_done[w]);
-          ++np;
-          if ((sb & 1) || sb == nsb - 1) tcgen05_commit(&bars->kv_empty[slot]);   // this warpgroup is done with the ring block
+          const uint32_t g = gblk + (j >> 1), slot = g % NSLOT;
+          const uint32_t va = sV + slot * RBLK_BYTES + b * (SB * 16);
+          if (!(var & 4)) {
+#pragma unroll
+            for (int kk = 0; kk < SB / 16; ++kk)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
+              umma_bf16_ts(tW + TM_O, tW + TM_S + b * SB + kk * 8, desc_nosw(va + kk * 256, 128, RGRP_BYTES), id_pv,
+                           (j == 0 && kk == 0) ? 0u : 1u);
+          }
+          if (b || j == nsb - 1) tcgen05_commit(&bars->kv_empty[slot]);   // this warpgroup is done with the ring block
+          if (j + 2 < nsb) issue_qk(j + 2);
+          tcgen05_commit(&bars->s_full[w][b]);
         }
         ++quse;
       }
@@ -414,73 +429,86 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
     const int w = (warp - SOFT_WARP0) >> 2, quarter = warp & 3;
     const int r = quarter * 32 + lane;                       // query row in tile = TMEM lane
     const uint32_t tbase = tmem + w * TM_WG + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t tS = tbase + TM_S, tP = tbase + TM_P, tO = tbase + TM_O;
+    const uint32_t tO = tbase + TM_O;
+    uint64_t* const sfull = &bars->s_full[w][0];
+    uint64_t* const pfull = &bars->p_full[w][0];
     const bool stamp = DBG && (r == 0 && w < 2);
-    uint32_t it = 0, gblk = 0;                               // S blocks consumed by this warpgroup; ring blocks of earlier units
-    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, gblk += nkb) {
+    uint32_t sc0 = 0, sc1 = 0;                               // s_full phases consumed per S buffer
+    uint32_t rslot = 0, rpar = 0;                            // ring position of the current unit's first block
+    uint32_t it = 0;
+    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
       const Unit u = decode_unit(p, unit, chunks_per_seq);
-      if (w >= u.ntiles) continue;
-      const int q = u.q_begin + w * QT + r;
-      float m_used = -INFINITY;
-      for (int sb = 0; sb < nsb; ++sb, ++it) {
-        const bool two = (sb < nsb - 1) || last_keys > 32;     // second 32-column chunk holds keys
-        const uint32_t g = gblk + (sb >> 1), slot = g % NSLOT;
-        uint32_t xa[32], xb[32], pk[16];
-        if ((sb & 1) == 0) mbar_wait(&bars->kv_full[slot], (g / NSLOT) & 1);   // acquire the producers' key masks
-        mbar_wait(&bars->s_full[w], it & 1);
-        tcgen05_fence_after();
-        if (stamp && it < 16) dbg_stamp(dbg, 16 + w * 40 + 2 * it);
-        tmem_ld_32x32b_x32(tS, xa);
-        if (two && !(var & 2)) tmem_ld_32x32b_x32(tS + 32, xb);
-        tmem_ld_wait();
-        if (var & 2) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) xb[j] = xa[j];
-        }
-        tcgen05_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->s_empty[w]);         // the next Q.K^T block may overwrite S
-        const uint2 km = *reinterpret_cast<const uint2*>(kmask + slot * 4 + (sb & 1) * 2);
-        soft_chunk(xa, pk, 0u, km.x, sb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1, var & 1);
-        if (sb > 0) {
-          mbar_wait(&bars->pv_done[w], (it - 1) & 1);          // P.V of the previous block has read P
+      if (w < u.ntiles) {
+        const int q = u.q_begin + w * QT + r;
+        float m_used = -INFINITY;
+        uint32_t cslot = rslot, cpar = rpar;                 // ring block of the current pair of softmax blocks
+        uint32_t k0 = 0, k1 = 0, k2 = 0;                     // its key-mask words
+        for (int j = 0; j < nsb; ++j, ++it) {
+          const int b = j & 1;
+          uint32_t x[SB], pk[SB / 2];
+          if (b == 0) {
+            mbar_wait(&bars->kv_full[cslot], cpar);          // acquire the producers' key masks
+            const uint4 km = *reinterpret_cast<const uint4*>(kmask + cslot * 4);
+            k0 = km.x; k1 = km.y; k2 = km.z;
+          }
+          const uint32_t spar = (b ? sc1 : sc0) & 1;
+          mbar_wait(sfull + b, spar);
+          if (b) ++sc1; else ++sc0;
           tcgen05_fence_after();
+          if (stamp && it < 16) dbg_stamp(dbg, 16 + w * 40 + 2 * it);
+          const uint32_t tS = tbase + TM_S + b * SB;
+          tmem_ld_32x32b_x32(tS, x);
+          tmem_ld_32x32b_x16(tS + 32, x + 32);
+          tmem_ld_wait();
+          const uint32_t mlo = b ? ((k1 >> 16) | (k2 << 16)) : k0;
+          const uint32_t mhi = b ? (k2 >> 16) : (k1 & 0xffffu);
+          // "P.V(j-1) has retired" = the next, not yet consumed phase of the other S buffer
+          soft_block<DBG>(x, pk, mlo, mhi, j > 0, m_used, tO, sfull + (b ^ 1), (b ? sc0 : sc1) & 1, var);
+          if (!(var & 16)) {
+            tmem_st_32x32b_x16(tS, pk);
+            tmem_st_32x32b_x8(tS + 16, pk + 16);
+          }
+          tmem_st_wait();
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(pfull + b);
+          if (stamp && it < 16) dbg_stamp(dbg, 17 + w * 40 + 2 * it);
+          if (b) {
+            if (++cslot == NSLOT) { cslot = 0; cpar ^= 1; }
+          }
         }
-        if (!(var & 16)) tmem_st_32x32b_x16(tP, pk);
-        if (two) {
-          soft_chunk(xb, pk, tP, km.y, sb > 0, m_used, tO, &bars->pv_done[w], (it - 1) & 1, var & 1);
-          if (!(var & 16)) tmem_st_32x32b_x16(tP + 16, pk);
-        }
-        tmem_st_wait();
-        tcgen05_fence_before();
+        // ---- epilogue: both S buffers signal once more (P.V(n-2), P.V(n-1) retired); O / rowsum -> bf16 -> global.
+        // The next unit's P.V cannot start before this warpgroup has stored P of its first block, i.e. after O
+        // has been read here.
+        mbar_wait(sfull + 0, sc0 & 1);
+        mbar_wait(sfull + 1, sc1 & 1);
+        ++sc0; ++sc1;
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->p_full[w]);
-        if (stamp && it < 16) dbg_stamp(dbg, 17 + w * 40 + 2 * it);
-      }
-      // ---- epilogue: O / rowsum -> bf16 -> global.  The next unit's P.V cannot start before this warpgroup has
-      // stored P of its first block, i.e. after O has been read here.
-      mbar_wait(&bars->pv_done[w], (it - 1) & 1);
-      tcgen05_fence_after();
-      uint32_t o[32];
-      tmem_ld_32x32b_x32(tO, o);
-      tmem_ld_wait();
-      tcgen05_fence_before();
-      if (stamp && unit == (int)blockIdx.x) dbg_stamp(dbg, 48 + w * 40);
-      if (q < S) {
-        const float inv = 1.0f / __uint_as_float(o[HD]);
-        uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(u.seq_row0 + (uint32_t)q * p.inner) * p.ldo + u.h * HD);
+        if (lane == 0) mbar_arrive(&bars->o_free[w]);
+        tcgen05_fence_after();
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(tO, o);
+        tmem_ld_wait();
+        tcgen05_fence_before();
+        if (stamp && unit == (int)blockIdx.x) dbg_stamp(dbg, 48 + w * 40);
+        if (q < S) {
+          const float inv = 1.0f / __uint_as_float(o[HD]);
+          uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)(u.seq_row0 + (uint32_t)q * p.inner) * p.ldo + u.h * HD);
 #pragma unroll
-        for (int g2 = 0; g2 < 3; ++g2)
-          dst[g2] = make_uint4(pack_bf16(__uint_as_float(o[g2 * 8]) * inv, __uint_as_float(o[g2 * 8 + 1]) * inv),
-                               pack_bf16(__uint_as_float(o[g2 * 8 + 2]) * inv, __uint_as_float(o[g2 * 8 + 3]) * inv),
-                               pack_bf16(__uint_as_float(o[g2 * 8 + 4]) * inv, __uint_as_float(o[g2 * 8 + 5]) * inv),
-                               pack_bf16(__uint_as_float(o[g2 * 8 + 6]) * inv, __uint_as_float(o[g2 * 8 + 7]) * inv));
+          for (int g2 = 0; g2 < 3; ++g2)
+            dst[g2] = make_uint4(pack_bf16(__uint_as_float(o[g2 * 8]) * inv, __uint_as_float(o[g2 * 8 + 1]) * inv),
+                                 pack_bf16(__uint_as_float(o[g2 * 8 + 2]) * inv, __uint_as_float(o[g2 * 8 + 3]) * inv),
+                                 pack_bf16(__uint_as_float(o[g2 * 8 + 4]) * inv, __uint_as_float(o[g2 * 8 + 5]) * inv),
+                                 pack_bf16(__uint_as_float(o[g2 * 8 + 6]) * inv, __uint_as_float(o[g2 * 8 + 7]) * inv));
+        }
       }
+      rslot += nkb;                                          // every unit advances the ring by nkb blocks
+      while (rslot >= NSLOT) { rslot -= NSLOT; rpar ^= 1; }
     }
   } else {
     // =============================== producers ===============================
     // Thread r of the 128 stages row r of every operand block: Q tiles of the unit first (into the buffer the
-    // warpgroup is not reading), then the unit's K / V blocks through the ring.
+    // warpgroup is not reading), then the unit's K / V ring blocks (96 rows: the last producer warp only arrives).
     setmaxnreg_dec<REGS_PROD>();
     const int r = tid - PROD_WARP0 * 32, pw = r >> 5;
     uint32_t gblk = 0;
@@ -508,46 +536,48 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
         const uint32_t slot = gblk % NSLOT;
         mbar_wait(&bars->kv_empty[slot], ((gblk / NSLOT) & 1) ^ 1);
         if (DBG && r == 0 && nbatch < 48) dbg_stamp(dbg, 96 + 2 * nbatch);
-        const int key = kb * KB + r;
-        const uint32_t row = u.seq_row0 + (uint32_t)(key < S ? key : 0) * p.inner;
-        const bf16* src = qkv_h + (size_t)row * p.ld;
-        // V: cp.async 16-byte pieces straight into the MN-major operand layout (rows >= S zero-filled)
-        const uint32_t vrow = sV + slot * BLK_BYTES + r * 16;
+        if (r < RB) {
+          const int key = kb * RB + r;
+          const uint32_t row = u.seq_row0 + (uint32_t)(key < S ? key : 0) * p.inner;
+          const bf16* src = qkv_h + (size_t)row * p.ld;
+          // V: cp.async 16-byte pieces straight into the MN-major operand layout (rows >= S zero-filled)
+          const uint32_t vrow = sV + slot * RBLK_BYTES + r * 16;
 #pragma unroll
-        for (int c = 0; c < 3; ++c) cp_async16(vrow + c * GRP_BYTES, src + 2 * C + c * 8, key < S ? 16u : 0u);
-        cp_async_commit();
-        // K: global -> registers -> RoPE -> K-major operand layout; key S = learned bias token (mha.py:265-268)
-        uint4 g[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-        float valid = (key == S) ? 1.f : 0.f;
-        if (key < S) {
-          const uint4* ks = reinterpret_cast<const uint4*>(src + C);
+          for (int c = 0; c < 3; ++c) cp_async16(vrow + c * RGRP_BYTES, src + 2 * C + c * 8, key < S ? 16u : 0u);
+          cp_async_commit();
+          // K: global -> registers -> RoPE -> K-major operand layout; key S = learned bias token (mha.py:265-268)
+          uint4 g[3] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
+          float valid = (key == S) ? 1.f : 0.f;
+          if (key < S) {
+            const uint4* ks = reinterpret_cast<const uint4*>(src + C);
 #pragma unroll
-          for (int j = 0; j < 3; ++j) g[j] = __ldg(ks + j);
-          valid = __ldg(p.key_valid + row % (uint32_t)p.mask_mod);
-        } else if (key == S) {
-          uint32_t* gw = reinterpret_cast<uint32_t*>(g);
+            for (int j = 0; j < 3; ++j) g[j] = __ldg(ks + j);
+            valid = __ldg(p.key_valid + row % (uint32_t)p.mask_mod);
+          } else if (key == S) {
+            uint32_t* gw = reinterpret_cast<uint32_t*>(g);
 #pragma unroll
-          for (int e = 0; e < HD / 2; ++e) gw[e] = pack_bf16(p.bias_k[u.h * HD + 2 * e], p.bias_k[u.h * HD + 2 * e + 1]);
-        }
-        if (p.cs && key <= S) rope_row(g, p.cs + key * (HD / 2), p.sn + key * (HD / 2));
-        uint8_t* kr = smem + OFF_K + slot * BLK_BYTES + r * 16;
-#pragma unroll
-        for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * GRP_BYTES) = g[j];
-        const uint32_t bits = __ballot_sync(0xffffffffu, valid != 0.f);
-        if (lane == 0) kmask[slot * 4 + pw] = bits;
-        cp_async_wait<0>();
-        if (key == S) {                   // bias_v row, after this thread's zero-filling cp.async has landed
-          uint8_t* vr = smem + OFF_V + slot * BLK_BYTES + r * 16;
-#pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            uint4 v;
-            uint32_t* vw = reinterpret_cast<uint32_t*>(&v);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) vw[e] = pack_bf16(p.bias_v[u.h * HD + c * 8 + 2 * e], p.bias_v[u.h * HD + c * 8 + 2 * e + 1]);
-            *reinterpret_cast<uint4*>(vr + c * GRP_BYTES) = v;
+            for (int e = 0; e < HD / 2; ++e) gw[e] = pack_bf16(p.bias_k[u.h * HD + 2 * e], p.bias_k[u.h * HD + 2 * e + 1]);
           }
+          if (p.cs && key <= S) rope_row(g, p.cs + key * (HD / 2), p.sn + key * (HD / 2));
+          uint8_t* kr = smem + OFF_K + slot * RBLK_BYTES + r * 16;
+#pragma unroll
+          for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * RGRP_BYTES) = g[j];
+          const uint32_t bits = __ballot_sync(0xffffffffu, valid != 0.f);
+          if (lane == 0) kmask[slot * 4 + pw] = bits;
+          cp_async_wait<0>();
+          if (key == S) {                   // bias_v row, after this thread's zero-filling cp.async has landed
+            uint8_t* vr = smem + OFF_V + slot * RBLK_BYTES + r * 16;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              uint4 v;
+              uint32_t* vw = reinterpret_cast<uint32_t*>(&v);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) vw[e] = pack_bf16(p.bias_v[u.h * HD + c * 8 + 2 * e], p.bias_v[u.h * HD + c * 8 + 2 * e + 1]);
+              *reinterpret_cast<uint4*>(vr + c * RGRP_BYTES) = v;
+            }
+          }
+          fence_async_smem();
         }
-        fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->kv_full[slot]);
         if (DBG && r == 0 && nbatch < 48) dbg_stamp(dbg, 97 + 2 * nbatch);

@@ -152,7 +152,7 @@ def attn_rows(b, S, inner):
 
 
 @pytest.mark.parametrize("nb,S,inner,rope", [(4, 200, 2, 1), (3, 130, 1, 0), (2, 1000, 2, 1), (5, 256, 1, 1),
-                                              (4, 64, 4, 1), (2, 1023, 1, 1), (3, 513, 1, 1)])
+                                              (4, 64, 4, 1), (2, 1023, 1, 1), (3, 513, 1, 1), (2, 1500, 2, 1), (3, 95, 1, 1), (40, 100, 4, 1)])
 def test_attention_tcgen05(nb, S, inner, rope):
     H, hd = 16, 24
     C = H * hd
