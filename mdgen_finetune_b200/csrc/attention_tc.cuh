@@ -63,7 +63,7 @@ constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups of a Q
 constexpr int RGRP_BYTES = RB * 16;      // 1536: stride between d-groups of a K/V ring block (K-major LBO / MN-major SBO)
 constexpr int RBLK_BYTES = 4 * RGRP_BYTES;   // 6 KB
 constexpr int OFF_K = 0, OFF_V = OFF_K + NSLOT * RBLK_BYTES, OFF_Q = OFF_V + NSLOT * RBLK_BYTES,
-              OFF_MASK = OFF_Q + 2 * NWG * BLK_BYTES, OFF_BAR = OFF_MASK + NSLOT * 4 * 4, SMEM_BYTES = OFF_BAR + 512;
+              OFF_BAR = OFF_Q + 2 * NWG * BLK_BYTES, SMEM_BYTES = OFF_BAR + 512;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 constexpr uint32_t TMEM_COLS = 512;
 // per-warpgroup TMEM columns: S0 fp32 [48], S1 fp32 [48] (P packed bf16 overwrites the first 24 of its S), O fp32 [32]
@@ -233,21 +233,30 @@ __device__ __forceinline__ void tmem_st_32x32b_x8(uint32_t taddr, const uint32_t
                : "memory");
 }
 
-// One 48-key block of scores of one query row (x[0..47], fp32 bit patterns): key mask, running-max update with
+// exp2 on the FMA / ALU pipes (the MUFU unit does 16 ex2 / clk / SM and is this kernel's busiest pipe): round-to-nearest
+// split x = n + f with the 1.5 * 2^23 trick, degree-3 minimax polynomial for 2^f on [-0.5, 0.5] (relative error
+// 7.5e-5, far below the bf16 rounding of P), n added into the exponent field.  x <= 8 by construction (lazy
+// rescaling); x = -inf (masked key) gives 2^-126 instead of 0, which vanishes against the row sum.
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -126.0f);
+  const float t = x + 12582912.0f;
+  const float f = x - (t - 12582912.0f);
+  const float p = fmaf(fmaf(fmaf(0.0551716611f, f, 0.2426111251f), f, 0.6932609677f), f, 0.9999280572f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+// element j of a block takes the polynomial path when POLY > 0 and j % POLY == POLY - 1
+template <int POLY> __device__ __forceinline__ float ex2_sel(float x, int j) {
+  return (POLY > 0 && (j % (POLY > 0 ? POLY : 1)) == POLY - 1) ? ex2_poly(x) : ex2(x);
+}
+
+// One 48-key block of scores of one query row (x[0..47], fp32 bit patterns; padded keys arrive as ~ -32768 through
+// the mask column of K, see the producers): running-max update with
 // lazy rescale of O (in TMEM; `pv_bar` / `pv_parity` = the barrier phase that tells every P.V issued so far has
 // retired), then P = exp2(x log2e - m) packed to bf16 (pk[0..23]).
-template <bool DBG>
-__device__ __forceinline__ void soft_block(uint32_t (&x)[SB], uint32_t (&pk)[SB / 2], uint32_t mlo, uint32_t mhi, bool have_o,
+template <bool DBG, int POLY>
+__device__ __forceinline__ void soft_block(uint32_t (&x)[SB], uint32_t (&pk)[SB / 2], bool have_o,
                                            float& m_used, uint32_t tO, uint64_t* pv_bar, uint32_t pv_parity, int var) {
   const float LOG2E = 1.4426950408889634f;
-  if ((mlo & (mhi | 0xffff0000u)) != 0xffffffffu) {       // some key of the block is padding (or beyond the last key)
-#pragma unroll
-    for (int j = 0; j < 32; ++j)
-      if (!((mlo >> j) & 1u)) x[j] = 0xff800000u;   // -inf
-#pragma unroll
-    for (int j = 0; j < SB - 32; ++j)
-      if (!((mhi >> j) & 1u)) x[32 + j] = 0xff800000u;
-  }
   float bm[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
   for (int j = 0; j < SB; j += 2) bm[(j >> 1) & 3] = max3(bm[(j >> 1) & 3], __uint_as_float(x[j]), __uint_as_float(x[j + 1]));
@@ -279,7 +288,8 @@ __device__ __forceinline__ void soft_block(uint32_t (&x)[SB], uint32_t (&pk)[SB 
   }
 #pragma unroll
   for (int j = 0; j < SB / 2; ++j)
-    pk[j] = pack_bf16(ex2(fmaf(__uint_as_float(x[2 * j]), LOG2E, mneg)), ex2(fmaf(__uint_as_float(x[2 * j + 1]), LOG2E, mneg)));
+    pk[j] = pack_bf16(ex2_sel<POLY>(fmaf(__uint_as_float(x[2 * j]), LOG2E, mneg), 2 * j),
+                      ex2_sel<POLY>(fmaf(__uint_as_float(x[2 * j + 1]), LOG2E, mneg), 2 * j + 1));
 }
 
 // work unit -> (sequence, head, query range)
@@ -300,7 +310,7 @@ template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile
 template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
 
-template <bool DBG>
+template <bool DBG, int POLY>
 __global__ void __launch_bounds__(THREADS, 1)
 attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long long* dbg_buf, int dbg_cta, int dbg_var) {
   const int var = DBG ? dbg_var : 0;   // timing experiments (tools/attn_probe.py); results are wrong when non-zero
@@ -310,7 +320,6 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 127u) != 0) __trap();     // dynamic shared memory starts at the window base (no static shared)
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
-  uint32_t* kmask = reinterpret_cast<uint32_t*>(smem + OFF_MASK);   // [slot][4]: bit j of word w: key 32 w + j of the ring block is attendable
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
   long long* dbg = (DBG && dbg_buf && (int)blockIdx.x == dbg_cta) ? dbg_buf : nullptr;
   if (tid == 0) dbg_stamp(dbg, 0);
@@ -337,13 +346,15 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&bars->tmem_base)), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // padding d-group (d = 24..31) of every operand block, written once: zeros for K and Q, [1, 0, ..] for V
-  for (int i = tid; i < 2 * NSLOT * RB; i += THREADS) {
+  // padding d-group (d = 24..31) of the V and Q operand blocks, written once: [1, 0, ..] for both.  V's ones column
+  // makes O[:, 24] the row sum; Q's multiplies the MASK COLUMN of K (d = 24: 0 for an attendable key, -32768 for a
+  // padded one, written per key by the producers), so key padding costs the softmax warps nothing.
+  for (int i = tid; i < NSLOT * RB; i += THREADS) {
     const int blk = i / RB, r = i - blk * RB;
-    *reinterpret_cast<uint4*>(smem + OFF_K + blk * RBLK_BYTES + 3 * RGRP_BYTES + r * 16) = make_uint4(blk >= NSLOT ? 0x3F80u : 0u, 0, 0, 0);
+    *reinterpret_cast<uint4*>(smem + OFF_V + blk * RBLK_BYTES + 3 * RGRP_BYTES + r * 16) = make_uint4(0x3F80u, 0, 0, 0);
   }
   for (int i = tid; i < 2 * NWG * KB; i += THREADS)
-    *reinterpret_cast<uint4*>(smem + OFF_Q + (i >> 7) * BLK_BYTES + 3 * GRP_BYTES + (i & 127) * 16) = make_uint4(0, 0, 0, 0);
+    *reinterpret_cast<uint4*>(smem + OFF_Q + (i >> 7) * BLK_BYTES + 3 * GRP_BYTES + (i & 127) * 16) = make_uint4(0x3F80u, 0, 0, 0);
   fence_async_smem();
   tcgen05_fence_before();
   __syncthreads();
@@ -434,23 +445,15 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
     uint64_t* const pfull = &bars->p_full[w][0];
     const bool stamp = DBG && (r == 0 && w < 2);
     uint32_t sc0 = 0, sc1 = 0;                               // s_full phases consumed per S buffer
-    uint32_t rslot = 0, rpar = 0;                            // ring position of the current unit's first block
     uint32_t it = 0;
     for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
       const Unit u = decode_unit(p, unit, chunks_per_seq);
       if (w < u.ntiles) {
         const int q = u.q_begin + w * QT + r;
         float m_used = -INFINITY;
-        uint32_t cslot = rslot, cpar = rpar;                 // ring block of the current pair of softmax blocks
-        uint32_t k0 = 0, k1 = 0, k2 = 0;                     // its key-mask words
         for (int j = 0; j < nsb; ++j, ++it) {
           const int b = j & 1;
           uint32_t x[SB], pk[SB / 2];
-          if (b == 0) {
-            mbar_wait(&bars->kv_full[cslot], cpar);          // acquire the producers' key masks
-            const uint4 km = *reinterpret_cast<const uint4*>(kmask + cslot * 4);
-            k0 = km.x; k1 = km.y; k2 = km.z;
-          }
           const uint32_t spar = (b ? sc1 : sc0) & 1;
           mbar_wait(sfull + b, spar);
           if (b) ++sc1; else ++sc0;
@@ -460,10 +463,8 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
           tmem_ld_32x32b_x32(tS, x);
           tmem_ld_32x32b_x16(tS + 32, x + 32);
           tmem_ld_wait();
-          const uint32_t mlo = b ? ((k1 >> 16) | (k2 << 16)) : k0;
-          const uint32_t mhi = b ? (k2 >> 16) : (k1 & 0xffffu);
           // "P.V(j-1) has retired" = the next, not yet consumed phase of the other S buffer
-          soft_block<DBG>(x, pk, mlo, mhi, j > 0, m_used, tO, sfull + (b ^ 1), (b ? sc0 : sc1) & 1, var);
+          soft_block<DBG, POLY>(x, pk, j > 0, m_used, tO, sfull + (b ^ 1), (b ? sc0 : sc1) & 1, var);
           if (!(var & 16)) {
             tmem_st_32x32b_x16(tS, pk);
             tmem_st_32x32b_x8(tS + 16, pk + 16);
@@ -473,9 +474,6 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
           __syncwarp();
           if (lane == 0) mbar_arrive(pfull + b);
           if (stamp && it < 16) dbg_stamp(dbg, 17 + w * 40 + 2 * it);
-          if (b) {
-            if (++cslot == NSLOT) { cslot = 0; cpar ^= 1; }
-          }
         }
         // ---- epilogue: both S buffers signal once more (P.V(n-2), P.V(n-1) retired); O / rowsum -> bf16 -> global.
         // The next unit's P.V cannot start before this warpgroup has stored P of its first block, i.e. after O
@@ -502,15 +500,13 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
                                  pack_bf16(__uint_as_float(o[g2 * 8 + 6]) * inv, __uint_as_float(o[g2 * 8 + 7]) * inv));
         }
       }
-      rslot += nkb;                                          // every unit advances the ring by nkb blocks
-      while (rslot >= NSLOT) { rslot -= NSLOT; rpar ^= 1; }
     }
   } else {
     // =============================== producers ===============================
     // Thread r of the 128 stages row r of every operand block: Q tiles of the unit first (into the buffer the
     // warpgroup is not reading), then the unit's K / V ring blocks (96 rows: the last producer warp only arrives).
     setmaxnreg_dec<REGS_PROD>();
-    const int r = tid - PROD_WARP0 * 32, pw = r >> 5;
+    const int r = tid - PROD_WARP0 * 32;
     uint32_t gblk = 0;
     int nbatch = 0;                       // DBG: producer batches (Q tiles and K/V blocks) stamped so far
     uint32_t quse[NWG] = {0, 0, 0, 0};
@@ -562,8 +558,9 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
           uint8_t* kr = smem + OFF_K + slot * RBLK_BYTES + r * 16;
 #pragma unroll
           for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4*>(kr + j * RGRP_BYTES) = g[j];
-          const uint32_t bits = __ballot_sync(0xffffffffu, valid != 0.f);
-          if (lane == 0) kmask[slot * 4 + pw] = bits;
+          // mask column (d = 24): -32768 for padded keys and for the rows behind the bias token -- far below any
+          // score, yet small enough that fp32 rounding of (s - max) log2e stays ~2^-8 while only padded keys have been seen
+          *reinterpret_cast<uint4*>(kr + 3 * RGRP_BYTES) = make_uint4(valid != 0.f ? 0u : 0xC700u, 0, 0, 0);
           cp_async_wait<0>();
           if (key == S) {                   // bias_v row, after this thread's zero-filling cp.async has landed
             uint8_t* vr = smem + OFF_V + slot * RBLK_BYTES + r * 16;
@@ -603,14 +600,23 @@ int num_sms();
 extern long long* g_dbg_buf;   // device buffer for dbg_stamp (mdgen_debug_set_buffer), normally null
 extern int g_dbg_cta;
 
-inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStream_t st) {
-  MD_CHECK(attention_tc_supported(p, head_dim), "attention_tc: unsupported shape");
+constexpr int ATTN_POLY_DEFAULT = 0;   // MDGEN_ATTN_POLY=3: every third exp2 on the FMA pipe -- measured SLOWER (216 -> 234 us on config 3:
+                                       // the kernel is issue-bound, not MUFU-bound), kept for A/B runs
+
+template <bool DBG, int POLY>
+inline cudaError_t launch_attention_tc_variant(const AttnParams<bf16>& p, int grid, int chunks, int nunits, int var, cudaStream_t st) {
   static bool configured = false;
   if (!configured) {
-    MD_CUDA(cudaFuncSetAttribute(atc::attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
-    MD_CUDA(cudaFuncSetAttribute(atc::attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    cudaError_t e = cudaFuncSetAttribute(atc::attention_tc_kernel<DBG, POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
     configured = true;
   }
+  atc::attention_tc_kernel<DBG, POLY><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, nunits, DBG ? g_dbg_buf : nullptr, g_dbg_cta, var);
+  return cudaSuccess;
+}
+
+inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStream_t st) {
+  MD_CHECK(attention_tc_supported(p, head_dim), "attention_tc: unsupported shape");
   // work units of up to NWG query tiles; unit id = (sequence, head, chunk) with the chunk fastest, so the CTAs
   // that share a head's K / V run side by side (second reader hits L2)
   const int qtiles = (p.S + atc::QT - 1) / atc::QT;
@@ -619,10 +625,16 @@ inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStre
   const int grid = (int)(nunits < num_sms() ? nunits : num_sms());
   ProfScope ps(PC_ATTN_TC, st);
   static const int var = getenv("MDGEN_ATTN_VAR") ? atoi(getenv("MDGEN_ATTN_VAR")) : 0;
-  if (g_dbg_buf || var)
-    atc::attention_tc_kernel<true><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, (int)nunits, g_dbg_buf, g_dbg_cta, var);
-  else
-    atc::attention_tc_kernel<false><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, (int)nunits, nullptr, 0, 0);
+  static const int poly = getenv("MDGEN_ATTN_POLY") ? atoi(getenv("MDGEN_ATTN_POLY")) : ATTN_POLY_DEFAULT;
+  if (g_dbg_buf || var) {
+    MD_CUDA((launch_attention_tc_variant<true, ATTN_POLY_DEFAULT>(p, grid, chunks, (int)nunits, var, st)));
+  } else {
+    switch (poly) {
+      case 0: MD_CUDA((launch_attention_tc_variant<false, 0>(p, grid, chunks, (int)nunits, 0, st))); break;
+      case 3: MD_CUDA((launch_attention_tc_variant<false, 3>(p, grid, chunks, (int)nunits, 0, st))); break;
+      default: MD_CHECK(false, "MDGEN_ATTN_POLY must be 0 or 3");
+    }
+  }
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
