@@ -381,6 +381,187 @@ attention_seq_kernel(AttnParams<AT> p, long long total_groups) {
   for (int t = 0; t < S_; ++t) store24(p.out + attn_row(nbi, t, S_, p.inner) * p.ldo + h * HD, q[t]);
 }
 
+// ---- residue-axis attention at S = 4 on contiguous sequences (inner == 1, ld == 3C): the block's rows are ONE
+// contiguous byte range, so a single bulk copy (cp.async.bulk, mbarrier completion) brings q | k | v of ASB_SEQ
+// sequences into shared memory at full memory-level parallelism.  K is rotated in place (bf16, as the tensor-core
+// kernel stages it), then thread = (sequence, query, head) works out of shared memory (48-byte slices at a 48-byte
+// lane stride: conflict-free 128-bit LDS, the two queries of a warp share their K / V reads) and writes one
+// coalesced output row slice.  64 registers -> 40 warps per SM; attention_seq_kernel (thread = (sequence, head),
+// three dependent global-load phases at ~11 warps per SM) took 36 us for the 98 MB of config 3.
+__device__ __forceinline__ void load24_smem(const bf16* p, float* o) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const uint4 v = reinterpret_cast<const uint4*>(p)[i];
+    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = __bfloat1622float2(h2[j]);
+      o[8 * i + 2 * j] = f.x; o[8 * i + 2 * j + 1] = f.y;
+    }
+  }
+}
+__device__ __forceinline__ void rope24s(float* x, const float* cs, const float* sn, int pos) {   // tables in shared memory
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float4 c4 = reinterpret_cast<const float4*>(cs + pos * 12)[j];
+    const float4 s4 = reinterpret_cast<const float4*>(sn + pos * 12)[j];
+    const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int i = 4 * j + e;
+      const float a = x[i], b = x[i + 12];
+      x[i] = a * cc[e] - b * ss[e];
+      x[i + 12] = b * cc[e] + a * ss[e];
+    }
+  }
+}
+// dot product of 24 fp32 values with 24 bf16 values in shared memory
+__device__ __forceinline__ float dot24_smem(const float* q, const bf16* k) {
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const uint4 v = reinterpret_cast<const uint4*>(k)[i];
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      s0 = fmaf(q[8 * i + 2 * j], __uint_as_float(w[j] << 16), s0);
+      s1 = fmaf(q[8 * i + 2 * j + 1], __uint_as_float(w[j] & 0xffff0000u), s1);
+    }
+  }
+  return s0 + s1;
+}
+// acc[0..23] += pr * v[0..23] (bf16 values in shared memory)
+__device__ __forceinline__ void axpy24_smem(float* acc, float pr, const bf16* vp) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const uint4 v = reinterpret_cast<const uint4*>(vp)[i];
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      acc[8 * i + 2 * j] = fmaf(pr, __uint_as_float(w[j] << 16), acc[8 * i + 2 * j]);
+      acc[8 * i + 2 * j + 1] = fmaf(pr, __uint_as_float(w[j] & 0xffff0000u), acc[8 * i + 2 * j + 1]);
+    }
+  }
+}
+template <int HD, int ASB_SEQ>   // ASB_SEQ sequences per block; thread = (sequence, query, head), head fastest
+__global__ void __launch_bounds__(ASB_SEQ * 64)
+attention_seq4_bulk_kernel(AttnParams<bf16> p) {
+  constexpr int S_ = 4, HALF = HD / 2, ASB_THREADS = ASB_SEQ * 64;
+  static_assert(HD == 24, "rope24 is written for head_dim 24");
+  extern __shared__ __align__(128) uint8_t asb_smem[];
+  const int C = p.H * HD, ld = 3 * C;
+  bf16* tile = reinterpret_cast<bf16*>(asb_smem);                       // [ASB_SEQ * 4 rows][3C]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(asb_smem + (size_t)ASB_SEQ * S_ * ld * sizeof(bf16));
+  float* rope_cs = reinterpret_cast<float*>(bar + 2);                     // [5][12] cos, [5][12] sin
+  float* rope_sn = rope_cs + (S_ + 1) * HALF;
+  float* bias_kr = rope_sn + (S_ + 1) * HALF;                             // [H][24] bias key rotated to position S
+  float* bias_vs = bias_kr + 16 * HD;                                     // [H][24]
+  const int tid = threadIdx.x;
+  const int seq0 = blockIdx.x * ASB_SEQ;
+  const int nseq = min(ASB_SEQ, p.nb - seq0);
+  const uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(bar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const uint32_t bytes = (uint32_t)nseq * S_ * ld * (uint32_t)sizeof(bf16);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(tile)),
+                 "l"(p.qkv + (size_t)seq0 * S_ * ld), "r"(bytes), "r"(bar_a)
+                 : "memory");
+  }
+  for (int i = tid; i < (S_ + 1) * HALF; i += ASB_THREADS) {
+    rope_cs[i] = p.cs ? p.cs[i] : 1.f;
+    rope_sn[i] = p.cs ? p.sn[i] : 0.f;
+  }
+  for (int i = tid; i < 16 * HD; i += ASB_THREADS) bias_vs[i] = p.bias_v[i];
+  __syncthreads();                                                       // barrier initialised, rope tables visible
+  if (tid < 16) {                                                        // bias key of head tid, rotated by position S
+    float k[HD];
+#pragma unroll
+    for (int i = 0; i < HD; ++i) k[i] = p.bias_k[tid * HD + i];
+    rope24s(k, rope_cs, rope_sn, S_);
+#pragma unroll
+    for (int i = 0; i < HD; ++i) bias_kr[tid * HD + i] = k[i];
+  }
+  const int h = tid & 15, t = (tid >> 4) & 3, sl = tid >> 6;
+  const int nbi = seq0 + sl;
+  float valid[S_];
+#pragma unroll
+  for (int j = 0; j < S_; ++j) valid[j] = (sl < nseq) ? p.key_valid[((size_t)nbi * S_ + j) % p.mask_mod] : 0.f;
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t"
+      "ASB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], 0;\n\t"
+      "@P1 bra ASB_DONE;\n\t"
+      "bra ASB_WAIT;\n\t"
+      "ASB_DONE:\n\t}" ::"r"(bar_a)
+      : "memory");
+  // ---- rotate K in place (bf16, like the tensor-core kernel's staged K): this thread owns row (sl, t), head h
+  bf16* rows = tile + (size_t)sl * S_ * ld + h * HD;
+  if (sl < nseq) {
+    float k[HD];
+    load24_smem(rows + t * ld + C, k);
+    rope24s(k, rope_cs, rope_sn, t);
+    store24(rows + t * ld + C, k);
+  }
+  __syncthreads();
+  if (sl >= nseq) return;
+  float q[HD];
+  load24_smem(rows + t * ld, q);
+  rope24s(q, rope_cs, rope_sn, t);
+  // ---- scores: keys 0..3 from the tokens, key 4 = learned bias token (mha.py:265-268); fp32 softmax
+  float sc[S_ + 1];
+#pragma unroll
+  for (int j = 0; j < S_; ++j) {
+    const float d = dot24_smem(q, rows + j * ld + C);
+    sc[j] = valid[j] != 0.f ? d : -INFINITY;
+  }
+  {
+    float s0 = 0.f;
+#pragma unroll
+    for (int i = 0; i < HD; ++i) s0 = fmaf(q[i], bias_kr[h * HD + i], s0);
+    sc[S_] = s0;
+  }
+  float m = sc[S_];
+#pragma unroll
+  for (int j = 0; j < S_; ++j) m = fmaxf(m, sc[j]);
+  float l = 0.f;
+#pragma unroll
+  for (int j = 0; j <= S_; ++j) {
+    sc[j] = __expf(sc[j] - m);
+    l += sc[j];
+  }
+  const float inv = 1.0f / l;
+  // ---- P.V (q's registers are dead: the accumulators take their place)
+#pragma unroll
+  for (int i = 0; i < HD; ++i) q[i] = sc[S_] * inv * bias_vs[h * HD + i];
+#pragma unroll
+  for (int j = 0; j < S_; ++j) axpy24_smem(q, sc[j] * inv, rows + j * ld + 2 * C);
+  store24(p.out + ((size_t)nbi * S_ + t) * p.ldo + h * HD, q);
+}
+inline bool attention_seq4_bulk_supported(const AttnParams<bf16>& p) {
+  return p.S == 4 && p.inner == 1 && p.H == 16 && p.ld == 3 * p.H * 24 && (((uintptr_t)p.qkv) & 15) == 0 && !getenv("MDGEN_NO_ATTN_BULK");
+}
+inline bool attention_seq4_bulk_supported(const AttnParams<float>&) { return false; }
+template <int NSEQ>
+inline cudaError_t launch_attention_seq4_bulk_n(const AttnParams<bf16>& p, cudaStream_t st) {
+  const int smem = NSEQ * 4 * p.ld * (int)sizeof(bf16) + 16 + 2 * 5 * 12 * 4 + 2 * 16 * 24 * 4;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(attention_seq4_bulk_kernel<24, NSEQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  attention_seq4_bulk_kernel<24, NSEQ><<<(p.nb + NSEQ - 1) / NSEQ, NSEQ * 64, smem, st>>>(p);
+  return cudaSuccess;
+}
+inline cudaError_t launch_attention_seq4_bulk(const AttnParams<bf16>& p, cudaStream_t st) {
+  static const int nseq = getenv("MDGEN_ASB_SEQ") ? atoi(getenv("MDGEN_ASB_SEQ")) : 4;
+  return nseq == 1 ? launch_attention_seq4_bulk_n<1>(p, st) : nseq == 2 ? launch_attention_seq4_bulk_n<2>(p, st) : launch_attention_seq4_bulk_n<4>(p, st);
+}
+inline cudaError_t launch_attention_seq4_bulk(const AttnParams<float>&, cudaStream_t) { return cudaErrorNotSupported; }
+
 template <typename AT, int S_>
 inline void launch_attention_short(const AttnParams<AT>& p, cudaStream_t st) {
   const long long groups = (long long)p.nb * p.H;
@@ -394,7 +575,9 @@ inline int launch_attention_simt(const AttnParams<AT>& p, int head_dim, cudaStre
   if (p.nb <= 0 || p.S <= 0) return 0;
   const bool is_short = (p.S <= 4 && p.S >= 2) || ((p.S == 8 || p.S == 16) && p.H <= 16);
   ProfScope ps(is_short ? PC_ATTN_SHORT : PC_ATTN_SIMT, st);
-  if (p.S == 4 || p.S == 2 || p.S == 3) {
+  if (attention_seq4_bulk_supported(p)) {
+    MD_CUDA(launch_attention_seq4_bulk(p, st));
+  } else if (p.S == 4 || p.S == 2 || p.S == 3) {
     const long long groups = (long long)p.nb * p.H;
     const unsigned grid = (unsigned)((groups + ASQ_THREADS - 1) / ASQ_THREADS);
     if (p.S == 4) attention_seq_kernel<AT, 24, 4><<<grid, ASQ_THREADS, 0, st>>>(p, groups);

@@ -1465,7 +1465,7 @@ int mdgen_test_attention(int32_t nb, int32_t S, int32_t inner, int32_t heads, in
     AttnParams<bf16> pb;
     pb.qkv = qb; pb.ld = 3 * C; pb.out = ob; pb.ldo = C; pb.nb = nb; pb.S = S; pb.inner = inner; pb.H = heads;
     pb.bias_k = bias_k; pb.bias_v = bias_v; pb.key_valid = key_valid; pb.mask_mod = nb * S; pb.cs = cs; pb.sn = sn;
-    r = launch_attention_tc(pb, head_dim, st);
+    r = use_tc == 2 ? launch_attention_simt<bf16>(pb, head_dim, st) : launch_attention_tc(pb, head_dim, st);   // 2: bf16 short-axis kernels
     if (r == 0) bf16_to_f32_kernel<<<(unsigned)((rows * C + 255) / 256), 256, 0, st>>>(ob, out, rows * C);
   } else {
     r = launch_attention_simt<float>(p, head_dim, st);

@@ -147,6 +147,31 @@ def test_attention_simt(nb, S, inner, rope):
     assert float((out.cpu() - ref).norm() / ref.norm()) < 1e-5
 
 
+@pytest.mark.parametrize("nb,S,inner,rope", [(6, 4, 1, 1), (1001, 4, 1, 1), (8000, 4, 1, 1), (10, 4, 1, 0), (12, 4, 4, 1), (9, 3, 1, 1)])
+def test_attention_short_bf16(nb, S, inner, rope):
+    """bf16 short-axis kernels (residue axis of the 4AA configs): bulk-copy kernel for contiguous S = 4 sequences,
+    thread-per-(sequence, head) kernel otherwise."""
+    H, hd = 16, 24
+    C = H * hd
+    g = torch.Generator().manual_seed(nb * 1000 + S)
+    qkv = (torch.randn(nb * S, 3 * C, generator=g) * 0.7).bfloat16().float()
+    bk, bv = torch.randn(C, generator=g), torch.randn(C, generator=g)
+    valid = (torch.rand(nb * S, generator=g) > 0.2).float()
+    valid[:S * inner] = 1.0
+    if nb > 2:
+        valid[attn_rows(1, S, inner)] = 0.0
+    out = torch.full((nb * S, C), float("nan"), device="cuda")
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    dq, dk, dv, dm = qkv.cuda(), bk.cuda(), bv.cuda(), valid.cuda()
+    _lib.check(_lib.lib().mdgen_test_attention(nb, S, inner, H, hd, _p(dq), _p(dk), _p(dv), _p(dm), _p(out), 2,
+                                               rope, st), "test_attention")
+    ref = _attn_ref(qkv, bk, bv, valid, nb, S, inner, H, hd, rope)
+    o = out.cpu()
+    assert torch.isfinite(o).all()
+    err = float((o - ref).norm() / ref.norm())
+    assert err < 8e-3, err      # bf16 q/k/v (K rotated in bf16), fp32 arithmetic, bf16 output
+
+
 def attn_rows(b, S, inner):
     return torch.tensor([(b // inner) * S * inner + s * inner + (b % inner) for s in range(S)])
 
