@@ -243,7 +243,8 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
     const long t256 = (long)((M + 255) / 256) * ((N + 255) / 256);
     // measured on config 3 (tools/gemm_probe.py): the pair kernel wins for the K = 1536 projection (fc2) and the plain
     // bf16 stores of wide N; the K = 384 residual / GELU epilogues are shared-memory-bandwidth bound either way
-    if (t256 >= num_sms() / 2 && (K >= 1024 || (epi == EPI_STORE && N >= 1024))) block_n = 256;
+    static const bool gelu_pair = getenv("MDGEN_GELU_2CTA") != nullptr;
+    if (t256 >= num_sms() / 2 && (K >= 1024 || ((epi == EPI_STORE || (gelu_pair && epi == EPI_GELU)) && N >= 1024))) block_n = 256;
   }
   CUtensorMap ta, tw;
   MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
