@@ -168,6 +168,64 @@ embed_kernel(const float* __restrict__ x, int D, const float* __restrict__ xc, i
   }
 }
 
+// Per-step part of the embedding: out[m,:] = stat[m,:] + ipa[b,l] + W_x x[m].  `stat` holds everything that does not
+// change between sampler steps (W_c x_cond + biases + mask / position / time embeddings, written once per
+// conditioning by embed_kernel with D = 0).  thread = CH channels (c, c + C/CH, ...) with their weight columns in
+// registers, so one broadcast LDS.128 of the staged inputs feeds 4 * CH FMAs: the one-channel kernel above was
+// LSU-bound (ncu: 78 % LSU, 68 us for config 3).
+constexpr int EMB_STEP_TOK = 16;    // tokens per block: 2000 blocks on config 3, ~13 resident warps per SM stay busy
+template <int C, int DP, int CH>
+__global__ void __launch_bounds__(C / CH)
+embed_step_kernel(const float* __restrict__ x, int D, const float* __restrict__ WT, const float* __restrict__ stat,
+                  const float* __restrict__ ipa, float* __restrict__ out, int N, int T, int L) {
+  constexpr int NT = C / CH;
+  static_assert(NT >= EMB_STEP_TOK, "one thread per staged token for the row table");
+  __shared__ __align__(16) float sm[EMB_STEP_TOK][DP];
+  __shared__ int ipa_row[EMB_STEP_TOK];
+  const int c0 = threadIdx.x;
+  const int m0 = blockIdx.x * EMB_STEP_TOK;
+  float w[CH][DP];
+#pragma unroll
+  for (int k = 0; k < CH; ++k)
+#pragma unroll
+    for (int d = 0; d < DP; ++d) w[k][d] = d < D ? WT[(size_t)d * C + c0 + k * NT] : 0.f;
+  for (int i = threadIdx.x; i < EMB_STEP_TOK * DP; i += NT) {
+    const int tk = i / DP, d = i % DP, m = m0 + tk;
+    sm[tk][d] = (m < N && d < D) ? x[(size_t)m * D + d] : 0.f;
+  }
+  if (threadIdx.x < EMB_STEP_TOK) {
+    const int m = min(m0 + (int)threadIdx.x, N - 1);
+    ipa_row[threadIdx.x] = (m / (L * T)) * L + m % L;
+  }
+  __syncthreads();
+  const int ntk = min(EMB_STEP_TOK, N - m0);
+#pragma unroll 2
+  for (int tk = 0; tk < ntk; ++tk) {
+    const size_t row = (size_t)(m0 + tk) * C;
+    float a[CH];
+#pragma unroll
+    for (int k = 0; k < CH; ++k) a[k] = __ldg(stat + row + c0 + k * NT);
+    if (ipa) {
+      const size_t ir = (size_t)ipa_row[tk] * C;
+#pragma unroll
+      for (int k = 0; k < CH; ++k) a[k] += __ldg(ipa + ir + c0 + k * NT);
+    }
+#pragma unroll
+    for (int d = 0; d < DP; d += 4) {
+      const float4 xv = *reinterpret_cast<const float4*>(&sm[tk][d]);
+#pragma unroll
+      for (int k = 0; k < CH; ++k) {
+        a[k] = fmaf(w[k][d], xv.x, a[k]);
+        a[k] = fmaf(w[k][d + 1], xv.y, a[k]);
+        a[k] = fmaf(w[k][d + 2], xv.z, a[k]);
+        a[k] = fmaf(w[k][d + 3], xv.w, a[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < CH; ++k) out[row + c0 + k * NT] = a[k];
+  }
+}
+
 // WT[d, c] = d < D ? Wx[c, d] : Wc[c, d - D];  bsum[c] = bx[c] + bc[c]
 __global__ void pack_embed_weights_kernel(const float* __restrict__ Wx, int D, const float* __restrict__ Wc, int Dc,
                                           const float* __restrict__ bx, const float* __restrict__ bc, int C,

@@ -325,6 +325,8 @@ struct MdgenHandle {
   std::vector<MainLayerW> layers;
   LinearW final_lin, design_fc1, design_fc2, design_fc3, design_logits;
   float *emb_wt = nullptr, *emb_bsum = nullptr, *emb_bx = nullptr;  // transposed [D+Dc, C] embedding weights
+  float* emb_static = nullptr;     // [N, C] step-invariant part of the token embedding (per conditioning)
+  bool emb_static_valid = false;
   float* ada_w = nullptr;  // [ada_cols, C]
   float* ada_b = nullptr;
   int ada_cols = 0, ada_final_off = 0;
@@ -562,6 +564,7 @@ static int finalize_weights(MdgenHandle* h, cudaStream_t st) {
     MD_TRY(pack_linear(h, "emb_to_logits", &h->design_logits, false, st));
   }
   h->finalized = true;
+  h->emb_static_valid = false;
   return 0;
 }
 
@@ -616,7 +619,9 @@ static int alloc_workspace(MdgenHandle* h, int B, int T, int L) {
   WS(h->rope_t_cs, (size_t)(T + 1) * half * 4);
   WS(h->rope_t_sn, (size_t)(T + 1) * half * 4);
   WS(h->ipa_emb0, Mi * C * 4);
+  WS(h->emb_static, N * C * 4);
 #undef WS
+  h->emb_static_valid = false;
   h->B = B;
   h->T = T;
   h->L = L;
@@ -717,6 +722,7 @@ static int set_conditioning(MdgenHandle* h, int B, int T, int L, const float* ma
   MD_CUDA(cudaMemcpyAsync(h->mask, mask, N * 4, cudaMemcpyDeviceToDevice, st));
   take_first_frame_mask_kernel<<<(unsigned)((BL + 255) / 256), 256, 0, st>>>(h->mask, B, T, L, h->mask_bl);
   h->has_cond = false;
+  h->emb_static_valid = false;
   if (x_cond) {
     MD_CHECK(cmask, "x_cond needs x_cond_mask");
     MD_CUDA(cudaMemcpyAsync(h->x_cond, x_cond, N * Dc * 4, cudaMemcpyDeviceToDevice, st));
@@ -1042,15 +1048,27 @@ static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state,
     MD_CHECK(DD <= 80, "latent_dim + cond_dim > 80 not supported by the embedding kernel");
     ProfScope ps(PC_EMBED, st);
     const dim3 grid((N + EMB_TOK - 1) / EMB_TOK);
+    if (!h->emb_static_valid) {
+      // step-invariant part, once per conditioning: W_c x_cond + biases + mask / position / time embeddings
+      // (embed_kernel with D = 0 reads only the conditioning rows of the transposed weight)
+      const int Ds = hc ? Dc : 0;
 #define MD_EMBED(DDP)                                                                                               \
-  embed_kernel<384, DDP><<<grid, 384, 0, st>>>(x, D, hc ? h->x_cond : nullptr, hc ? Dc : 0,                          \
-                                               hc ? h->cond_mask : nullptr, h->emb_wt, hc ? h->emb_bsum : h->emb_bx, \
-                                               me->d, pe ? pe->d : nullptr, te ? te->d : nullptr, ipa_out, h->xres, \
-                                               N, T, L)
-    if (DD <= 48) MD_EMBED(48);
-    else if (DD <= 64) MD_EMBED(64);
-    else MD_EMBED(80);
+  embed_kernel<384, DDP><<<grid, 384, 0, st>>>(nullptr, 0, hc ? h->x_cond : nullptr, Ds,                            \
+                                               hc ? h->cond_mask : nullptr, h->emb_wt + (size_t)D * C,              \
+                                               hc ? h->emb_bsum : h->emb_bx, me->d, pe ? pe->d : nullptr,           \
+                                               te ? te->d : nullptr, nullptr, h->emb_static, N, T, L)
+      if (Ds <= 48) MD_EMBED(48);
+      else if (Ds <= 64) MD_EMBED(64);
+      else MD_EMBED(80);
 #undef MD_EMBED
+      MD_LAUNCHED();
+      MD_CUDA(cudaGetLastError());
+      h->emb_static_valid = true;
+    }
+    const dim3 sgrid((N + EMB_STEP_TOK - 1) / EMB_STEP_TOK);
+    if (D <= 24) embed_step_kernel<384, 24, 4><<<sgrid, 96, 0, st>>>(x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L);
+    else if (D <= 48) embed_step_kernel<384, 48, 2><<<sgrid, 192, 0, st>>>(x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L);
+    else embed_step_kernel<384, 80, 1><<<sgrid, 384, 0, st>>>(x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L);
     MD_LAUNCHED();
     MD_CUDA(cudaGetLastError());
   }
