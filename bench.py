@@ -183,8 +183,15 @@ def run_gpu(a, rank, world, local_rank):
     # ---------------- device-resident arm ----------------
     kw_dev = kwargs_on(lambda v: v.to(dev))
     x0_dev = inp["x0"].to(dev)
+    if args.design:
+        # design mode: the per-step Dirichlet flow needs t-dependent host tables, so the rollout is the sampler loop
+        # over forward_inference (one mdgen_forward + one mdgen_dirichlet_flow per step) instead of the fused C-ABI call
+        _fn = Sampler(create_transport(args)).sample_ode(sampling_method="euler", num_steps=NUM_STEPS)
+        rollout = lambda: _fn(x0_dev, functools.partial(model.forward_inference, **kw_dev))[-1]
+    else:
+        rollout = lambda: model.euler_rollout(x0_dev, NUM_STEPS, **kw_dev)
     for _ in range(a.warmup):
-        model.euler_rollout(x0_dev, NUM_STEPS, **kw_dev)
+        rollout()
     clocks = ClockSampler(local_rank)
     clocks.start()
     l0 = _lib.lib().mdgen_launch_count()
@@ -192,7 +199,7 @@ def run_gpu(a, rank, world, local_rank):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(a.steps):
-        out = model.euler_rollout(x0_dev, NUM_STEPS, **kw_dev)
+        out = rollout()
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1) / a.steps)
@@ -228,7 +235,7 @@ def run_gpu(a, rank, world, local_rank):
     clocks.join(timeout=2)
     # ---------------- per-kernel-family timing (one extra profiled step) ----------------
     _lib.profile_begin()
-    model.euler_rollout(x0_dev, NUM_STEPS, **kw_dev)
+    rollout()
     prof = _lib.profile_end()
     if rank != 0:
         return

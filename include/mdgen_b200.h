@@ -109,6 +109,18 @@ int mdgen_forward(MdgenHandle* h, const float* x, const float* t, float* out,
 int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, float* traj,
                         float* out_final, mdgen_stream_t stream);
 
+/* Design mode: turns the logits in the last 20 channels of `latent` [B,T,L,D] (what mdgen_forward wrote) into the
+ * Dirichlet conditional-flow velocity, in place: the tail of LatentMDGenModel.forward_inference
+ * (latent_model.py:296-326) with DirichletConditionalFlow.c_factor (utils.py:45-57) evaluated on the device instead
+ * of through .cpu().numpy().  x [B,T,L,D] f32 (device) = the state the velocity was evaluated at; ifunc [1000] f64
+ * (device) = row of beta_cdfs_derivative nearest to alpha (utils.py:53); beta = B(alpha, 19); temp =
+ * args.dirichlet_flow_temp; dalpha = alpha_max - 1 (transport.py:52-57).  flags_out [2] i32 (host): tokens of x off
+ * the simplex (the reference prints a warning), NaN c-factors (the reference raises unless allow_nan_cfactor; with
+ * allow_nan != 0 they are replaced like torch.nan_to_num).  Synchronises the stream to read the flags. */
+int mdgen_dirichlet_flow(MdgenHandle* h, const float* x, float* latent, const double* ifunc, double alpha,
+                         double beta, float temp, float dalpha, int32_t allow_nan, int32_t* flags_out,
+                         mdgen_stream_t stream);
+
 /* introspection ------------------------------------------------------------------------ */
 /* Number of kernels one mdgen_forward launches for the current conditioning shape. */
 int mdgen_launches_per_forward(MdgenHandle* h);

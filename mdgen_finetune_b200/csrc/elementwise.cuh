@@ -226,6 +226,82 @@ embed_step_kernel(const float* __restrict__ x, int D, const float* __restrict__ 
   }
 }
 
+// ---- design mode: Dirichlet conditional-flow velocity of the 20 sequence channels -----------------------------
+// LatentMDGenModel.forward_inference (latent_model.py:279-326) with DirichletConditionalFlow.c_factor (utils.py:45-57)
+// on the device.  thread = token.  In place on `latent` [N, D]: the last 20 channels hold the logits on entry and
+//   flow_i = dalpha * sum_j softmax(logits / temp)_j * (delta_ij - x_i) * c_j        on exit,
+//   c_j = -interp(x_j; linspace(0, 1, 1000), ifunc) * [x_j^(alpha-1) > 0] * [x_j < 1] * beta / ((1 - x_j)^19 * x_j^(alpha-1))
+// with numpy's types: the powers in float32 (float32 array ** python scalar), the quotients and the interpolation in
+// float64, the result cast to float32.  `ifunc` = the row of d/dalpha I_b(alpha, 19) nearest to alpha, `beta` =
+// B(alpha, 19): both come from the host tables (scipy at model construction, like the reference).
+// flags[0] += tokens off the simplex (|sum - 1| > 1e-4 or a negative entry: the reference prints a warning),
+// flags[1] += NaN c-factors (RuntimeError in the reference unless allow_nan_cfactor, which maps them like nan_to_num).
+constexpr int DFLOW_K = 20, DFLOW_GRID = 1000;
+__global__ void dirichlet_flow_kernel(const float* __restrict__ x, float* __restrict__ latent, int N, int D,
+                                      const double* __restrict__ ifunc, float alpha_m1, double beta, float temp, float dalpha,
+                                      int allow_nan, int* __restrict__ flags) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= N) return;
+  const float* xd = x + (size_t)m * D + (D - DFLOW_K);
+  float* lg = latent + (size_t)m * D + (D - DFLOW_K);
+  float xv[DFLOW_K], p[DFLOW_K];
+  float sum = 0.f, mx = -INFINITY;
+  bool neg = false;
+#pragma unroll
+  for (int j = 0; j < DFLOW_K; ++j) {
+    xv[j] = xd[j];
+    sum += xv[j];
+    neg |= xv[j] < 0.f;
+    p[j] = lg[j] / temp;
+    mx = fmaxf(mx, p[j]);
+  }
+  if (neg || !(fabsf(sum - 1.0f) <= 1e-4f)) atomicAdd(&flags[0], 1);
+  float ps = 0.f;
+#pragma unroll
+  for (int j = 0; j < DFLOW_K; ++j) {
+    p[j] = expf(p[j] - mx);
+    ps += p[j];
+  }
+  float pc = 0.f;          // sum_j p_j c_j
+  float c[DFLOW_K];
+  int nans = 0;
+#pragma unroll
+  for (int j = 0; j < DFLOW_K; ++j) {
+    p[j] /= ps;
+    const float b = xv[j];
+    const float om = 1.0f - b;
+    float om19 = om;                                   // (1 - b)^19 in float32
+#pragma unroll
+    for (int e = 1; e < DFLOW_K - 1; ++e) om19 *= om;
+    const double beta_div = b < 1.0f ? beta / (double)om19 : 0.0;
+    const float bp = powf(b, alpha_m1);                // NaN for b < 0: the comparison below is false like numpy's
+    const double full = bp > 0.f ? beta_div / (double)bp : 0.0;
+    // np.interp on the uniform grid (clamped at both ends)
+    const double bd = (double)b;
+    double iv;
+    if (!(bd > 0.0)) iv = ifunc[0];
+    else if (bd >= 1.0) iv = ifunc[DFLOW_GRID - 1];
+    else {
+      int k = (int)(bd * (DFLOW_GRID - 1));
+      k = k > DFLOW_GRID - 2 ? DFLOW_GRID - 2 : k;
+      const double x0 = (double)k / (DFLOW_GRID - 1), x1 = (double)(k + 1) / (DFLOW_GRID - 1);
+      iv = (ifunc[k + 1] - ifunc[k]) / (x1 - x0) * (bd - x0) + ifunc[k];
+    }
+    float cj = (float)(-iv * full);
+    if (isnan(cj)) {
+      ++nans;
+      if (allow_nan) cj = 0.f;
+    } else if (allow_nan && isinf(cj)) {
+      cj = cj > 0.f ? 3.4028234663852886e38f : -3.4028234663852886e38f;
+    }
+    c[j] = cj;
+    pc += p[j] * cj;
+  }
+  if (nans) atomicAdd(&flags[1], nans);
+#pragma unroll
+  for (int i = 0; i < DFLOW_K; ++i) lg[i] = (p[i] * c[i] - xv[i] * pc) * dalpha;
+}
+
 // WT[d, c] = d < D ? Wx[c, d] : Wc[c, d - D];  bsum[c] = bx[c] + bc[c]
 __global__ void pack_embed_weights_kernel(const float* __restrict__ Wx, int D, const float* __restrict__ Wc, int Dc,
                                           const float* __restrict__ bx, const float* __restrict__ bc, int C,

@@ -1266,6 +1266,28 @@ int mdgen_set_conditioning(MdgenHandle* h, int32_t B, int32_t T, int32_t L, cons
                           x_cond_mask, aatype, (cudaStream_t)stream);
 }
 
+int mdgen_dirichlet_flow(MdgenHandle* h, const float* x, float* latent, const double* ifunc, double alpha, double beta,
+                         float temp, float dalpha, int32_t allow_nan, int32_t* flags_out, mdgen_stream_t stream) {
+  MD_CHECK(h && x && latent && ifunc && flags_out, "null argument");
+  MD_CHECK(h->flag(MDGEN_F_DESIGN), "mdgen_dirichlet_flow: the model was not created with the design flag");
+  MD_CHECK(h->B > 0, "mdgen_dirichlet_flow: set_conditioning has not been called");
+  MD_CHECK(h->D() > DFLOW_K && temp > 0.f, "mdgen_dirichlet_flow: bad latent_dim / temperature");
+  DeviceGuard g(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int N = h->B * h->T * h->L;
+  int* dflags = nullptr;
+  MD_CUDA(cudaMallocAsync((void**)&dflags, 2 * sizeof(int), st));
+  MD_CUDA(cudaMemsetAsync(dflags, 0, 2 * sizeof(int), st));
+  dirichlet_flow_kernel<<<(N + 127) / 128, 128, 0, st>>>(x, latent, N, h->D(), ifunc, (float)(alpha - 1.0), beta, temp, dalpha,
+                                                       allow_nan, dflags);
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  MD_CUDA(cudaMemcpyAsync(flags_out, dflags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  MD_CUDA(cudaFreeAsync(dflags, st));
+  MD_CUDA(cudaStreamSynchronize(st));
+  return MDGEN_OK;
+}
+
 int mdgen_forward(MdgenHandle* h, const float* x, const float* t, float* out, mdgen_stream_t stream) {
   MD_CHECK(h && x && t && out, "null argument");
   if (!h->finalized || h->B == 0) {

@@ -130,6 +130,40 @@ def _rel7_eigh(start, end):
     return one(*start, *end), one(*end, *start)
 
 
+class _DirichletFlowTables:
+    """Host tables of mdgen.utils.DirichletConditionalFlow (utils.py:33-43) -- scipy, like the reference; the
+    arithmetic that uses them (c_factor, utils.py:45-57) runs in dirichlet_flow_kernel.  One row (the alpha nearest
+    to the requested one, utils.py:53) is uploaded per distinct alpha and cached."""
+
+    def __init__(self, K=20, alpha_min=1, alpha_max=100, alpha_spacing=0.01):
+        import numpy as np
+        import scipy.special
+        self.alphas = np.arange(alpha_min, alpha_max + alpha_spacing, alpha_spacing)
+        self.bs = np.linspace(0, 1, 1000)
+        cdfs = np.array([scipy.special.betainc(al, K - 1, self.bs) for al in self.alphas])
+        self.beta_cdfs_derivative = np.diff(cdfs, axis=0) / alpha_spacing
+        self.alpha_spacing = alpha_spacing
+        self.K = K
+        self._rows = {}
+
+    def index(self, alpha):
+        import numpy as np
+        return int(np.argmin(np.abs(alpha - self.alphas)))
+
+    def row(self, alpha, device):
+        i = self.index(alpha)
+        key = (i, str(device))
+        if key not in self._rows:
+            if len(self._rows) > 256:
+                self._rows.clear()
+            self._rows[key] = torch.from_numpy(self.beta_cdfs_derivative[i].copy()).to(device=device, dtype=torch.float64)
+        return self._rows[key]
+
+    def beta(self, alpha):
+        import scipy.special
+        return float(scipy.special.beta(alpha, self.K - 1))
+
+
 class LatentMDGenModel(nn.Module):
     """Drop-in for mdgen.model.latent_model.LatentMDGenModel (latent_model.py:43)."""
 
@@ -145,6 +179,7 @@ class LatentMDGenModel(nn.Module):
         assert quat_sign in ("eigh", "eigh_cpu", "closed_form")
         self.precision = precision
         self.quat_sign = quat_sign
+        self._condflow = None
         self.latent_dim = latent_dim
         C = args.embed_dim
         self.latent_to_emb = nn.Linear(latent_dim, C)
@@ -343,8 +378,43 @@ class LatentMDGenModel(nn.Module):
         """latent_model.py:272-326.  Non-design: pass-through to forward."""
         if not self.args.design:
             return self.forward(x, t, mask, start_frames, end_frames, x_cond, x_cond_mask, aatype)
-        raise NotImplementedError("design-mode Dirichlet conditional flow (latent_model.py:279-326) is row N3 "
-                                  "of DESIGN.md; forward() (latent + logits) is available")
+        # ---- design: logits -> Dirichlet conditional-flow velocity of the 20 sequence channels (:279-326).
+        # forward() leaves latent[..., -20:] = logits; the softmax, c_factor and the flow reduction run in one CUDA
+        # kernel (mdgen_dirichlet_flow) instead of the reference's .cpu().numpy() round trip.
+        latent = self.forward(x, t, mask, start_frames, end_frames, x_cond, x_cond_mask, aatype)
+        dev = self.device
+        xx = x.detach().to(dev, torch.float32).contiguous()
+        a = self.args
+        t0 = float(t.reshape(-1)[0])
+        alpha = 1.0 * (1.0 - t0) + t0 * a.alpha_max                       # transport.py:52-57 (t_to_alpha)
+        dalpha = float(a.alpha_max - 1)
+        cf = self.condflow
+        if alpha > a.alpha_max:                                           # :308-309
+            alpha = a.alpha_max - cf.alpha_spacing
+        row = cf.row(alpha, dev)
+        flags = (ctypes.c_int32 * 2)()
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().mdgen_dirichlet_flow(
+                self._handle, xx.data_ptr(), latent.data_ptr(), row.data_ptr(), alpha, cf.beta(alpha),
+                float(a.dirichlet_flow_temp), dalpha, int(bool(getattr(a, "allow_nan_cfactor", False))), flags,
+                self._stream()), "mdgen_dirichlet_flow")
+        if flags[0]:                                                      # :282-290
+            print(f"WARNING: {flags[0]} positions of xt do not lie on the simplex (negative entries or sum != 1).")
+        if flags[1]:                                                      # :312-319
+            print(f"NAN cfactor: {flags[1]} entries")
+            if not getattr(a, "allow_nan_cfactor", False):
+                raise RuntimeError(f"NAN cfactor: {flags[1]} entries")
+        return latent
+
+    @property
+    def condflow(self):
+        """DirichletConditionalFlow tables (utils.py:33-43; built by the reference constructor, latent_model.py:124-126,
+        here on first use): d/dalpha of the regularised incomplete beta function on a 1000-point grid."""
+        if not self.args.design:
+            raise AttributeError("condflow exists only in design mode (latent_model.py:124)")
+        if self._condflow is None:
+            self._condflow = _DirichletFlowTables(K=20, alpha_spacing=0.001, alpha_max=self.args.alpha_max)
+        return self._condflow
 
     @torch.no_grad()
     def euler_rollout(self, x0, num_steps=50, return_trajectory=False, **model_kwargs):
