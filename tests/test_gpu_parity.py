@@ -88,6 +88,40 @@ def test_design_euler_rollout_vs_reference_sampler(prec):
     assert m.condflow.K == 20 and m.condflow.alpha_spacing == 0.001
 
 
+@pytest.mark.parametrize("tv", [0.0, 0.37, 48 / 49])   # t = 1 indexes past the derivative table in the reference too
+def test_dirichlet_flow_kernel_edge_cases(tv, capsys):
+    """mdgen_dirichlet_flow against the oracle's c_factor / flow arithmetic (utils.py:45-57, latent_model.py:296-324)
+    on states with exact zeros, a vertex of the simplex, slightly negative entries and rows that do not sum to one."""
+    import torch.nn.functional as F
+    g, c, args, sd, inp = load_case("design_small")
+    args.allow_nan_cfactor = True
+    m = build(args, c["D"], sd, "fp32")
+    kw = gpu_kwargs(inp)
+    x = inp["x0"].clone()
+    xd = x[..., -20:]
+    xd[0, 0, 0] = 0.0
+    xd[0, 0, 0, 3] = 1.0                       # a vertex: zeros and a one
+    xd[0, 0, 1, :2] = torch.tensor([-1e-3, 1e-3]) + xd[0, 0, 1, :2]      # slightly outside the simplex
+    xd[0, 1, 0] = xd[0, 1, 0] * 1.01           # does not sum to one
+    xd[1, 0, 0, 5] = 0.0                       # one exact zero
+    t = torch.full((c["B"],), tv)
+    with torch.no_grad():
+        raw = m.forward(x.cuda(), t.cuda(), **kw).cpu()
+        v = m.forward_inference(x.cuda(), t.cuda(), **kw).cpu()
+    assert "simplex" in capsys.readouterr().out                       # the reference's warning (latent_model.py:282-290)
+    tab = O.DirichletFlowTables(alpha_max=args.alpha_max)
+    alpha = float(1 * (1 - tv) + tv * args.alpha_max)
+    if alpha > args.alpha_max:
+        alpha = args.alpha_max - tab.alpha_spacing
+    cf = torch.nan_to_num(torch.from_numpy(tab.c_factor(xd.numpy(), alpha)).to(xd))
+    probs = F.softmax(raw[..., -20:] / args.dirichlet_flow_temp, -1)
+    cond = (torch.eye(20) - xd.unsqueeze(-1)) * cf.unsqueeze(-2)
+    flow = (probs.unsqueeze(-2) * cond).sum(-1) * (args.alpha_max - 1)
+    assert torch.isfinite(v).all()
+    assert torch.equal(v[..., :-20], raw[..., :-20])
+    assert rel_l2(v[..., -20:], flow) < 1e-4, rel_l2(v[..., -20:], flow)
+
+
 def test_closed_form_quaternion_matches_eigh_up_to_sign():
     g, c, args, sd, inp = load_case("tps_small")
     start, end = frames_of(inp)
