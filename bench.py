@@ -183,13 +183,7 @@ def run_gpu(a, rank, world, local_rank):
     # ---------------- device-resident arm ----------------
     kw_dev = kwargs_on(lambda v: v.to(dev))
     x0_dev = inp["x0"].to(dev)
-    if args.design:
-        # design mode: the per-step Dirichlet flow needs t-dependent host tables, so the rollout is the sampler loop
-        # over forward_inference (one mdgen_forward + one mdgen_dirichlet_flow per step) instead of the fused C-ABI call
-        _fn = Sampler(create_transport(args)).sample_ode(sampling_method="euler", num_steps=NUM_STEPS)
-        rollout = lambda: _fn(x0_dev, functools.partial(model.forward_inference, **kw_dev))[-1]
-    else:
-        rollout = lambda: model.euler_rollout(x0_dev, NUM_STEPS, **kw_dev)
+    rollout = lambda: model.euler_rollout(x0_dev, NUM_STEPS, **kw_dev)   # design mode: Dirichlet flow applied per step inside
     for _ in range(a.warmup):
         rollout()
     clocks = ClockSampler(local_rank)

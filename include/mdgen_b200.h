@@ -121,6 +121,15 @@ int mdgen_dirichlet_flow(MdgenHandle* h, const float* x, float* latent, const do
                          double beta, float temp, float dalpha, int32_t allow_nan, int32_t* flags_out,
                          mdgen_stream_t stream);
 
+/* Design-mode sampler: the tables mdgen_euler_rollout needs to apply the Dirichlet flow at every step of the next
+ * rollout (nt = num_steps - 1).  HOST pointers: rows [nt, 1000] f64 (the beta_cdfs_derivative row nearest to alpha_i,
+ * utils.py:53), alphas [nt], betas [nt] (B(alpha_i, 19)); temp / dalpha / allow_nan as in mdgen_dirichlet_flow.
+ * After the rollout mdgen_dirichlet_flags returns the counters accumulated over all steps (off-simplex tokens,
+ * NaN c-factors): the reference warns / raises at the step where they occur, the fused rollout at its end. */
+int mdgen_set_dirichlet_tables(MdgenHandle* h, int32_t nt, const double* rows, const double* alphas,
+                               const double* betas, float temp, float dalpha, int32_t allow_nan);
+int mdgen_dirichlet_flags(MdgenHandle* h, int32_t* flags_out, mdgen_stream_t stream);
+
 /* introspection ------------------------------------------------------------------------ */
 /* Number of kernels one mdgen_forward launches for the current conditioning shape. */
 int mdgen_launches_per_forward(MdgenHandle* h);

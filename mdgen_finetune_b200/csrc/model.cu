@@ -325,6 +325,15 @@ struct MdgenHandle {
   std::vector<MainLayerW> layers;
   LinearW final_lin, design_fc1, design_fc2, design_fc3, design_logits;
   float *emb_wt = nullptr, *emb_bsum = nullptr, *emb_bx = nullptr;  // transposed [D+Dc, C] embedding weights
+  // design-mode sampler: per-step Dirichlet-flow tables of the next mdgen_euler_rollout (mdgen_set_dirichlet_tables)
+  double* dflow_rows = nullptr;    // device [nt, 1000]
+  int* dflow_flags = nullptr;      // device [2]: off-simplex tokens, NaN c-factors (accumulated over the rollout)
+  int dflow_nt = 0;
+  int dflow_step = 0;              // sampler step of the evaluation in flight (its time tables hold a single row)
+  std::vector<float> dflow_am1;    // alpha_i - 1 per step
+  std::vector<double> dflow_beta;  // B(alpha_i, 19)
+  float dflow_temp = 1.f, dflow_dalpha = 0.f;
+  int dflow_allow_nan = 0;
   float* emb_static = nullptr;     // [N, C] step-invariant part of the token embedding (per conditioning)
   bool emb_static_valid = false;
   float* ada_w = nullptr;  // [ada_cols, C]
@@ -1122,6 +1131,14 @@ static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state,
     add_logits_kernel<<<(N * 20 + 255) / 256, 256, 0, st>>>(out, D, h->dh_logits, B, T, L);
     MD_LAUNCHED();
     if (state) {
+      // sampler step: logits -> Dirichlet conditional-flow velocity (forward_inference, latent_model.py:296-326),
+      // evaluated at the current state, then the Euler update
+      const int ds = h->dflow_step;
+      MD_CHECK(h->dflow_nt > ds && h->dflow_rows, "design-mode rollout without Dirichlet tables (mdgen_set_dirichlet_tables)");
+      dirichlet_flow_kernel<<<(N + 127) / 128, 128, 0, st>>>(state, out, N, D, h->dflow_rows + (size_t)ds * DFLOW_GRID,
+                                                           h->dflow_am1[ds], h->dflow_beta[ds], h->dflow_temp,
+                                                           h->dflow_dalpha, h->dflow_allow_nan, h->dflow_flags);
+      MD_LAUNCHED();
       axpy_kernel<<<(unsigned)(((size_t)N * D + 255) / 256), 256, 0, st>>>(state, out, dt, (size_t)N * D);
       MD_LAUNCHED();
     }
@@ -1155,10 +1172,16 @@ static int rollout_impl(MdgenHandle* h, float* state, int num_steps, float* traj
   }
   MD_CUDA(cudaMemcpyAsync(h->tbuf, tv.data(), tv.size() * 4, cudaMemcpyHostToDevice, st));
   MD_CUDA(cudaStreamSynchronize(st));   // tv is a stack-lifetime host buffer
-  MD_TRY(time_tables<AT>(f, h->tbuf, nt, nullptr));
+  // design mode: the IPA input embeds x_d = mean_T x[..., -20:], so the time tables are rebuilt from the state at every step
+  const bool design = h->flag(MDGEN_F_DESIGN);
+  if (!design) MD_TRY(time_tables<AT>(f, h->tbuf, nt, nullptr));
   for (int i = 0; i < nt; ++i) {
     const long long l0 = g_launches;
-    MD_TRY(trunk<AT>(f, state, i, h->vel, state, dts[i]));
+    if (design) {
+      MD_TRY(time_tables<AT>(f, h->tbuf + (size_t)i * B, 1, state));
+      h->dflow_step = i;
+    }
+    MD_TRY(trunk<AT>(f, state, design ? 0 : i, h->vel, state, dts[i]));
     h->launches_last_forward = (int)(g_launches - l0);
     if (traj) MD_CUDA(cudaMemcpyAsync(traj + (size_t)(i + 1) * n, state, n * 4, cudaMemcpyDeviceToDevice, st));
   }
@@ -1225,6 +1248,8 @@ int mdgen_destroy(MdgenHandle* h) {
   free_workspace(h);
   for (void* p : h->packed) cudaFree(p);
   for (auto& kv : h->weights) cudaFree(kv.second.d);
+  if (h->dflow_rows) cudaFree(h->dflow_rows);
+  if (h->dflow_flags) cudaFree(h->dflow_flags);
   delete h;
   return MDGEN_OK;
 }
@@ -1264,6 +1289,41 @@ int mdgen_set_conditioning(MdgenHandle* h, int32_t B, int32_t T, int32_t L, cons
   DeviceGuard g(h->device);
   return set_conditioning(h, B, T, L, mask, start_rot, start_trans, end_rot, end_trans, rel_f7, rel_r7, x_cond,
                           x_cond_mask, aatype, (cudaStream_t)stream);
+}
+
+int mdgen_set_dirichlet_tables(MdgenHandle* h, int32_t nt, const double* rows, const double* alphas, const double* betas,
+                               float temp, float dalpha, int32_t allow_nan) {
+  MD_CHECK(h && nt > 0 && rows && alphas && betas && temp > 0.f, "bad argument");
+  MD_CHECK(h->flag(MDGEN_F_DESIGN), "mdgen_set_dirichlet_tables: the model was not created with the design flag");
+  DeviceGuard g(h->device);
+  if (nt > h->dflow_nt || !h->dflow_rows) {
+    if (h->dflow_rows) cudaFree(h->dflow_rows);
+    h->dflow_rows = nullptr;
+    h->dflow_nt = 0;
+    MD_CUDA(cudaMalloc((void**)&h->dflow_rows, (size_t)nt * DFLOW_GRID * sizeof(double)));
+  }
+  if (!h->dflow_flags) MD_CUDA(cudaMalloc((void**)&h->dflow_flags, 2 * sizeof(int)));
+  MD_CUDA(cudaMemcpy(h->dflow_rows, rows, (size_t)nt * DFLOW_GRID * sizeof(double), cudaMemcpyHostToDevice));
+  MD_CUDA(cudaMemset(h->dflow_flags, 0, 2 * sizeof(int)));
+  h->dflow_am1.resize(nt);
+  h->dflow_beta.assign(betas, betas + nt);
+  for (int i = 0; i < nt; ++i) h->dflow_am1[i] = (float)(alphas[i] - 1.0);
+  h->dflow_nt = nt;
+  h->dflow_temp = temp;
+  h->dflow_dalpha = dalpha;
+  h->dflow_allow_nan = allow_nan;
+  return MDGEN_OK;
+}
+
+int mdgen_dirichlet_flags(MdgenHandle* h, int32_t* flags_out, mdgen_stream_t stream) {
+  MD_CHECK(h && flags_out, "null argument");
+  flags_out[0] = flags_out[1] = 0;
+  if (!h->dflow_flags) return MDGEN_OK;
+  DeviceGuard g(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  MD_CUDA(cudaMemcpyAsync(flags_out, h->dflow_flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  MD_CUDA(cudaStreamSynchronize(st));
+  return MDGEN_OK;
 }
 
 int mdgen_dirichlet_flow(MdgenHandle* h, const float* x, float* latent, const double* ifunc, double alpha, double beta,
@@ -1340,9 +1400,12 @@ int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, floa
     set_error("mdgen_euler_rollout before finalize_weights / set_conditioning");
     return MDGEN_ESTATE;
   }
-  MD_CHECK(!h->flag(MDGEN_F_DESIGN), "design-mode Dirichlet flow sampler not implemented (DESIGN.md, row N3)");
   DeviceGuard g(h->device);
   cudaStream_t st = (cudaStream_t)stream;
+  if (h->flag(MDGEN_F_DESIGN)) {
+    MD_CHECK(h->dflow_nt == num_steps - 1, "design-mode rollout: call mdgen_set_dirichlet_tables for num_steps - 1 steps first");
+    MD_CUDA(cudaMemsetAsync(h->dflow_flags, 0, 2 * sizeof(int), st));
+  }
   const size_t n = (size_t)h->B * h->T * h->L * h->D();
   if (out_final != x0) MD_CUDA(cudaMemcpyAsync(out_final, x0, n * 4, cudaMemcpyDeviceToDevice, st));
   if (traj) MD_CUDA(cudaMemcpyAsync(traj, x0, n * 4, cudaMemcpyDeviceToDevice, st));

@@ -385,12 +385,9 @@ class LatentMDGenModel(nn.Module):
         dev = self.device
         xx = x.detach().to(dev, torch.float32).contiguous()
         a = self.args
-        t0 = float(t.reshape(-1)[0])
-        alpha = 1.0 * (1.0 - t0) + t0 * a.alpha_max                       # transport.py:52-57 (t_to_alpha)
-        dalpha = float(a.alpha_max - 1)
         cf = self.condflow
-        if alpha > a.alpha_max:                                           # :308-309
-            alpha = a.alpha_max - cf.alpha_spacing
+        alpha = self._alpha_of(t.reshape(-1)[0])
+        dalpha = float(a.alpha_max - 1)
         row = cf.row(alpha, dev)
         flags = (ctypes.c_int32 * 2)()
         with torch.cuda.device(dev):
@@ -398,13 +395,25 @@ class LatentMDGenModel(nn.Module):
                 self._handle, xx.data_ptr(), latent.data_ptr(), row.data_ptr(), alpha, cf.beta(alpha),
                 float(a.dirichlet_flow_temp), dalpha, int(bool(getattr(a, "allow_nan_cfactor", False))), flags,
                 self._stream()), "mdgen_dirichlet_flow")
-        if flags[0]:                                                      # :282-290
+        self._report_flow_flags(flags)
+        return latent
+
+    def _alpha_of(self, t0):
+        """t_to_alpha (transport.py:52-57) on t[0] in the tensor's own precision, then .item() and the clamp of
+        latent_model.py:305-309."""
+        t0 = torch.as_tensor(t0, dtype=torch.float32).detach().cpu()
+        alpha = (1 * (1 - t0) + t0 * self.args.alpha_max).item()
+        if alpha > self.args.alpha_max:
+            alpha = self.args.alpha_max - self.condflow.alpha_spacing
+        return alpha
+
+    def _report_flow_flags(self, flags):
+        if flags[0]:                                                      # latent_model.py:282-290
             print(f"WARNING: {flags[0]} positions of xt do not lie on the simplex (negative entries or sum != 1).")
         if flags[1]:                                                      # :312-319
             print(f"NAN cfactor: {flags[1]} entries")
-            if not getattr(a, "allow_nan_cfactor", False):
+            if not getattr(self.args, "allow_nan_cfactor", False):
                 raise RuntimeError(f"NAN cfactor: {flags[1]} entries")
-        return latent
 
     @property
     def condflow(self):
@@ -428,10 +437,28 @@ class LatentMDGenModel(nn.Module):
         xx = x0.detach().to(dev, torch.float32).contiguous()
         out = torch.empty_like(xx)
         traj = torch.empty((num_steps,) + tuple(xx.shape), device=dev) if return_trajectory else None
+        design = bool(self.args.design)
+        if design:
+            # per-step Dirichlet-flow tables (forward_inference, latent_model.py:305-311): alpha_i of the grid times,
+            # the nearest beta-CDF-derivative row and B(alpha_i, 19); the flow itself runs inside the fused rollout
+            cf, a = self.condflow, self.args
+            grid = torch.linspace(0, 1, num_steps)                      # integrators.py:90
+            alphas = np.array([self._alpha_of(grid[i]) for i in range(num_steps - 1)], dtype=np.float64)
+            rows = np.ascontiguousarray(np.stack([cf.beta_cdfs_derivative[cf.index(al)] for al in alphas]), dtype=np.float64)
+            betas = np.array([cf.beta(al) for al in alphas], dtype=np.float64)
+            with torch.cuda.device(dev):
+                _lib.check(_lib.lib().mdgen_set_dirichlet_tables(
+                    self._handle, num_steps - 1, rows.ctypes.data, alphas.ctypes.data, betas.ctypes.data,
+                    float(a.dirichlet_flow_temp), float(a.alpha_max - 1),
+                    int(bool(getattr(a, "allow_nan_cfactor", False)))), "mdgen_set_dirichlet_tables")
         with torch.cuda.device(dev):
             _lib.check(_lib.lib().mdgen_euler_rollout(
                 self._handle, xx.data_ptr(), int(num_steps), None if traj is None else traj.data_ptr(),
                 out.data_ptr(), self._stream()), "mdgen_euler_rollout")
+            if design:      # the reference warns / raises at the offending step; the fused rollout reports at its end
+                flags = (ctypes.c_int32 * 2)()
+                _lib.check(_lib.lib().mdgen_dirichlet_flags(self._handle, flags, self._stream()), "mdgen_dirichlet_flags")
+                self._report_flow_flags(flags)
         return traj if return_trajectory else out
 
     def launches_per_forward(self):

@@ -68,8 +68,8 @@ def _unwrap_native(model):
         owner = fn
     elif not (isinstance(owner, LatentMDGenModel) and fn.__name__ in ("forward", "forward_inference", "__call__")):
         return None, None
-    if owner.args.design:
-        return None, None
+    if owner.args.design and getattr(fn, "__name__", "") != "forward_inference":
+        return None, None            # design: only forward_inference carries the Dirichlet flow the fused rollout applies
     return owner, kw
 
 

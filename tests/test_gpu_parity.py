@@ -86,6 +86,9 @@ def test_design_euler_rollout_vs_reference_sampler(prec):
     assert torch.isfinite(traj).all()
     assert rel_l2(traj[-1], g["euler_final"]) < TOL[prec] * 2, rel_l2(traj[-1], g["euler_final"])
     assert m.condflow.K == 20 and m.condflow.alpha_spacing == 0.001
+    # the generic python loop (one mdgen_forward + one mdgen_dirichlet_flow per step) must agree with the fused rollout
+    loop = fn(inp["x0"].cuda(), lambda x, t, **k: m.forward_inference(x, t, **kw)).cpu()
+    assert rel_l2(loop[-1], traj[-1]) < (1e-5 if prec == "fp32" else 2e-3), rel_l2(loop[-1], traj[-1])
 
 
 @pytest.mark.parametrize("tv", [0.0, 0.37, 48 / 49])   # t = 1 indexes past the derivative table in the reference too
