@@ -156,3 +156,24 @@ def test_full_size_config1_velocity_and_launch_count():
             v = m.forward(inp["x0"].cuda(), t.cuda(), **kw).cpu()
         assert rel_l2(v, g["v_t0"]) < TOL[prec], (prec, rel_l2(v, g["v_t0"]))
         assert m.launches_per_forward() > 0
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_full_size_config1_rollout_ca_rmsd(prec):
+    """north_star: a 1000-frame deterministic Euler rollout (config 1: B = 1, T = 1000, L = 4, 49 steps) stays within
+    0.05 A coordinate RMSD per frame of the reference's own sampler (golden `euler_final`).  Coordinates compared here
+    are the residue frame origins (C-alpha): decode composes the first frame with the offset, frames = rigids[:, 0:1]
+    .compose(Rigid.from_tensor_7(latent[..., :7])) (wrapper.py:497-500), so a C-alpha displacement is the (rotated)
+    difference of the translation channels latent[..., 4:7], in Angstrom.  The side-chain atoms need the torsion
+    decode with the residue tables (row N2)."""
+    g, c, args, sd, inp = load_case("sim_full")
+    m = build(args, c["D"], sd, prec)
+    kw = gpu_kwargs(inp)
+    with torch.no_grad():
+        out = m.euler_rollout(inp["x0"].cuda(), g["euler_steps"], **kw).cpu()
+    ref = g["euler_final"]
+    assert rel_l2(out, ref) < TOL[prec] * 2, rel_l2(out, ref)
+    d = out[..., 4:7] - ref[..., 4:7]                                  # [B, T, L, 3] Angstrom
+    rmsd = d.pow(2).sum(-1).mean(-1).sqrt()                            # per frame, over the residues
+    print(f"C-alpha RMSD per frame [{prec}]: max {float(rmsd.max()):.4g} A, mean {float(rmsd.mean()):.4g} A")
+    assert float(rmsd.max()) < 0.05, float(rmsd.max())
