@@ -41,6 +41,25 @@ class ClockSampler(threading.Thread):
         self.idx, self.stop_flag, self.rows = idx, False, []
 
     def run(self):
+        # NVML in-process: forking nvidia-smi out of a process with a CUDA context every 200 ms stalled the launching
+        # thread for milliseconds at a time (one device-arm measurement came out 10 % slow); nvidia-smi is the fallback
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.idx)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            bits = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+            while not self.stop_flag:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                except Exception:
+                    r = 0
+                self.rows.append([str(sm), str(mx)] + ["Active" if r & bit else "Not Active" for _, bit in bits])
+                time.sleep(0.1)
+            return
+        except Exception:
+            pass
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         while not self.stop_flag:
@@ -51,7 +70,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([c.strip() for c in o.split(",")])
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.5)
 
     def summary(self):
         if not self.rows:
@@ -184,10 +203,17 @@ def run_gpu(a, rank, world, local_rank):
     kw_dev = kwargs_on(lambda v: v.to(dev))
     x0_dev = inp["x0"].to(dev)
     rollout = lambda: model.euler_rollout(x0_dev, NUM_STEPS, **kw_dev)   # design mode: Dirichlet flow applied per step inside
-    for _ in range(a.warmup):
-        rollout()
     clocks = ClockSampler(local_rank)
-    clocks.start()
+    clocks.start()                  # NVML initialises during the warm-up, not inside the timed region
+    # warm-up: the W requested steps, and at least ~1.5 s of load -- on a fresh box the first process measured 3 % slow
+    # with only W = 3 rollouts (0.34 s) of warm-up (clock / power state ramp, first-touch of the workspace)
+    t_warm = time.perf_counter()
+    n_warm = 0
+    while n_warm < a.warmup or time.perf_counter() - t_warm < 1.5:
+        rollout()
+        torch.cuda.synchronize(dev)
+        n_warm += 1
+    clocks.rows.clear()             # keep only the samples taken under the timed load
     l0 = _lib.lib().mdgen_launch_count()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
