@@ -357,3 +357,76 @@ def rerandomize_zero_params(sd, seed=0, std=0.02):
         if v.dtype.is_floating_point and v.numel() > 1 and not v.any() and "pos_embed" not in k:
             sd[k] = torch.randn(v.shape, generator=g) * std
     return sd
+
+
+# ------------------------------------------------------------------------------------
+# prep_batch (wrapper.py:283-365): trajectory frames -> latents + conditioning, the step before the sampler
+DESIGN_IDX = [1, 2]                 # wrapper.py:41-43
+COND_IDX = [0, 3]
+DESIGN_MAP_TO_COND = [0, 0, 3, 3]
+
+
+def get_offsets(ref_rot, ref_trans, rot, trans):
+    """utils.get_offsets (utils.py:7-14): ref^-1 o rigids as 7-vectors, then the sign fix of wrapper.py:308-309
+    (quaternion real part >= 0), which also removes the sign ambiguity of the eigenvector in rot_to_quat."""
+    ri, ti = rigid_invert(ref_rot, ref_trans)
+    off = to_tensor_7(*rigid_compose(ri, ti, rot, trans))
+    sign = torch.where(off[..., 0:1] < 0, -1.0, 1.0)
+    return torch.cat([off[..., :4] * sign, off[..., 4:]], -1)
+
+
+def prep_batch(args, batch):
+    """NewMDGenWrapper.prep_batch (wrapper.py:283-365), frames path (no --no_frames, no hyena latents).
+    batch: trans [B,T,L,3], rots [B,T,L,3,3], torsions [B,T,L,7,2], torsion_mask [B,L,7], mask [B,L], seqres [B,L]."""
+    rot, trans = batch["rots"], batch["trans"]
+    B, T, L = trans.shape[:3]
+    if getattr(args, "design_key_frames", False):                                     # :296-302
+        idx = torch.tensor(DESIGN_MAP_TO_COND)
+        rot = torch.cat([rot[:, :1, idx], rot[:, 1:-1], rot[:, -1:, idx]], 1)
+        trans = torch.cat([trans[:, :1, idx], trans[:, 1:-1], trans[:, -1:, idx]], 1)
+    if getattr(args, "no_offsets", False):                                            # :304-305
+        offsets = get_offsets(torch.eye(3).expand(B, 1, L, 3, 3), torch.zeros(B, 1, L, 3), rot, trans)
+    else:
+        offsets = get_offsets(rot[:, 0:1], trans[:, 0:1], rot, trans)                 # :307-309
+    frame_loss_mask = batch["mask"].unsqueeze(-1).expand(-1, -1, 7)
+    torsion_loss_mask = batch["torsion_mask"].unsqueeze(-1).expand(-1, -1, -1, 2).reshape(B, L, 14)
+    if args.tps_condition or args.inpainting or getattr(args, "dynamic_mpnn", False):  # :314-318
+        offsets = torch.cat([offsets, get_offsets(rot[:, -1:], trans[:, -1:], rot, trans)], -1)
+        frame_loss_mask = torch.cat([frame_loss_mask, frame_loss_mask], -1)
+    tors = batch["torsions"].reshape(B, T, L, 14)
+    if getattr(args, "no_torsion", False):                                            # :320-327
+        tors = torch.zeros_like(tors)
+    elif getattr(args, "no_design_torsion", False):
+        tors = tors.clone()
+        tors[:, :, DESIGN_IDX] = 0
+    latents = torch.cat([offsets, tors], -1)
+    if getattr(args, "supervise_all_torsions", False):                                # :329-332
+        torsion_loss_mask = torch.ones_like(torsion_loss_mask)
+    elif getattr(args, "supervise_no_torsions", False):
+        torsion_loss_mask = torch.zeros_like(torsion_loss_mask)
+    loss_mask = torch.cat([frame_loss_mask, torsion_loss_mask], -1).unsqueeze(1).expand(-1, T, -1, -1)
+    cond_mask = torch.zeros(B, T, L, dtype=torch.int64)                               # :338-346
+    if args.sim_condition:
+        cond_mask[:, 0] = 1
+    if args.tps_condition:
+        cond_mask[:, 0] = cond_mask[:, -1] = 1
+    if getattr(args, "cond_interval", None):
+        cond_mask[:, ::args.cond_interval] = 1
+    if args.inpainting or getattr(args, "dynamic_mpnn", False) or getattr(args, "mpnn", False):
+        cond_mask[:, :, COND_IDX] = 1
+    aatype_mask = torch.ones_like(batch["seqres"])
+    if args.design:
+        aatype_mask[:, DESIGN_IDX] = 0
+    return {
+        "rigids": (rot, trans),
+        "latents": latents,
+        "loss_mask": loss_mask,
+        "model_kwargs": {
+            "start_frames": (rot[:, 0], trans[:, 0]),
+            "end_frames": (rot[:, -1], trans[:, -1]),
+            "mask": batch["mask"].unsqueeze(1).expand(-1, T, -1),
+            "aatype": torch.where(aatype_mask.bool(), batch["seqres"], 20),
+            "x_cond": torch.where(cond_mask.unsqueeze(-1).bool(), latents, 0.0),
+            "x_cond_mask": cond_mask,
+        },
+    }
