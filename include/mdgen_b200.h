@@ -130,6 +130,15 @@ int mdgen_set_dirichlet_tables(MdgenHandle* h, int32_t nt, const double* rows, c
                                const double* betas, float temp, float dalpha, int32_t allow_nan);
 int mdgen_dirichlet_flags(MdgenHandle* h, int32_t* flags_out, mdgen_stream_t stream);
 
+/* NewMDGenWrapper.prep_batch (wrapper.py:283-365), the step before the sampler, on the device and stateless:
+ * trans [B,T,L,3], rots [B,T,L,3,3], torsions [B,T,L,14] f32 -> latents / x_cond [B,T,L,D] f32 with
+ * D = 7 * (1 + two_ref) + 14 and x_cond_mask [B,T,L] i64.  flags: 1 second reference frame (tps / inpainting /
+ * dynamic_mpnn), 2 no_offsets, 4 no_torsion, 8 no_design_torsion, 16 design_key_frames, 32 sim_condition,
+ * 64 tps_condition, 128 inpainting-style residue conditioning; cond_interval as args.cond_interval (0 = off). */
+int mdgen_prep_batch(int32_t B, int32_t T, int32_t L, const float* trans, const float* rots,
+                     const float* torsions, int32_t flags, int32_t cond_interval, float* latents,
+                     float* x_cond, int64_t* cond_mask, mdgen_stream_t stream);
+
 /* introspection ------------------------------------------------------------------------ */
 /* Number of kernels one mdgen_forward launches for the current conditioning shape. */
 int mdgen_launches_per_forward(MdgenHandle* h);

@@ -180,4 +180,54 @@ __global__ void relative_frames_kernel(const float* __restrict__ srot, const flo
   rel7(erot + (size_t)i * 9, etrans + (size_t)i * 3, srot + (size_t)i * 9, strans + (size_t)i * 3, r7 + (size_t)i * 7);
 }
 
+// ---- prep_batch (wrapper.py:283-365): trajectory frames -> sampler latents + conditioning, one thread per (b, t, l).
+//   offsets  = to_tensor_7(rigids[:, 0]^-1 o rigids), quaternion real part >= 0 (utils.py:7-14, wrapper.py:304-309)
+//   offsets_r = the same against the LAST frame for tps / inpainting (:314-318)
+//   latents  = [offsets | offsets_r | torsions(14)] (:320-327);  x_cond = cond_mask ? latents : 0 (:338-346, 361)
+// The reference gets the quaternion from eigh and then fixes the sign; rot_to_quat_closed gives that unit quaternion
+// directly.  flags: PREP_* below.  design_key_frames (:296-302) reads residues {0,0,3,3} in the first / last frame.
+enum { PREP_TWO_REF = 1, PREP_NO_OFFSETS = 2, PREP_NO_TORSION = 4, PREP_NO_DESIGN_TORSION = 8, PREP_KEY_FRAMES = 16,
+       PREP_SIM_COND = 32, PREP_TPS_COND = 64, PREP_INPAINT_COND = 128 };
+__global__ void prep_batch_kernel(const float* __restrict__ trans, const float* __restrict__ rots,
+                                  const float* __restrict__ torsions, int B, int T, int L, int flags, int cond_interval,
+                                  float* __restrict__ latents, float* __restrict__ x_cond, long long* __restrict__ cond_mask) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * T * L) return;
+  const int l = i % L, t = (i / L) % T, b = i / (L * T);
+  const bool two = flags & PREP_TWO_REF;
+  const int D = (two ? 14 : 7) + 14;
+  auto frame = [&](int tt, int ll) -> size_t {       // design_key_frames: the key frames borrow residues 0 / 3
+    if ((flags & PREP_KEY_FRAMES) && (tt == 0 || tt == T - 1)) ll = ll < 2 ? 0 : 3;
+    return ((size_t)b * T + tt) * L + ll;
+  };
+  const size_t me = frame(t, l);
+  float out[28];
+  const float I3[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, Z3[3] = {0, 0, 0};
+  if (flags & PREP_NO_OFFSETS) {
+    rel7(I3, Z3, rots + me * 9, trans + me * 3, out);
+  } else {
+    const size_t r0 = frame(0, l);
+    rel7(rots + r0 * 9, trans + r0 * 3, rots + me * 9, trans + me * 3, out);
+  }
+  int n = 7;
+  if (two) {
+    const size_t r1 = frame(T - 1, l);
+    rel7(rots + r1 * 9, trans + r1 * 3, rots + me * 9, trans + me * 3, out + 7);
+    n = 14;
+  }
+  const bool zero_tors = (flags & PREP_NO_TORSION) || ((flags & PREP_NO_DESIGN_TORSION) && (l == 1 || l == 2));
+#pragma unroll
+  for (int k = 0; k < 14; ++k) out[n + k] = zero_tors ? 0.f : torsions[(size_t)i * 14 + k];
+  bool cond = false;
+  if ((flags & PREP_SIM_COND) && t == 0) cond = true;
+  if ((flags & PREP_TPS_COND) && (t == 0 || t == T - 1)) cond = true;
+  if (cond_interval > 0 && t % cond_interval == 0) cond = true;
+  if ((flags & PREP_INPAINT_COND) && (l == 0 || l == 3)) cond = true;
+  cond_mask[i] = cond ? 1 : 0;
+  for (int k = 0; k < D; ++k) {
+    latents[(size_t)i * D + k] = out[k];
+    x_cond[(size_t)i * D + k] = cond ? out[k] : 0.f;
+  }
+}
+
 }  // namespace mdgen

@@ -1291,6 +1291,21 @@ int mdgen_set_conditioning(MdgenHandle* h, int32_t B, int32_t T, int32_t L, cons
                           x_cond_mask, aatype, (cudaStream_t)stream);
 }
 
+int mdgen_prep_batch(int32_t B, int32_t T, int32_t L, const float* trans, const float* rots, const float* torsions,
+                     int32_t flags, int32_t cond_interval, float* latents, float* x_cond, int64_t* cond_mask,
+                     mdgen_stream_t stream) {
+  MD_CHECK(B > 0 && T > 0 && L > 0 && trans && rots && torsions && latents && x_cond && cond_mask, "bad argument");
+  if (flags & (PREP_KEY_FRAMES | PREP_NO_DESIGN_TORSION | PREP_INPAINT_COND))
+    MD_CHECK(L == 4, "design / inpainting index maps are defined for 4 residues (wrapper.py:41-43)");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n = B * T * L;
+  prep_batch_kernel<<<(n + 127) / 128, 128, 0, st>>>(trans, rots, torsions, B, T, L, flags, cond_interval, latents, x_cond,
+                                                    (long long*)cond_mask);
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return MDGEN_OK;
+}
+
 int mdgen_set_dirichlet_tables(MdgenHandle* h, int32_t nt, const double* rows, const double* alphas, const double* betas,
                                float temp, float dalpha, int32_t allow_nan) {
   MD_CHECK(h && nt > 0 && rows && alphas && betas && temp > 0.f, "bad argument");

@@ -51,4 +51,4 @@ def test_cuda_prep_batch_vs_reference_golden(name):
     args, batch, ref = load(name)
     got = prep_batch(args, {k: v.cuda() for k, v in batch.items()})
     assert got["latents"].is_cuda
-    check(got, ref, 5e-6)
+    check(got, ref, 2e-5)     # fp32 rounding of R^T (t - t0) on coordinates of tens of Angstrom
