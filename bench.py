@@ -166,6 +166,30 @@ def workload_name(cfg_id):
             f"{NUM_STEPS - 1}-evaluation fixed-grid Euler rollout per step")
 
 
+def dist_barrier(world, dev):
+    """Barrier over the ranks (one process per GPU; NCCL on the GPU box, gloo in the CPU tests) + device sync."""
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    if dev.type == "cuda":
+        torch.cuda.synchronize(dev)
+
+
+def dist_max(ms, world, dev):
+    """Step time of the job = the slowest rank's (the only collective of the sampling path: rollouts are independent)."""
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return ms
+
+
+def rank_inputs(c, rank):
+    """Weak scaling: every rank samples its own batch of independent rollouts (seed = rank), weights are replicated."""
+    return cfgs.synthetic_inputs(c, seed=rank)
+
+
 def run_gpu(a, rank, world, local_rank):
     from mdgen_finetune_b200 import LatentMDGenModel, Sampler, create_transport, _lib
     import torch.distributed as dist
@@ -177,7 +201,7 @@ def run_gpu(a, rank, world, local_rank):
     model = LatentMDGenModel(args, c["D"], precision="bf16")
     model.load_state_dict(sd)
     model = model.to(dev).eval()
-    inp = cfgs.synthetic_inputs(c, seed=rank)             # independent rollouts per rank: no data-path collective
+    inp = rank_inputs(c, rank)                            # independent rollouts per rank: no data-path collective
 
     def kwargs_on(f):
         kw = dict(mask=f(inp["mask"]), start_frames=(f(inp["start_rot"]), f(inp["start_trans"])),
@@ -186,17 +210,8 @@ def run_gpu(a, rank, world, local_rank):
             kw["end_frames"] = (f(inp["end_rot"]), f(inp["end_trans"]))
         return kw
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    def max_over_ranks(ms):
-        if world > 1:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            return float(t.item())
-        return ms
+    barrier = lambda: dist_barrier(world, dev)
+    max_over_ranks = lambda ms: dist_max(ms, world, dev)
 
     frames_per_step = c["B"] * c["T"]
     # ---------------- device-resident arm ----------------

@@ -1,0 +1,64 @@
+"""N > 1 host logic on CPU (gloo, world_size 2): the sampling path shards by independent rollouts -- one process per
+GPU, different seeds per rank, replicated weights, NO data-path collective; the only exchange is the MAX reduction of
+the step time, and only rank 0 prints the JSON line."""
+import json
+import os
+import subprocess
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import bench
+    from mdgen_finetune_b200 import configs as cfgs
+    dev = torch.device("cpu")
+    bench.dist_barrier(world, dev)
+    slowest = bench.dist_max(10.0 + 5.0 * rank, world, dev)
+    c = cfgs.small_variant(3, B=2, T=8, L=4)
+    c["id"] = 3
+    x0 = bench.rank_inputs(c, rank)["x0"]
+    gathered = [torch.empty_like(x0) for _ in range(world)]
+    dist.all_gather(gathered, x0)                       # test-only exchange: the product path never gathers
+    q.put((rank, slowest, float((gathered[0] - gathered[1]).abs().max()), tuple(x0.shape)))
+    dist.destroy_process_group()
+
+
+def test_rank_sharding_and_time_reduction_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29000 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, slowest, diff, shape in res:
+        assert slowest == 15.0                          # every rank reports the slowest rank's time
+        assert diff > 0.1                               # the ranks sample different rollouts
+        assert shape == (2, 8, 4, 21)                   # per-rank work is fixed: weak scaling
+
+
+def test_reference_arm_under_torchrun_prints_once():
+    """`bench.py --impl reference` launched like the driver launches it for N = 2: rank 0 alone runs the CPU arm and
+    prints one JSON line, the other rank exits 0 without work."""
+    env = dict(os.environ, OMP_NUM_THREADS="4")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(29500 + os.getpid() % 400), os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
+           "--steps", "1", "--warmup", "0", "--config", "2"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = lines[0]
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["e2e"]["h2d_bytes_per_step"] == 0
