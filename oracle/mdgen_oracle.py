@@ -430,3 +430,67 @@ def prep_batch(args, batch):
             "x_cond_mask": cond_mask,
         },
     }
+
+
+# ------------------------------------------------------------------------------------
+# decode (wrapper.py:487-508): sampled latents -> atom14 coordinates, the step after the sampler
+def quat_to_rot(q):
+    """rigid_utils.quat_to_rot (rigid_utils.py:129-165) for a (normalised) quaternion [*, 4] -> [*, 3, 3]."""
+    w, x, y, z = q.unbind(-1)
+    return torch.stack([w * w + x * x - y * y - z * z, 2 * (x * y - w * z), 2 * (x * z + w * y),
+                        2 * (x * y + w * z), w * w - x * x + y * y - z * z, 2 * (y * z - w * x),
+                        2 * (x * z - w * y), 2 * (y * z + w * x), w * w - x * x - y * y + z * z], -1).reshape(*q.shape[:-1], 3, 3)
+
+
+def torsion_angles_to_frames(rot, trans, alpha, aatype, rrgdf):
+    """geometry.torsion_angles_to_frames (geometry.py:273-334): rot/trans [*, N], alpha [*, N, 7, 2] -> 8 global frames."""
+    d4 = rrgdf[aatype]                                               # [*, N, 8, 4, 4]
+    d_rot, d_trans = d4[..., :3, :3], d4[..., :3, 3]
+    bb = alpha.new_zeros(*alpha.shape[:-2], 1, 2)
+    bb[..., 1] = 1
+    alpha = torch.cat([bb, alpha], -2)                               # [*, N, 8, 2]
+    rx = alpha.new_zeros(*alpha.shape[:-1], 3, 3)
+    rx[..., 0, 0] = 1
+    rx[..., 1, 1] = alpha[..., 1]
+    rx[..., 1, 2] = -alpha[..., 0]
+    rx[..., 2, 1] = alpha[..., 0]
+    rx[..., 2, 2] = alpha[..., 1]
+    f_rot, f_trans = d_rot @ rx, d_trans                              # default_r.compose(all_rots)
+    rots, transs = [f_rot[..., g, :, :] for g in range(8)], [f_trans[..., g, :] for g in range(8)]
+    for g in (5, 6, 7):                                               # chi2..chi4 chained onto chi1 (:314-319)
+        rots[g], transs[g] = rigid_compose(rots[g - 1], transs[g - 1], rots[g], transs[g])
+    to_bb_rot, to_bb_trans = torch.stack(rots, -3), torch.stack(transs, -2)
+    return rigid_compose(rot[..., None, :, :], trans[..., None, :], to_bb_rot, to_bb_trans)
+
+
+def frames_torsions_to_atom14(rot, trans, torsions, aatype, tables):
+    """geometry.frames_torsions_to_atom14 (geometry.py:61-79, 236-270).  tables = the four residue_constants arrays:
+    default_frames [21,8,4,4], group_idx [21,14], atom_mask [21,14], lit_positions [21,14,3]."""
+    g_rot, g_trans = torsion_angles_to_frames(rot, trans, torsions, aatype, tables["default_frames"])
+    gi = tables["group_idx"][aatype].long()                           # [*, N, 14]
+    a_rot = torch.gather(g_rot, -3, gi[..., None, None].expand(*gi.shape, 3, 3))
+    a_trans = torch.gather(g_trans, -2, gi[..., None].expand(*gi.shape, 3))
+    pos = rot_apply(a_rot, tables["lit_positions"][aatype]) + a_trans
+    return pos * tables["atom_mask"][aatype].unsqueeze(-1)
+
+
+def decode_samples(args, samples, rot0, trans0, seqres, tables):
+    """wrapper.py:487-508: samples [B,T,L,D], first-frame rigids rot0/trans0 [B,1,L], seqres [B,L] -> atom14 [B,T,L,14,3],
+    aa_out [B,T,L]."""
+    B, T, L = samples.shape[:3]
+    offsets = samples[..., :7]
+    two = args.tps_condition or args.inpainting
+    torsions = samples[..., 14:28] if two else samples[..., 7:21]
+    logits = samples[..., -20:]
+    q = offsets[..., :4]
+    q = q / torch.linalg.norm(q, dim=-1, keepdim=True)               # Rigid.from_tensor_7(normalize_quats=True)
+    rot, trans = quat_to_rot(q), offsets[..., 4:]
+    if not getattr(args, "no_offsets", False):
+        rot, trans = rigid_compose(rot0, trans0, rot, trans)          # rigids[:, 0:1].compose(...)
+    torsions = torsions.reshape(B, T, L, 7, 2)
+    if not getattr(args, "oracle", False):
+        torsions = torsions / torch.linalg.norm(torsions, dim=-1, keepdim=True)
+    aatype = seqres[:, None].expand(B, T, L)
+    atom14 = frames_torsions_to_atom14(rot, trans, torsions, aatype, tables)
+    aa_out = torch.argmax(logits, -1) if args.design else aatype
+    return atom14, aa_out
