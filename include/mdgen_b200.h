@@ -139,6 +139,18 @@ int mdgen_prep_batch(int32_t B, int32_t T, int32_t L, const float* trans, const 
                      const float* torsions, int32_t flags, int32_t cond_interval, float* latents,
                      float* x_cond, int64_t* cond_mask, mdgen_stream_t stream);
 
+/* The decode step of NewMDGenWrapper.inference (wrapper.py:487-508), the step after the sampler: samples [B,T,L,D] f32 ->
+ * atom14 [B,T,L,14,3] f32 (frames_torsions_to_atom14, geometry.py:61-79,236-334) and aa_out [B,T,L] i64 (NULL to skip).
+ * tors_off = first torsion channel (7, or 14 with tps / inpainting); rot0 [B,L,3,3] / trans0 [B,L,3] = rigids[:, 0]
+ * (NULL with flag 1 = no_offsets); seqres [B,L] i64.  The caller supplies the four mdgen.residue_constants tables:
+ * default_frames [21,8,4,4] f32, group_idx [21,14] i64, atom_mask [21,14] f32, lit_positions [21,14,3] f32.
+ * flags: 1 no_offsets, 2 --oracle (torsions not re-normalised), 4 design (aa_out = argmax of the last 20 channels). */
+int mdgen_decode_atom14(int32_t B, int32_t T, int32_t L, int32_t D, const float* samples, int32_t tors_off,
+                        const float* rot0, const float* trans0, const int64_t* seqres,
+                        const float* default_frames, const int64_t* group_idx, const float* atom_mask,
+                        const float* lit_positions, int32_t flags, float* atom14, int64_t* aa_out,
+                        mdgen_stream_t stream);
+
 /* introspection ------------------------------------------------------------------------ */
 /* Number of kernels one mdgen_forward launches for the current conditioning shape. */
 int mdgen_launches_per_forward(MdgenHandle* h);

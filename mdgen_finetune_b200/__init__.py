@@ -2,4 +2,4 @@
 the LatentMDGenModel velocity network + fixed-grid Euler transport sampler, behind a C ABI."""
 from .model import LatentMDGenModel  # noqa: F401
 from .transport import Sampler, Transport, create_transport  # noqa: F401
-from .prep import prep_batch  # noqa: F401
+from .prep import prep_batch, decode_samples  # noqa: F401

@@ -19,7 +19,7 @@ F_SIM, F_TPS, F_INPAINT, F_DESIGN, F_NO_AA_EMB, F_ABS_POS, F_ABS_TIME, F_NO_ROPE
     1 << 0, 1 << 1, 1 << 2, 1 << 3, 1 << 4, 1 << 5, 1 << 6, 1 << 7, 1 << 8)
 PREC_BF16, PREC_FP32_CHECK = 0, 1
 EXPORTS = ["mdgen_create", "mdgen_destroy", "mdgen_last_error", "mdgen_abi_version", "mdgen_load_weight",
-           "mdgen_finalize_weights", "mdgen_set_conditioning", "mdgen_forward", "mdgen_euler_rollout", "mdgen_dirichlet_flow", "mdgen_set_dirichlet_tables", "mdgen_dirichlet_flags", "mdgen_prep_batch",
+           "mdgen_finalize_weights", "mdgen_set_conditioning", "mdgen_forward", "mdgen_euler_rollout", "mdgen_dirichlet_flow", "mdgen_set_dirichlet_tables", "mdgen_dirichlet_flags", "mdgen_prep_batch", "mdgen_decode_atom14",
            "mdgen_launches_per_forward", "mdgen_launch_count", "mdgen_workspace_bytes", "mdgen_profile_begin", "mdgen_profile_end",
            "mdgen_profile_category_name", "mdgen_debug_set_buffer", "mdgen_test_gemm", "mdgen_test_attention"]
 
@@ -82,6 +82,7 @@ def lib():
                                        ctypes.POINTER(ctypes.c_int32), vp]
     L.mdgen_set_dirichlet_tables.argtypes = [vp, i32, vp, vp, vp, ctypes.c_float, ctypes.c_float, i32]
     L.mdgen_dirichlet_flags.argtypes = [vp, ctypes.POINTER(ctypes.c_int32), vp]
+    L.mdgen_decode_atom14.argtypes = [i32, i32, i32, i32, fp, i32, fp, fp, vp, fp, vp, fp, fp, i32, fp, vp, vp]
     L.mdgen_prep_batch.argtypes = [i32, i32, i32, fp, fp, fp, i32, i32, fp, fp, vp, vp]
     L.mdgen_launches_per_forward.argtypes = [vp]
     L.mdgen_workspace_bytes.argtypes = [vp]

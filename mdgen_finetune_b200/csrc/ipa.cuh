@@ -230,4 +230,97 @@ __global__ void prep_batch_kernel(const float* __restrict__ trans, const float* 
   }
 }
 
+// ---- decode (wrapper.py:487-508): sampled latent -> atom14, one thread per (b, t, l).
+//   frame   = rigids[:, 0] o Rigid.from_tensor_7(latent[:7], normalize_quats=True)        (:497-500)
+//   torsion frames: default frame of the residue type o rotation about x by the (normalised) torsion, chi2..chi4
+//   chained onto chi1 (geometry.py:273-334); atom = frame of its rigid group applied to the literature position,
+//   masked (geometry.py:236-270).  The four residue tables are the caller's (mdgen.residue_constants).
+enum { DEC_NO_OFFSETS = 1, DEC_RAW_TORSIONS = 2, DEC_DESIGN = 4 };
+struct Rig { float R[9]; float t[3]; };
+__device__ inline void rig_compose(const Rig& a, const Rig& b, Rig& o) {      // a o b  (rigid_utils.py:1031-1045)
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) o.R[r * 3 + c] = a.R[r * 3] * b.R[c] + a.R[r * 3 + 1] * b.R[3 + c] + a.R[r * 3 + 2] * b.R[6 + c];
+    o.t[r] = a.R[r * 3] * b.t[0] + a.R[r * 3 + 1] * b.t[1] + a.R[r * 3 + 2] * b.t[2] + a.t[r];
+  }
+}
+__global__ void decode_atom14_kernel(const float* __restrict__ samples, int D, int tors_off, const float* __restrict__ rot0,
+                                     const float* __restrict__ trans0, const long long* __restrict__ seqres, int B, int T, int L,
+                                     const float* __restrict__ default_frames, const long long* __restrict__ group_idx,
+                                     const float* __restrict__ atom_mask, const float* __restrict__ lit_positions, int flags,
+                                     float* __restrict__ atom14, long long* __restrict__ aa_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * T * L) return;
+  const int l = i % L, b = i / (L * T);
+  const float* x = samples + (size_t)i * D;
+  const int aa = (int)seqres[b * L + l];
+  // ---- backbone frame
+  Rig off, fr;
+  {
+    float w = x[0], qx = x[1], qy = x[2], qz = x[3];
+    const float n = 1.0f / sqrtf(w * w + qx * qx + qy * qy + qz * qz);
+    w *= n; qx *= n; qy *= n; qz *= n;                                  // rigid_utils.quat_to_rot (:129-165)
+    off.R[0] = w * w + qx * qx - qy * qy - qz * qz; off.R[1] = 2 * (qx * qy - w * qz); off.R[2] = 2 * (qx * qz + w * qy);
+    off.R[3] = 2 * (qx * qy + w * qz); off.R[4] = w * w - qx * qx + qy * qy - qz * qz; off.R[5] = 2 * (qy * qz - w * qx);
+    off.R[6] = 2 * (qx * qz - w * qy); off.R[7] = 2 * (qy * qz + w * qx); off.R[8] = w * w - qx * qx - qy * qy + qz * qz;
+    off.t[0] = x[4]; off.t[1] = x[5]; off.t[2] = x[6];
+  }
+  if (flags & DEC_NO_OFFSETS) {
+    fr = off;
+  } else {
+    Rig f0;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) f0.R[k] = rot0[(size_t)(b * L + l) * 9 + k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) f0.t[k] = trans0[(size_t)(b * L + l) * 3 + k];
+    rig_compose(f0, off, fr);
+  }
+  // ---- the 8 rigid-group frames in the backbone frame, then global
+  Rig grp[8];
+  for (int g = 0; g < 8; ++g) {
+    const float* d4 = default_frames + ((size_t)aa * 8 + g) * 16;
+    float s = 0.f, c = 1.f;                                             // backbone group: no rotation
+    if (g > 0) {
+      s = x[tors_off + 2 * (g - 1)];
+      c = x[tors_off + 2 * (g - 1) + 1];
+      if (!(flags & DEC_RAW_TORSIONS)) {
+        const float n = sqrtf(s * s + c * c);
+        s /= n; c /= n;
+      }
+    }
+    Rig f;                                                              // default o Rx(torsion): [[1,0,0],[0,c,-s],[0,s,c]]
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const float d0 = d4[r * 4], d1 = d4[r * 4 + 1], d2 = d4[r * 4 + 2];
+      f.R[r * 3] = d0;
+      f.R[r * 3 + 1] = d1 * c + d2 * s;
+      f.R[r * 3 + 2] = -d1 * s + d2 * c;
+      f.t[r] = d4[r * 4 + 3];
+    }
+    if (g >= 5) rig_compose(grp[g - 1], f, grp[g]);                     // chi2..chi4 chained onto chi1
+    else grp[g] = f;
+  }
+  for (int a = 0; a < 14; ++a) {
+    const int g = (int)group_idx[aa * 14 + a];
+    Rig G;
+    rig_compose(fr, grp[g], G);
+    const float* lp = lit_positions + ((size_t)aa * 14 + a) * 3;
+    const float m = atom_mask[aa * 14 + a];
+    float* o = atom14 + ((size_t)i * 14 + a) * 3;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) o[r] = (G.R[r * 3] * lp[0] + G.R[r * 3 + 1] * lp[1] + G.R[r * 3 + 2] * lp[2] + G.t[r]) * m;
+  }
+  if (aa_out) {
+    long long best = aa;
+    if (flags & DEC_DESIGN) {                                           // torch.argmax over the 20 logits (first maximum)
+      best = 0;
+      float bv = x[D - 20];
+      for (int k = 1; k < 20; ++k)
+        if (x[D - 20 + k] > bv) { bv = x[D - 20 + k]; best = k; }
+    }
+    aa_out[i] = best;
+  }
+}
+
 }  // namespace mdgen

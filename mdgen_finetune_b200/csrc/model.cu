@@ -1306,6 +1306,25 @@ int mdgen_prep_batch(int32_t B, int32_t T, int32_t L, const float* trans, const 
   return MDGEN_OK;
 }
 
+int mdgen_decode_atom14(int32_t B, int32_t T, int32_t L, int32_t D, const float* samples, int32_t tors_off, const float* rot0,
+                        const float* trans0, const int64_t* seqres, const float* default_frames, const int64_t* group_idx,
+                        const float* atom_mask, const float* lit_positions, int32_t flags, float* atom14, int64_t* aa_out,
+                        mdgen_stream_t stream) {
+  MD_CHECK(B > 0 && T > 0 && L > 0 && samples && seqres && default_frames && group_idx && atom_mask && lit_positions && atom14,
+           "bad argument");
+  MD_CHECK(tors_off >= 7 && tors_off + 14 <= D, "mdgen_decode_atom14: torsion channels outside the latent");
+  MD_CHECK((flags & DEC_NO_OFFSETS) || (rot0 && trans0), "mdgen_decode_atom14: first-frame rigids needed unless no_offsets");
+  if (flags & DEC_DESIGN) MD_CHECK(D >= 41, "mdgen_decode_atom14: design latents carry 20 logits");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n = B * T * L;
+  decode_atom14_kernel<<<(n + 127) / 128, 128, 0, st>>>(samples, D, tors_off, rot0, trans0, (const long long*)seqres, B, T, L,
+                                                       default_frames, (const long long*)group_idx, atom_mask, lit_positions,
+                                                       flags, atom14, (long long*)aa_out);
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return MDGEN_OK;
+}
+
 int mdgen_set_dirichlet_tables(MdgenHandle* h, int32_t nt, const double* rows, const double* alphas, const double* betas,
                                float temp, float dalpha, int32_t allow_nan) {
   MD_CHECK(h && nt > 0 && rows && alphas && betas && temp > 0.f, "bad argument");

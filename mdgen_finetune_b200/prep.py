@@ -73,3 +73,39 @@ def prep_batch(args, batch):
             "x_cond_mask": cond_mask,
         },
     }
+
+
+def decode_samples(args, samples, first_frames, seqres, tables):
+    """The decode lines of NewMDGenWrapper.inference (wrapper.py:487-508): samples [B,T,L,D] (the sampler's last state),
+    first_frames = rigids[:, 0:1] as (rot_mats [B,1,L,3,3] or [B,L,3,3], trans), seqres [B,L] ->
+    (atom14 [B,T,L,14,3], aa_out [B,T,L]).  `tables`: dict with the caller's mdgen.residue_constants arrays
+    'default_frames' (restype_rigid_group_default_frame), 'group_idx' (restype_atom14_to_rigid_group), 'atom_mask'
+    (restype_atom14_mask), 'lit_positions' (restype_atom14_rigid_group_positions) as tensors."""
+    g = lambda name: bool(getattr(args, name, False))
+    if g("no_frames"):
+        raise NotImplementedError("--no_frames is outside the B200 hot path (DESIGN.md, out of scope)")
+    if not samples.is_cuda:
+        raise RuntimeError("mdgen_finetune_b200.decode_samples needs CUDA tensors: there is no CPU fallback")
+    dev = samples.device
+    B, T, L, D = samples.shape
+    f32 = lambda v: v.detach().to(dev, torch.float32).contiguous()
+    i64 = lambda v: v.detach().to(dev, torch.int64).contiguous()
+    xs = f32(samples)
+    no_off = g("no_offsets")
+    rot0 = trans0 = None
+    if not no_off:
+        rot0, trans0 = f32(first_frames[0]).reshape(B, L, 3, 3), f32(first_frames[1]).reshape(B, L, 3)
+    tb = {"default_frames": f32(tables["default_frames"]), "group_idx": i64(tables["group_idx"]),
+          "atom_mask": f32(tables["atom_mask"]), "lit_positions": f32(tables["lit_positions"])}
+    atom14 = torch.empty(B, T, L, 14, 3, device=dev)
+    aa_out = torch.empty(B, T, L, dtype=torch.int64, device=dev)
+    flags = (1 if no_off else 0) | (2 if g("oracle") else 0) | (4 if g("design") else 0)
+    tors_off = 14 if (g("tps_condition") or g("inpainting")) else 7
+    p = lambda v: None if v is None else ctypes.c_void_p(v.data_ptr())
+    seq = i64(seqres)
+    with torch.cuda.device(dev):
+        st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(_lib.lib().mdgen_decode_atom14(B, T, L, D, p(xs), tors_off, p(rot0), p(trans0), p(seq), p(tb["default_frames"]),
+                                                  p(tb["group_idx"]), p(tb["atom_mask"]), p(tb["lit_positions"]), flags, p(atom14),
+                                                  p(aa_out), st), "mdgen_decode_atom14")
+    return atom14, aa_out

@@ -159,7 +159,7 @@ def test_full_size_config1_velocity_and_launch_count():
 
 
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
-def test_full_size_config1_rollout_ca_rmsd(prec):
+def test_full_size_config1_rollout_rmsd(prec):
     """north_star: a 1000-frame deterministic Euler rollout (config 1: B = 1, T = 1000, L = 4, 49 steps) stays within
     0.05 A coordinate RMSD per frame of the reference's own sampler (golden `euler_final`).  Coordinates compared here
     are the residue frame origins (C-alpha): decode composes the first frame with the offset, frames = rigids[:, 0:1]
@@ -177,3 +177,16 @@ def test_full_size_config1_rollout_ca_rmsd(prec):
     rmsd = d.pow(2).sum(-1).mean(-1).sqrt()                            # per frame, over the residues
     print(f"C-alpha RMSD per frame [{prec}]: max {float(rmsd.max()):.4g} A, mean {float(rmsd.mean()):.4g} A")
     assert float(rmsd.max()) < 0.05, float(rmsd.max())
+    # all-atom: both final states through the device decode (wrapper.py:487-508) with the reference's residue tables
+    from mdgen_finetune_b200 import decode_samples
+    import os
+    tables = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "decode.pt"))["tables"]
+    first = (inp["start_rot"].cuda(), inp["start_trans"].cuda())
+    seq = inp["aatype"].cuda()
+    a_out, _ = decode_samples(args, out.cuda(), first, seq, tables)
+    a_ref, _ = decode_samples(args, ref.cuda(), first, seq, tables)
+    msk = tables["atom_mask"][inp["aatype"]][:, None].expand(-1, out.shape[1], -1, -1)          # [B, T, L, 14]
+    d2 = ((a_out - a_ref).cpu().pow(2).sum(-1) * msk).sum((-1, -2)) / msk.sum((-1, -2))
+    aa_rmsd = d2.sqrt()
+    print(f"all-atom RMSD per frame [{prec}]: max {float(aa_rmsd.max()):.4g} A, mean {float(aa_rmsd.mean()):.4g} A")
+    assert float(aa_rmsd.max()) < 0.05, float(aa_rmsd.max())
