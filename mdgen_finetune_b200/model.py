@@ -301,10 +301,16 @@ class LatentMDGenModel(nn.Module):
                 _lib.lib().mdgen_destroy(self._handle)
             except Exception:
                 pass
-            self._handle = None
+            try:
+                self._handle = None
+            except Exception:        # interpreter shutdown: torch's module machinery may already be torn down
+                pass
 
     def __del__(self):
-        self._destroy()
+        try:
+            self._destroy()
+        except Exception:
+            pass
 
     def __deepcopy__(self, memo):
         import copy
