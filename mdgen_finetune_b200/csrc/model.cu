@@ -789,7 +789,10 @@ struct Fwd {
   int resid_gemm(const AT* A, int lda, const LinearW& w, int M, EpiParams ep, const float* nshift, const float* nscale) {
     h_ready = false;
     if constexpr (sizeof(AT) == 2) {
-      if (nshift && nscale && ep.resid == h->xres) {
+      // The fused kernel owns whole 256-row slabs: M / 256 CTA pairs.  Below ~8k rows (config 1: 16 tiles on 74 pairs)
+      // the machine is mostly idle and the plain 64-column-tile GEMM + a separate LayerNorm kernel is faster
+      // (config 1: 36.3 -> 33.3 ms per rollout, tools/ab_small.sh).
+      if (nshift && nscale && ep.resid == h->xres && M >= 8192) {
         ep.bias = w.b;
         tcln::LnFuse ln;
         ln.out = (bf16*)h->hbuf;
