@@ -1530,21 +1530,22 @@ int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float
     ep.nbatch = 1;
     r = launch_gemm_tc(Ab, K, Wb, K, M, N, K, EPI_GATE_RESID, false, ep, block_n, st);
   } else if (use_tc == 5) {
-    // fused residual + next LayerNorm/modulate (gemm_ln.cuh).  bias holds 2 * N floats: batch element b = (m / 200) % 2
-    // uses bias[b * N ..] as gate, shift and scale; the linear bias is bias[0 .. N).  Cout is [2 * M, N]: rows [0, M) are
-    // the residual stream (in / out), rows [M, 2 M) receive the normalised bf16 rows (as fp32).
+    // fused residual + next LayerNorm/modulate (gemm_ln.cuh).  bias holds 7 * N floats, four DISTINCT operands:
+    // [linear bias (N) | gate (2, N) | shift (2, N) | scale (2, N)], batch element b = (m / 200) % 2 (a batch boundary
+    // falls inside 256-row slabs).  Cout is [2 * M, N]: rows [0, M) are the residual stream (in / out), rows [M, 2 M)
+    // receive the normalised bf16 rows (as fp32).
     ep.out = nullptr;
     ep.resid = Cout;
     ep.ldr = N;
-    ep.gate = bias;
+    ep.gate = bias + N;
     ep.gate_stride = N;
     ep.rows_per_batch = 200;
     ep.nbatch = 2;
     MD_CUDA(cudaMalloc((void**)&Cb, (size_t)M * N * 2));
     tcln::LnFuse ln;
     ln.out = Cb;
-    ln.shift = bias;
-    ln.scale = bias;
+    ln.shift = bias + 3 * N;
+    ln.scale = bias + 5 * N;
     ln.eps = 1e-6f;
     r = launch_gemm_resid_ln(Ab, K, Wb, K, M, N, K, ep, ln, st);
     if (r == 1) {

@@ -33,8 +33,17 @@ CASES = {
     "atlas_small": (5, dict(B=1, T=6, L=24), 5),
     "atlas_mid": (5, dict(B=1, T=20, L=72), 9),
     "sim_full": (1, dict(), 0),
+    # BASELINE configs at FULL size: the shapes that select the kernels bench.py times (fused projection + LayerNorm
+    # from 8192 rows, CTA-pair GEMM from 74 tiles of 256 x 256, tcgen05 attention on both axes of ATLAS, IPA at L = 256)
+    "tps_full": (2, dict(), 0),
+    "upsample_full": (3, dict(), 0),
+    "design_full": (4, dict(), 0),
+    "atlas_full": (5, dict(), 32),
 }
 T_VALUES = [0.0, 0.3, 48.0 / 49.0]
+# full-size cases: (velocity times, Euler grid points of the short reference-sampler rollout)
+FULL = {"sim_full": ([0.3], 50), "tps_full": ([0.3], 5), "upsample_full": ([0.3, 48.0 / 49.0], 5),
+        "design_full": ([0.3], 4), "atlas_full": ([0.3], 3)}
 
 
 def case_config(name):
@@ -76,18 +85,18 @@ def main(only=None):
         kw = ref_kwargs(ref, inp)
         B = c["B"]
         out = {"case": name, "config": c, "pad_last": pad}
-        tvals = T_VALUES if name != "sim_full" else [0.3]
+        tvals = FULL[name][0] if name in FULL else T_VALUES
         for i, tv in enumerate(tvals):
             t = torch.full((B,), tv)
             out[f"v_t{i}"] = model.forward_inference(inp["x0"], t, **kw).clone()
         out["t_values"] = tvals
-        if B > 1:  # per-sample t (training / RTB call convention)
+        if B > 1 and name not in FULL:  # per-sample t (training / RTB call convention)
             t = torch.linspace(0.1, 0.9, B)
             out["v_tvec"] = model.forward_inference(inp["x0"], t, **kw).clone()
         # sampler: the reference's own Sampler / ode classes (transport.py:407-450)
         transport = ref.create_transport(args, args.path_type, args.prediction)
-        steps = 50 if name in ("sim_full",) else 6
-        if name in ("sim_small", "tps_small", "design_small", "atlas_small", "sim_full"):
+        steps = FULL[name][1] if name in FULL else 6
+        if name in ("sim_small", "tps_small", "design_small", "atlas_small") or name in FULL:
             fn = ref.Sampler(transport).sample_ode(sampling_method="euler", num_steps=steps)
             traj = fn(inp["x0"], lambda x, t, **k: model.forward_inference(x, t, **k), **kw)
             out["euler_steps"] = steps

@@ -1,11 +1,10 @@
 """TEST INFRASTRUCTURE ONLY -- golden vectors for prep_batch (wrapper.py:283-365), row N1.
 
-`mdgen.wrapper` itself cannot be imported here (pytorch_lightning is absent), so the body of
-NewMDGenWrapper.prep_batch is replayed line by line on the reference's OWN classes and helpers
-(`mdgen.rigid_utils.Rigid / Rotation`, `mdgen.utils.get_offsets`, the module constants of wrapper.py:41-43):
-everything numeric (invert, compose, rot_to_quat through eigh, to_tensor_7) is the reference's code.
+The goldens are the outputs of the reference's OWN `NewMDGenWrapper.prep_batch` (mdgen/wrapper.py, unmodified),
+imported through oracle/ref_loader.load_wrapper() (pytorch_lightning / wandb stubbed: absent from this image, no
+arithmetic).  Control flow (flag handling, key-frame remapping, mask assembly) and arithmetic (invert, compose,
+rot_to_quat through eigh, to_tensor_7) are therefore both the reference's.
 Run in the build container:  python -m oracle.make_prep_golden   ->  tests/golden/prep_batch.pt"""
-import argparse
 import os
 import sys
 
@@ -13,29 +12,28 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from oracle.ref_loader import load_reference  # noqa: E402
+from mdgen_finetune_b200 import configs as cfgs  # noqa: E402
+from oracle.ref_loader import load_wrapper  # noqa: E402
 
-DESIGN_IDX = [1, 2]                 # wrapper.py:41-43
-COND_IDX = [0, 3]
-DESIGN_MAP_TO_COND = [0, 0, 3, 3]
-
+# name -> (BASELINE config whose model flags the wrapper is built with, prep_batch flags)
 CASES = {
-    "sim": dict(sim_condition=True),
-    "upsample": dict(sim_condition=True, cond_interval=3),
-    "tps": dict(tps_condition=True),
-    "design": dict(inpainting=True, design=True, no_torsion=True),
-    "design_key_frames": dict(inpainting=True, design=True, design_key_frames=True, no_design_torsion=True),
-    "no_offsets": dict(sim_condition=True, no_offsets=True, supervise_all_torsions=True),
+    "sim": (1, dict()),
+    "upsample": (1, dict(cond_interval=3)),
+    "tps": (2, dict()),
+    "design": (4, dict(no_torsion=True)),
+    "design_key_frames": (4, dict(design_key_frames=True, no_design_torsion=True)),
+    "no_offsets": (1, dict(no_offsets=True, supervise_all_torsions=True)),
 }
-FLAGS = ("sim_condition", "tps_condition", "inpainting", "design", "dynamic_mpnn", "mpnn", "no_offsets", "no_torsion",
-         "no_design_torsion", "design_key_frames", "supervise_all_torsions", "supervise_no_torsions", "no_frames")
+WRAPPER_FLAGS = dict(no_torsion=False, supervise_all_torsions=False, supervise_no_torsions=False, design_key_frames=False,
+                     no_design_torsion=False, cond_interval=None, no_offsets=False, no_frames=False, oracle=False, ema=False)
 
 
-def make_args(**kw):
-    a = argparse.Namespace(**{f: False for f in FLAGS}, cond_interval=None)
-    for k, v in kw.items():
-        setattr(a, k, v)
-    return a
+def wrapper_args(cfg_id, T, **kw):
+    """Namespace for NewMDGenWrapper(args): the model flags of BASELINE config `cfg_id` at T frames x 4 residues + the
+    wrapper's own flags (wrapper.py:178-194)."""
+    c = cfgs.small_variant(cfg_id, T=T, L=4)
+    a = cfgs.make_args(c, **{**WRAPPER_FLAGS, **kw})
+    return a, c
 
 
 def synthetic_batch(B=2, T=7, L=4, seed=0):
@@ -53,70 +51,36 @@ def synthetic_batch(B=2, T=7, L=4, seed=0):
             "mask": torch.ones(B, L), "seqres": torch.randint(0, 20, (B, L), generator=g)}
 
 
-def reference_prep_batch(ref, utils, args, batch):
-    """wrapper.py:283-365 replayed on the reference's classes (frames path)."""
-    Rigid, Rotation = ref.Rigid, ref.Rotation
-    rigids = Rigid(trans=batch["trans"], rots=Rotation(rot_mats=batch["rots"]))
-    B, T, L = rigids.shape
-    if args.design_key_frames:
-        rigids = Rigid.cat([rigids[:, :1, DESIGN_MAP_TO_COND], rigids[:, 1:-1], rigids[:, -1:, DESIGN_MAP_TO_COND]], 1)
-    if args.no_offsets:
-        offsets = rigids.to_tensor_7()
-    else:
-        offsets = utils.get_offsets(rigids[:, 0:1], rigids)
-    offsets[..., :4] *= torch.where(offsets[:, :, :, 0:1] < 0, -1, 1)
-    frame_loss_mask = batch["mask"].unsqueeze(-1).expand(-1, -1, 7)
-    torsion_loss_mask = batch["torsion_mask"].unsqueeze(-1).expand(-1, -1, -1, 2).reshape(B, L, 14)
-    if args.tps_condition or args.inpainting or args.dynamic_mpnn:
-        offsets_r = utils.get_offsets(rigids[:, -1:], rigids)
-        offsets_r[..., :4] *= torch.where(offsets_r[:, :, :, 0:1] < 0, -1, 1)
-        offsets = torch.cat([offsets, offsets_r], -1)
-        frame_loss_mask = torch.cat([frame_loss_mask, frame_loss_mask], -1)
-    if args.no_torsion:
-        latents = torch.cat([offsets, torch.zeros_like(batch["torsions"].view(B, T, L, 14))], -1)
-    elif args.no_design_torsion:
-        torsions_ = batch["torsions"].clone()
-        torsions_[:, :, DESIGN_IDX] = 0
-        latents = torch.cat([offsets, torsions_.view(B, T, L, 14)], -1)
-    else:
-        latents = torch.cat([offsets, batch["torsions"].view(B, T, L, 14)], -1)
-    if args.supervise_all_torsions:
-        torsion_loss_mask = torch.ones_like(torsion_loss_mask)
-    elif args.supervise_no_torsions:
-        torsion_loss_mask = torch.zeros_like(torsion_loss_mask)
-    loss_mask = torch.cat([frame_loss_mask, torsion_loss_mask], -1)
-    loss_mask = loss_mask.unsqueeze(1).expand(-1, T, -1, -1)
-    cond_mask = torch.zeros(B, T, L, dtype=int, device=offsets.device)
-    if args.sim_condition:
-        cond_mask[:, 0] = 1
-    if args.tps_condition:
-        cond_mask[:, 0] = cond_mask[:, -1] = 1
-    if args.cond_interval:
-        cond_mask[:, ::args.cond_interval] = 1
-    if args.inpainting or args.dynamic_mpnn or args.mpnn:
-        cond_mask[:, :, COND_IDX] = 1
-    aatype_mask = torch.ones_like(batch["seqres"])
-    if args.design:
-        aatype_mask[:, DESIGN_IDX] = 0
+def flags_of(args):
+    """the prep_batch-relevant flags as a plain dict (what the tests rebuild their Namespace from)"""
+    keys = ("sim_condition", "tps_condition", "inpainting", "design", "dynamic_mpnn", "mpnn", "no_offsets", "no_torsion",
+            "no_design_torsion", "design_key_frames", "supervise_all_torsions", "supervise_no_torsions", "cond_interval")
+    return {k: getattr(args, k) for k in keys if getattr(args, k, None)}
+
+
+def run_prep(wrapper, batch):
+    out = wrapper.prep_batch({k: v.clone() for k, v in batch.items()})
+    kw, rigids = out["model_kwargs"], out["rigids"]
     return {
-        "latents": latents.clone(), "loss_mask": loss_mask.clone(),
-        "start_rot": rigids[:, 0].get_rots().get_rot_mats().clone(), "start_trans": rigids[:, 0].get_trans().clone(),
-        "end_rot": rigids[:, -1].get_rots().get_rot_mats().clone(), "end_trans": rigids[:, -1].get_trans().clone(),
-        "mask": batch["mask"].unsqueeze(1).expand(-1, T, -1).clone(),
-        "aatype": torch.where(aatype_mask.bool(), batch["seqres"], 20),
-        "x_cond": torch.where(cond_mask.unsqueeze(-1).bool(), latents, 0.0), "x_cond_mask": cond_mask,
+        "latents": out["latents"].clone(), "loss_mask": out["loss_mask"].clone(),
+        "start_rot": kw["start_frames"].get_rots().get_rot_mats().clone(), "start_trans": kw["start_frames"].get_trans().clone(),
+        "end_rot": kw["end_frames"].get_rots().get_rot_mats().clone(), "end_trans": kw["end_frames"].get_trans().clone(),
+        "rigids_rot": rigids.get_rots().get_rot_mats().clone(), "rigids_trans": rigids.get_trans().clone(),
+        "mask": kw["mask"].clone(), "aatype": kw["aatype"].clone(), "x_cond": kw["x_cond"].clone(),
+        "x_cond_mask": kw["x_cond_mask"].clone(),
     }
 
 
+@torch.no_grad()
 def main():
-    ref = load_reference()
-    import importlib
-    utils = importlib.import_module("mdgen.utils")
-    out = {"cases": {}}
-    for name, kw in CASES.items():
-        args = make_args(**kw)
+    ref = load_wrapper()
+    out = {"cases": {}, "source": "NewMDGenWrapper.prep_batch (reference, unmodified)"}
+    for name, (cfg_id, kw) in CASES.items():
+        args, _ = wrapper_args(cfg_id, T=7, **kw)
+        w = ref.NewMDGenWrapper(args).eval()
         batch = synthetic_batch(seed=len(name))
-        out["cases"][name] = {"args": kw, "batch": batch, "out": reference_prep_batch(ref, utils, args, batch)}
+        out["cases"][name] = {"args": flags_of(args), "batch": batch, "out": run_prep(w, batch)}
+        print(name, flags_of(args), tuple(out["cases"][name]["out"]["latents"].shape))
     path = os.path.join(ROOT, "tests", "golden", "prep_batch.pt")
     torch.save(out, path)
     print("wrote", path, os.path.getsize(path), "bytes")

@@ -29,7 +29,12 @@ import types
 
 import torch
 
-REF_SRC = "/root/reference/src"
+import os
+
+# The reference's sources: /root/reference/src in the build container; on the GPU box (no /root/reference) the staged
+# copy under oracle/_ref/src made by oracle/stage_ref.py (git-ignored build output, shipped like the built .so files).
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_SRC = "/root/reference/src" if os.path.isdir("/root/reference/src") else os.path.join(_HERE, "_ref", "src")
 
 
 def _stub(name, **attrs):
@@ -113,6 +118,8 @@ def load_reference():
     _stub("tree", map_structure=map_structure)
     _stub("Bio")
     _stub("Bio.PDB", PDBParser=object)
+    if not os.path.isdir(REF_SRC):
+        raise RuntimeError(f"reference sources not found at {REF_SRC}: run `python oracle/stage_ref.py` in the build container")
     if REF_SRC not in sys.path:
         sys.path.insert(0, REF_SRC)
 
@@ -154,3 +161,33 @@ def load_reference():
         MultiheadAttention=MultiheadAttention, InvariantPointAttention=InvariantPointAttention,
     )
     return _loaded
+
+
+# ---- mdgen.wrapper (NewMDGenWrapper: prep_batch / inference, rows N1 / N2) ---------------------------------------
+class _LightningModuleStub(torch.nn.Module):
+    """pytorch_lightning.LightningModule as far as mdgen/wrapper.py uses it outside a Trainer: an nn.Module with
+    `save_hyperparameters()` (wrapper.py:48) and a `device` property (wrapper.py:228,431-433,458-460)."""
+
+    def save_hyperparameters(self, *a, **k):
+        pass
+
+    @property
+    def device(self):
+        try:
+            return next(self.parameters()).device
+        except StopIteration:
+            return torch.device("cpu")
+
+
+def load_wrapper():
+    """The reference's NewMDGenWrapper (src/mdgen/wrapper.py:175) with `pytorch_lightning` and `wandb` stubbed
+    (both absent from this image; neither does arithmetic on the prep_batch / inference path)."""
+    ref = load_reference()
+    if "pytorch_lightning" not in sys.modules:
+        _stub("pytorch_lightning", LightningModule=_LightningModuleStub)
+    if "wandb" not in sys.modules:
+        _stub("wandb", log=lambda *a, **k: None)
+    from mdgen import wrapper
+    ref.wrapper = wrapper
+    ref.NewMDGenWrapper = wrapper.NewMDGenWrapper
+    return ref

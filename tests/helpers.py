@@ -8,6 +8,8 @@ from mdgen_finetune_b200.weights import random_state_dict
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = ["sim_small", "tps_small", "upsample_small", "design_small", "atlas_small", "atlas_mid"]
+# BASELINE configs 2-5 at FULL size (oracle/make_golden.py FULL): the shapes that select the kernels bench.py times
+FULL_CASES = ["tps_full", "upsample_full", "design_full", "atlas_full"]
 
 
 def load_case(name, seed=0):

@@ -87,21 +87,27 @@ def test_gemm_tcgen05_fused_residual_layernorm(M, K):
     N = 384
     g = torch.Generator().manual_seed(M + K)
     A, W = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5
-    vec = torch.randn(2, N, generator=g) * 0.5          # row b: gate = shift = scale of batch element b; row 0 also the bias
+    # four DISTINCT operands (a swap of gate / shift / scale / bias inside the kernel changes the expected value):
+    # vec = [linear bias (1, N) | gate (2, N) | shift (2, N) | scale (2, N)], row b of each pair = batch element b
+    vec = torch.randn(7, N, generator=g) * 0.5
+    bias, gate, shift, scale = vec[0], vec[1:3], vec[3:5], vec[5:7]
     x0 = torch.randn(M, N, generator=g) * 2.0 + 0.3
     C = torch.cat([x0, torch.zeros(M, N)]).cuda()
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-    dA, dW, dv = A.cuda(), W.cuda(), vec.cuda()
+    dA, dW, dv = A.cuda(), W.cuda(), vec.contiguous().cuda()
     _lib.check(_lib.lib().mdgen_test_gemm(M, N, K, _p(dA), _p(dW), _p(dv), _p(C), 5, 0, st), "test_gemm")
     torch.cuda.synchronize()
-    b = (torch.arange(M) // 200) % 2
-    acc = A.bfloat16().double() @ W.bfloat16().double().T + vec[0].double()
-    x = x0.double() + vec[b].double() * acc
-    h = torch.nn.functional.layer_norm(x, (N,), eps=1e-6) * (1 + vec[b].double()) + vec[b].double()
+    b = (torch.arange(M) // 200) % 2              # batch boundaries fall inside the 256-row slabs
+    acc = A.bfloat16().double() @ W.bfloat16().double().T + bias.double()
+    x = x0.double() + gate[b].double() * acc
+    h = torch.nn.functional.layer_norm(x, (N,), eps=1e-6) * (1 + scale[b].double()) + shift[b].double()
     out = C.cpu()
     assert torch.isfinite(out).all()
     assert float((out[:M] - x.float()).norm() / x.norm()) < 1e-5
     assert float((out[M:] - h.float()).norm() / h.norm()) < 4e-3      # one bf16 rounding
+    # sanity of the test itself: swapping shift and scale must be visible at this tolerance
+    h_sw = torch.nn.functional.layer_norm(x, (N,), eps=1e-6) * (1 + shift[b].double()) + scale[b].double()
+    assert float((h_sw - h).norm() / h.norm()) > 0.1
 
 
 def _attn_ref(qkv, bk, bv, valid, nb, S, inner, H, hd, rope):
