@@ -6,8 +6,10 @@
  * host) pointers; no torch types cross this boundary.  Every call returns 0 on success and a
  * negative MDGEN_E* code otherwise; mdgen_last_error() returns the message of the last failure
  * on the calling thread.  A handle is bound to the CUDA device that was current at
- * mdgen_create(); calls are asynchronous on the stream passed in and are CUDA-graph capturable
- * after the first mdgen_set_conditioning() of a given shape (no allocation in the step).
+ * mdgen_create(); calls are asynchronous on the stream passed in.  mdgen_euler_rollout replays ONE CUDA graph of the
+ * whole solve (captured on first use per shape / step count, MDGEN_NO_GRAPH=1 disables it); under a caller's own
+ * stream capture it emits the plain launch sequence instead (no allocation, copy from host or synchronisation in the
+ * step; one un-captured call of the same shape must have run first) -- tests/test_graph.py covers both.
  */
 #ifndef MDGEN_B200_H
 #define MDGEN_B200_H
@@ -124,10 +126,13 @@ int mdgen_dirichlet_flow(MdgenHandle* h, const float* x, float* latent, const do
 /* Design-mode sampler: the tables mdgen_euler_rollout needs to apply the Dirichlet flow at every step of the next
  * rollout (nt = num_steps - 1).  HOST pointers: rows [nt, 1000] f64 (the beta_cdfs_derivative row nearest to alpha_i,
  * utils.py:53), alphas [nt], betas [nt] (B(alpha_i, 19)); temp / dalpha / allow_nan as in mdgen_dirichlet_flow.
+ * The upload is asynchronous on `stream` (ordered after a rollout still in flight there) from a handle-owned staging
+ * copy, so the host buffers are free on return; unchanged tables are not uploaded again.
  * After the rollout mdgen_dirichlet_flags returns the counters accumulated over all steps (off-simplex tokens,
  * NaN c-factors): the reference warns / raises at the step where they occur, the fused rollout at its end. */
 int mdgen_set_dirichlet_tables(MdgenHandle* h, int32_t nt, const double* rows, const double* alphas,
-                               const double* betas, float temp, float dalpha, int32_t allow_nan);
+                               const double* betas, float temp, float dalpha, int32_t allow_nan,
+                               mdgen_stream_t stream);
 int mdgen_dirichlet_flags(MdgenHandle* h, int32_t* flags_out, mdgen_stream_t stream);
 
 /* NewMDGenWrapper.prep_batch (wrapper.py:283-365), the step before the sampler, on the device and stateless:
@@ -154,8 +159,12 @@ int mdgen_decode_atom14(int32_t B, int32_t T, int32_t L, int32_t D, const float*
 /* introspection ------------------------------------------------------------------------ */
 /* Number of kernels one mdgen_forward launches for the current conditioning shape. */
 int mdgen_launches_per_forward(MdgenHandle* h);
-/* Total kernels launched by the library on the calling thread since load. */
+/* Total kernels launched by the library on the calling thread since load (graph replays count their kernel nodes). */
 long long mdgen_launch_count(void);
+/* Launches per kernel variant since load: 0 gemm_ln (fused projection + residual + LayerNorm), 1 gemm_tc2 (CTA pair),
+ * 2 gemm_tc, 3 attention_tc, 4 attention_seq4 (residue axis, 5 keys), 5 whole-rollout graph replays; -1 if out of range.
+ * Launches captured into a rollout graph are counted once, at capture. */
+long long mdgen_variant_launches(int32_t which);
 /* Bytes of device workspace currently held by the handle. */
 int64_t mdgen_workspace_bytes(MdgenHandle* h);
 
@@ -173,7 +182,9 @@ int mdgen_debug_set_buffer(long long* device_buf, int32_t cta);
 /* C[M,N] = A[M,K] . W[N,K]^T + bias, A/W fp32 on device (converted to bf16 inside when
  * use_tc != 0 -> tcgen05 path; fp32 SIMT path otherwise).  tcgen05 epilogue variants: use_tc = 1 fp32 store,
  * 2 bf16 store, 3 bf16 erf-GELU (both converted back to fp32 into C), 4 C[m,n] += bias[n] * (acc + bias[n])
- * (the gated-residual epilogue with gate = bias). */
+ * (the gated-residual epilogue with gate = bias), 5 the fused projection + gated residual + LayerNorm/modulate kernel
+ * (N = 384): bias = [linear bias (N) | gate (2,N) | shift (2,N) | scale (2,N)], batch element (m / 200) % 2,
+ * C = [2M, N]: rows [0,M) residual stream in/out, rows [M,2M) the normalised rows. */
 int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float* W,
                     const float* bias, float* C, int32_t use_tc, int32_t block_n,
                     mdgen_stream_t stream);

@@ -21,7 +21,10 @@ PREC_BF16, PREC_FP32_CHECK = 0, 1
 EXPORTS = ["mdgen_create", "mdgen_destroy", "mdgen_last_error", "mdgen_abi_version", "mdgen_load_weight",
            "mdgen_finalize_weights", "mdgen_set_conditioning", "mdgen_forward", "mdgen_euler_rollout", "mdgen_dirichlet_flow", "mdgen_set_dirichlet_tables", "mdgen_dirichlet_flags", "mdgen_prep_batch", "mdgen_decode_atom14",
            "mdgen_launches_per_forward", "mdgen_launch_count", "mdgen_workspace_bytes", "mdgen_profile_begin", "mdgen_profile_end",
-           "mdgen_profile_category_name", "mdgen_debug_set_buffer", "mdgen_test_gemm", "mdgen_test_attention"]
+           "mdgen_profile_category_name", "mdgen_debug_set_buffer", "mdgen_test_gemm", "mdgen_test_attention",
+           "mdgen_variant_launches"]
+# kernel variants counted by mdgen_variant_launches(i) (tests assert that the full-size cases reach the timed kernels)
+VARIANTS = ["gemm_ln", "gemm_tc2", "gemm_tc", "attention_tc", "attention_seq4", "graph_replays"]
 
 
 class MdgenConfig(ctypes.Structure):
@@ -80,7 +83,7 @@ def lib():
     L.mdgen_euler_rollout.argtypes = [vp, fp, i32, fp, fp, vp]
     L.mdgen_dirichlet_flow.argtypes = [vp, fp, fp, vp, ctypes.c_double, ctypes.c_double, ctypes.c_float, ctypes.c_float, i32,
                                        ctypes.POINTER(ctypes.c_int32), vp]
-    L.mdgen_set_dirichlet_tables.argtypes = [vp, i32, vp, vp, vp, ctypes.c_float, ctypes.c_float, i32]
+    L.mdgen_set_dirichlet_tables.argtypes = [vp, i32, vp, vp, vp, ctypes.c_float, ctypes.c_float, i32, vp]
     L.mdgen_dirichlet_flags.argtypes = [vp, ctypes.POINTER(ctypes.c_int32), vp]
     L.mdgen_decode_atom14.argtypes = [i32, i32, i32, i32, fp, i32, fp, fp, vp, fp, vp, fp, fp, i32, fp, vp, vp]
     L.mdgen_prep_batch.argtypes = [i32, i32, i32, fp, fp, fp, i32, i32, fp, fp, vp, vp]
@@ -88,6 +91,8 @@ def lib():
     L.mdgen_workspace_bytes.argtypes = [vp]
     L.mdgen_workspace_bytes.restype = ctypes.c_int64
     L.mdgen_launch_count.restype = ctypes.c_int64
+    L.mdgen_variant_launches.argtypes = [i32]
+    L.mdgen_variant_launches.restype = ctypes.c_int64
     L.mdgen_test_gemm.argtypes = [i32, i32, i32, fp, fp, fp, fp, i32, i32, vp]
     L.mdgen_test_attention.argtypes = [i32] * 5 + [fp] * 5 + [i32, i32, vp]
     L.mdgen_debug_set_buffer.argtypes = [vp, i32]
@@ -96,7 +101,7 @@ def lib():
     L.mdgen_profile_category_name.restype = ctypes.c_char_p
     for name in EXPORTS:
         if name not in ("mdgen_last_error", "mdgen_workspace_bytes", "mdgen_profile_category_name",
-                        "mdgen_launch_count"):
+                        "mdgen_launch_count", "mdgen_variant_launches"):
             getattr(L, name).restype = ctypes.c_int32
     _lib = L
     return L

@@ -541,23 +541,25 @@ attention_seq4_bulk_kernel(AttnParams<bf16> p) {
   store24(p.out + ((size_t)nbi * S_ + t) * p.ldo + h * HD, q);
 }
 inline bool attention_seq4_bulk_supported(const AttnParams<bf16>& p) {
-  return p.S == 4 && p.inner == 1 && p.H == 16 && p.ld == 3 * p.H * 24 && (((uintptr_t)p.qkv) & 15) == 0 && !getenv("MDGEN_NO_ATTN_BULK");
+  return p.S == 4 && p.inner == 1 && p.H == 16 && p.ld == 3 * p.H * 24 && (((uintptr_t)p.qkv) & 15) == 0 && !g_sw.no_attn_bulk;
 }
 inline bool attention_seq4_bulk_supported(const AttnParams<float>&) { return false; }
 template <int NSEQ>
 inline cudaError_t launch_attention_seq4_bulk_n(const AttnParams<bf16>& p, cudaStream_t st) {
   const int smem = NSEQ * 4 * p.ld * (int)sizeof(bf16) + 16 + 2 * 5 * 12 * 4 + 2 * 16 * 24 * 4;
-  static bool configured = false;
-  if (!configured) {
+  static DevOnce once;
+  const int dev = cur_device();
+  if (once.need(dev)) {
     cudaError_t e = cudaFuncSetAttribute(attention_seq4_bulk_kernel<24, NSEQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done(dev);
   }
+  MD_VARIANT(V_ATTN_SEQ4);
   attention_seq4_bulk_kernel<24, NSEQ><<<(p.nb + NSEQ - 1) / NSEQ, NSEQ * 64, smem, st>>>(p);
   return cudaSuccess;
 }
 inline cudaError_t launch_attention_seq4_bulk(const AttnParams<bf16>& p, cudaStream_t st) {
-  static const int nseq = getenv("MDGEN_ASB_SEQ") ? atoi(getenv("MDGEN_ASB_SEQ")) : 4;
+  const int nseq = g_sw.asb_seq;
   return nseq == 1 ? launch_attention_seq4_bulk_n<1>(p, st) : nseq == 2 ? launch_attention_seq4_bulk_n<2>(p, st) : launch_attention_seq4_bulk_n<4>(p, st);
 }
 inline cudaError_t launch_attention_seq4_bulk(const AttnParams<float>&, cudaStream_t) { return cudaErrorNotSupported; }

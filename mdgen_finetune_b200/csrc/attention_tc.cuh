@@ -596,21 +596,22 @@ inline bool attention_tc_supported(const AttnParams<bf16>& p, int head_dim) {
   return head_dim == atc::HD && p.S + 1 <= atc::MAX_KEYS && p.S >= 64 && (p.ld % 8) == 0 && (p.ldo % 8) == 0;
 }
 
-int num_sms();
-extern long long* g_dbg_buf;   // device buffer for dbg_stamp (mdgen_debug_set_buffer), normally null
-extern int g_dbg_cta;
+extern thread_local long long* g_dbg_buf;   // device buffer for dbg_stamp (mdgen_debug_set_buffer), normally null
+extern thread_local int g_dbg_cta;
 
 constexpr int ATTN_POLY_DEFAULT = 0;   // MDGEN_ATTN_POLY=3: every third exp2 on the FMA pipe -- measured SLOWER (216 -> 234 us on config 3:
                                        // the kernel is issue-bound, not MUFU-bound), kept for A/B runs
 
 template <bool DBG, int POLY>
 inline cudaError_t launch_attention_tc_variant(const AttnParams<bf16>& p, int grid, int chunks, int nunits, int var, cudaStream_t st) {
-  static bool configured = false;
-  if (!configured) {
+  static DevOnce once;
+  const int dev = cur_device();
+  if (once.need(dev)) {
     cudaError_t e = cudaFuncSetAttribute(atc::attention_tc_kernel<DBG, POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done(dev);
   }
+  MD_VARIANT(V_ATTN_TC);
   atc::attention_tc_kernel<DBG, POLY><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, nunits, DBG ? g_dbg_buf : nullptr, g_dbg_cta, var);
   return cudaSuccess;
 }
@@ -624,8 +625,7 @@ inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStre
   const long nunits = (long)p.nb * p.H * chunks;
   const int grid = (int)(nunits < num_sms() ? nunits : num_sms());
   ProfScope ps(PC_ATTN_TC, st);
-  static const int var = getenv("MDGEN_ATTN_VAR") ? atoi(getenv("MDGEN_ATTN_VAR")) : 0;
-  static const int poly = getenv("MDGEN_ATTN_POLY") ? atoi(getenv("MDGEN_ATTN_POLY")) : ATTN_POLY_DEFAULT;
+  const int var = g_sw.attn_var, poly = g_sw.attn_poly;
   if (g_dbg_buf || var) {
     MD_CUDA((launch_attention_tc_variant<true, ATTN_POLY_DEFAULT>(p, grid, chunks, (int)nunits, var, st)));
   } else {

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -40,6 +41,41 @@ void set_error(const std::string& msg);
 extern thread_local long long g_launches;
 #define MD_LAUNCHED() (++mdgen::g_launches)
 
+// ---- per-DEVICE (not per-process) launcher state ---------------------------------------------------------------
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) and the SM count belong to a device: a process that drives several
+// GPUs (nn.DataParallel replicas, samplers.py:75-79; one handle per device) configures each kernel once per device.
+int cur_device();
+int num_sms();                                     // SM count of the current device (cached per device)
+struct DevOnce {
+  std::atomic<unsigned long long> mask{0};         // bit d set: configured on device d (d < 64)
+  bool need(int dev) const { return dev < 0 || dev >= 64 || !((mask.load(std::memory_order_acquire) >> dev) & 1ull); }
+  void done(int dev) { if (dev >= 0 && dev < 64) mask.fetch_or(1ull << dev, std::memory_order_release); }
+};
+#define MD_SMEM_ONCE(kern, bytes)                                                                           \
+  do {                                                                                                      \
+    static mdgen::DevOnce once__;                                                                           \
+    const int dev__ = mdgen::cur_device();                                                                  \
+    if (once__.need(dev__)) {                                                                               \
+      MD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));       \
+      once__.done(dev__);                                                                                   \
+    }                                                                                                       \
+  } while (0)
+
+// Kernel-variant switches (A/B measurements, debugging): the environment is read ONCE PER C-ABI
+// CALL (read_switches() at the entry points), never per launch.
+struct Switches {
+  bool no_gemm_ln = false, no_gemm_2cta = false, no_gemm_ws = false, no_l2_persist = false, no_attn_tc = false,
+       no_attn_bulk = false, gelu_2cta = false, no_graph = false;
+  int attn_var = 0, attn_poly = 0, asb_seq = 4;
+};
+extern thread_local Switches g_sw;
+void read_switches();
+
+// launches per kernel variant (mdgen_variant_launches): tests assert that the full-size cases reach the timed kernels
+enum Variant : int { V_GEMM_LN = 0, V_GEMM_TC2, V_GEMM_TC, V_ATTN_TC, V_ATTN_SEQ4, V_GRAPH_REPLAY, V_COUNT };
+extern std::atomic<long long> g_variant[V_COUNT];
+#define MD_VARIANT(v) (mdgen::g_variant[v].fetch_add(1, std::memory_order_relaxed))
+
 // optional per-kernel-family timing with CUDA events on the launching stream (bench.py roofline)
 enum ProfCat : int { PC_GEMM_TC = 0, PC_GEMM_SIMT, PC_ATTN_TC, PC_ATTN_SIMT, PC_ATTN_SHORT, PC_LN, PC_EMBED, PC_IPA,
                      PC_ADALN, PC_MISC, PC_COUNT };
@@ -48,7 +84,7 @@ struct Profiler {
   bool on = false;
   std::vector<ProfRec> recs;
 };
-extern Profiler g_prof;
+extern thread_local Profiler g_prof;
 struct ProfScope {
   cudaStream_t st;
   bool active;

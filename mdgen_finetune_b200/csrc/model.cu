@@ -26,10 +26,30 @@ namespace mdgen {
 
 static thread_local std::string g_err;
 thread_local long long g_launches = 0;
-Profiler g_prof;
-long long* g_dbg_buf = nullptr;
-int g_dbg_cta = 0;
+thread_local Profiler g_prof;
+thread_local long long* g_dbg_buf = nullptr;
+thread_local int g_dbg_cta = 0;
+thread_local Switches g_sw;
+std::atomic<long long> g_variant[V_COUNT];
 void set_error(const std::string& msg) { g_err = msg; }
+
+void read_switches() {
+  auto on = [](const char* n) { return getenv(n) != nullptr; };
+  auto num = [](const char* n, int d) { const char* v = getenv(n); return v ? atoi(v) : d; };
+  Switches s;
+  s.no_gemm_ln = on("MDGEN_NO_GEMM_LN");
+  s.no_gemm_2cta = on("MDGEN_NO_GEMM_2CTA");
+  s.no_gemm_ws = on("MDGEN_NO_GEMM_WS");
+  s.no_l2_persist = on("MDGEN_NO_L2_PERSIST");
+  s.no_attn_tc = on("MDGEN_NO_ATTN_TC");
+  s.no_attn_bulk = on("MDGEN_NO_ATTN_BULK");
+  s.gelu_2cta = on("MDGEN_GELU_2CTA");
+  s.no_graph = on("MDGEN_NO_GRAPH");
+  s.attn_var = num("MDGEN_ATTN_VAR", 0);
+  s.attn_poly = num("MDGEN_ATTN_POLY", 0);
+  s.asb_seq = num("MDGEN_ASB_SEQ", 4);
+  g_sw = s;
+}
 
 // ---- driver entry point for TMA descriptors (no link-time dependency on libcuda) ----------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -80,27 +100,30 @@ static int make_tmap_2d_box(CUtensorMap* m, const void* ptr, CUtensorMapDataType
   return 0;
 }
 
-static int g_num_sms = 0;
+int cur_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+static std::atomic<int> g_num_sms[64];   // per device; 0 = not queried yet
 int num_sms() {
-  if (!g_num_sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_num_sms <= 0) g_num_sms = 148;
+  const int dev = cur_device();
+  int n = (dev >= 0 && dev < 64) ? g_num_sms[dev].load(std::memory_order_relaxed) : 0;
+  if (!n) {
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+    if (dev >= 0 && dev < 64) g_num_sms[dev].store(n, std::memory_order_relaxed);
   }
-  return g_num_sms;
+  return n;
 }
 
 template <int BN, int EPI, typename OT, int WS, int STG>
 static int launch_tc_ws(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K,
                         const EpiParams& ep, cudaStream_t st) {
-  static bool configured = false;
   auto kern = tc::gemm_tc_kernel<BN, EPI, OT, WS, STG>;
   constexpr int smem = WS ? tc::ws_smem_bytes(BN) : tc::smem_bytes(BN);
-  if (!configured) {
-    MD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
+  MD_SMEM_ONCE(kern, smem);
+  MD_VARIANT(V_GEMM_TC);
   int tiles = ((M + tc::BLOCK_M - 1) / tc::BLOCK_M) * ((N + BN - 1) / BN);
   int grid = tiles < num_sms() ? tiles : num_sms();
   ProfScope ps(PC_GEMM_TC, st);
@@ -121,7 +144,7 @@ static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, const CU
       // weight-stationary when the [BN, K] slice fits and every CTA gets a tile of its fixed n tile
       if constexpr (BN == 128) {
         const int num_n = (N + BN - 1) / BN, num_m = (M + tc::BLOCK_M - 1) / tc::BLOCK_M;
-        if (K <= tc::WS_MAX_KB * tc::BLOCK_K && num_n <= num_sms() && num_m >= 2 && !getenv("MDGEN_NO_GEMM_WS"))
+        if (K <= tc::WS_MAX_KB * tc::BLOCK_K && num_n <= num_sms() && num_m >= 2 && !g_sw.no_gemm_ws)
           return launch_tc_ws<BN, EPI, OT, 1, STG>(ta, tw, tcm, M, N, K, ep, st);
       }
       return launch_tc_ws<BN, EPI, OT, 0, STG>(ta, tw, tcm, M, N, K, ep, st);
@@ -134,12 +157,9 @@ static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, const CU
 template <int EPI, typename OT>
 static int launch_tc2_inst(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K,
                            const EpiParams& ep, cudaStream_t st) {
-  static bool configured = false;
   auto kern = tc2::gemm_tc2_kernel<EPI, OT>;
-  if (!configured) {
-    MD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc2::SMEM2_BYTES));
-    configured = true;
-  }
+  MD_SMEM_ONCE(kern, tc2::SMEM2_BYTES);
+  MD_VARIANT(V_GEMM_TC2);
   const int tiles = ((M + tc2::TILE_M - 1) / tc2::TILE_M) * ((N + tc2::TILE_N - 1) / tc2::TILE_N);
   const int pairs = num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
@@ -166,16 +186,13 @@ static int launch_tc2(const CUtensorMap& ta, const CUtensorMap& tw, const CUtens
 int launch_gemm_resid_ln(const bf16* A, int lda, const bf16* W, int ldw, int M, int N, int K, const EpiParams& ep,
                          const tcln::LnFuse& ln, cudaStream_t st) {
   auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
-  if (getenv("MDGEN_NO_GEMM_LN")) return 1;
+  if (g_sw.no_gemm_ln) return 1;
   if (N != tcln::LN_N || K % tc::BLOCK_K != 0 || M < tcln::TILE_M || ep.rows_per_batch < tc::BLOCK_M) return 1;
   if (!al16(ep.resid) || ep.ldr % 4 != 0 || (ep.bias && !al16(ep.bias)) || (ep.gate && !al16(ep.gate)) || ep.gate_stride % 4 != 0 ||
       !al16(ln.shift) || !al16(ln.scale) || !al16(ln.out))
     return 1;
-  static bool configured = false;
-  if (!configured) {
-    MD_CUDA(cudaFuncSetAttribute(tcln::gemm_ln_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcln::SMEM_BYTES));
-    configured = true;
-  }
+  MD_SMEM_ONCE(tcln::gemm_ln_kernel, tcln::SMEM_BYTES);
+  MD_VARIANT(V_GEMM_LN);
   CUtensorMap ta, tw1, tw2, tx, th;
   MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
   MD_TRY(make_tmap_2d(&tw1, W, N, K, ldw, tcln::W1_ROWS));
@@ -239,11 +256,11 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
   // CTA-pair kernel: staged epilogues only, N in whole 128-column halves, enough 256 x 256 tiles to fill the pairs
   const bool pair_ok = epp.staged && N % 128 == 0 && epi != EPI_EULER && (epi == EPI_GATE_RESID || epi == EPI_RESID || out_bf16);
   if (block_n == 256) MD_CHECK(pair_ok, "launch_gemm_tc: shape / epilogue not supported by the CTA-pair kernel");
-  if (auto_bn && pair_ok && !getenv("MDGEN_NO_GEMM_2CTA")) {
+  if (auto_bn && pair_ok && !g_sw.no_gemm_2cta) {
     const long t256 = (long)((M + 255) / 256) * ((N + 255) / 256);
     // measured on config 3 (tools/gemm_probe.py): the pair kernel wins for the K = 1536 projection (fc2) and the plain
     // bf16 stores of wide N; the K = 384 residual / GELU epilogues are shared-memory-bandwidth bound either way
-    static const bool gelu_pair = getenv("MDGEN_GELU_2CTA") != nullptr;
+    const bool gelu_pair = g_sw.gelu_2cta;
     if (t256 >= num_sms() / 2 && (K >= 1024 || ((epi == EPI_STORE || (gelu_pair && epi == EPI_GELU)) && N >= 1024))) block_n = 256;
   }
   CUtensorMap ta, tw;
@@ -328,7 +345,8 @@ struct MdgenHandle {
   // design-mode sampler: per-step Dirichlet-flow tables of the next mdgen_euler_rollout (mdgen_set_dirichlet_tables)
   double* dflow_rows = nullptr;    // device [nt, 1000]
   int* dflow_flags = nullptr;      // device [2]: off-simplex tokens, NaN c-factors (accumulated over the rollout)
-  int dflow_nt = 0;
+  int dflow_nt = 0, dflow_cap = 0;
+  std::vector<double> dflow_rows_host;   // staging / change detection for mdgen_set_dirichlet_tables
   int dflow_step = 0;              // sampler step of the evaluation in flight (its time tables hold a single row)
   std::vector<float> dflow_am1;    // alpha_i - 1 per step
   std::vector<double> dflow_beta;  // B(alpha_i, 19)
@@ -373,6 +391,20 @@ struct MdgenHandle {
         *ipa_cat = nullptr, *ipa_out = nullptr;
   float *xd = nullptr, *dh_mean = nullptr, *dh_a = nullptr, *dh_b = nullptr, *dh_logits = nullptr;
   int launches_last_forward = 0;
+  bool alloc_scratch = false;       // dev_alloc books into scratch_owned (ensure_scratch) instead of ws_owned
+  // ---- whole-rollout CUDA graph (mdgen_euler_rollout): every node references handle-owned memory only
+  long long generation = 0;         // bumped whenever a pointer or a by-value kernel argument baked into the graph may change
+  cudaStream_t cap_stream = nullptr;   // internal stream the graph is captured on (the caller's may be the legacy stream)
+  cudaGraphExec_t rg_exec = nullptr;
+  long long rg_generation = -1;
+  int rg_num_steps = 0, rg_launches = 0, rg_launches_per_eval = 0;
+  bool rg_traj = false;
+  unsigned rg_switches = 0;
+  float* state_buf = nullptr;       // [N, D] ODE state of the graph
+  float* traj_buf = nullptr;        // [num_steps, N, D] trajectory of the graph
+  size_t traj_cap = 0;
+  bool l2_limit_set = false;
+  size_t l2_prev_limit = 0;
 
   int C() const { return cfg.embed_dim; }
   int D() const { return cfg.latent_dim; }
@@ -384,7 +416,6 @@ struct MdgenHandle {
 
 namespace mdgen {
 
-static bool g_alloc_scratch = false;
 static int dev_alloc(MdgenHandle* h, void** out, size_t bytes, bool packed = false) {
   void* p = nullptr;
   if (bytes == 0) bytes = 16;
@@ -394,7 +425,7 @@ static int dev_alloc(MdgenHandle* h, void** out, size_t bytes, bool packed = fal
     DevBuf b;
     b.p = p;
     b.bytes = bytes;
-    (g_alloc_scratch ? h->scratch_owned : h->ws_owned).push_back(b);
+    (h->alloc_scratch ? h->scratch_owned : h->ws_owned).push_back(b);
     h->ws_bytes += bytes;
   }
   *out = p;
@@ -477,6 +508,7 @@ static int pack_mha(MdgenHandle* h, const std::string& p, MhaW* m, cudaStream_t 
 }
 
 static int finalize_weights(MdgenHandle* h, cudaStream_t st) {
+  ++h->generation;
   for (void* p : h->packed) cudaFree(p);
   h->packed.clear();
   h->ipa.clear();
@@ -609,6 +641,7 @@ __global__ void take_first_frame_mask_kernel(const float* __restrict__ mask, int
 
 static int alloc_workspace(MdgenHandle* h, int B, int T, int L) {
   free_workspace(h);
+  ++h->generation;
   const int C = h->C(), Dc = h->Dc();
   const size_t N = (size_t)B * T * L;
   const int streams = h->two_stream() ? 2 : 1;
@@ -642,7 +675,8 @@ static int alloc_workspace(MdgenHandle* h, int B, int T, int L) {
 static int ensure_scratch(MdgenHandle* h, int nt) {
   if (nt <= h->nt_cap) return 0;
   free_scratch(h);
-  g_alloc_scratch = true;
+  h->alloc_scratch = true;
+  ++h->generation;
   const int C = h->C(), D = h->D(), B = h->B, T = h->T, L = h->L;
   const size_t N = (size_t)B * T * L;
   const size_t Mi = (size_t)h->streams * B * L * nt;
@@ -676,8 +710,9 @@ static int ensure_scratch(MdgenHandle* h, int nt) {
   WS(h->dh_a, (size_t)B * L * C * 4);
   WS(h->dh_b, (size_t)B * L * C * 4);
   WS(h->dh_logits, (size_t)B * L * 20 * 4);
+  WS(h->state_buf, N * D * 4);
 #undef WS
-  g_alloc_scratch = false;
+  h->alloc_scratch = false;
   if (rc == 0) h->nt_cap = nt;
   return rc;
 }
@@ -849,7 +884,7 @@ struct Fwd {
     p.cs = rope ? (frame_axis ? h->rope_t_cs : h->rope_l_cs) : nullptr;
     p.sn = rope ? (frame_axis ? h->rope_t_sn : h->rope_l_sn) : nullptr;
     if constexpr (sizeof(AT) == 2) {
-      if (attention_tc_supported(p, hd) && !getenv("MDGEN_NO_ATTN_TC")) return launch_attention_tc(p, hd, st);
+      if (attention_tc_supported(p, hd) && !g_sw.no_attn_tc) return launch_attention_tc(p, hd, st);
     }
     return launch_attention_simt<AT>(p, hd, st);
   }
@@ -1035,6 +1070,37 @@ static int time_tables(Fwd<AT>& f, const float* t, int nt, const float* x_for_de
   return 0;
 }
 
+// Step-invariant part of the token embedding, once per conditioning (latent_model.py:243-250):
+// W_c x_cond + biases + mask / position / time embeddings -> emb_static [N, C]
+// (embed_kernel with D = 0 reads only the conditioning rows of the transposed weight).
+static int ensure_emb_static(MdgenHandle* h, cudaStream_t st) {
+  if (h->emb_static_valid) return 0;
+  const int C = h->C(), T = h->T, L = h->L, D = h->D(), Dc = h->Dc();
+  const int N = h->B * T * L;
+  const Tensor* me = find_w(h, "mask_to_emb.weight");
+  const Tensor* pe = h->flag(MDGEN_F_ABS_POS) ? find_w(h, "pos_embed") : nullptr;
+  const Tensor* te = h->flag(MDGEN_F_ABS_TIME) ? find_w(h, "time_embed") : nullptr;
+  MD_CHECK(me, "missing embedding weights");
+  if (h->flag(MDGEN_F_ABS_POS)) MD_CHECK(pe, "missing pos_embed");
+  const bool hc = h->has_cond;
+  const int Ds = hc ? Dc : 0;
+  ProfScope ps(PC_EMBED, st);
+  const dim3 grid((N + EMB_TOK - 1) / EMB_TOK);
+#define MD_EMBED(DDP)                                                                                               \
+  embed_kernel<384, DDP><<<grid, 384, 0, st>>>(nullptr, 0, hc ? h->x_cond : nullptr, Ds,                            \
+                                               hc ? h->cond_mask : nullptr, h->emb_wt + (size_t)D * C,              \
+                                               hc ? h->emb_bsum : h->emb_bx, me->d, pe ? pe->d : nullptr,           \
+                                               te ? te->d : nullptr, nullptr, h->emb_static, N, T, L)
+  if (Ds <= 48) MD_EMBED(48);
+  else if (Ds <= 64) MD_EMBED(64);
+  else MD_EMBED(80);
+#undef MD_EMBED
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  h->emb_static_valid = true;
+  return 0;
+}
+
 // Embedding + 5 factorised blocks + final projection for time row `step` of the current tables.
 // If `state` != null the final epilogue also does state += dt * v (the Euler step fused into the
 // last projection; SURVEY Q4: no clamp on conditioned frames).
@@ -1050,33 +1116,9 @@ static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state,
   const float* ipa_out = pre ? h->ipa_out + (size_t)step * B * L * C : nullptr;
   // ---- token embedding (latent_model.py:242-255)
   {
-    const Tensor* me = find_w(h, "mask_to_emb.weight");
-    const Tensor* pe = h->flag(MDGEN_F_ABS_POS) ? find_w(h, "pos_embed") : nullptr;
-    const Tensor* te = h->flag(MDGEN_F_ABS_TIME) ? find_w(h, "time_embed") : nullptr;
-    MD_CHECK(me, "missing embedding weights");
-    if (h->flag(MDGEN_F_ABS_POS)) MD_CHECK(pe, "missing pos_embed");
-    const bool hc = h->has_cond;
-    const int DD = D + (hc ? Dc : 0);
-    MD_CHECK(DD <= 80, "latent_dim + cond_dim > 80 not supported by the embedding kernel");
+    MD_TRY(ensure_emb_static(h, st));
+    MD_CHECK(D + (h->has_cond ? Dc : 0) <= 80, "latent_dim + cond_dim > 80 not supported by the embedding kernel");
     ProfScope ps(PC_EMBED, st);
-    const dim3 grid((N + EMB_TOK - 1) / EMB_TOK);
-    if (!h->emb_static_valid) {
-      // step-invariant part, once per conditioning: W_c x_cond + biases + mask / position / time embeddings
-      // (embed_kernel with D = 0 reads only the conditioning rows of the transposed weight)
-      const int Ds = hc ? Dc : 0;
-#define MD_EMBED(DDP)                                                                                               \
-  embed_kernel<384, DDP><<<grid, 384, 0, st>>>(nullptr, 0, hc ? h->x_cond : nullptr, Ds,                            \
-                                               hc ? h->cond_mask : nullptr, h->emb_wt + (size_t)D * C,              \
-                                               hc ? h->emb_bsum : h->emb_bx, me->d, pe ? pe->d : nullptr,           \
-                                               te ? te->d : nullptr, nullptr, h->emb_static, N, T, L)
-      if (Ds <= 48) MD_EMBED(48);
-      else if (Ds <= 64) MD_EMBED(64);
-      else MD_EMBED(80);
-#undef MD_EMBED
-      MD_LAUNCHED();
-      MD_CUDA(cudaGetLastError());
-      h->emb_static_valid = true;
-    }
     const dim3 sgrid((N + EMB_STEP_TOK - 1) / EMB_STEP_TOK);
     if (D <= 24) embed_step_kernel<384, 24, 4><<<sgrid, 96, 0, st>>>(x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L);
     else if (D <= 48) embed_step_kernel<384, 48, 2><<<sgrid, 192, 0, st>>>(x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L);
@@ -1161,33 +1203,140 @@ static int forward_impl(MdgenHandle* h, const float* x, const float* t, float* o
   return 0;
 }
 
+// t_vec = ones(B) * t_i for every grid interval (integrators.py:98-99) with t = torch.linspace(0, 1, n) in fp32
+// (start + step * i below the midpoint, end - step * (n - 1 - i) above it; no FMA contraction), written on the device so
+// that a rollout needs no host-to-device copy (and no stream synchronisation) of its own.
+__global__ void time_grid_kernel(float* __restrict__ t, int nt, int B, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nt * B) return;
+  const int k = i / B;
+  const float step = __fdiv_rn(1.0f, (float)(n - 1));
+  t[i] = k < n / 2 ? __fmul_rn(step, (float)k) : __fsub_rn(1.0f, __fmul_rn(step, (float)(n - 1 - k)));
+}
+
 // Fixed-grid Euler solve: tables for all steps once, then one trunk per step with the AXPY fused in.
+// No allocation, no synchronisation, no host-to-device copy: the launch sequence is capturable as one CUDA graph.
 template <typename AT>
 static int rollout_impl(MdgenHandle* h, float* state, int num_steps, float* traj, cudaStream_t st) {
   Fwd<AT> f{h, st, h->C(), h->cfg.mha_heads, h->C() / h->cfg.mha_heads};
   const int nt = num_steps - 1, B = h->B;
   const size_t n = (size_t)B * h->T * h->L * h->D();
-  std::vector<float> tv((size_t)nt * B), dts(nt);
-  for (int i = 0; i < nt; ++i) {
-    const float t0 = linspace01(i, num_steps), t1 = linspace01(i + 1, num_steps);
-    dts[i] = t1 - t0;
-    for (int b = 0; b < B; ++b) tv[(size_t)i * B + b] = t0;   // t_vec = ones(B) * t_i  (integrators.py:98-99)
-  }
-  MD_CUDA(cudaMemcpyAsync(h->tbuf, tv.data(), tv.size() * 4, cudaMemcpyHostToDevice, st));
-  MD_CUDA(cudaStreamSynchronize(st));   // tv is a stack-lifetime host buffer
+  time_grid_kernel<<<(nt * B + 127) / 128, 128, 0, st>>>(h->tbuf, nt, B, num_steps);
+  MD_LAUNCHED();
   // design mode: the IPA input embeds x_d = mean_T x[..., -20:], so the time tables are rebuilt from the state at every step
   const bool design = h->flag(MDGEN_F_DESIGN);
   if (!design) MD_TRY(time_tables<AT>(f, h->tbuf, nt, nullptr));
   for (int i = 0; i < nt; ++i) {
     const long long l0 = g_launches;
+    const float dt = linspace01(i + 1, num_steps) - linspace01(i, num_steps);
     if (design) {
       MD_TRY(time_tables<AT>(f, h->tbuf + (size_t)i * B, 1, state));
       h->dflow_step = i;
     }
-    MD_TRY(trunk<AT>(f, state, design ? 0 : i, h->vel, state, dts[i]));
+    MD_TRY(trunk<AT>(f, state, design ? 0 : i, h->vel, state, dt));
     h->launches_last_forward = (int)(g_launches - l0);
     if (traj) MD_CUDA(cudaMemcpyAsync(traj + (size_t)(i + 1) * n, state, n * 4, cudaMemcpyDeviceToDevice, st));
   }
+  return 0;
+}
+
+// ---- L2 residency of the fp32 residual stream -----------------------------------------------------------------
+// xres (49 MB on config 3) is read and rewritten by every block (LayerNorm read, out_proj / fc2 read-modify-write)
+// while the activations in between (h, qkv, mlp hidden) stream through once: it gets a persisting access-policy window
+// on the launching stream for the duration of a rollout (and, for the graph, baked into the captured kernel nodes).
+// The device-wide persisting-L2 carve-out is raised ONCE per handle (never per call) and restored by mdgen_destroy.
+static bool l2_window_set(MdgenHandle* h, cudaStream_t st, void* ptr, size_t bytes) {
+  if (g_sw.no_l2_persist || !ptr || bytes == 0) return false;
+  int max_persist = 0, max_win = 0;
+  cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, h->device);
+  cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
+  if (max_persist <= 0 || max_win <= 0) return false;
+  const size_t carve = bytes < (size_t)max_persist ? bytes : (size_t)max_persist;
+  size_t cur = 0;
+  cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
+  if (cur < carve) {
+    if (!h->l2_limit_set) {
+      h->l2_prev_limit = cur;
+      h->l2_limit_set = true;
+    }
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) != cudaSuccess) {
+      cudaGetLastError();
+      return false;
+    }
+  }
+  cudaStreamAttrValue v = {};
+  v.accessPolicyWindow.base_ptr = ptr;
+  v.accessPolicyWindow.num_bytes = bytes < (size_t)max_win ? bytes : (size_t)max_win;
+  v.accessPolicyWindow.hitRatio = (float)((double)carve / (double)v.accessPolicyWindow.num_bytes);
+  v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+  v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess) return true;
+  cudaGetLastError();
+  return false;
+}
+static void l2_window_clear(cudaStream_t st) {
+  cudaStreamAttrValue v = {};
+  v.accessPolicyWindow.num_bytes = 0;
+  cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v);
+}
+
+static unsigned switches_hash() {
+  const Switches& s = g_sw;
+  unsigned hsh = 0;
+  const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta};
+  for (bool b : bits) hsh = (hsh << 1) | (b ? 1u : 0u);
+  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq);
+}
+
+static void rollout_graph_drop(MdgenHandle* h) {
+  if (h->rg_exec) cudaGraphExecDestroy(h->rg_exec);
+  h->rg_exec = nullptr;
+  h->rg_generation = -1;
+}
+
+static int rollout_eager(MdgenHandle* h, float* state, int num_steps, float* traj, cudaStream_t st) {
+  return h->bf16_mode() ? rollout_impl<bf16>(h, state, num_steps, traj, st) : rollout_impl<float>(h, state, num_steps, traj, st);
+}
+
+// Captures the whole rollout (every launch of all num_steps - 1 evaluations) on the handle's internal stream into one
+// CUDA graph over handle-owned buffers (state_buf, traj_buf); replayed until a pointer or a by-value argument changes.
+static int rollout_graph_build(MdgenHandle* h, int num_steps, bool want_traj) {
+  rollout_graph_drop(h);
+  if (!h->cap_stream) MD_CUDA(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+  cudaStream_t cs = h->cap_stream;
+  const bool win = l2_window_set(h, cs, h->xres, (size_t)h->B * h->T * h->L * h->C() * sizeof(float));
+  const long long l0 = g_launches;
+  MD_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+  const int rc = rollout_eager(h, h->state_buf, num_steps, want_traj ? h->traj_buf : nullptr, cs);
+  cudaGraph_t graph = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+  if (win) l2_window_clear(cs);
+  const int launches = (int)(g_launches - l0);
+  g_launches = l0;                      // nothing ran yet: launches are counted per replay
+  if (rc != 0) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    return rc;
+  }
+  if (ce != cudaSuccess || !graph) {
+    cudaGetLastError();
+    set_error(std::string("rollout graph capture failed: ") + cudaGetErrorString(ce));
+    return MDGEN_ECUDA;
+  }
+  const cudaError_t ie = cudaGraphInstantiate(&h->rg_exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ie != cudaSuccess) {
+    h->rg_exec = nullptr;
+    cudaGetLastError();
+    set_error(std::string("cudaGraphInstantiate failed: ") + cudaGetErrorString(ie));
+    return MDGEN_ECUDA;
+  }
+  h->rg_generation = h->generation;
+  h->rg_num_steps = num_steps;
+  h->rg_traj = want_traj;
+  h->rg_switches = switches_hash();
+  h->rg_launches = launches;
+  h->rg_launches_per_eval = h->launches_last_forward;
   return 0;
 }
 
@@ -1248,6 +1397,11 @@ int mdgen_create(const MdgenConfig* cfg, MdgenHandle** out) {
 int mdgen_destroy(MdgenHandle* h) {
   if (!h) return MDGEN_OK;
   DeviceGuard g(h->device);
+  cudaDeviceSynchronize();
+  rollout_graph_drop(h);
+  if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
+  if (h->traj_buf) cudaFree(h->traj_buf);
+  if (h->l2_limit_set) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, h->l2_prev_limit);
   free_workspace(h);
   for (void* p : h->packed) cudaFree(p);
   for (auto& kv : h->weights) cudaFree(kv.second.d);
@@ -1329,22 +1483,35 @@ int mdgen_decode_atom14(int32_t B, int32_t T, int32_t L, int32_t D, const float*
 }
 
 int mdgen_set_dirichlet_tables(MdgenHandle* h, int32_t nt, const double* rows, const double* alphas, const double* betas,
-                               float temp, float dalpha, int32_t allow_nan) {
+                               float temp, float dalpha, int32_t allow_nan, mdgen_stream_t stream) {
   MD_CHECK(h && nt > 0 && rows && alphas && betas && temp > 0.f, "bad argument");
   MD_CHECK(h->flag(MDGEN_F_DESIGN), "mdgen_set_dirichlet_tables: the model was not created with the design flag");
   DeviceGuard g(h->device);
-  if (nt > h->dflow_nt || !h->dflow_rows) {
+  cudaStream_t st = (cudaStream_t)stream;
+  // unchanged tables (the usual case: same grid every rollout) leave the device copy and the captured graph alone
+  const size_t nrow = (size_t)nt * DFLOW_GRID;
+  std::vector<float> am1(nt);
+  for (int i = 0; i < nt; ++i) am1[i] = (float)(alphas[i] - 1.0);
+  const bool same = h->dflow_rows && h->dflow_nt == nt && h->dflow_rows_host.size() == nrow &&
+                    memcmp(h->dflow_rows_host.data(), rows, nrow * sizeof(double)) == 0 && h->dflow_am1 == am1 &&
+                    h->dflow_beta.size() == (size_t)nt && memcmp(h->dflow_beta.data(), betas, nt * sizeof(double)) == 0 &&
+                    h->dflow_temp == temp && h->dflow_dalpha == dalpha && h->dflow_allow_nan == allow_nan;
+  if (!h->dflow_flags) MD_CUDA(cudaMalloc((void**)&h->dflow_flags, 2 * sizeof(int)));
+  MD_CUDA(cudaMemsetAsync(h->dflow_flags, 0, 2 * sizeof(int), st));
+  if (same) return MDGEN_OK;
+  ++h->generation;                        // by-value kernel arguments (alpha - 1, beta, temp) are baked into a rollout graph
+  MD_CUDA(cudaStreamSynchronize(st));     // a rollout in flight on this stream may still read the old table / staging copy
+  if (nt > h->dflow_cap || !h->dflow_rows) {
     if (h->dflow_rows) cudaFree(h->dflow_rows);
     h->dflow_rows = nullptr;
-    h->dflow_nt = 0;
-    MD_CUDA(cudaMalloc((void**)&h->dflow_rows, (size_t)nt * DFLOW_GRID * sizeof(double)));
+    h->dflow_nt = h->dflow_cap = 0;
+    MD_CUDA(cudaMalloc((void**)&h->dflow_rows, nrow * sizeof(double)));
+    h->dflow_cap = nt;
   }
-  if (!h->dflow_flags) MD_CUDA(cudaMalloc((void**)&h->dflow_flags, 2 * sizeof(int)));
-  MD_CUDA(cudaMemcpy(h->dflow_rows, rows, (size_t)nt * DFLOW_GRID * sizeof(double), cudaMemcpyHostToDevice));
-  MD_CUDA(cudaMemset(h->dflow_flags, 0, 2 * sizeof(int)));
-  h->dflow_am1.resize(nt);
+  h->dflow_rows_host.assign(rows, rows + nrow);   // handle-owned staging copy: the caller's buffer is free on return
+  MD_CUDA(cudaMemcpyAsync(h->dflow_rows, h->dflow_rows_host.data(), nrow * sizeof(double), cudaMemcpyHostToDevice, st));
+  h->dflow_am1 = am1;
   h->dflow_beta.assign(betas, betas + nt);
-  for (int i = 0; i < nt; ++i) h->dflow_am1[i] = (float)(alphas[i] - 1.0);
   h->dflow_nt = nt;
   h->dflow_temp = temp;
   h->dflow_dalpha = dalpha;
@@ -1392,43 +1559,9 @@ int mdgen_forward(MdgenHandle* h, const float* x, const float* t, float* out, md
     return MDGEN_ESTATE;
   }
   DeviceGuard g(h->device);
+  read_switches();
   return forward_dispatch(h, x, t, out, (cudaStream_t)stream);
 }
-
-// Keeps the fp32 residual stream (xres, 49 MB on config 3) resident in the 126 MB L2 for the duration of a call: every
-// block reads and rewrites it (LayerNorm read, out_proj / fc2 read-modify-write) while the activations in between
-// (h, qkv, mlp hidden) stream through once.  Scoped: the stream's access-policy window is cleared again on exit.
-struct L2Residency {
-  cudaStream_t st;
-  bool on = false;
-  L2Residency(cudaStream_t s, void* ptr, size_t bytes) : st(s) {
-    if (getenv("MDGEN_NO_L2_PERSIST") || !ptr || bytes == 0) return;
-    int dev = 0, max_persist = 0, max_win = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
-    cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, dev);
-    if (max_persist <= 0 || max_win <= 0) return;
-    const size_t carve = bytes < (size_t)max_persist ? bytes : (size_t)max_persist;
-    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) != cudaSuccess) {
-      cudaGetLastError();
-      return;
-    }
-    cudaStreamAttrValue v = {};
-    v.accessPolicyWindow.base_ptr = ptr;
-    v.accessPolicyWindow.num_bytes = bytes < (size_t)max_win ? bytes : (size_t)max_win;
-    v.accessPolicyWindow.hitRatio = (float)((double)carve / (double)v.accessPolicyWindow.num_bytes);
-    v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-    v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-    if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess) on = true;
-    else cudaGetLastError();
-  }
-  ~L2Residency() {
-    if (!on) return;
-    cudaStreamAttrValue v = {};
-    v.accessPolicyWindow.num_bytes = 0;
-    cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v);
-  }
-};
 
 int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, float* traj, float* out_final,
                         mdgen_stream_t stream) {
@@ -1438,18 +1571,55 @@ int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, floa
     return MDGEN_ESTATE;
   }
   DeviceGuard g(h->device);
+  read_switches();
   cudaStream_t st = (cudaStream_t)stream;
-  if (h->flag(MDGEN_F_DESIGN)) {
-    MD_CHECK(h->dflow_nt == num_steps - 1, "design-mode rollout: call mdgen_set_dirichlet_tables for num_steps - 1 steps first");
-    MD_CUDA(cudaMemsetAsync(h->dflow_flags, 0, 2 * sizeof(int), st));
-  }
+  const bool design = h->flag(MDGEN_F_DESIGN);
+  if (design) MD_CHECK(h->dflow_nt == num_steps - 1, "design-mode rollout: call mdgen_set_dirichlet_tables for num_steps - 1 steps first");
   const size_t n = (size_t)h->B * h->T * h->L * h->D();
-  if (out_final != x0) MD_CUDA(cudaMemcpyAsync(out_final, x0, n * 4, cudaMemcpyDeviceToDevice, st));
-  if (traj) MD_CUDA(cudaMemcpyAsync(traj, x0, n * 4, cudaMemcpyDeviceToDevice, st));
-  MD_TRY(ensure_scratch(h, num_steps - 1));
-  L2Residency keep(st, h->xres, (size_t)h->B * h->T * h->L * h->C() * sizeof(float));
-  return h->bf16_mode() ? rollout_impl<bf16>(h, out_final, num_steps, traj, st)
-                        : rollout_impl<float>(h, out_final, num_steps, traj, st);
+  // A caller that is itself capturing (torch.cuda.graph around this call) gets the plain launch sequence into ITS graph;
+  // the per-family profiler needs real launches too.
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cap);
+  const bool eager = g_sw.no_graph || g_prof.on || cap != cudaStreamCaptureStatusNone;
+  if (cap == cudaStreamCaptureStatusNone) MD_TRY(ensure_scratch(h, num_steps - 1));
+  else MD_CHECK(h->nt_cap >= num_steps - 1 && h->emb_static_valid,
+                "mdgen_euler_rollout under stream capture: run one un-captured call first (scratch allocation)");
+  if (design) MD_CUDA(cudaMemsetAsync(h->dflow_flags, 0, 2 * sizeof(int), st));
+  if (eager) {
+    if (out_final != x0) MD_CUDA(cudaMemcpyAsync(out_final, x0, n * 4, cudaMemcpyDeviceToDevice, st));
+    if (traj) MD_CUDA(cudaMemcpyAsync(traj, x0, n * 4, cudaMemcpyDeviceToDevice, st));
+    const bool win = cap == cudaStreamCaptureStatusNone &&
+                     l2_window_set(h, st, h->xres, (size_t)h->B * h->T * h->L * h->C() * sizeof(float));
+    const int rc = rollout_eager(h, out_final, num_steps, traj, st);
+    if (win) l2_window_clear(st);
+    return rc;
+  }
+  // ---- graph path
+  const bool want_traj = traj != nullptr;
+  if (want_traj && h->traj_cap < (size_t)num_steps * n) {
+    if (h->traj_buf) {
+      MD_CUDA(cudaStreamSynchronize(st));
+      cudaFree(h->traj_buf);
+    }
+    h->traj_buf = nullptr;
+    h->traj_cap = 0;
+    MD_CUDA(cudaMalloc((void**)&h->traj_buf, (size_t)num_steps * n * 4));
+    h->traj_cap = (size_t)num_steps * n;
+    ++h->generation;
+  }
+  MD_TRY(ensure_emb_static(h, st));        // step-invariant embedding: outside the graph, on the caller's stream
+  if (!h->rg_exec || h->rg_generation != h->generation || h->rg_num_steps != num_steps || h->rg_traj != want_traj ||
+      h->rg_switches != switches_hash())
+    MD_TRY(rollout_graph_build(h, num_steps, want_traj));
+  MD_CUDA(cudaMemcpyAsync(h->state_buf, x0, n * 4, cudaMemcpyDeviceToDevice, st));
+  if (want_traj) MD_CUDA(cudaMemcpyAsync(h->traj_buf, x0, n * 4, cudaMemcpyDeviceToDevice, st));
+  MD_CUDA(cudaGraphLaunch(h->rg_exec, st));
+  g_launches += h->rg_launches;
+  h->launches_last_forward = h->rg_launches_per_eval;
+  MD_VARIANT(V_GRAPH_REPLAY);
+  MD_CUDA(cudaMemcpyAsync(out_final, h->state_buf, n * 4, cudaMemcpyDeviceToDevice, st));
+  if (want_traj) MD_CUDA(cudaMemcpyAsync(traj, h->traj_buf, (size_t)num_steps * n * 4, cudaMemcpyDeviceToDevice, st));
+  return MDGEN_OK;
 }
 
 int mdgen_profile_begin(void) {
@@ -1489,6 +1659,9 @@ int mdgen_debug_set_buffer(long long* device_buf, int32_t cta) {
   return MDGEN_OK;
 }
 long long mdgen_launch_count(void) { return g_launches; }
+long long mdgen_variant_launches(int32_t which) {
+  return (which >= 0 && which < V_COUNT) ? g_variant[which].load(std::memory_order_relaxed) : -1;
+}
 int mdgen_launches_per_forward(MdgenHandle* h) { return h ? h->launches_last_forward : 0; }
 int64_t mdgen_workspace_bytes(MdgenHandle* h) { return h ? (int64_t)h->ws_bytes : 0; }
 
@@ -1500,6 +1673,7 @@ extern "C" {
 int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float* W, const float* bias, float* Cout,
                     int32_t use_tc, int32_t block_n, mdgen_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
+  read_switches();
   EpiParams ep;
   ep.bias = bias;
   ep.out = Cout;
@@ -1571,6 +1745,7 @@ int mdgen_test_attention(int32_t nb, int32_t S, int32_t inner, int32_t heads, in
                          const float* bias_k, const float* bias_v, const float* key_valid, float* out, int32_t use_tc,
                          int32_t rope, mdgen_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
+  read_switches();
   const int C = heads * head_dim, half = head_dim / 2;
   float *cs = nullptr, *sn = nullptr, *inv = nullptr;
   if (rope) {

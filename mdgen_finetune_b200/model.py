@@ -321,7 +321,15 @@ class LatentMDGenModel(nn.Module):
     # ---- conditioning (everything forward() gets besides x, t) -----------------------------
     @staticmethod
     def _tkey(t):
-        return None if t is None else (t.data_ptr(), t._version, tuple(t.shape), t.dtype)
+        return None if t is None else (t.data_ptr(), t._version, tuple(t.shape), tuple(t.stride()), t.dtype, str(t.device))
+
+    def invalidate(self):
+        """Drops the cached weights / conditioning of the CUDA handle.  Needed only after in-place edits that bypass
+        autograd's version counter (`p.data.copy_()`, EMA-style updates): those change neither `_version` nor the
+        address, so the caches cannot see them."""
+        self._weights_key = None
+        self._cond_key = None
+        self._keepalive = None
 
     def _set_conditioning(self, x, mask, start_frames, end_frames, x_cond, x_cond_mask, aatype):
         dev = self.device
@@ -330,8 +338,8 @@ class LatentMDGenModel(nn.Module):
             mask = mask.repeat(B, 1, 1)
         srot, strans = frames_to_tensors(start_frames)
         erot, etrans = frames_to_tensors(end_frames)
-        key = (B, T, L, self.quat_sign) + tuple(self._tkey(v) for v in (
-            mask, srot, strans, erot, etrans, x_cond, x_cond_mask, aatype))
+        originals = (mask, srot, strans, erot, etrans, x_cond, x_cond_mask, aatype)
+        key = (B, T, L, self.quat_sign) + tuple(self._tkey(v) for v in originals)
         if key == self._cond_key:
             return
         f32 = lambda v: None if v is None else v.detach().to(dev, torch.float32).contiguous()
@@ -353,7 +361,9 @@ class LatentMDGenModel(nn.Module):
             _lib.check(_lib.lib().mdgen_set_conditioning(
                 self._handle, B, T, L, p(m), p(sr), p(stt), p(er), p(et), p(f7), p(r7), p(xc), p(cm), p(aa),
                 self._stream()), "mdgen_set_conditioning")
-        self._keepalive = (m, sr, stt, er, et, xc, cm, aa, f7, r7)
+        # The key holds data_ptr() / _version of the CALLER's tensors: keep those alive (not only the converted copies),
+        # so that the address cannot be recycled by a different tensor while the key is current.
+        self._keepalive = originals + (m, sr, stt, er, et, xc, cm, aa, f7, r7)
         self._cond_key = key
 
     # ---- the reference API ---------------------------------------------------------------------
@@ -361,9 +371,14 @@ class LatentMDGenModel(nn.Module):
                 aatype=None, *args, **kwargs):
         """One velocity evaluation (latent_model.py:216-269).  Unknown kwargs (e.g. `peptide=`) are
         swallowed like the reference's **kwargs; `t` may be int64 (RTB DDPM timesteps)."""
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()) and x.requires_grad:
-            raise NotImplementedError("backward through the CUDA denoiser is row N4 (DESIGN.md); "
-                                      "call under torch.no_grad()")
+        if self.device.type != "cuda":
+            raise RuntimeError("mdgen_finetune_b200.LatentMDGenModel runs on CUDA only (no CPU fallback); "
+                               "call .cuda() first")
+        if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())):
+            # The output is written by the C ABI and carries no grad_fn: returning it to a caller that expects
+            # gradients (RTB: parameters require grad, the noise sample does not) would train nothing, silently.
+            raise NotImplementedError("backward through the CUDA denoiser is row N4 (DESIGN.md): call under "
+                                      "torch.no_grad(), or freeze the module (requires_grad_(False)) for sampling")
         self._sync_weights()
         dev = self.device
         if x.dim() != 4 or x.shape[-1] != self.latent_dim:
@@ -456,7 +471,7 @@ class LatentMDGenModel(nn.Module):
                 _lib.check(_lib.lib().mdgen_set_dirichlet_tables(
                     self._handle, num_steps - 1, rows.ctypes.data, alphas.ctypes.data, betas.ctypes.data,
                     float(a.dirichlet_flow_temp), float(a.alpha_max - 1),
-                    int(bool(getattr(a, "allow_nan_cfactor", False)))), "mdgen_set_dirichlet_tables")
+                    int(bool(getattr(a, "allow_nan_cfactor", False))), self._stream()), "mdgen_set_dirichlet_tables")
         with torch.cuda.device(dev):
             _lib.check(_lib.lib().mdgen_euler_rollout(
                 self._handle, xx.data_ptr(), int(num_steps), None if traj is None else traj.data_ptr(),

@@ -51,6 +51,20 @@ def test_cpu_call_fails_loudly():
         m.forward(x, torch.zeros(1), torch.ones(1, 2, 4))
 
 
+def test_forward_refuses_to_return_a_gradless_output_when_gradients_are_expected(monkeypatch):
+    """RTB call convention (samplers.py:136-139): parameters require grad, x does not.  The C ABI output has no grad_fn,
+    so forward() must refuse instead of silently training nothing."""
+    from mdgen_finetune_b200 import LatentMDGenModel
+    from mdgen_finetune_b200 import model as M
+    args = cfgs.make_args(cfgs.small_variant(1, B=1, T=2, L=4))
+    m = LatentMDGenModel(args, 21)
+    monkeypatch.setattr(M.LatentMDGenModel, "device", property(lambda self: torch.device("cuda", 0)))
+    x = torch.zeros(1, 2, 4, 21)
+    assert not x.requires_grad and any(p.requires_grad for p in m.parameters())
+    with pytest.raises(NotImplementedError, match="row N4"):
+        m.forward(x, torch.zeros(1), torch.ones(1, 2, 4))
+
+
 def test_sampler_generic_callable_matches_oracle_euler():
     """Sampler.sample_ode('euler') on a plain callable == oracle euler_sample (torchdiffeq restatement)."""
     from mdgen_finetune_b200 import Sampler, create_transport

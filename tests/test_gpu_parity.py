@@ -5,7 +5,7 @@ import torch
 
 from mdgen_finetune_b200 import LatentMDGenModel, Sampler, create_transport
 from oracle import mdgen_oracle as O
-from tests.helpers import CASES, frames_of, load_case, rel_l2
+from tests.helpers import CASES, FULL_CASES, frames_of, load_case, rel_l2
 
 pytestmark = pytest.mark.gpu
 TOL = {"fp32": 1e-4, "bf16": 2e-2}
@@ -199,3 +199,71 @@ def test_full_size_config1_rollout_rmsd(prec):
     assert ok.float().mean() > 0.9
     assert float(aa_rmsd[ok].max()) < 0.05, float(aa_rmsd[ok].max())
     assert float(aa_rmsd.median()) < 0.02
+
+
+# ---- BASELINE configs 2-5 at FULL size: the kernel variants bench.py times ---------------------------------------
+def _variant_counts():
+    from mdgen_finetune_b200 import _lib
+    return {k: int(_lib.lib().mdgen_variant_launches(i)) for i, k in enumerate(_lib.VARIANTS)}
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", FULL_CASES)
+def test_full_size_velocity_and_short_rollout_vs_reference(name, prec):
+    """Goldens from the UNMODIFIED reference at the full BASELINE shapes (oracle/make_golden.py FULL): velocities and a
+    short run of the reference's own Euler sampler.  At these sizes the bf16 path goes through the fused projection +
+    residual + LayerNorm kernel (rows >= 8192), the CTA-pair GEMM (>= 74 tiles of 256 x 256), the tcgen05 attention on
+    the frame axis (and on the residue axis of ATLAS: 257 keys, 32 of them padded) and IPA at L = 256."""
+    import functools
+    g, c, args, sd, inp = load_case(name)
+    m = build(args, c["D"], sd, prec)
+    kw = gpu_kwargs(inp)
+    before = _variant_counts()
+    with torch.no_grad():
+        for i, tv in enumerate(g["t_values"]):
+            t = torch.full((c["B"],), tv)
+            v = m.forward_inference(inp["x0"].cuda(), t.cuda(), **kw).cpu()
+            assert torch.isfinite(v).all()
+            err = rel_l2(v, g[f"v_t{i}"])
+            assert err < TOL[prec], (name, prec, tv, err)
+            if args.design:
+                errd = rel_l2(v[..., -20:], g[f"v_t{i}"][..., -20:])
+                assert errd < TOL[prec] * 2, errd
+        fn = Sampler(create_transport(args)).sample_ode(sampling_method="euler", num_steps=g["euler_steps"])
+        traj = fn(inp["x0"].cuda(), functools.partial(m.forward_inference, **kw))
+        err = rel_l2(traj[-1].cpu(), g["euler_final"])
+        assert err < TOL[prec] * 2, (name, prec, "euler", err)
+    after = _variant_counts()
+    used = {k: after[k] - before[k] for k in after}
+    print(name, prec, used)
+    N = c["B"] * c["T"] * c["L"]
+    if prec == "bf16":
+        assert used["attention_tc"] > 0
+        assert used["graph_replays"] > 0, used            # the sampler call replays the whole-rollout graph
+        if N >= 8192:
+            assert used["gemm_ln"] > 0, used              # fused projection + residual + next LayerNorm
+        if N >= 74 * 256:
+            assert used["gemm_tc2"] > 0, used             # CTA-pair kernel (cta_group::2)
+        if c["L"] == 4:
+            assert used["attention_seq4"] > 0, used
+
+
+@pytest.mark.parametrize("switch", ["MDGEN_NO_GEMM_LN", "MDGEN_NO_GEMM_2CTA", "MDGEN_NO_GEMM_WS", "MDGEN_NO_L2_PERSIST",
+                                    "MDGEN_NO_GRAPH"])
+def test_config3_kernel_variants_agree(switch, monkeypatch):
+    """Every variant switch of DESIGN.md section 2 must leave the config-3 result within bf16 rounding of the default
+    dispatch and within the north_star tolerance of the reference golden."""
+    g, c, args, sd, inp = load_case("upsample_full")
+    kw = gpu_kwargs(inp)
+    t = torch.full((c["B"],), g["t_values"][0]).cuda()
+    m = build(args, c["D"], sd, "bf16")
+    with torch.no_grad():
+        v0 = m.forward(inp["x0"].cuda(), t, **kw).cpu()
+        r0 = m.euler_rollout(inp["x0"].cuda(), g["euler_steps"], **kw).cpu()
+        monkeypatch.setenv(switch, "1")
+        v1 = m.forward(inp["x0"].cuda(), t, **kw).cpu()
+        r1 = m.euler_rollout(inp["x0"].cuda(), g["euler_steps"], **kw).cpu()
+    assert rel_l2(v1, g["v_t0"]) < TOL["bf16"]
+    assert rel_l2(v1, v0) < 5e-3, rel_l2(v1, v0)
+    assert rel_l2(r1, g["euler_final"]) < TOL["bf16"] * 2
+    assert rel_l2(r1, r0) < 5e-3, rel_l2(r1, r0)
