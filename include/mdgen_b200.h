@@ -197,6 +197,24 @@ int mdgen_test_attention(int32_t nb, int32_t S, int32_t inner, int32_t heads, in
                          const float* key_valid, float* out, int32_t use_tc, int32_t rope,
                          mdgen_stream_t stream);
 
+/* Allocation-free GEMM.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * C[M,N] (fp32) = bf16(A[M,K]) . bf16(W[N,K])^T + bias[N] (bias may be NULL) on the tcgen05 GEMM -- the arithmetic of
+ * mdgen_test_gemm(use_tc = 1) -- with the bf16 operand copies held in a file-scope `static __device__` array of
+ * MDGEN_NOALLOC_SCRATCH_BYTES (8 MiB; every GPU that loads the library holds it until the process exits) instead of
+ * cudaMalloc'ed scratch.  All pointers are device pointers on the CURRENT device; K % 8 == 0.
+ * Limit: M*K <= MDGEN_NOALLOC_MAX_OPERAND_ELEMS and N*K <= MDGEN_NOALLOC_MAX_OPERAND_ELEMS (2^21 elements each, e.g.
+ * 5461 x 384 or 1365 x 1536); larger problems return MDGEN_EINVAL with a message naming the limit.
+ * The call performs no cudaMalloc / cudaFree / allocating library call, does not synchronise, and is asynchronous on
+ * `stream` (capturable).  ALL calls share the one array, which keeps the previous call's contents (nothing in it has to
+ * start at zero: every element read is rewritten first, on the same stream).  Calls on one stream are ordered; calls
+ * that overlap on the GPU (different streams, or replays of graphs that contain it, running concurrently) RACE on the
+ * scratch -- serialise them. */
+#define MDGEN_NOALLOC_MAX_OPERAND_ELEMS (1 << 21)
+#define MDGEN_NOALLOC_SCRATCH_BYTES (2 * MDGEN_NOALLOC_MAX_OPERAND_ELEMS * 2)
+int mdgen_gemm_noalloc(int32_t M, int32_t N, int32_t K, const float* A, const float* W, const float* bias,
+                       float* C, mdgen_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1801,3 +1801,60 @@ int mdgen_test_attention(int32_t nb, int32_t S, int32_t inner, int32_t heads, in
 }
 
 }  // extern "C"
+
+// ---- allocation-free GEMM entry point ---------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic as
+// mdgen_test_gemm(use_tc = 1): C = bf16(A) . bf16(W)^T + bias on the tcgen05 GEMM with fp32 output -- but the bf16 operand
+// copies live in a file-scope __device__ array instead of cudaMalloc'ed scratch.  Every GPU that loads the library holds
+// the array (MDGEN_NOALLOC_SCRATCH_BYTES = 8 MiB) until the process exits.
+namespace mdgen {
+constexpr size_t NOALLOC_HALF_ELEMS = (size_t)MDGEN_NOALLOC_MAX_OPERAND_ELEMS;      // bf16 elements per operand
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MDGEN_NOALLOC_SCRATCH_BYTES];
+static_assert(2 * NOALLOC_HALF_ELEMS * sizeof(bf16) == (size_t)MDGEN_NOALLOC_SCRATCH_BYTES, "scratch = two operand halves");
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up
+// once per device (with that device current) through cudaGetSymbolAddress and cached here.
+static std::atomic<void*> g_noalloc_ptr[64];
+static int noalloc_scratch_ptr(void** out) {
+  const int dev = cur_device();
+  MD_CHECK(dev >= 0 && dev < 64, "mdgen_gemm_noalloc: device ordinal out of range");
+  void* p = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    MD_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    MD_CHECK(p != nullptr && ((uintptr_t)p & 255) == 0, "mdgen_gemm_noalloc: bad scratch symbol address");
+    g_noalloc_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return 0;
+}
+}  // namespace mdgen
+
+extern "C" int mdgen_gemm_noalloc(int32_t M, int32_t N, int32_t K, const float* A, const float* W, const float* bias,
+                                  float* C, mdgen_stream_t stream) {
+  MD_CHECK(A && W && C, "mdgen_gemm_noalloc: null argument");
+  MD_CHECK(M > 0 && N > 0 && K > 0 && K % 8 == 0, "mdgen_gemm_noalloc: M, N, K must be positive and K a multiple of 8");
+  if ((size_t)M * K > NOALLOC_HALF_ELEMS || (size_t)N * K > NOALLOC_HALF_ELEMS) {
+    set_error("mdgen_gemm_noalloc: operand too large for the static scratch: M*K = " + std::to_string((size_t)M * K) +
+              ", N*K = " + std::to_string((size_t)N * K) + ", limit " + std::to_string(NOALLOC_HALF_ELEMS) +
+              " elements each (MDGEN_NOALLOC_MAX_OPERAND_ELEMS); use mdgen_test_gemm or split the problem");
+    return MDGEN_EINVAL;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  read_switches();
+  void* scratch = nullptr;
+  MD_TRY(noalloc_scratch_ptr(&scratch));
+  bf16* Ab = (bf16*)scratch;
+  bf16* Wb = Ab + NOALLOC_HALF_ELEMS;
+  // Nothing in the scratch has to start at zero: every element the GEMM reads ([M, K] and [N, K], exact TMA extents,
+  // out-of-bounds tile rows are zero-filled by TMA itself) is rewritten here, on the same stream, before it is read.
+  f32_to_bf16_kernel<<<(unsigned)(((size_t)M * K + 255) / 256), 256, 0, st>>>(A, Ab, (size_t)M * K, 1.f);
+  MD_LAUNCHED();
+  f32_to_bf16_kernel<<<(unsigned)(((size_t)N * K + 255) / 256), 256, 0, st>>>(W, Wb, (size_t)N * K, 1.f);
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  EpiParams ep;
+  ep.bias = bias;
+  ep.out = C;
+  ep.ldo = N;
+  return launch_gemm_tc(Ab, K, Wb, K, M, N, K, EPI_STORE, false, ep, 0, st);
+}
