@@ -82,38 +82,75 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.rows)}
 
 
-def oracle_time_forward(cfg_id, nfwd=3):
-    """CPU oracle port: seconds per velocity evaluation on a B=1 slice of the workload."""
-    from oracle import mdgen_oracle as O
-    c = dict(cfgs.CONFIGS[cfg_id]); c["B"] = 1; c["id"] = cfg_id
+_REF_CACHE = {}
+
+
+def reference_forward_fn(cfg_id, B):
+    """The REFERENCE'S OWN LatentMDGenModel (unmodified sources: /root/reference/src in the build container, the copy
+    staged by oracle/stage_ref.py under oracle/_ref/src on the GPU box) on the host cores, fp32, all threads: returns
+    (fn(t_scalar) -> velocity, config dict, threads).  Falls back to the oracle port only if the sources are missing."""
+    key = (cfg_id, B)
+    if key in _REF_CACHE:
+        return _REF_CACHE[key]
+    c = dict(cfgs.CONFIGS[cfg_id]); c["B"] = B; c["id"] = cfg_id
     args = cfgs.make_args(c)
     sd = random_state_dict(args, c["D"], seed=0)
     inp = cfgs.synthetic_inputs(c, seed=0)
     torch.set_num_threads(os.cpu_count() or 1)
-    start = (inp["start_rot"], inp["start_trans"])
-    end = (inp["end_rot"], inp["end_trans"]) if "end_rot" in inp else None
-    f = lambda x, t: O.forward(sd, args, x, t, inp["mask"], start, end, inp["x_cond"], inp["x_cond_mask"], inp["aatype"])
+    try:
+        from oracle.ref_loader import load_reference
+        ref = load_reference()
+        model = ref.LatentMDGenModel(args, c["D"])
+        model.load_state_dict(sd, strict=True)
+        model.eval()
+        rigid = lambda r, t: ref.Rigid(ref.Rotation(rot_mats=r), t)
+        kw = dict(mask=inp["mask"], start_frames=rigid(inp["start_rot"], inp["start_trans"]), x_cond=inp["x_cond"],
+                  x_cond_mask=inp["x_cond_mask"], aatype=inp["aatype"])
+        if "end_rot" in inp:
+            kw["end_frames"] = rigid(inp["end_rot"], inp["end_trans"])
+        f = lambda tv: model.forward_inference(inp["x0"], torch.full((B,), tv), **kw)
+        kind = "reference"
+    except Exception as e:      # sources not staged: the restated port (oracle/mdgen_oracle.py), and say so
+        sys.stderr.write(f"bench.py: reference sources unavailable ({e}); timing the oracle port instead\n")
+        from oracle import mdgen_oracle as O
+        start = (inp["start_rot"], inp["start_trans"])
+        end = (inp["end_rot"], inp["end_trans"]) if "end_rot" in inp else None
+        f = lambda tv: O.forward_inference(sd, args, inp["x0"], torch.full((B,), tv), inp["mask"], start, end, inp["x_cond"],
+                                           inp["x_cond_mask"], inp["aatype"])
+        kind = "port"
+    _REF_CACHE[key] = (f, c, torch.get_num_threads(), kind)
+    return _REF_CACHE[key]
+
+
+def reference_time_forward(cfg_id, B, nfwd=3, warm=1):
+    """Median seconds per velocity evaluation of the reference on the host cores at batch B."""
+    f, c, cores, kind = reference_forward_fn(cfg_id, B)
     ts = []
     with torch.no_grad():
-        f(inp["x0"], torch.zeros(1))
+        for _ in range(warm):
+            f(0.0)
         for i in range(nfwd):
             t0 = time.perf_counter()
-            f(inp["x0"], torch.full((1,), i / 49.0))
+            f(i / 49.0)
             ts.append(time.perf_counter() - t0)
     ts.sort()
-    return ts[len(ts) // 2], c, torch.get_num_threads()
+    return ts[len(ts) // 2], c, cores, kind
 
 
 def ncu_traffic(category, cfg_id):
     """DRAM bytes (read + write) per launch of the dominant kernel family from the committed `ncu --set full` capture
     (profiles/r01/traffic_cfg<id>.json, written by tools/ncu_traffic.py); None when no capture exists for this config."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01", f"traffic_cfg{cfg_id}.json")
     names = {"gemm_tcgen05": ("gemm_tc_kernel", "gemm_tc2_kernel", "gemm_ln_kernel"), "attention_tcgen05": ("attention_tc_kernel",),
              "attention_short": ("attention_seq4_bulk_kernel", "attention_seq_kernel", "attention_short_kernel"),
              "layernorm_modulate": ("ln_modulate_kernel",), "embed": ("embed_step_kernel", "embed_kernel")}
-    try:
-        t = json.load(open(path))
-    except (OSError, ValueError):
+    t = None
+    for rnd in ("r02", "r01"):          # the latest committed capture
+        try:
+            t = json.load(open(os.path.join(ROOT, "profiles", rnd, f"traffic_cfg{cfg_id}.json")))
+            break
+        except (OSError, ValueError):
+            continue
+    if t is None:
         return None
     tot = n = 0
     for k in names.get(category, ()):
@@ -137,26 +174,44 @@ def algorithmic_flops(c):
 
 
 def run_reference(a, rank, world):
-    """--impl reference: the reference's CPU implementation of the path (oracle port; the reference is
-    pure Python and cannot travel to the GPU box) on all host threads.  Rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the path (its unmodified LatentMDGenModel.forward_
+    inference, staged under oracle/_ref) on all host threads.  Rank 0 only.  A step = ONE velocity evaluation of the
+    workload's full batch when the whole run then fits in a few minutes, else of a B = 1 slice; the metric extrapolates
+    the 49 evaluations of a rollout from it (a full reference rollout of config 3 takes minutes per step)."""
     if rank != 0:
         return
+    cfg = cfgs.CONFIGS[a.config]
+    Bfull = cfg["B"]
+    nev = NUM_STEPS - 1
+    budget_s = 200.0
+    t1, _, cores, kind = reference_time_forward(a.config, 1, nfwd=1, warm=1)
+    full_s = None
+    B = 1
+    if Bfull > 1 and t1 * Bfull * 1.5 * (a.steps + 2) < budget_s:
+        full_s, _, _, _ = reference_time_forward(a.config, Bfull, nfwd=1, warm=0)
+        if full_s * (a.steps + 1) < budget_s:
+            B = Bfull
+    elif Bfull == 1:
+        B = 1
     secs = []
-    cores = 1
-    for _ in range(max(1, a.warmup // 3)):
-        oracle_time_forward(a.config, 1)
+    for _ in range(max(0, min(a.warmup, 2) - 1)):
+        reference_time_forward(a.config, B, nfwd=1, warm=0)
     for _ in range(a.steps):
-        s, c, cores = oracle_time_forward(a.config, 1)
+        s, c, cores, kind = reference_time_forward(a.config, B, nfwd=1, warm=0)
         secs.append(s)
-    secs.sort()
-    s = secs[len(secs) // 2]
-    value = c["T"] / ((NUM_STEPS - 1) * s)
-    sample = f"1 velocity evaluation of a B=1 slice ({c['T']} frames x {c['L']} residues) per step; x49 extrapolated to a full Euler call"
+    s = sum(secs) / len(secs)
+    value = B * cfg["T"] / (nev * s)
+    sample = (f"1 velocity evaluation of {'the full batch' if B == Bfull else 'a B=1 slice'} (B={B} x {cfg['T']} frames x {cfg['L']} "
+              f"residues) per step on the reference's own LatentMDGenModel; x{nev} extrapolated to a full Euler call")
+    cb = {"value": value, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample, "batch": B,
+          "same_config": B == Bfull}
+    if full_s is not None:
+        cb["full_batch_forward_s"] = full_s
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a.config)},
-        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": cb,
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
@@ -190,25 +245,82 @@ def rank_inputs(c, rank):
     return cfgs.synthetic_inputs(c, seed=rank)
 
 
+def build_model(cfg_id, dev, B=None, precision="bf16"):
+    from mdgen_finetune_b200 import LatentMDGenModel
+    c = dict(cfgs.CONFIGS[cfg_id]); c["id"] = cfg_id
+    if B is not None:
+        c["B"] = B
+    args = cfgs.make_args(c)
+    sd = random_state_dict(args, c["D"], seed=0)
+    model = LatentMDGenModel(args, c["D"], precision=precision)
+    model.load_state_dict(sd)
+    return model.to(dev).eval().requires_grad_(False), c, args
+
+
+def kwargs_from(inp, f):
+    kw = dict(mask=f(inp["mask"]), start_frames=(f(inp["start_rot"]), f(inp["start_trans"])),
+              x_cond=f(inp["x_cond"]), x_cond_mask=f(inp["x_cond_mask"]), aatype=f(inp["aatype"]))
+    if "end_rot" in inp:
+        kw["end_frames"] = (f(inp["end_rot"]), f(inp["end_trans"]))
+    return kw
+
+
+def time_device_rollouts(model, x0, kw, steps, warm, world, dev):
+    """ms per rollout (device-resident inputs), CUDA events on the launching stream, barrier + sync on both sides, MAX over ranks."""
+    for _ in range(warm):
+        model.euler_rollout(x0, NUM_STEPS, **kw)
+    dist_barrier(world, dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        model.euler_rollout(x0, NUM_STEPS, **kw)
+    e1.record()
+    dist_barrier(world, dev)
+    return dist_max(e0.elapsed_time(e1) / steps, world, dev)
+
+
+def other_config_lines(a, rank, world, dev, pk):
+    """north_star: throughput on tetrapeptide AND ATLAS-shaped trajectories at every GPU count.  Configs 1, 2, 4, 5 at
+    their full BASELINE shapes, measured in the same run with the same timing rules (device-resident arm, weak scaling:
+    every rank its own rollouts), fewer steps."""
+    out = {}
+    for cid in (1, 2, 4, 5):
+        if cid == a.config:
+            continue
+        model, c, _ = build_model(cid, dev)
+        inp = cfgs.synthetic_inputs(c, seed=rank)
+        kw = kwargs_from(inp, lambda v: v.to(dev))
+        x0 = inp["x0"].to(dev)
+        ms = time_device_rollouts(model, x0, kw, max(3, a.steps // 4), 3, world, dev)
+        fps = world * c["B"] * c["T"] / (ms * 1e-3)
+        out[f"config{cid}"] = {"workload": workload_name(cid), "value": fps, "unit": "frames/s", "ms_per_step": ms,
+                               "tensor_core_frac": cfgs.flops_per_forward(c) * (NUM_STEPS - 1) / (ms * 1e-3) / 1e12 / pk["tflops"],
+                               "launches_per_evaluation": model.launches_per_forward()}
+        del model
+        torch.cuda.empty_cache()
+    return out
+
+
 def run_gpu(a, rank, world, local_rank):
-    from mdgen_finetune_b200 import LatentMDGenModel, Sampler, create_transport, _lib
+    from mdgen_finetune_b200 import Sampler, create_transport, _lib
     import torch.distributed as dist
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
-    c = dict(cfgs.CONFIGS[a.config]); c["id"] = a.config
-    args = cfgs.make_args(c)
-    sd = random_state_dict(args, c["D"], seed=0)
-    model = LatentMDGenModel(args, c["D"], precision="bf16")
-    model.load_state_dict(sd)
-    model = model.to(dev).eval()
-    inp = rank_inputs(c, rank)                            # independent rollouts per rank: no data-path collective
-
-    def kwargs_on(f):
-        kw = dict(mask=f(inp["mask"]), start_frames=(f(inp["start_rot"]), f(inp["start_trans"])),
-                  x_cond=f(inp["x_cond"]), x_cond_mask=f(inp["x_cond_mask"]), aatype=f(inp["aatype"]))
-        if "end_rot" in inp:
-            kw["end_frames"] = (f(inp["end_rot"]), f(inp["end_trans"]))
-        return kw
+    strong = a.scaling == "strong"
+    Bfull = cfgs.CONFIGS[a.config]["B"]
+    if strong and Bfull % world != 0:
+        raise SystemExit(f"--scaling strong shards the batch of {Bfull} over the ranks: --gpus must divide it")
+    model, c, args = build_model(a.config, dev, B=Bfull // world if strong else None)
+    # weak: every rank samples its own full batch (seed = rank).  strong: the ONE batch of the config (seed 0) is sharded
+    # contiguously over the ranks.  Either way rollouts are independent: no data-path collective.
+    if strong:
+        cf = dict(cfgs.CONFIGS[a.config]); cf["id"] = a.config
+        full = cfgs.synthetic_inputs(cf, seed=0)
+        per = Bfull // world
+        inp = {k: v[rank * per:(rank + 1) * per].contiguous() for k, v in full.items()}
+    else:
+        inp = rank_inputs(c, rank)
+    kwargs_on = lambda f: kwargs_from(inp, f)
 
     barrier = lambda: dist_barrier(world, dev)
     max_over_ranks = lambda ms: dist_max(ms, world, dev)
@@ -229,6 +341,19 @@ def run_gpu(a, rank, world, local_rank):
         torch.cuda.synchronize(dev)
         n_warm += 1
     clocks.rows.clear()             # keep only the samples taken under the timed load
+    # parity of the timed dispatch, once, after warm-up: finite, and one bf16 velocity against the fp32 check mode of the
+    # same library (itself pinned to the reference at 1e-4 by tests/test_gpu_parity.py) within north_star's 2e-2
+    t_chk = torch.full((c["B"],), 0.3, device=dev)
+    v_bf16 = model.forward_inference(x0_dev, t_chk, **kw_dev)
+    m32, _, _ = build_model(a.config, dev, B=c["B"], precision="fp32")
+    v_f32 = m32.forward_inference(x0_dev, t_chk, **kw_dev)
+    parity = float((v_bf16.double() - v_f32.double()).norm() / v_f32.double().norm())
+    del m32, v_f32
+    torch.cuda.empty_cache()
+    if not (torch.isfinite(v_bf16).all() and torch.isfinite(rollout()).all() and parity < 2e-2):
+        raise SystemExit(f"bench.py: parity check failed (rel-L2 bf16 vs fp32 check mode = {parity})")
+    rollout()
+    torch.cuda.synchronize(dev)
     l0 = _lib.lib().mdgen_launch_count()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -272,9 +397,22 @@ def run_gpu(a, rank, world, local_rank):
     _lib.profile_begin()
     rollout()
     prof = _lib.profile_end()
+    pk = peaks()
+    others = other_config_lines(a, rank, world, dev, pk) if not a.no_other_configs else None
+    strong_block = None
+    if world > 1 and not strong and Bfull % world == 0 and not a.no_other_configs:
+        # BASELINE config 3 read literally ("batch 8 ... data-parallel across 1/2/4/8"): the ONE batch sharded over the ranks
+        ms_model, cs, _ = build_model(a.config, dev, B=Bfull // world)
+        cf = dict(cfgs.CONFIGS[a.config]); cf["id"] = a.config
+        full = cfgs.synthetic_inputs(cf, seed=0)
+        per = Bfull // world
+        sh = {k: v[rank * per:(rank + 1) * per].contiguous() for k, v in full.items()}
+        ms_s = time_device_rollouts(ms_model, sh["x0"].to(dev), kwargs_from(sh, lambda v: v.to(dev)), max(3, a.steps // 2), 3, world, dev)
+        strong_block = {"value": Bfull * c["T"] / (ms_s * 1e-3), "unit": "frames/s", "ms_per_step": ms_s,
+                        "batch_per_gpu": per, "note": "fixed total batch sharded over the ranks (strong scaling), same timing rules"}
+        del ms_model
     if rank != 0:
         return
-    pk = peaks()
     total_prof = sum(v[0] for v in prof.values()) or 1.0
     fl = algorithmic_flops(c)
     nev = NUM_STEPS - 1
@@ -313,7 +451,7 @@ def run_gpu(a, rank, world, local_rank):
     value = world * frames_per_step / (ms * 1e-3)
     line = {
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic", "gpu_launches": launches,
         "config": {"workload": workload_name(a.config), "frames_per_step_per_gpu": frames_per_step,
                    "l2": "no explicit flush: the per-evaluation activation working set (>0.4 GB) exceeds the 126 MB L2",
@@ -323,11 +461,23 @@ def run_gpu(a, rank, world, local_rank):
         "e2e": {"value": world * frames_per_step / (ms_e2e * 1e-3), "unit": "frames/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "api": "Sampler.sample_ode('euler')(x0, partial(model.forward_inference, **kw))"},
         "roofline": roof, "kernels": kernels,
+        "parity_check": {"rel_l2_velocity_bf16_vs_fp32_check": parity, "tolerance": 2e-2, "finite": True},
+        "rollout": "one CUDA graph per Euler call (all 49 evaluations), replayed; launches counted per graph kernel node",
     }
+    if others is not None:
+        line["other_configs"] = others
+    if strong_block is not None:
+        line["strong_scaling"] = strong_block
     if world == 1 and not a.no_cpu_baseline:
-        s, cc, cores = oracle_time_forward(a.config, 3)
-        line["cpu_baseline"] = {"value": cc["T"] / (nev * s), "unit": "frames/s", "cores": cores, "kind": "port",
-                                "sample": "median of 3 velocity evaluations of a B=1 slice (1 of 8 rollouts), x49 extrapolated"}
+        s, cc, cores, kind = reference_time_forward(a.config, 1, nfwd=3, warm=1)
+        cb = {"value": cc["T"] / (nev * s), "unit": "frames/s", "cores": cores, "kind": kind, "batch": 1,
+              "sample": f"median of 3 velocity evaluations of a B=1 slice (1 of {Bfull} rollouts) on the reference's own "
+                        f"LatentMDGenModel, x{nev} extrapolated"}
+        if Bfull > 1 and s * Bfull < 20.0:
+            sf, _, _, _ = reference_time_forward(a.config, Bfull, nfwd=1, warm=0)
+            cb["full_batch_forward_s"] = sf
+            cb["full_batch_value"] = Bfull * cc["T"] / (nev * sf)
+        line["cpu_baseline"] = cb
     print(json.dumps(line))
 
 
@@ -339,6 +489,9 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--config", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    ap.add_argument("--no-other-configs", dest="no_other_configs", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every rank its own full batch (default); strong: the config's one batch sharded over the ranks")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

@@ -61,4 +61,20 @@ def test_reference_arm_under_torchrun_prints_once():
     assert len(lines) == 1
     d = lines[0]
     assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["value"] > 0
-    assert d["cpu_baseline"]["kind"] == "port" and d["e2e"]["h2d_bytes_per_step"] == 0
+    # the reference's own modules (staged under oracle/_ref by __graft_entry__.build(), or /root/reference/src here)
+    assert d["cpu_baseline"]["kind"] == "reference" and d["e2e"]["h2d_bytes_per_step"] == 0
+    assert d["cpu_baseline"]["same_config"] in (True, False) and d["cpu_baseline"]["cores"] >= 1
+
+
+def test_strong_scaling_shards_partition_the_batch():
+    """--scaling strong: the config's ONE batch is cut contiguously over the ranks; the union of the shards is the batch."""
+    from mdgen_finetune_b200 import configs as cfgs
+    cf = dict(cfgs.CONFIGS[3]); cf["id"] = 3
+    cf["T"] = 20
+    full = cfgs.synthetic_inputs(cf, seed=0)
+    for world in (2, 4, 8):
+        per = cf["B"] // world
+        shards = [{k: v[r * per:(r + 1) * per] for k, v in full.items()} for r in range(world)]
+        for k in full:
+            assert torch.equal(torch.cat([s[k] for s in shards]), full[k])
+        assert all(s["x0"].shape[0] == per for s in shards)
