@@ -111,6 +111,22 @@ int mdgen_forward(MdgenHandle* h, const float* x, const float* t, float* out,
 int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, float* traj,
                         float* out_final, mdgen_stream_t stream);
 
+/* Gradients of one velocity evaluation (row N4): what autograd does when the reference trains through the module --
+ * `policy.unet(x, t_, **condition)` with gradients in HGFNode.run_policy (src/models/samplers.py:120-146), the RTB loss
+ * (src/rtb_utils/gfn_diffusion.py:459-460) and Transport.training_losses (src/mdgen/transport/transport.py:173-188).
+ * Given dout = dLoss/d(forward output) [B,T,L,D] it RECOMPUTES LatentMDGenModel.forward (latent_model.py:216-269, the
+ * raw forward: design logits added, no Dirichlet flow) in fp32 for the conditioning last set, and back-propagates:
+ *   dx     [B,T,L,D] f32 or NULL: receives dLoss/dx (overwritten)
+ *   names / grads [nparams]: reference state_dict names and device fp32 buffers of the parameter's shape; the parameter
+ *       gradients are ACCUMULATED (+=) into them (zero them first for a fresh gradient).  Parameters not listed are
+ *       treated as frozen (no gradient computed).  q/k/v projections, bias_k / bias_v, IPA weights incl. head_weights,
+ *       LayerNorm affine, embeddings (aatype_to_emb.weight / mask_to_emb.weight as tables), adaLN and timestep MLP.
+ *   out    [B,T,L,D] f32 or NULL: the recomputed fp32 forward output
+ * All arithmetic is fp32 regardless of the handle's precision (a bf16 handle: the gradient is that of the fp32 function,
+ * within the bf16 tolerance of the bf16 forward).  The first call of a shape allocates the activation tape. */
+int mdgen_backward(MdgenHandle* h, const float* x, const float* t, const float* dout, float* dx, int32_t nparams,
+                   const char* const* names, float* const* grads, float* out, mdgen_stream_t stream);
+
 /* Design mode: turns the logits in the last 20 channels of `latent` [B,T,L,D] (what mdgen_forward wrote) into the
  * Dirichlet conditional-flow velocity, in place: the tail of LatentMDGenModel.forward_inference
  * (latent_model.py:296-326) with DirichletConditionalFlow.c_factor (utils.py:45-57) evaluated on the device instead

@@ -22,7 +22,7 @@ EXPORTS = ["mdgen_create", "mdgen_destroy", "mdgen_last_error", "mdgen_abi_versi
            "mdgen_finalize_weights", "mdgen_set_conditioning", "mdgen_forward", "mdgen_euler_rollout", "mdgen_dirichlet_flow", "mdgen_set_dirichlet_tables", "mdgen_dirichlet_flags", "mdgen_prep_batch", "mdgen_decode_atom14",
            "mdgen_launches_per_forward", "mdgen_launch_count", "mdgen_workspace_bytes", "mdgen_profile_begin", "mdgen_profile_end",
            "mdgen_profile_category_name", "mdgen_debug_set_buffer", "mdgen_test_gemm", "mdgen_test_attention",
-           "mdgen_variant_launches", "mdgen_gemm_noalloc"]
+           "mdgen_variant_launches", "mdgen_gemm_noalloc", "mdgen_backward"]
 NOALLOC_MAX_OPERAND_ELEMS = 1 << 21      # MDGEN_NOALLOC_MAX_OPERAND_ELEMS
 # kernel variants counted by mdgen_variant_launches(i) (tests assert that the full-size cases reach the timed kernels)
 VARIANTS = ["gemm_ln", "gemm_tc2", "gemm_tc", "attention_tc", "attention_seq4", "graph_replays"]
@@ -96,6 +96,7 @@ def lib():
     L.mdgen_variant_launches.restype = ctypes.c_int64
     L.mdgen_test_gemm.argtypes = [i32, i32, i32, fp, fp, fp, fp, i32, i32, vp]
     L.mdgen_test_attention.argtypes = [i32] * 5 + [fp] * 5 + [i32, i32, vp]
+    L.mdgen_backward.argtypes = [vp, fp, fp, fp, fp, i32, ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(ctypes.c_void_p), fp, vp]
     L.mdgen_gemm_noalloc.argtypes = [i32, i32, i32, fp, fp, fp, fp, vp]
     L.mdgen_debug_set_buffer.argtypes = [vp, i32]
     L.mdgen_profile_end.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int32), i32]

@@ -405,6 +405,7 @@ struct MdgenHandle {
   size_t traj_cap = 0;
   bool l2_limit_set = false;
   size_t l2_prev_limit = 0;
+  std::vector<DevBuf> train_slots;  // activation / gradient tape of mdgen_backward (train_tape.cuh), reused call to call
 
   int C() const { return cfg.embed_dim; }
   int D() const { return cfg.latent_dim; }
@@ -1343,6 +1344,11 @@ static int rollout_graph_build(MdgenHandle* h, int num_steps, bool want_traj) {
 }  // namespace mdgen
 
 // =============================================================================================
+// backward (row N4)
+// =============================================================================================
+#include "train_model.cuh"
+
+// =============================================================================================
 // C ABI
 // =============================================================================================
 namespace mdgen {
@@ -1401,6 +1407,7 @@ int mdgen_destroy(MdgenHandle* h) {
   rollout_graph_drop(h);
   if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
   if (h->traj_buf) cudaFree(h->traj_buf);
+  for (auto& b : h->train_slots) cudaFree(b.p);
   if (h->l2_limit_set) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, h->l2_prev_limit);
   free_workspace(h);
   for (void* p : h->packed) cudaFree(p);
@@ -1619,6 +1626,31 @@ int mdgen_euler_rollout(MdgenHandle* h, const float* x0, int32_t num_steps, floa
   MD_VARIANT(V_GRAPH_REPLAY);
   MD_CUDA(cudaMemcpyAsync(out_final, h->state_buf, n * 4, cudaMemcpyDeviceToDevice, st));
   if (want_traj) MD_CUDA(cudaMemcpyAsync(traj, h->traj_buf, (size_t)num_steps * n * 4, cudaMemcpyDeviceToDevice, st));
+  return MDGEN_OK;
+}
+
+int mdgen_backward(MdgenHandle* h, const float* x, const float* t, const float* dout, float* dx, int32_t nparams,
+                   const char* const* names, float* const* grads, float* out, mdgen_stream_t stream) {
+  MD_CHECK(h && x && t && dout, "null argument");
+  MD_CHECK(nparams == 0 || (names && grads), "mdgen_backward: names / grads missing");
+  if (!h->finalized || h->B == 0) {
+    set_error("mdgen_backward before finalize_weights / set_conditioning");
+    return MDGEN_ESTATE;
+  }
+  DeviceGuard g(h->device);
+  read_switches();
+  cudaStream_t st = (cudaStream_t)stream;
+  train::Tape tape(h, st);
+  for (int i = 0; i < nparams; ++i)
+    if (names[i] && grads[i]) tape.pgrad[names[i]] = grads[i];
+  train::ForwardOut fo;
+  MD_TRY(train::build_forward(tape, x, t, dx != nullptr, &fo));
+  const size_t n = fo.latent.n();
+  if (out) MD_CUDA(cudaMemcpyAsync(out, fo.latent.v, n * 4, cudaMemcpyDeviceToDevice, st));
+  MD_CUDA(cudaMemcpyAsync(fo.latent.g, dout, n * 4, cudaMemcpyDeviceToDevice, st));
+  MD_TRY(tape.run_backward());
+  if (dx) MD_CUDA(cudaMemcpyAsync(dx, fo.x_in.g, n * 4, cudaMemcpyDeviceToDevice, st));
+  MD_CUDA(cudaGetLastError());
   return MDGEN_OK;
 }
 

@@ -3,7 +3,7 @@
 Same constructor (`LatentMDGenModel(args, latent_dim)`), same `forward` / `forward_inference`
 signatures, same parameter / buffer names and shapes (strict `load_state_dict` of a reference
 checkpoint works), real `nn.Linear` children under the reference names (PEFT/LoRA attaches by
-name, gfn_diffusion.py:58-83).  The modules below are parameter CONTAINERS only: every call is
+name, gfn_diffusion.py:58-83; the merged weights reach the CUDA path, autograd.py).  The modules below are parameter CONTAINERS only: every call is
 forwarded to the CUDA library through the C ABI (include/mdgen_b200.h); there is no PyTorch
 compute path and no CPU fallback.
 """
@@ -215,6 +215,7 @@ class LatentMDGenModel(nn.Module):
         expect = param_shapes(args, latent_dim)
         got = {k: tuple(v.shape) for k, v in self.state_dict().items()}
         assert got == {k: tuple(v) for k, v in expect.items()}, "state_dict layout drifted from SURVEY 8b"
+        self._ref_names = tuple(expect.keys())        # reference state_dict names (stable under PEFT wrapping of children)
 
     @property
     def device(self):
@@ -268,15 +269,22 @@ class LatentMDGenModel(nn.Module):
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
+    def _raw_key(self):
+        """Identity of every tensor the effective weights are built from (parameters incl. LoRA adapters, buffers)."""
+        items = list(self.named_parameters()) + list(self.named_buffers())
+        return tuple((k, v.data_ptr(), v._version) for k, v in items)
+
     def _sync_weights(self):
         dev = self.device
         if dev.type != "cuda":
             raise RuntimeError("mdgen_finetune_b200.LatentMDGenModel runs on CUDA only (no CPU fallback); "
                                "call .cuda() first")
-        sd = self.state_dict()
-        key = (dev.index, self.precision) + tuple((k, v.data_ptr(), v._version) for k, v in sd.items())
+        key = (dev.index, self.precision) + self._raw_key()
         if key == self._weights_key:
             return
+        from .autograd import effective_tensors
+        with torch.no_grad():
+            sd = effective_tensors(self, self._ref_names)      # LoRA-wrapped linears contribute W + scaling * B @ A
         L = _lib.lib()
         with torch.cuda.device(dev):
             if self._handle is None or self._weights_key is None or self._weights_key[:2] != key[:2]:
@@ -287,7 +295,7 @@ class LatentMDGenModel(nn.Module):
                 self._handle = h
             st = self._stream()
             for name, v in sd.items():
-                t = v.detach().to(torch.float32).contiguous()
+                t = v.detach().to(dev, torch.float32).contiguous()
                 shape = (ctypes.c_int64 * t.dim())(*t.shape)
                 _lib.check(L.mdgen_load_weight(self._handle, name.encode(), t.data_ptr(), shape, t.dim(), 1, st),
                            f"mdgen_load_weight({name})")
@@ -370,24 +378,31 @@ class LatentMDGenModel(nn.Module):
     def forward(self, x, t, mask, start_frames=None, end_frames=None, x_cond=None, x_cond_mask=None,
                 aatype=None, *args, **kwargs):
         """One velocity evaluation (latent_model.py:216-269).  Unknown kwargs (e.g. `peptide=`) are
-        swallowed like the reference's **kwargs; `t` may be int64 (RTB DDPM timesteps)."""
+        swallowed like the reference's **kwargs; `t` may be int64 (RTB DDPM timesteps).
+
+        With gradients enabled and x or any parameter requiring them (RTB posterior: samplers.py:136-139, also under
+        torch.utils.checkpoint) the call goes through autograd.VelocityFn: forward = mdgen_forward, backward =
+        mdgen_backward (row N4).  Otherwise the output is a plain tensor."""
         if self.device.type != "cuda":
             raise RuntimeError("mdgen_finetune_b200.LatentMDGenModel runs on CUDA only (no CPU fallback); "
                                "call .cuda() first")
-        if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())):
-            # The output is written by the C ABI and carries no grad_fn: returning it to a caller that expects
-            # gradients (RTB: parameters require grad, the noise sample does not) would train nothing, silently.
-            raise NotImplementedError("backward through the CUDA denoiser is row N4 (DESIGN.md): call under "
-                                      "torch.no_grad(), or freeze the module (requires_grad_(False)) for sampling")
-        self._sync_weights()
-        dev = self.device
         if x.dim() != 4 or x.shape[-1] != self.latent_dim:
             raise ValueError(f"x must be [B,T,L,{self.latent_dim}], got {tuple(x.shape)}")
-        self._set_conditioning(x, mask, start_frames, end_frames, x_cond, x_cond_mask, aatype)
+        if t.numel() != x.shape[0]:
+            raise ValueError("t must have one entry per batch element")
+        cond = (mask, start_frames, end_frames, x_cond, x_cond_mask, aatype)
+        if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())):
+            from .autograd import VelocityFn, effective_tensors
+            eff = effective_tensors(self, self._ref_names)
+            return VelocityFn.apply(self, cond, self._ref_names, x, t, *[eff[n] for n in self._ref_names])
+        return self._forward_no_grad(x, t, cond)
+
+    def _forward_no_grad(self, x, t, cond):
+        self._sync_weights()
+        dev = self.device
+        self._set_conditioning(x, *cond)
         xx = x.detach().to(dev, torch.float32).contiguous()
         tt = t.detach().to(dev, torch.float32).contiguous()
-        if tt.numel() != x.shape[0]:
-            raise ValueError("t must have one entry per batch element")
         out = torch.empty_like(xx)
         with torch.cuda.device(dev):
             _lib.check(_lib.lib().mdgen_forward(self._handle, xx.data_ptr(), tt.data_ptr(), out.data_ptr(),

@@ -35,3 +35,41 @@ def oracle_velocity(O, sd, args, inp, x, t):
     start, end = frames_of(inp)
     return O.forward_inference(sd, args, x, t, inp["mask"], start, end, inp["x_cond"],
                                inp["x_cond_mask"], inp["aatype"])
+
+
+# ---- gradient goldens (oracle/make_grad_golden.py) -----------------------------------------------------------------
+GRAD_CASES = ["sim_small", "tps_small", "design_small", "atlas_small"]
+
+
+def grad_cotangent(shape):
+    return torch.randn(shape, generator=torch.Generator().manual_seed(123))
+
+
+def grad_projections(name_index, g, nproj=8):
+    gen = torch.Generator().manual_seed(7919 * (name_index + 1))
+    r = torch.randn(nproj, g.numel(), generator=gen)
+    return r @ g.reshape(-1).double().float()
+
+
+def check_grads(dx, named_grads, gold, tol):
+    """dx and {name: grad} against one case of tests/golden/grads.pt.  Every parameter: norm and 8 random projections
+    (a gradient error e changes a projection by ~|e|, so the bound is tol * |g| with a 4-sigma margin); parameters with
+    <= 4096 elements and dx: full rel-L2.  Returns the worst relative error seen."""
+    worst = rel_l2(dx, gold["dx"])
+    assert worst < tol, ("dx", worst)
+    assert set(named_grads) == set(gold["params"]), set(named_grads) ^ set(gold["params"])
+    for name, e in gold["params"].items():
+        g = named_grads[name].detach().cpu().float()
+        n = e["norm"]
+        if n == 0.0:
+            assert float(g.norm()) == 0.0, name
+            continue
+        err_n = abs(float(g.double().norm()) - n) / n
+        err_p = float((grad_projections(e["index"], g) - e["proj"]).abs().max()) / n
+        assert err_n < tol and err_p < 4 * tol, (name, err_n, err_p)
+        worst = max(worst, err_n, err_p / 4)
+        if "full" in e:
+            err_f = float((g.reshape(-1).double() - e["full"].reshape(-1).double()).norm()) / n
+            assert err_f < tol, (name, err_f)
+            worst = max(worst, err_f)
+    return worst

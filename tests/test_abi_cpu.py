@@ -51,18 +51,68 @@ def test_cpu_call_fails_loudly():
         m.forward(x, torch.zeros(1), torch.ones(1, 2, 4))
 
 
-def test_forward_refuses_to_return_a_gradless_output_when_gradients_are_expected(monkeypatch):
-    """RTB call convention (samplers.py:136-139): parameters require grad, x does not.  The C ABI output has no grad_fn,
-    so forward() must refuse instead of silently training nothing."""
+def test_forward_routes_gradient_calls_through_the_autograd_function(monkeypatch):
+    """RTB call convention (samplers.py:136-139): parameters require grad, x does not.  The output must carry a grad_fn
+    (autograd.VelocityFn -> mdgen_backward); frozen modules / no_grad return plain tensors.  CPU: the C-ABI call is
+    replaced by a stub, only the dispatch is checked."""
     from mdgen_finetune_b200 import LatentMDGenModel
     from mdgen_finetune_b200 import model as M
     args = cfgs.make_args(cfgs.small_variant(1, B=1, T=2, L=4))
     m = LatentMDGenModel(args, 21)
     monkeypatch.setattr(M.LatentMDGenModel, "device", property(lambda self: torch.device("cuda", 0)))
+    monkeypatch.setattr(M.LatentMDGenModel, "_forward_no_grad", lambda self, x, t, cond: torch.zeros_like(x))
     x = torch.zeros(1, 2, 4, 21)
-    assert not x.requires_grad and any(p.requires_grad for p in m.parameters())
-    with pytest.raises(NotImplementedError, match="row N4"):
-        m.forward(x, torch.zeros(1), torch.ones(1, 2, 4))
+    y = m.forward(x, torch.zeros(1), torch.ones(1, 2, 4), peptide=["AAAA"])
+    assert y.requires_grad and "VelocityFn" in type(y.grad_fn).__name__
+    with torch.no_grad():
+        assert not m.forward(x, torch.zeros(1), torch.ones(1, 2, 4)).requires_grad
+    m.requires_grad_(False)
+    assert m.forward(x, torch.zeros(1), torch.ones(1, 2, 4)).grad_fn is None
+    assert m.forward(x.clone().requires_grad_(), torch.zeros(1), torch.ones(1, 2, 4)).grad_fn is not None
+
+
+class _LoraLinear(torch.nn.Module):
+    """PEFT's LoraLayer layout (peft is not in this image): base_layer + lora_A / lora_B ModuleDicts + scaling."""
+
+    def __init__(self, base, r=4, alpha=8.0):
+        super().__init__()
+        self.base_layer = base
+        self.lora_A = torch.nn.ModuleDict({"default": torch.nn.Linear(base.in_features, r, bias=False)})
+        self.lora_B = torch.nn.ModuleDict({"default": torch.nn.Linear(r, base.out_features, bias=False)})
+        self.scaling = {"default": alpha / r}
+        self.active_adapters = ["default"]
+        self.merged = False
+
+
+def test_lora_wrapped_linears_contribute_merged_weights():
+    """gfn_diffusion.py:58-83 attaches LoRA to the named Linear children; the CUDA path must see W + scaling * B @ A and
+    autograd must route the weight gradient to A and B."""
+    from mdgen_finetune_b200 import LatentMDGenModel
+    from mdgen_finetune_b200.autograd import effective_tensors
+    args = cfgs.make_args(cfgs.small_variant(1, B=1, T=2, L=4))
+    m = LatentMDGenModel(args, 21)
+    base = m.layers[0].mha_t.attn.q_proj
+    w0 = base.weight.detach().clone()
+    m.requires_grad_(False)
+    lora = _LoraLinear(base)
+    torch.nn.init.normal_(lora.lora_B["default"].weight, std=0.1)
+    m.layers[0].mha_t.attn.q_proj = lora
+    names = m._ref_names
+    assert "layers.0.mha_t.attn.q_proj.weight" in names              # reference names are kept
+    eff = effective_tensors(m, names)
+    A, B = lora.lora_A["default"].weight, lora.lora_B["default"].weight
+    assert torch.allclose(eff["layers.0.mha_t.attn.q_proj.weight"], w0 + 2.0 * (B @ A))
+    assert eff["layers.0.mha_t.attn.q_proj.bias"] is base.bias
+    assert eff["layers.0.mha_t.attn.k_proj.weight"] is m.layers[0].mha_t.attn.k_proj.weight
+    g = torch.randn_like(w0)
+    (eff["layers.0.mha_t.attn.q_proj.weight"] * g).sum().backward()
+    assert torch.allclose(A.grad, 2.0 * B.detach().T @ g) and torch.allclose(B.grad, 2.0 * g @ A.detach().T)
+    assert base.weight.grad is None
+    # the weight cache key sees the adapter parameters
+    k0 = m._raw_key()
+    with torch.no_grad():
+        A.add_(1.0)
+    assert m._raw_key() != k0
 
 
 def test_sampler_generic_callable_matches_oracle_euler():

@@ -63,3 +63,26 @@ def test_full_size_config1_velocity():
     with torch.no_grad():
         v = oracle_velocity(O, sd, args, inp, inp["x0"], torch.full((c["B"],), g["t_values"][0]))
     assert rel_l2(v, g["v_t0"]) < TOL
+
+
+# ---- row N4: the oracle's autograd against the reference's autograd ----------------------------------------------
+from tests.helpers import GRAD_CASES, check_grads, grad_cotangent  # noqa: E402
+
+
+@pytest.mark.parametrize("name", GRAD_CASES)
+def test_oracle_gradients_match_reference_autograd(name):
+    """The oracle is a functional restatement in torch, so torch's autograd through it is the gradient of the pinned
+    function; this pins it to the gradients of the UNMODIFIED reference (tests/golden/grads.pt)."""
+    import os
+    g, c, args, sd, inp = load_case(name)
+    gold = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "grads.pt"), weights_only=False)[name]
+    names = list(gold["params"].keys())
+    sdg = {k: (v.clone().requires_grad_(True) if k in gold["params"] else v) for k, v in sd.items()}
+    x = inp["x0"].clone().requires_grad_(True)
+    start, end = frames_of(inp)
+    y = O.forward(sdg, args, x, gold["t"], inp["mask"], start, end, inp["x_cond"], inp["x_cond_mask"], inp["aatype"])
+    assert rel_l2(y.detach(), gold["y"]) < TOL
+    loss = (y * grad_cotangent(y.shape)).sum()
+    grads = torch.autograd.grad(loss, [x] + [sdg[n] for n in names])
+    worst = check_grads(grads[0], dict(zip(names, grads[1:])), gold, 2e-5)
+    print(name, "worst relative gradient error", worst)
