@@ -3,3 +3,4 @@ the LatentMDGenModel velocity network + fixed-grid Euler transport sampler, behi
 from .model import LatentMDGenModel  # noqa: F401
 from .transport import Sampler, Transport, create_transport  # noqa: F401
 from .prep import prep_batch, decode_samples  # noqa: F401
+from .ddp import GradAllReduce, all_reduce_mean_scalar  # noqa: F401

@@ -37,7 +37,7 @@ def make_args(cfg, **overrides):
         allow_nan_cfactor=False, flow_matching=False, prior_variance=1.0,
         # transport flags read by Transport.__init__ (transport.py:67-83)
         path_type="GVP", prediction="velocity", sampling_method="euler",
-        design_variance=1.0, weight_loss_var_x0=0.0, dirichlet_flow_matching=False,
+        design_variance=1.0, weight_loss_var_x0=0.0, dirichlet_flow_matching=False, discrete_loss_weight=0.5,
     )
     task = c["task"]
     if task == "sim":

@@ -12,12 +12,59 @@ callable the loop runs here, one `model(x, t, **kw)` per grid step, exactly like
 torchdiffeq's fixed-grid Euler.
 """
 import functools
+import math
 
 import torch
 
 
+def expand_t_like_x(t, x):
+    """path.py:5-13: t [B] -> [B, 1, ...] broadcastable against x."""
+    return t.view(t.size(0), *([1] * (x.dim() - 1)))
+
+
+class ICPlan:
+    """Linear interpolant (path.py:18-135): x_t = t x1 + (1 - t) x0, u_t = x1 - x0."""
+
+    def compute_alpha_t(self, t):
+        return t, 1
+
+    def compute_sigma_t(self, t):
+        return 1 - t, -1
+
+    def plan(self, t, x0, x1):          # path.py:112-135
+        te = expand_t_like_x(t, x1)
+        alpha_t, d_alpha_t = self.compute_alpha_t(te)
+        sigma_t, d_sigma_t = self.compute_sigma_t(te)
+        xt = alpha_t * x1 + sigma_t * x0
+        ut = d_alpha_t * x1 + d_sigma_t * x0
+        return t, xt, ut
+
+
+class GVPCPlan(ICPlan):
+    """Trigonometric interpolant (path.py:173-190): alpha = sin(pi t / 2), sigma = cos(pi t / 2)."""
+
+    def compute_alpha_t(self, t):
+        return torch.sin(t * math.pi / 2), math.pi / 2 * torch.cos(t * math.pi / 2)
+
+    def compute_sigma_t(self, t):
+        return torch.cos(t * math.pi / 2), -math.pi / 2 * torch.sin(t * math.pi / 2)
+
+
+def mean_flat(x, mask):
+    """transport.py:12-16: masked mean over all non-batch dimensions."""
+    dims = list(range(1, x.dim()))
+    return torch.sum(x * mask, dim=dims) / torch.sum(mask, dim=dims)
+
+
+def t_to_alpha(t, args):
+    """transport.py:52-57."""
+    return 1 * (1 - t) + t * args.alpha_max, (args.alpha_max - 1)
+
+
 class Transport:
-    """transport.py:60-83 (state only) + check_interval for velocity models (transport.py:94-123)."""
+    """transport.py:60-222 for velocity models on Linear / GVP paths: interpolant + training loss (training_losses) and the
+    sampling interval (check_interval, transport.py:94-123).  The model call inside training_losses is the only heavy
+    step; with mdgen_finetune_b200.LatentMDGenModel it runs on the CUDA path with gradients (autograd.VelocityFn)."""
 
     def __init__(self, *, args, model_type="velocity", path_type="Linear", loss_type=None,
                  train_eps=0, sample_eps=0):
@@ -27,6 +74,50 @@ class Transport:
         self.loss_type = loss_type
         self.train_eps = train_eps
         self.sample_eps = sample_eps
+        self.path_sampler = GVPCPlan() if path_type == "GVP" else ICPlan()
+
+    def sample(self, x1):
+        """transport.py:125-135: x0 ~ N(0, 1) like x1, t ~ U(t0, t1) per batch element (drawn on the CPU generator like the
+        reference's th.rand, then moved)."""
+        x0 = torch.randn_like(x1)
+        t0, t1 = self.check_interval(self.train_eps, self.sample_eps)
+        t = torch.rand((x1.shape[0],)) * (t1 - t0) + t0
+        return t.to(x1), x0, x1
+
+    def training_losses(self, model, x1, aatype1=None, mask=None, model_kwargs=None):
+        """transport.py:137-222 (velocity branch; the mpnn / dynamic_mpnn variants are out of scope):
+        masked MSE between the model output and u_t; design adds the Dirichlet-noised sequence channels to x_t and a
+        cross-entropy on the logits."""
+        if model_kwargs is None:
+            model_kwargs = {}
+        args = self.args
+        t, x0, x1 = self.sample(x1)
+        t, xt, ut = self.path_sampler.plan(t, x0, x1)
+        design = bool(getattr(args, "design", False))
+        if design:
+            seq_one_hot = torch.nn.functional.one_hot(aatype1, num_classes=20)
+            alphas, _ = t_to_alpha(t, args)
+            alphas = 1 + seq_one_hot * (alphas[:, None, None] - 1)
+            x_d = torch.distributions.Dirichlet(alphas).sample()
+            x_d = x_d[:, None, :, :].expand(-1, xt.shape[1], -1, -1)
+            xt = torch.cat([xt, x_d], dim=-1)
+        model_output = model(xt, t, **model_kwargs)
+        B, *_, C = xt.shape
+        assert model_output.size() == (B, *xt.size()[1:-1], C)
+        if design:
+            logits = model_output[:, :, :, -20:]
+            model_output = model_output[:, :, :, :-20]
+        terms = {"t": t, "pred": model_output}
+        terms["loss"] = mean_flat((model_output - ut) ** 2, mask)
+        if design:
+            terms["loss_continuous"] = terms["loss"]
+            seq_expanded = aatype1[:, None, :].expand(-1, xt.shape[1], -1)
+            loss_d = torch.nn.functional.cross_entropy(logits.reshape(-1, 20), seq_expanded.reshape(-1))
+            w = args.discrete_loss_weight
+            terms["loss"] = loss_d * w + (1 - w) * terms["loss"]
+            terms["loss_discrete"] = loss_d
+            terms["logits"] = logits
+        return terms
 
     def check_interval(self, train_eps, sample_eps, *, diffusion_form="SBDM", sde=False, reverse=False,
                        eval=False, last_step_size=0.0):

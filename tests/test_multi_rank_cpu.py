@@ -78,3 +78,53 @@ def test_strong_scaling_shards_partition_the_batch():
         for k in full:
             assert torch.equal(torch.cat([s[k] for s in shards]), full[k])
         assert all(s["x0"].shape[0] == per for s in shards)
+
+
+def _grad_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from mdgen_finetune_b200 import GradAllReduce, LatentMDGenModel, all_reduce_mean_scalar, configs as cfgs
+    args = cfgs.make_args(cfgs.small_variant(4, B=2, T=1, L=4))
+    torch.manual_seed(0)
+    m = LatentMDGenModel(args, 48)
+    # LoRA-style: only part of the model is trainable; some trainable parameters get no gradient at all
+    m.requires_grad_(False)
+    train = [p for n, p in m.named_parameters() if ".fc1." in n or "bias_k" in n or "head_weights" in n]
+    for p in train:
+        p.requires_grad_(True)
+    g = torch.Generator().manual_seed(100 + rank)
+    for i, p in enumerate(train):
+        if i % 7 != 3:                                   # the same subset on every rank, as under DDP
+            p.grad = torch.randn(p.shape, generator=g)
+    mine = {i: p.grad.clone() for i, p in enumerate(train) if p.grad is not None}
+    red = GradAllReduce(m.parameters(), bucket_mb=1.0)
+    nb = len(red.buckets())
+    nbytes = red.sync()
+    logz = all_reduce_mean_scalar(torch.tensor(float(rank + 1)))
+    # plain numpy copies: tensors would travel as shared-memory handles that die with this process
+    q.put((rank, nb, nbytes, {i: p.grad.numpy().copy() for i, p in enumerate(train) if p.grad is not None},
+           {i: v.numpy().copy() for i, v in mine.items()}, float(logz)))
+    dist.destroy_process_group()
+
+
+def test_gradient_allreduce_gloo_world2():
+    """RTB data parallelism (gfn_diffusion.py:154-161, 213-219): after sync() every rank holds the MEAN of the ranks'
+    gradients, bucketed; parameters without a gradient are skipped; the vargrad scalar is averaged too."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31000 + os.getpid() % 2000
+    procs = [ctx.Process(target=_grad_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted((q.get(timeout=180) for _ in range(2)), key=lambda r: r[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, nb0, bytes0, red0, mine0, z0), (_, nb1, bytes1, red1, mine1, z1) = res
+    assert nb0 == nb1 and nb0 > 1 and bytes0 == bytes1 > 0          # several buckets at bucket_mb = 1
+    assert set(red0) == set(mine0) == set(mine1)
+    import numpy as np
+    for i in mine0:
+        mean = (mine0[i] + mine1[i]) / 2
+        assert np.allclose(red0[i], mean, atol=1e-6) and np.array_equal(red0[i], red1[i])
+    assert z0 == z1 == 1.5
