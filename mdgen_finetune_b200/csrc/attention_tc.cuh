@@ -48,8 +48,13 @@ using tc::umma_bf16;
 constexpr int HD = 24, DP = 32;          // head dim and its MMA-padded width
 constexpr int QT = 128;                  // query tile rows
 constexpr int KB = 128;                  // rows of a Q operand block
-constexpr int SB = 48;                   // keys per MMA / softmax block
-constexpr int RB = 2 * SB;               // keys (rows) per K/V ring block
+constexpr int RB = 96;                   // keys (rows) per K/V ring block = 2 softmax blocks of 48 or 3 of 32
+constexpr int MAXBUF = 3;                // S buffers per warpgroup: 2 x 48 or 3 x 32 columns (both 96)
+// Kernel variants <SB, NBUF> (keys per MMA / softmax block, S buffers in flight per warpgroup):
+//   <48, 2>  v7: Q.K^T(j+2) is queued behind "P(j) ready" -- one block of slack for the round trip softmax -> issuer ->
+//            tensor pipe -> commit -> softmax, which the clock stamps (tools/attn_probe.py) show exposed: 400-1000 of every
+//            ~2200 cycles per block the softmax warps wait for S while the MUFU, saturated in between, idles.
+//   <32, 3>  v8: the same 96 S columns as THREE buffers of 32 keys: Q.K^T(j+3) behind P(j), two blocks of slack.
 constexpr int MAX_KEYS = 2048;           // S + 1 <= MAX_KEYS (K/V are streamed; the limit only bounds what is tested)
 constexpr int NWG = 4;                   // softmax warpgroups = query tiles in flight per CTA
 constexpr int NPW = 4;                   // producer warps (thread = one key row / one query row of a block)
@@ -63,22 +68,22 @@ constexpr int GRP_BYTES = KB * 16;       // 2048: stride between d-groups of a Q
 constexpr int RGRP_BYTES = RB * 16;      // 1536: stride between d-groups of a K/V ring block (K-major LBO / MN-major SBO)
 constexpr int RBLK_BYTES = 4 * RGRP_BYTES;   // 6 KB
 constexpr int OFF_K = 0, OFF_V = OFF_K + NSLOT * RBLK_BYTES, OFF_Q = OFF_V + NSLOT * RBLK_BYTES,
-              OFF_BAR = OFF_Q + 2 * NWG * BLK_BYTES, SMEM_BYTES = OFF_BAR + 512;
+              OFF_BAR = OFF_Q + 2 * NWG * BLK_BYTES, SMEM_BYTES = OFF_BAR + 1024;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 constexpr uint32_t TMEM_COLS = 512;
-// per-warpgroup TMEM columns: S0 fp32 [48], S1 fp32 [48] (P packed bf16 overwrites the first 24 of its S), O fp32 [32]
+// per-warpgroup TMEM columns: S buffers fp32 [96 in all] (P packed bf16 overwrites the first half of its S), O fp32 [32]
 constexpr uint32_t TM_WG = 128, TM_S = 0, TM_O = 96;
 constexpr float RESCALE_TAU = 8.0f;      // log2 units: P <= 2^8 between rescales
 
 struct Bars {
-  uint64_t s_full[NWG][2];    // Q.K^T of a block has landed in S buffer b (and every MMA queued before it has retired)
-  uint64_t p_full[NWG][2];    // the warpgroup has written P over S buffer b
+  uint64_t s_full[NWG][MAXBUF];    // Q.K^T of a block has landed in S buffer b (and every MMA queued before it has retired)
+  uint64_t p_full[NWG][MAXBUF];    // the warpgroup has written P over S buffer b
   uint64_t q_full[2][NWG], q_empty[2][NWG];      // per warpgroup: two Q buffers
   uint64_t kv_full[NSLOT], kv_empty[NSLOT];      // K/V ring
   uint64_t o_free[NWG];       // the warpgroup has consumed the unit's last two s_full phases: the next unit may signal again
   uint32_t tmem_base;
 };
-static_assert(sizeof(Bars) <= 512, "barrier block");
+static_assert(sizeof(Bars) <= 1024, "barrier block");
 
 // no-swizzle descriptor: start>>4 | LBO>>4 << 16 | SBO>>4 << 32 | version 1 << 46 | layout 0
 __device__ __forceinline__ uint64_t desc_nosw(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
@@ -253,7 +258,7 @@ template <int POLY> __device__ __forceinline__ float ex2_sel(float x, int j) {
 // the mask column of K, see the producers): running-max update with
 // lazy rescale of O (in TMEM; `pv_bar` / `pv_parity` = the barrier phase that tells every P.V issued so far has
 // retired), then P = exp2(x log2e - m) packed to bf16 (pk[0..23]).
-template <bool DBG, int POLY>
+template <bool DBG, int POLY, int SB>
 __device__ __forceinline__ void soft_block(uint32_t (&x)[SB], uint32_t (&pk)[SB / 2], bool have_o,
                                            float& m_used, uint32_t tO, uint64_t* pv_bar, uint32_t pv_parity, int var) {
   const float LOG2E = 1.4426950408889634f;
@@ -310,9 +315,11 @@ template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile
 template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
 
-template <bool DBG, int POLY>
+template <bool DBG, int POLY, int SB, int NBUF>
 __global__ void __launch_bounds__(THREADS, 1)
 attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long long* dbg_buf, int dbg_cta, int dbg_var) {
+  static_assert(SB * NBUF == 96 && RB % SB == 0 && NBUF <= MAXBUF && SB % 16 == 0, "S buffers fill 96 TMEM columns");
+  constexpr int BPR = RB / SB;         // softmax blocks per K/V ring block
   const int var = DBG ? dbg_var : 0;   // timing experiments (tools/attn_probe.py); results are wrong when non-zero
   // No integer round trip on this pointer: the compiler must keep seeing a shared-space address, otherwise every
   // staging access becomes a generic LD.E / ST.E (long-scoreboard latency instead of LDS / STS).
@@ -325,16 +332,19 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
   if (tid == 0) dbg_stamp(dbg, 0);
   const int C = p.H * HD, S = p.S, nkeys = S + 1;
   const int nkb = (nkeys + RB - 1) / RB;                     // ring blocks per unit
-  const int nsb = (nkeys + SB - 1) / SB;                     // MMA / softmax blocks of 48 keys (>= 2)
+  const int nsb = (nkeys + SB - 1) / SB;                     // MMA / softmax blocks of SB keys (>= NBUF: S >= 64)
 
   if (tid == 0) {
-    for (int i = 0; i < NWG; ++i)
-      for (int b = 0; b < 2; ++b) {
+    for (int i = 0; i < NWG; ++i) {
+      for (int b = 0; b < MAXBUF; ++b) {
         mbar_init(&bars->s_full[i][b], 1);
         mbar_init(&bars->p_full[i][b], 4);
+      }
+      for (int b = 0; b < 2; ++b) {
         mbar_init(&bars->q_full[b][i], NPW);
         mbar_init(&bars->q_empty[b][i], 1);
       }
+    }
     for (int i = 0; i < NWG; ++i) mbar_init(&bars->o_free[i], 4);
     for (int i = 0; i < NSLOT; ++i) {
       mbar_init(&bars->kv_full[i], NPW);
@@ -372,7 +382,7 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
     setmaxnreg_dec<REGS_MMA>();
     const int w = warp;
     if (lane == 0) {
-      uint32_t np0 = 0, np1 = 0;          // P-ready phases consumed per S buffer
+      uint32_t np0 = 0, np1 = 0, np2 = 0; // P-ready phases consumed per S buffer
       uint32_t gblk = 0, quse = 0;        // ring blocks consumed by earlier units, units this warpgroup was active in
       const uint32_t id_qk = idesc(QT, SB, false), id_pv = idesc(QT, DP, true);
       if (w == 0) dbg_stamp(dbg, 14);
@@ -395,39 +405,42 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
         const uint32_t qa = sQ + (qbuf * NWG + w) * BLK_BYTES;
         const uint32_t tW = tmem + w * TM_WG;
         auto issue_qk = [&](int j) {
-          const uint32_t g = gblk + (j >> 1), slot = g % NSLOT;
-          if ((j & 1) == 0) {                                      // first use of the ring block
+          const int sub = j % BPR;                                 // position of the block inside its ring block
+          const uint32_t g = gblk + j / BPR, slot = g % NSLOT;
+          if (sub == 0) {                                          // first use of the ring block
             mbar_wait(&bars->kv_full[slot], (g / NSLOT) & 1);
             tcgen05_fence_after();
           }
-          const uint32_t ka = sK + slot * RBLK_BYTES + (j & 1) * (SB * 16);
-          if (!(var & 8) || j < 2) {
+          const uint32_t ka = sK + slot * RBLK_BYTES + sub * (SB * 16);
+          if (!(var & 8) || j < NBUF) {
 #pragma unroll
             for (int jj = 0; jj < DP / 16; ++jj)
-              umma_bf16(tW + TM_S + (j & 1) * SB, desc_nosw(qa + jj * 2 * GRP_BYTES, GRP_BYTES, 128),
+              umma_bf16(tW + TM_S + (j % NBUF) * SB, desc_nosw(qa + jj * 2 * GRP_BYTES, GRP_BYTES, 128),
                         desc_nosw(ka + jj * 2 * RGRP_BYTES, RGRP_BYTES, 128), id_qk, jj);
           }
           if (j == nsb - 1) tcgen05_commit(&bars->q_empty[qbuf][w]);   // every Q.K^T of the unit is queued: Q buffer free when they retire
         };
-        issue_qk(0);
-        tcgen05_commit(&bars->s_full[w][0]);
-        issue_qk(1);
-        tcgen05_commit(&bars->s_full[w][1]);
+#pragma unroll
+        for (int j0 = 0; j0 < NBUF; ++j0) {                        // prime every S buffer (nsb >= NBUF)
+          issue_qk(j0);
+          tcgen05_commit(&bars->s_full[w][j0]);
+        }
         for (int j = 0; j < nsb; ++j) {
-          const int b = j & 1;
-          mbar_wait(&bars->p_full[w][b], (b ? np1 : np0) & 1);
-          if (b) ++np1; else ++np0;
+          const int b = j % NBUF, sub = j % BPR;
+          const uint32_t par = (b == 0 ? np0 : b == 1 ? np1 : np2) & 1;
+          mbar_wait(&bars->p_full[w][b], par);
+          if (b == 0) ++np0; else if (b == 1) ++np1; else ++np2;
           tcgen05_fence_after();
-          const uint32_t g = gblk + (j >> 1), slot = g % NSLOT;
-          const uint32_t va = sV + slot * RBLK_BYTES + b * (SB * 16);
+          const uint32_t g = gblk + j / BPR, slot = g % NSLOT;
+          const uint32_t va = sV + slot * RBLK_BYTES + sub * (SB * 16);
           if (!(var & 4)) {
 #pragma unroll
             for (int kk = 0; kk < SB / 16; ++kk)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
               umma_bf16_ts(tW + TM_O, tW + TM_S + b * SB + kk * 8, desc_nosw(va + kk * 256, 128, RGRP_BYTES), id_pv,
                            (j == 0 && kk == 0) ? 0u : 1u);
           }
-          if (b || j == nsb - 1) tcgen05_commit(&bars->kv_empty[slot]);   // this warpgroup is done with the ring block
-          if (j + 2 < nsb) issue_qk(j + 2);
+          if (sub == BPR - 1 || j == nsb - 1) tcgen05_commit(&bars->kv_empty[slot]);   // this warpgroup is done with the ring block
+          if (j + NBUF < nsb) issue_qk(j + NBUF);
           tcgen05_commit(&bars->s_full[w][b]);
         }
         ++quse;
@@ -444,43 +457,50 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
     uint64_t* const sfull = &bars->s_full[w][0];
     uint64_t* const pfull = &bars->p_full[w][0];
     const bool stamp = DBG && (r == 0 && w < 2);
-    uint32_t sc0 = 0, sc1 = 0;                               // s_full phases consumed per S buffer
+    uint32_t sc0 = 0, sc1 = 0, sc2 = 0;                      // s_full phases consumed per S buffer
     uint32_t it = 0;
     for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
       const Unit u = decode_unit(p, unit, chunks_per_seq);
       if (w < u.ntiles) {
         const int q = u.q_begin + w * QT + r;
         float m_used = -INFINITY;
+        int b = 0;
         for (int j = 0; j < nsb; ++j, ++it) {
-          const int b = j & 1;
           uint32_t x[SB], pk[SB / 2];
-          const uint32_t spar = (b ? sc1 : sc0) & 1;
+          const uint32_t spar = (b == 0 ? sc0 : b == 1 ? sc1 : sc2) & 1;
           mbar_wait(sfull + b, spar);
-          if (b) ++sc1; else ++sc0;
+          if (b == 0) ++sc0; else if (b == 1) ++sc1; else ++sc2;
           tcgen05_fence_after();
           if (stamp && it < 16) dbg_stamp(dbg, 16 + w * 40 + 2 * it);
           const uint32_t tS = tbase + TM_S + b * SB;
           tmem_ld_32x32b_x32(tS, x);
-          tmem_ld_32x32b_x16(tS + 32, x + 32);
+          if constexpr (SB == 48) tmem_ld_32x32b_x16(tS + 32, x + 32);
           tmem_ld_wait();
-          // "P.V(j-1) has retired" = the next, not yet consumed phase of the other S buffer
-          soft_block<DBG, POLY>(x, pk, j > 0, m_used, tO, sfull + (b ^ 1), (b ? sc0 : sc1) & 1, var);
+          // "P.V(j-1) has retired" = the next, not yet consumed phase of the S buffer block j-1 used (its commit follows
+          // [P.V(j-1), Q.K^T(j-1+NBUF)])
+          const int bp = b == 0 ? NBUF - 1 : b - 1;
+          soft_block<DBG, POLY, SB>(x, pk, j > 0, m_used, tO, sfull + bp, (bp == 0 ? sc0 : bp == 1 ? sc1 : sc2) & 1, var);
           if (!(var & 16)) {
             tmem_st_32x32b_x16(tS, pk);
-            tmem_st_32x32b_x8(tS + 16, pk + 16);
+            if constexpr (SB == 48) tmem_st_32x32b_x8(tS + 16, pk + 16);
           }
           tmem_st_wait();
           tcgen05_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(pfull + b);
           if (stamp && it < 16) dbg_stamp(dbg, 17 + w * 40 + 2 * it);
+          b = (b + 1 == NBUF) ? 0 : b + 1;
         }
-        // ---- epilogue: both S buffers signal once more (P.V(n-2), P.V(n-1) retired); O / rowsum -> bf16 -> global.
+        // ---- epilogue: every S buffer signals once more (the last NBUF P.V retired); O / rowsum -> bf16 -> global.
         // The next unit's P.V cannot start before this warpgroup has stored P of its first block, i.e. after O
         // has been read here.
         mbar_wait(sfull + 0, sc0 & 1);
         mbar_wait(sfull + 1, sc1 & 1);
         ++sc0; ++sc1;
+        if constexpr (NBUF == 3) {
+          mbar_wait(sfull + 2, sc2 & 1);
+          ++sc2;
+        }
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->o_free[w]);
         tcgen05_fence_after();
@@ -602,17 +622,17 @@ extern thread_local int g_dbg_cta;
 constexpr int ATTN_POLY_DEFAULT = 0;   // MDGEN_ATTN_POLY=3: every third exp2 on the FMA pipe -- measured SLOWER (216 -> 234 us on config 3:
                                        // the kernel is issue-bound, not MUFU-bound), kept for A/B runs
 
-template <bool DBG, int POLY>
+template <bool DBG, int POLY, int SB, int NBUF>
 inline cudaError_t launch_attention_tc_variant(const AttnParams<bf16>& p, int grid, int chunks, int nunits, int var, cudaStream_t st) {
   static DevOnce once;
   const int dev = cur_device();
   if (once.need(dev)) {
-    cudaError_t e = cudaFuncSetAttribute(atc::attention_tc_kernel<DBG, POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(atc::attention_tc_kernel<DBG, POLY, SB, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES);
     if (e != cudaSuccess) return e;
     once.done(dev);
   }
   MD_VARIANT(V_ATTN_TC);
-  atc::attention_tc_kernel<DBG, POLY><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, nunits, DBG ? g_dbg_buf : nullptr, g_dbg_cta, var);
+  atc::attention_tc_kernel<DBG, POLY, SB, NBUF><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, nunits, DBG ? g_dbg_buf : nullptr, g_dbg_cta, var);
   return cudaSuccess;
 }
 
@@ -626,12 +646,17 @@ inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStre
   const int grid = (int)(nunits < num_sms() ? nunits : num_sms());
   ProfScope ps(PC_ATTN_TC, st);
   const int var = g_sw.attn_var, poly = g_sw.attn_poly;
+  const bool v8 = g_sw.attn_sb == 32;       // <32, 3>: three S buffers of 32 keys; <48, 2>: v7
   if (g_dbg_buf || var) {
-    MD_CUDA((launch_attention_tc_variant<true, ATTN_POLY_DEFAULT>(p, grid, chunks, (int)nunits, var, st)));
+    if (v8) MD_CUDA((launch_attention_tc_variant<true, 0, 32, 3>(p, grid, chunks, (int)nunits, var, st)));
+    else MD_CUDA((launch_attention_tc_variant<true, 0, 48, 2>(p, grid, chunks, (int)nunits, var, st)));
+  } else if (v8) {
+    MD_CHECK(poly == 0, "MDGEN_ATTN_POLY is only built for the 48-key variant (MDGEN_ATTN_SB=48)");
+    MD_CUDA((launch_attention_tc_variant<false, 0, 32, 3>(p, grid, chunks, (int)nunits, 0, st)));
   } else {
     switch (poly) {
-      case 0: MD_CUDA((launch_attention_tc_variant<false, 0>(p, grid, chunks, (int)nunits, 0, st))); break;
-      case 3: MD_CUDA((launch_attention_tc_variant<false, 3>(p, grid, chunks, (int)nunits, 0, st))); break;
+      case 0: MD_CUDA((launch_attention_tc_variant<false, 0, 48, 2>(p, grid, chunks, (int)nunits, 0, st))); break;
+      case 3: MD_CUDA((launch_attention_tc_variant<false, 3, 48, 2>(p, grid, chunks, (int)nunits, 0, st))); break;
       default: MD_CHECK(false, "MDGEN_ATTN_POLY must be 0 or 3");
     }
   }

@@ -48,6 +48,7 @@ void read_switches() {
   s.attn_var = num("MDGEN_ATTN_VAR", 0);
   s.attn_poly = num("MDGEN_ATTN_POLY", 0);
   s.asb_seq = num("MDGEN_ASB_SEQ", 4);
+  s.attn_sb = num("MDGEN_ATTN_SB", 48);
   g_sw = s;
 }
 
@@ -1286,7 +1287,7 @@ static unsigned switches_hash() {
   unsigned hsh = 0;
   const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta};
   for (bool b : bits) hsh = (hsh << 1) | (b ? 1u : 0u);
-  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq);
+  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009);
 }
 
 static void rollout_graph_drop(MdgenHandle* h) {
