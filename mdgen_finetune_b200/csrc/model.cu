@@ -20,6 +20,7 @@
 #include "gemm_tc.cuh"
 #include "gemm_tc2.cuh"
 #include "gemm_ln.cuh"
+#include "gemm_qkv_attn.cuh"
 #include "ipa.cuh"
 
 namespace mdgen {
@@ -45,6 +46,7 @@ void read_switches() {
   s.no_attn_bulk = on("MDGEN_NO_ATTN_BULK");
   s.gelu_2cta = on("MDGEN_GELU_2CTA");
   s.no_graph = on("MDGEN_NO_GRAPH");
+  s.no_qkv_attn = on("MDGEN_NO_QKV_ATTN");
   s.attn_var = num("MDGEN_ATTN_VAR", 0);
   s.attn_poly = num("MDGEN_ATTN_POLY", 0);
   s.asb_seq = num("MDGEN_ASB_SEQ", 4);
@@ -230,6 +232,13 @@ static int launch_tc_bn(const CUtensorMap& ta, const CUtensorMap& tw, const CUte
   return -1;
 }
 
+struct MhaW_view {     // what launch_qkv_attn4 needs of an MhaW (declared before the handle types)
+  const bf16* wp;
+  const float* bp;
+  const float* bias_k;
+  const float* bias_v;
+};
+
 // C = A[M,K] . W[N,K]^T on tcgen05.  block_n = 0 picks a tile width from the problem shape.
 int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N, int K, int epi, bool out_bf16,
                    const EpiParams& ep, int block_n, cudaStream_t st) {
@@ -280,6 +289,39 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
   return -1;
 }
 
+// q/k/v projection + residue-axis attention at L = 4 in one kernel (gemm_qkv_attn.cuh).  Returns 1 when the shape is not
+// supported (caller falls back to the qkv GEMM + stand-alone attention kernel).
+int launch_qkv_attn4(const bf16* A, int lda, const MhaW_view& m, int M, int K, int H, bf16* att, int ldo,
+                     const float* key_valid, int mask_mod, const float* cs, const float* sn, cudaStream_t st) {
+  auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
+  if (g_sw.no_qkv_attn || !m.wp || M < 1024 || M % tqa::SEQ != 0 || H > 16 || K % tc::BLOCK_K != 0 || !al16(att) || ldo % 8 != 0)
+    return 1;
+  MD_SMEM_ONCE(tqa::gemm_qkv_attn4_kernel, tqa::SMEM_BYTES);
+  MD_VARIANT(V_QKV_ATTN);
+  const int num_n = tqa::num_n_tiles(H);
+  CUtensorMap ta, tw;
+  MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
+  MD_TRY(make_tmap_2d(&tw, m.wp, num_n * tqa::TILE_N, K, K, tqa::HALF_N));
+  tqa::Params p;
+  p.att = att;
+  p.ldo = ldo;
+  p.bias = m.bp;
+  p.bias_k = m.bias_k;
+  p.bias_v = m.bias_v;
+  p.key_valid = key_valid;
+  p.mask_mod = mask_mod;
+  p.cs = cs;
+  p.sn = sn;
+  p.H = H;
+  const int tiles = ((M + tqa::TILE_M - 1) / tqa::TILE_M) * num_n, pairs = num_sms() / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  ProfScope ps(PC_GEMM_TC, st);
+  tqa::gemm_qkv_attn4_kernel<<<grid, tqa::THREADS, tqa::SMEM_BYTES, st>>>(ta, tw, M, K, num_n, p);
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // =============================================================================================
 // handle
 // =============================================================================================
@@ -309,6 +351,8 @@ struct MhaW {
   LinearW qkv, out;
   const float* bias_k = nullptr;
   const float* bias_v = nullptr;
+  const bf16* qkv_hm = nullptr;        // head-major packed q|k|v weight of gemm_qkv_attn.cuh (residue axis of the main layers)
+  const float* qkv_hm_bias = nullptr;
 };
 
 struct IpaLayerW {
@@ -478,7 +522,7 @@ static int copy_scaled(const float* src, float* dst, size_t n, float s, cudaStre
 }
 
 // fused [q*d^-0.5 | k | v] projection (mha.py:260-263) + out_proj + bias_k/bias_v
-static int pack_mha(MdgenHandle* h, const std::string& p, MhaW* m, cudaStream_t st) {
+static int pack_mha(MdgenHandle* h, const std::string& p, MhaW* m, cudaStream_t st, bool head_major = false) {
   const int C = h->C();
   const float scaling = 1.0f / sqrtf((float)(C / h->cfg.mha_heads));
   NEED_W(qw, p + ".attn.q_proj.weight");
@@ -506,6 +550,17 @@ static int pack_mha(MdgenHandle* h, const std::string& p, MhaW* m, cudaStream_t 
   MD_TRY(pack_linear(h, p + ".attn.out_proj", &m->out, h->bf16_mode(), st));
   m->bias_k = bk->d;
   m->bias_v = bv->d;
+  if (head_major && h->bf16_mode() && h->cfg.mha_heads <= 16) {       // gemm_qkv_attn.cuh: [q_h | k_h | v_h] per head, 3 heads per tile
+    const int rows = tqa::num_n_tiles(h->cfg.mha_heads) * tqa::TILE_N;
+    bf16* wp;
+    float* bp;
+    MD_TRY(dev_alloc(h, (void**)&wp, (size_t)rows * C * sizeof(bf16), true));
+    MD_TRY(dev_alloc(h, (void**)&bp, (size_t)rows * 4, true));
+    tqa::pack_qkv_headmajor_kernel<<<(unsigned)(((size_t)rows * C + 255) / 256), 256, 0, st>>>(w, b, h->cfg.mha_heads, C, wp, bp, rows);
+    MD_CUDA(cudaGetLastError());
+    m->qkv_hm = wp;
+    m->qkv_hm_bias = bp;
+  }
   return 0;
 }
 
@@ -577,7 +632,7 @@ static int finalize_weights(MdgenHandle* h, cudaStream_t st) {
     const std::string p = "layers." + std::to_string(i);
     L.ada_off = off;
     MD_TRY(put_ada(p + ".adaLN_modulation.1", 9 * C));
-    MD_TRY(pack_mha(h, p + ".mha_l", &L.mha_l, st));
+    MD_TRY(pack_mha(h, p + ".mha_l", &L.mha_l, st, true));
     MD_TRY(pack_mha(h, p + ".mha_t", &L.mha_t, st));
     MD_TRY(pack_linear(h, p + ".fc1", &L.fc1, bfm, st));
     MD_TRY(pack_linear(h, p + ".fc2", &L.fc2, bfm, st));
@@ -898,11 +953,25 @@ struct Fwd {
     const float* scale = ada_row + (size_t)(chunk0 + 1) * C;
     const float* gate = ada_row + (size_t)(chunk0 + 2) * C;
     if (!h_ready) MD_TRY(lnmod(x, (AT*)h->hbuf, M, shift, scale, rows_per_batch, nbatch));
-    EpiParams e1;
-    e1.out = h->qkv;
-    e1.ldo = 3 * C;
-    MD_TRY(gemm((const AT*)h->hbuf, C, m.qkv, M, EPI_STORE, e1, true));
-    MD_TRY(attention(m, nb, S, inner, key_valid, mask_mod, frame_axis));
+    bool fused = false;
+    if constexpr (sizeof(AT) == 2) {
+      // residue axis of the 4AA configs: projection + 4 x 5 attention in one kernel, qkv never reaches HBM
+      if (!frame_axis && S == tqa::SEQ && inner == 1 && hd == tqa::HD && m.qkv_hm) {
+        const bool rope = !h->flag(MDGEN_F_NO_ROPE);
+        const MhaW_view v{m.qkv_hm, m.qkv_hm_bias, m.bias_k, m.bias_v};
+        const int r = launch_qkv_attn4((const bf16*)h->hbuf, C, v, M, C, H, (bf16*)h->att, C, key_valid, mask_mod,
+                                       rope ? h->rope_l_cs : nullptr, rope ? h->rope_l_sn : nullptr, st);
+        if (r < 0) return r;
+        fused = r == 0;
+      }
+    }
+    if (!fused) {
+      EpiParams e1;
+      e1.out = h->qkv;
+      e1.ldo = 3 * C;
+      MD_TRY(gemm((const AT*)h->hbuf, C, m.qkv, M, EPI_STORE, e1, true));
+      MD_TRY(attention(m, nb, S, inner, key_valid, mask_mod, frame_axis));
+    }
     EpiParams e2;
     e2.resid = x;
     e2.ldr = C;
@@ -1285,7 +1354,8 @@ static void l2_window_clear(cudaStream_t st) {
 static unsigned switches_hash() {
   const Switches& s = g_sw;
   unsigned hsh = 0;
-  const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta};
+  const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta,
+                       s.no_qkv_attn};
   for (bool b : bits) hsh = (hsh << 1) | (b ? 1u : 0u);
   return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009);
 }

@@ -262,11 +262,12 @@ def test_full_size_velocity_and_short_rollout_vs_reference(name, prec):
         if N >= 74 * 256:
             assert used["gemm_tc2"] > 0, used             # CTA-pair kernel (cta_group::2)
         if c["L"] == 4:
-            assert used["attention_seq4"] > 0, used
+            assert used["attention_seq4"] > 0, used       # the IPA layers' residue-axis attention (few rows)
+            assert used["qkv_attn4"] > 0, used            # main layers: q/k/v projection fused with the 4 x 5 attention
 
 
 @pytest.mark.parametrize("switch", ["MDGEN_NO_GEMM_LN", "MDGEN_NO_GEMM_2CTA", "MDGEN_NO_GEMM_WS", "MDGEN_NO_L2_PERSIST",
-                                    "MDGEN_NO_GRAPH"])
+                                    "MDGEN_NO_GRAPH", "MDGEN_NO_QKV_ATTN"])
 def test_config3_kernel_variants_agree(switch, monkeypatch):
     """Every variant switch of DESIGN.md section 2 must leave the config-3 result within bf16 rounding of the default
     dispatch and within the north_star tolerance of the reference golden."""
