@@ -26,54 +26,73 @@ __device__ __forceinline__ void apply_epilogue(int epi, const EpiParams& p, int 
   }
 }
 
-constexpr int SG_BM = 64, SG_BN = 64, SG_BK = 16;
+constexpr int SG_BK = 32;
 
-template <typename AT, typename OT>
+// BT x BT output tile per block of 256 threads (16 x 16 thread grid, (BT / 16)^2 outputs per thread), BT = 64 or 32.
+// The operand tiles of step k + 1 are loaded from global memory into registers BEFORE the FMAs of step k (register double
+// buffering), and problems too small to fill the machine with 64 x 64 tiles run on 32 x 32 tiles: the skinny GEMMs this
+// kernel serves in the product path (IPA projections of a few hundred rows, K = 384) were 44 blocks on 148 SMs paying the
+// load latency serially at every k step (38 us per launch on config 4, whose design sampler issues 15 of them per step).
+template <typename AT, typename OT, int BT>
 __global__ void __launch_bounds__(256)
 gemm_simt_kernel(const AT* __restrict__ A, int lda, const float* __restrict__ W, int ldw, int M, int N,
                  int K, int epi, EpiParams p) {
-  __shared__ float As[SG_BK][SG_BM + 4];
-  __shared__ float Ws[SG_BK][SG_BN + 4];
+  constexpr int TM = BT / 16;                      // outputs per thread along m and n
+  __shared__ __align__(16) float As[SG_BK][BT + 4];
+  __shared__ __align__(16) float Ws[SG_BK][BT + 4];
   const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
-  const int m0 = blockIdx.y * SG_BM, n0 = blockIdx.x * SG_BN;
-  float acc[4][4];
+  const int m0 = blockIdx.y * BT, n0 = blockIdx.x * BT;
+  float acc[TM][TM];
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < TM; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < TM; ++j) acc[i][j] = 0.f;
 
-  // each thread loads 4 elements of A and 4 of W per k-tile: row = tid/4, kk = (tid%4)*4..+3
-  const int lr = threadIdx.x / 4, lk = (threadIdx.x % 4) * 4;
+  // each thread loads PT consecutive k of one A row and one W row per step
+  constexpr int PT = BT * SG_BK / 256, TPR = SG_BK / PT;
+  const int lr = threadIdx.x / TPR, lk = (threadIdx.x % TPR) * PT;
+  const int am = m0 + lr, wn = n0 + lr;
+  const AT* arow = A + (size_t)(am < M ? am : 0) * lda;
+  const float* wrow = W + (size_t)(wn < N ? wn : 0) * ldw;
+  float ra[PT], rw[PT];
+  auto fetch = [&](int k0) {
+#pragma unroll
+    for (int e = 0; e < PT; ++e) {
+      const int k = k0 + lk + e;
+      ra[e] = (am < M && k < K) ? to_f(arow[k]) : 0.f;
+      rw[e] = (wn < N && k < K) ? wrow[k] : 0.f;
+    }
+  };
+  fetch(0);
   for (int k0 = 0; k0 < K; k0 += SG_BK) {
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      int k = k0 + lk + e;
-      int m = m0 + lr, n = n0 + lr;
-      As[lk + e][lr] = (m < M && k < K) ? to_f(A[(size_t)m * lda + k]) : 0.f;
-      Ws[lk + e][lr] = (n < N && k < K) ? W[(size_t)n * ldw + k] : 0.f;
+    for (int e = 0; e < PT; ++e) {
+      As[lk + e][lr] = ra[e];
+      Ws[lk + e][lr] = rw[e];
     }
     __syncthreads();
+    if (k0 + SG_BK < K) fetch(k0 + SG_BK);          // in flight during the FMAs below
 #pragma unroll
     for (int kk = 0; kk < SG_BK; ++kk) {
-      float a[4], w[4];
+      float a[TM], w[TM];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+      for (int i = 0; i < TM; ++i) a[i] = As[kk][ty * TM + i];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) w[j] = Ws[kk][tx * 4 + j];
+      for (int j = 0; j < TM; ++j) w[j] = Ws[kk][tx * TM + j];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < TM; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+        for (int j = 0; j < TM; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    int m = m0 + ty * 4 + i;
+  for (int i = 0; i < TM; ++i) {
+    int m = m0 + ty * TM + i;
     if (m >= M) continue;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      int n = n0 + tx * 4 + j;
+    for (int j = 0; j < TM; ++j) {
+      int n = n0 + tx * TM + j;
       if (n < N) apply_epilogue<OT>(epi, p, m, n, acc[i][j]);
     }
   }
@@ -84,8 +103,14 @@ inline int launch_gemm_simt(const AT* A, int lda, const float* W, int ldw, int M
                             const EpiParams& p, cudaStream_t st) {
   if (M <= 0 || N <= 0) return 0;
   ProfScope ps(PC_GEMM_SIMT, st);
-  dim3 grid((N + SG_BN - 1) / SG_BN, (M + SG_BM - 1) / SG_BM);
-  gemm_simt_kernel<AT, OT><<<grid, 256, 0, st>>>(A, lda, W, ldw, M, N, K, epi, p);
+  const long t64 = (long)((N + 63) / 64) * ((M + 63) / 64);
+  if (t64 >= 148) {
+    dim3 grid((N + 63) / 64, (M + 63) / 64);
+    gemm_simt_kernel<AT, OT, 64><<<grid, 256, 0, st>>>(A, lda, W, ldw, M, N, K, epi, p);
+  } else {                                           // too few 64 x 64 tiles to fill the machine
+    dim3 grid((N + 31) / 32, (M + 31) / 32);
+    gemm_simt_kernel<AT, OT, 32><<<grid, 256, 0, st>>>(A, lda, W, ldw, M, N, K, epi, p);
+  }
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;

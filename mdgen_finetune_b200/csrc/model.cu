@@ -1025,7 +1025,8 @@ static int rowvec(cudaStream_t st, const float* x, int ldx, int R, const float* 
 // fp32 linear for the IPA geometry path: warp-per-output kernel for skinny M, tiled SIMT GEMM otherwise
 static int linear_f32(cudaStream_t st, const float* A, int lda, const LinearW& w, int M, float* out, int ldo,
                       bool accumulate) {
-  if (M <= 128) return rowvec(st, A, lda, M, w.w, w.K, w.b, w.N, out, ldo, 0, 0, accumulate ? 1 : 0);
+  // the warp-per-output kernel walks the rows serially: only for a handful of rows (77 us at 128 rows on config 4)
+  if (M <= 16) return rowvec(st, A, lda, M, w.w, w.K, w.b, w.N, out, ldo, 0, 0, accumulate ? 1 : 0);
   EpiParams e;
   e.bias = w.b;
   if (accumulate) {
@@ -1045,10 +1046,14 @@ static int linear_f32(cudaStream_t st, const float* A, int lda, const LinearW& w
 // None of this depends on x (except design's x_d, which forces nt == 1), so a sampler call does it
 // ONCE for all its steps instead of once per step.
 template <typename AT>
-static int time_tables(Fwd<AT>& f, const float* t, int nt, const float* x_for_design) {
+static int ipa_stack(Fwd<AT>& f, int nt, const float* ada_base, const float* x_for_design);
+
+// State-independent part: timestep embedding and every adaLN modulation row for `nt` time rows (t ordered (step, b)).
+template <typename AT>
+static int time_embed(Fwd<AT>& f, const float* t, int nt) {
   MdgenHandle* h = f.h;
   cudaStream_t st = f.st;
-  const int C = f.C, B = h->B, T = h->T, L = h->L, BL = B * L, R = nt * B;
+  const int C = f.C, B = h->B, R = nt * B;
   MD_CHECK(nt >= 1 && nt <= h->nt_cap, "time_tables: scratch too small");
   const Tensor* w0 = find_w(h, "t_embedder.mlp.0.weight");
   const Tensor* b0 = find_w(h, "t_embedder.mlp.0.bias");
@@ -1081,6 +1086,24 @@ static int time_tables(Fwd<AT>& f, const float* t, int nt, const float* x_for_de
     MD_TRY((launch_gemm_simt<float, float>(h->th1, C, h->ada_w, C, R, h->ada_cols, C, EPI_STORE, e, st)));
   }
   h->nt_cur = nt;
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <typename AT>
+static int time_tables(Fwd<AT>& f, const float* t, int nt, const float* x_for_design) {
+  MD_TRY(time_embed<AT>(f, t, nt));
+  return ipa_stack<AT>(f, nt, f.h->ada, x_for_design);
+}
+
+// The prepended IPA stack (run_ipa) for `nt` time rows whose adaLN rows start at `ada_base` ([nt * B, ada_cols]); writes
+// ipa_out rows [0, nt * B * L).  Design mode: x_d = mean_T x[..., -20:] enters the stack's input, so the sampler calls this
+// once per step (nt = 1, ada_base = the step's rows of the table time_embed built for ALL steps).
+template <typename AT>
+static int ipa_stack(Fwd<AT>& f, int nt, const float* ada_base, const float* x_for_design) {
+  MdgenHandle* h = f.h;
+  cudaStream_t st = f.st;
+  const int C = f.C, B = h->B, T = h->T, L = h->L, BL = B * L, R = nt * B;
   if (!h->flag(MDGEN_F_PREPEND_IPA)) return 0;
   const int ntBL = nt * BL, M = h->streams * ntBL;
   const IpaDims d{h->cfg.ipa_heads, h->cfg.ipa_head_dim, h->cfg.ipa_qk, h->cfg.ipa_v};
@@ -1105,7 +1128,7 @@ static int time_tables(Fwd<AT>& f, const float* t, int nt, const float* x_for_de
   // ---- layers
   for (size_t i = 0; i < h->ipa.size(); ++i) {
     const IpaLayerW& Lw = h->ipa[i];
-    const float* ada_row = h->ada + Lw.ada_off;
+    const float* ada_row = ada_base + Lw.ada_off;
     {
       ProfScope ps(PC_LN, st);
       ln_modulate_kernel<float, 384><<<((M + LN_ROWS - 1) / LN_ROWS * 32 + 255) / 256, 256, 0, st>>>(h->ipa_s, h->ipa_n, M, nullptr, nullptr, 0, 1, 1,
@@ -1176,7 +1199,7 @@ static int ensure_emb_static(MdgenHandle* h, cudaStream_t st) {
 // If `state` != null the final epilogue also does state += dt * v (the Euler step fused into the
 // last projection; SURVEY Q4: no clamp on conditioned frames).
 template <typename AT>
-static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state, float dt) {
+static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state, float dt, int ipa_step = -1) {
   MdgenHandle* h = f.h;
   cudaStream_t st = f.st;
   const int C = f.C, B = h->B, T = h->T, L = h->L, D = h->D(), Dc = h->Dc();
@@ -1184,7 +1207,8 @@ static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state,
   MD_CHECK(step >= 0 && step < h->nt_cur, "trunk: time row out of range");
   const float* ada = h->ada + (size_t)step * B * h->ada_cols;
   const bool pre = h->flag(MDGEN_F_PREPEND_IPA);
-  const float* ipa_out = pre ? h->ipa_out + (size_t)step * B * L * C : nullptr;
+  if (ipa_step < 0) ipa_step = step;      // design sampler: adaLN rows of `step`, IPA output rebuilt into row 0
+  const float* ipa_out = pre ? h->ipa_out + (size_t)ipa_step * B * L * C : nullptr;
   // ---- token embedding (latent_model.py:242-255)
   {
     MD_TRY(ensure_emb_static(h, st));
@@ -1295,16 +1319,18 @@ static int rollout_impl(MdgenHandle* h, float* state, int num_steps, float* traj
   time_grid_kernel<<<(nt * B + 127) / 128, 128, 0, st>>>(h->tbuf, nt, B, num_steps);
   MD_LAUNCHED();
   // design mode: the IPA input embeds x_d = mean_T x[..., -20:], so the time tables are rebuilt from the state at every step
+  // (the timestep MLP and the adaLN table do not: they are built for all steps at once in either mode)
   const bool design = h->flag(MDGEN_F_DESIGN);
-  if (!design) MD_TRY(time_tables<AT>(f, h->tbuf, nt, nullptr));
+  MD_TRY(time_embed<AT>(f, h->tbuf, nt));
+  if (!design) MD_TRY(ipa_stack<AT>(f, nt, h->ada, nullptr));
   for (int i = 0; i < nt; ++i) {
     const long long l0 = g_launches;
     const float dt = linspace01(i + 1, num_steps) - linspace01(i, num_steps);
     if (design) {
-      MD_TRY(time_tables<AT>(f, h->tbuf + (size_t)i * B, 1, state));
+      MD_TRY(ipa_stack<AT>(f, 1, h->ada + (size_t)i * B * h->ada_cols, state));
       h->dflow_step = i;
     }
-    MD_TRY(trunk<AT>(f, state, design ? 0 : i, h->vel, state, dt));
+    MD_TRY(trunk<AT>(f, state, i, h->vel, state, dt, design ? 0 : i));
     h->launches_last_forward = (int)(g_launches - l0);
     if (traj) MD_CUDA(cudaMemcpyAsync(traj + (size_t)(i + 1) * n, state, n * 4, cudaMemcpyDeviceToDevice, st));
   }
