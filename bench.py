@@ -169,8 +169,12 @@ def algorithmic_flops(c):
     gemm = 5 * 32 * N * C * C + 2 * N * C * D + 5 * (8 * M * C * C + 4 * M * C * F)
     if c["task"] == "design":
         gemm += 2 * N * C * C
+    qkv_l = 5 * 6 * N * C * C                      # the residue-axis q/k/v projections of the 5 main layers
+    res_main = 5 * 4 * B * T * L * (L + 1) * C     # residue-axis attention of the main layers
     return {"gemm_tcgen05": float(gemm), "attention_frame": float(5 * 4 * B * L * T * (T + 1) * C),
-            "attention_residue": float(5 * 4 * B * T * L * (L + 1) * C + 5 * 4 * M * (L + 1) * C)}
+            "attention_residue": float(res_main + 5 * 4 * M * (L + 1) * C),
+            # gemm_qkv_attn4_kernel (L = 4): projection + 4 x 5 attention in one launch; its FLOPs leave the GEMM family
+            "qkv_attention_fused": float(qkv_l + res_main), "qkv_l": float(qkv_l)}
 
 
 def run_reference(a, rank, world):
@@ -350,7 +354,7 @@ def run_gpu(a, rank, world, local_rank):
     parity = float((v_bf16.double() - v_f32.double()).norm() / v_f32.double().norm())
     del m32, v_f32
     torch.cuda.empty_cache()
-    if not (torch.isfinite(v_bf16).all() and torch.isfinite(rollout()).all() and parity < 2e-2):
+    if not a.no_parity_check and not (torch.isfinite(v_bf16).all() and torch.isfinite(rollout()).all() and parity < 2e-2):
         raise SystemExit(f"bench.py: parity check failed (rel-L2 bf16 vs fp32 check mode = {parity})")
     rollout()
     torch.cuda.synchronize(dev)
@@ -418,8 +422,10 @@ def run_gpu(a, rank, world, local_rank):
     nev = NUM_STEPS - 1
     kernels = {k: {"ms_per_step": round(v[0], 3), "launches": v[1], "share": round(v[0] / total_prof, 4)} for k, v in prof.items()}
     dom = max(prof, key=lambda k: prof[k][0])
-    flop_of = {"gemm_tcgen05": fl["gemm_tcgen05"], "attention_tcgen05": fl["attention_frame"],
-               "attention_simt": fl["attention_frame"], "attention_short": fl["attention_residue"]}
+    fused = "qkv_attention_fused" in prof
+    flop_of = {"gemm_tcgen05": fl["gemm_tcgen05"] - (fl["qkv_l"] if fused else 0.0), "attention_tcgen05": fl["attention_frame"],
+               "attention_simt": fl["attention_frame"], "attention_short": fl["attention_residue"],
+               "qkv_attention_fused": fl["qkv_attention_fused"]}
     roof = {"bound": "tensor", "kernel": dom, "unit": "TFLOP/s", "peak": pk["tflops"], "peak_source": pk["src"] + " (sustained cuBLAS bf16)",
             "traffic": ncu_traffic(dom, a.config)}
     if dom.startswith("attention"):
@@ -432,7 +438,7 @@ def run_gpu(a, rank, world, local_rank):
                     algorithmic_gflop_per_launch=flop_of[dom] * nev / n / 1e9)
     else:
         roof.update(achieved=None, frac=None)
-    for other in ("gemm_tcgen05", "attention_tcgen05"):      # the second-largest family, same definition
+    for other in ("gemm_tcgen05", "attention_tcgen05", "qkv_attention_fused"):      # the other tensor-core families, same definition
         if other in prof and dom != other:
             t_ms, n = prof[other]
             g = flop_of[other] * nev / (t_ms * 1e-3) / 1e12
@@ -490,6 +496,8 @@ def main():
     ap.add_argument("--config", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
     ap.add_argument("--no-other-configs", dest="no_other_configs", action="store_true")
+    ap.add_argument("--no-parity-check", dest="no_parity_check", action="store_true",
+                    help="kernel timing experiments that break the results on purpose (MDGEN_ATTN_VAR); never for a reported number")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: every rank its own full batch (default); strong: the config's one batch sharded over the ranks")
     a = ap.parse_args()

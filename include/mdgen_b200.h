@@ -186,7 +186,7 @@ long long mdgen_variant_launches(int32_t which);
 int64_t mdgen_workspace_bytes(MdgenHandle* h);
 
 /* Per-kernel-family device timing (CUDA events on the launching stream) for bench.py's roofline:
- * between begin and end every launch of the library is bracketed by two events.  ncat <= 10. */
+ * between begin and end every launch of the library is bracketed by two events.  ncat <= 11. */
 int mdgen_profile_begin(void);
 int mdgen_profile_end(float* ms_by_cat, int32_t* launches_by_cat, int32_t ncat);
 const char* mdgen_profile_category_name(int32_t i);

@@ -120,7 +120,7 @@ def check(status, what="mdgen"):
     raise RuntimeError(f"{what} failed ({status}): {msg}")
 
 
-NCAT = 10
+NCAT = 11
 
 
 def profile_begin():

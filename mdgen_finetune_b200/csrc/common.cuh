@@ -78,7 +78,7 @@ extern std::atomic<long long> g_variant[V_COUNT];
 
 // optional per-kernel-family timing with CUDA events on the launching stream (bench.py roofline)
 enum ProfCat : int { PC_GEMM_TC = 0, PC_GEMM_SIMT, PC_ATTN_TC, PC_ATTN_SIMT, PC_ATTN_SHORT, PC_LN, PC_EMBED, PC_IPA,
-                     PC_ADALN, PC_MISC, PC_COUNT };
+                     PC_ADALN, PC_MISC, PC_QKV_ATTN, PC_COUNT };
 struct ProfRec { int cat; cudaEvent_t a, b; };
 struct Profiler {
   bool on = false;

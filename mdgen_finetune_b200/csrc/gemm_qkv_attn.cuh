@@ -8,10 +8,11 @@
 //   * the packed weight is HEAD-MAJOR: tile t holds heads 3t .. 3t+2 as [q_h | k_h | v_h] = 72 rows each (q rows pre-scaled
 //     by d^-0.5 like every packed qkv weight), padded to N = 224 (an MMA N for M = 256); 6 tiles cover the 16 heads;
 //   * 12 epilogue warps per CTA: TMEM lane quarter = warp % 4, head of the tile = (warp - 2) / 4.  A thread owns one token
-//     row and one head: tcgen05.ld brings its q, k, v (72 fp32), the 4 rows of a sequence are 4 consecutive lanes, so the
-//     other tokens' k / v arrive through 4-lane shuffles (packed bf16x2, the precision the stand-alone kernel stages K / V
-//     in); RoPE from a shared-memory table (position = row % 4; the bias token sits at position 4), key padding, the
-//     4 x 5 fp32 softmax and P.V run in registers; 48 bytes per (row, head) are stored.
+//     row and one head: tcgen05.ld brings its q, k, v (72 fp32); the 4 rows of a sequence are 4 consecutive lanes, which
+//     exchange their (rotated) k and v rows in fp32 through a per-warp shared-memory tile read back with 128-bit loads
+//     (a first version exchanged packed bf16x2 through 96 shuffles and spent twice the instructions on pack / unpack);
+//     RoPE from a shared-memory table (position = row % 4; the bias token sits at position 4), key padding, the 4 x 5 fp32
+//     softmax and P.V run in registers; 48 bytes per (row, head) are stored.
 #pragma once
 #include "gemm_tc2.cuh"
 
@@ -31,18 +32,22 @@ constexpr int HD = 24, HEADS_PER_TILE = 3, HEAD_COLS = 3 * HD;       // 72 accum
 constexpr int TILE_M = 256, TILE_N = 224, HALF_N = TILE_N / 2;         // 216 live columns + 8 zero rows of padding
 constexpr int ACC_STRIDE = 256;                                        // TMEM columns per accumulator stage
 constexpr int EPI_WARPS = 4 * HEADS_PER_TILE, THREADS = 64 + 32 * EPI_WARPS;
-constexpr int STAGES = 5;
+constexpr int STAGES = 4;                                              // (the kernel is epilogue-bound: the ring gives room to the exchange area)
 constexpr int STAGE_BYTES = A_STAGE_BYTES + HALF_N * BLOCK_K * 2;      // 16 KB + 14 KB
 static_assert(STAGE_BYTES % 1024 == 0, "SWIZZLE_128B operand tiles start on 1024-byte boundaries");
 constexpr int SEQ = 4;                                                 // tokens per sequence (L)
 // shared memory behind the operand ring: barriers | tmem slot | rope cos / sin [5][12] | bias_k rotated to position 4 [H][24]
-// | bias_v [H][24] | projection bias of the current tile's head, one copy per epilogue warp [12][72]
+// | bias_v [H][24] | the packed projection bias [6][224] | k / v exchange tiles
 constexpr int OFF_BAR = STAGES * STAGE_BYTES;
 constexpr int OFF_ROPE = OFF_BAR + 256;
 constexpr int OFF_BK = OFF_ROPE + 2 * (SEQ + 1) * (HD / 2) * 4;
 constexpr int OFF_BV = OFF_BK + 16 * HD * 4;
-constexpr int OFF_BIAS = OFF_BV + 16 * HD * 4;                         // per epilogue warp: the 72 projection biases of its head
-constexpr int SMEM_BYTES = OFF_BIAS + EPI_WARPS * HEAD_COLS * 4 + 64;
+constexpr int MAX_N_TILES = 6;                                         // 16 heads
+constexpr int OFF_BIAS = OFF_BV + 16 * HD * 4;                         // the whole packed projection bias [6 tiles][224], staged once
+// k / v exchange: per epilogue warp 32 rows x [k 24 | v 24] fp32, row pitch 208 B (rows 4 apart land in different banks)
+constexpr int XCH_PITCH = 208, XCH_WARP_BYTES = 32 * XCH_PITCH;
+constexpr int OFF_XCH = (OFF_BIAS + MAX_N_TILES * TILE_N * 4 + 15) / 16 * 16;
+constexpr int SMEM_BYTES = OFF_XCH + EPI_WARPS * XCH_WARP_BYTES + 64;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
 __host__ __device__ constexpr int num_n_tiles(int heads) { return (heads + HEADS_PER_TILE - 1) / HEADS_PER_TILE; }
@@ -58,6 +63,7 @@ struct Params {
   const float* cs;           // RoPE tables [5][12] (positions 0..4) or null
   const float* sn;
   int H;
+  int dbg_skip;              // timing experiment (MDGEN_ATTN_VAR bit 32): 1 = epilogue releases TMEM and stores nothing
 };
 
 __device__ __forceinline__ void tmem_ld_32x32b_x8(uint32_t taddr, uint32_t* r) {
@@ -69,8 +75,6 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-__device__ __forceinline__ float lo_f(uint32_t w) { return __uint_as_float(w << 16); }
-__device__ __forceinline__ float hi_f(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 // v[0..23] = acc + bias (bias through 128-bit shared-memory loads), then rotate_half pairing (i, i + 12) with the cos / sin
 // rows of the token's position held in registers
 __device__ __forceinline__ void bias_rope24(const uint32_t* acc, const float4* bias4, const float4* c4, const float4* s4,
@@ -113,12 +117,13 @@ __device__ __forceinline__ void tmem_ld24(uint32_t taddr, uint32_t* r) {
   tmem_ld_32x32b_x8(taddr + 16, r + 16);
 }
 
-// `taddr` = TMEM address of the head's 72 columns in this thread's lane; `release` is called once the accumulator has
-// been read completely (the caller hands the TMEM stage back to the MMA issuer there).
+// `taddr` = TMEM address of the head's 72 columns in this thread's lane; `xch` = the warp's exchange tile; `release` is
+// called once the accumulator has been read completely (the caller hands the TMEM stage back to the MMA issuer there).
+// All 32 lanes of the warp must call it.
 template <typename Release>
 __device__ __forceinline__ void attend_row(uint32_t taddr, const float* bias, const float* cs, const float* sn,
                                            const float* bias_kr, const float* bias_vs, float valid, int lane, bool rope,
-                                           float* out, Release release) {
+                                           uint8_t* xch, float* out, Release release) {
   const int t = lane & 3, base = lane & ~3;
   const float4* bias4 = reinterpret_cast<const float4*>(bias);
   float4 c4[3], s4[3];
@@ -127,44 +132,48 @@ __device__ __forceinline__ void attend_row(uint32_t taddr, const float* bias, co
     c4[g] = reinterpret_cast<const float4*>(cs + t * (HD / 2))[g];
     s4[g] = reinterpret_cast<const float4*>(sn + t * (HD / 2))[g];
   }
-  uint32_t kp[HD / 2], vp[HD / 2];
+  float4* mine = reinterpret_cast<float4*>(xch + lane * XCH_PITCH);
   float q[HD];
   {
     uint32_t acc[HD], accv[HD];
     tmem_ld24(taddr + HD, acc);          // k
     tmem_ld24(taddr + 2 * HD, accv);     // v (in flight while k is rotated)
     tmem_ld_wait();
+    __syncwarp();                        // every lane has finished reading the previous tile's exchange rows
     {
       float k[HD];
       bias_rope24(acc, bias4 + HD / 4, c4, s4, rope, k);
 #pragma unroll
-      for (int i = 0; i < HD / 2; ++i) kp[i] = pack2(k[2 * i], k[2 * i + 1]);
+      for (int g = 0; g < HD / 4; ++g) mine[g] = make_float4(k[4 * g], k[4 * g + 1], k[4 * g + 2], k[4 * g + 3]);
     }
-    tmem_ld24(taddr, acc);               // q (in flight while v is packed)
+    tmem_ld24(taddr, acc);               // q (in flight while v is stored)
 #pragma unroll
     for (int g = 0; g < HD / 4; ++g) {
       const float4 b = bias4[2 * (HD / 4) + g];
-      vp[2 * g] = pack2(__uint_as_float(accv[4 * g]) + b.x, __uint_as_float(accv[4 * g + 1]) + b.y);
-      vp[2 * g + 1] = pack2(__uint_as_float(accv[4 * g + 2]) + b.z, __uint_as_float(accv[4 * g + 3]) + b.w);
+      mine[HD / 4 + g] = make_float4(__uint_as_float(accv[4 * g]) + b.x, __uint_as_float(accv[4 * g + 1]) + b.y,
+                                     __uint_as_float(accv[4 * g + 2]) + b.z, __uint_as_float(accv[4 * g + 3]) + b.w);
     }
     tmem_ld_wait();
     release();
     bias_rope24(acc, bias4, c4, s4, rope, q);
   }
+  __syncwarp();                          // the 4 rows of every sequence are visible
   // ---- scores against the 4 tokens of the sequence and the bias token; fp32 softmax (mha.py:359-381)
-  float se[SEQ] = {0.f, 0.f, 0.f, 0.f}, so[SEQ] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-  for (int i = 0; i < HD / 2; ++i) {
-    uint32_t w[SEQ];
-#pragma unroll
-    for (int j = 0; j < SEQ; ++j) w[j] = __shfl_sync(0xffffffffu, kp[i], base + j);
-#pragma unroll
-    for (int j = 0; j < SEQ; ++j) {
-      se[j] = fmaf(q[2 * i], lo_f(w[j]), se[j]);
-      so[j] = fmaf(q[2 * i + 1], hi_f(w[j]), so[j]);
-    }
-  }
   float sc[SEQ + 1];
+#pragma unroll
+  for (int j = 0; j < SEQ; ++j) {
+    const float4* kj = reinterpret_cast<const float4*>(xch + (base + j) * XCH_PITCH);
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+    for (int g = 0; g < HD / 4; ++g) {
+      const float4 b = kj[g];
+      s0 = fmaf(q[4 * g], b.x, s0);
+      s1 = fmaf(q[4 * g + 1], b.y, s1);
+      s2 = fmaf(q[4 * g + 2], b.z, s2);
+      s3 = fmaf(q[4 * g + 3], b.w, s3);
+    }
+    sc[j] = (s0 + s1) + (s2 + s3);
+  }
   {
     const float4* bk4 = reinterpret_cast<const float4*>(bias_kr);
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
@@ -182,7 +191,7 @@ __device__ __forceinline__ void attend_row(uint32_t taddr, const float* bias, co
 #pragma unroll
   for (int j = 0; j < SEQ; ++j) {
     const float vj = __shfl_sync(0xffffffffu, valid, base + j);
-    sc[j] = vj != 0.f ? se[j] + so[j] : -INFINITY;
+    sc[j] = vj != 0.f ? sc[j] : -INFINITY;
     m = fmaxf(m, sc[j]);
   }
   float l = 0.f;
@@ -207,14 +216,15 @@ __device__ __forceinline__ void attend_row(uint32_t taddr, const float* bias, co
     }
   }
 #pragma unroll
-  for (int i = 0; i < HD / 2; ++i) {
-    uint32_t w[SEQ];
+  for (int j = 0; j < SEQ; ++j) {
+    const float4* vj = reinterpret_cast<const float4*>(xch + (base + j) * XCH_PITCH) + HD / 4;
 #pragma unroll
-    for (int j = 0; j < SEQ; ++j) w[j] = __shfl_sync(0xffffffffu, vp[i], base + j);
-#pragma unroll
-    for (int j = 0; j < SEQ; ++j) {
-      out[2 * i] = fmaf(sc[j], lo_f(w[j]), out[2 * i]);
-      out[2 * i + 1] = fmaf(sc[j], hi_f(w[j]), out[2 * i + 1]);
+    for (int g = 0; g < HD / 4; ++g) {
+      const float4 b = vj[g];
+      out[4 * g] = fmaf(sc[j], b.x, out[4 * g]);
+      out[4 * g + 1] = fmaf(sc[j], b.y, out[4 * g + 1]);
+      out[4 * g + 2] = fmaf(sc[j], b.z, out[4 * g + 2]);
+      out[4 * g + 3] = fmaf(sc[j], b.w, out[4 * g + 3]);
     }
   }
 }
@@ -276,6 +286,10 @@ gemm_qkv_attn4_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_co
     rope_sn[i] = rope ? p.sn[i] : 0.f;
   }
   for (int i = tid; i < p.H * HD; i += THREADS) bias_vs[i] = p.bias_v[i];
+  {
+    float* bias_all = reinterpret_cast<float*>(smem + OFF_BIAS);
+    for (int i = tid; i < num_n * TILE_N; i += THREADS) bias_all[i] = p.bias[i];
+  }
   if (tid >= 64 && tid < 64 + p.H) {
     const int h = tid - 64;
     float kk[HD];
@@ -360,21 +374,24 @@ gemm_qkv_attn4_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_co
   } else {
     // ===== epilogue warps 2..13: TMEM lane quarter = warp % 4, head of the tile = (warp - 2) / 4 =====
     const int quarter = warp & 3, hh = (warp - 2) >> 2;
-    float* bias_s = reinterpret_cast<float*>(smem + OFF_BIAS) + (warp - 2) * HEAD_COLS;
+    const float* bias_all = reinterpret_cast<const float*>(smem + OFF_BIAS);
     int acc = 0;
     uint32_t acc_phase = 0;
     int mb, nb;
+    // key-valid flag of this thread's row, prefetched one tile ahead (the only per-tile global read of the epilogue)
+    auto row_of = [&](int mbb) { return mbb * TILE_M + (int)rank * BLOCK_M + quarter * 32 + lane; };
+    auto valid_of = [&](int rw) { return rw < M ? __ldg(p.key_valid + (size_t)rw % (size_t)p.mask_mod) : 0.f; };
+    float valid_next = get_tile(0, mb, nb) ? valid_of(row_of(mb)) : 0.f;
     for (int i = 0; get_tile(i, mb, nb); ++i) {
       const int head = nb * HEADS_PER_TILE + hh;
-      const int row = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32 + lane;
+      const int row = row_of(mb);
       const uint32_t te = map_to_rank(smem_u32(&tmem_empty[acc]), 0);
       const bool live = head < p.H;                        // the last tile of 16 heads holds a single head
-      float valid = 0.f;
-      if (live) {                                          // global reads issued before the accumulator wait
-        __syncwarp();                                      // every lane is done with the previous tile's bias_s
-        for (int c = lane; c < HEAD_COLS; c += 32) bias_s[c] = __ldg(p.bias + nb * TILE_N + hh * HEAD_COLS + c);
-        if (row < M) valid = __ldg(p.key_valid + (size_t)row % (size_t)p.mask_mod);
-        __syncwarp();
+      const float valid = valid_next;
+      const float* bias_s = bias_all + nb * TILE_N + hh * HEAD_COLS;
+      {
+        int mb2, nb2;
+        valid_next = get_tile(i + 1, mb2, nb2) ? valid_of(row_of(mb2)) : 0.f;
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tcgen05_fence_after();
@@ -383,11 +400,12 @@ gemm_qkv_attn4_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_co
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(te);
       };
-      if (!live) release();
-      if (live) {
+      if (!live || p.dbg_skip) release();
+      if (live && !p.dbg_skip) {
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE + hh * HEAD_COLS);
         float o[HD];
-        attend_row(taddr, bias_s, rope_cs, rope_sn, bias_kr + head * HD, bias_vs + head * HD, valid, lane, rope, o, release);
+        attend_row(taddr, bias_s, rope_cs, rope_sn, bias_kr + head * HD, bias_vs + head * HD, valid, lane, rope,
+                   smem + OFF_XCH + (warp - 2) * XCH_WARP_BYTES, o, release);
         if (row < M) {
           uint4* dst = reinterpret_cast<uint4*>(p.att + (size_t)row * p.ldo + head * HD);
 #pragma unroll

@@ -313,9 +313,10 @@ int launch_qkv_attn4(const bf16* A, int lda, const MhaW_view& m, int M, int K, i
   p.cs = cs;
   p.sn = sn;
   p.H = H;
+  p.dbg_skip = (g_sw.attn_var & 32) ? 1 : 0;
   const int tiles = ((M + tqa::TILE_M - 1) / tqa::TILE_M) * num_n, pairs = num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
-  ProfScope ps(PC_GEMM_TC, st);
+  ProfScope ps(PC_QKV_ATTN, st);
   tqa::gemm_qkv_attn4_kernel<<<grid, tqa::THREADS, tqa::SMEM_BYTES, st>>>(ta, tw, M, K, num_n, p);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
@@ -1778,7 +1779,8 @@ int mdgen_profile_end(float* ms_by_cat, int32_t* launches_by_cat, int32_t ncat) 
 }
 const char* mdgen_profile_category_name(int32_t i) {
   static const char* names[PC_COUNT] = {"gemm_tcgen05", "gemm_simt_fp32", "attention_tcgen05", "attention_simt",
-                                        "attention_short", "layernorm_modulate", "embed", "ipa", "adaln_rowvec", "misc"};
+                                        "attention_short", "layernorm_modulate", "embed", "ipa", "adaln_rowvec", "misc",
+                                        "qkv_attention_fused"};
   return (i >= 0 && i < PC_COUNT) ? names[i] : "";
 }
 
