@@ -44,8 +44,11 @@ constexpr int OFF_BK = OFF_ROPE + 2 * (SEQ + 1) * (HD / 2) * 4;
 constexpr int OFF_BV = OFF_BK + 16 * HD * 4;
 constexpr int MAX_N_TILES = 6;                                         // 16 heads
 constexpr int OFF_BIAS = OFF_BV + 16 * HD * 4;                         // the whole packed projection bias [6 tiles][224], staged once
-// k / v exchange: per epilogue warp 32 rows x [k 24 | v 24] fp32, row pitch 208 B (rows 4 apart land in different banks)
-constexpr int XCH_PITCH = 208, XCH_WARP_BYTES = 32 * XCH_PITCH;
+// k / v exchange: per epilogue warp 32 rows x [k 24 | v 24] fp32 = 12 chunks of 16 B per row, pitch 192 B.  The 8 sequences
+// of a warp read the same chunk of rows 4 apart -- 4 x 192 B = a multiple of 16 banks whatever the pitch -- so sequence g
+// keeps chunk c at position (c + g) mod 12: the eight 16-byte reads of one load instruction fall on distinct banks
+// (the kernel is shared-memory-bandwidth bound: operand ring + 600 KB of exchange traffic per tile).
+constexpr int XCH_CHUNKS = 12, XCH_PITCH = XCH_CHUNKS * 16, XCH_WARP_BYTES = 32 * XCH_PITCH;
 constexpr int OFF_XCH = (OFF_BIAS + MAX_N_TILES * TILE_N * 4 + 15) / 16 * 16;
 constexpr int SMEM_BYTES = OFF_XCH + EPI_WARPS * XCH_WARP_BYTES + 64;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
@@ -133,6 +136,12 @@ __device__ __forceinline__ void attend_row(uint32_t taddr, const float* bias, co
     s4[g] = reinterpret_cast<const float4*>(sn + t * (HD / 2))[g];
   }
   float4* mine = reinterpret_cast<float4*>(xch + lane * XCH_PITCH);
+  int pos[XCH_CHUNKS];                   // position of chunk c in the rows of this lane's sequence
+#pragma unroll
+  for (int c = 0; c < XCH_CHUNKS; ++c) {
+    const int v = c + (lane >> 2);
+    pos[c] = v >= XCH_CHUNKS ? v - XCH_CHUNKS : v;
+  }
   float q[HD];
   {
     uint32_t acc[HD], accv[HD];
@@ -144,13 +153,13 @@ __device__ __forceinline__ void attend_row(uint32_t taddr, const float* bias, co
       float k[HD];
       bias_rope24(acc, bias4 + HD / 4, c4, s4, rope, k);
 #pragma unroll
-      for (int g = 0; g < HD / 4; ++g) mine[g] = make_float4(k[4 * g], k[4 * g + 1], k[4 * g + 2], k[4 * g + 3]);
+      for (int g = 0; g < HD / 4; ++g) mine[pos[g]] = make_float4(k[4 * g], k[4 * g + 1], k[4 * g + 2], k[4 * g + 3]);
     }
     tmem_ld24(taddr, acc);               // q (in flight while v is stored)
 #pragma unroll
     for (int g = 0; g < HD / 4; ++g) {
       const float4 b = bias4[2 * (HD / 4) + g];
-      mine[HD / 4 + g] = make_float4(__uint_as_float(accv[4 * g]) + b.x, __uint_as_float(accv[4 * g + 1]) + b.y,
+      mine[pos[HD / 4 + g]] = make_float4(__uint_as_float(accv[4 * g]) + b.x, __uint_as_float(accv[4 * g + 1]) + b.y,
                                      __uint_as_float(accv[4 * g + 2]) + b.z, __uint_as_float(accv[4 * g + 3]) + b.w);
     }
     tmem_ld_wait();
@@ -166,7 +175,7 @@ __device__ __forceinline__ void attend_row(uint32_t taddr, const float* bias, co
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
     for (int g = 0; g < HD / 4; ++g) {
-      const float4 b = kj[g];
+      const float4 b = kj[pos[g]];
       s0 = fmaf(q[4 * g], b.x, s0);
       s1 = fmaf(q[4 * g + 1], b.y, s1);
       s2 = fmaf(q[4 * g + 2], b.z, s2);
@@ -217,10 +226,10 @@ __device__ __forceinline__ void attend_row(uint32_t taddr, const float* bias, co
   }
 #pragma unroll
   for (int j = 0; j < SEQ; ++j) {
-    const float4* vj = reinterpret_cast<const float4*>(xch + (base + j) * XCH_PITCH) + HD / 4;
+    const float4* vj = reinterpret_cast<const float4*>(xch + (base + j) * XCH_PITCH);
 #pragma unroll
     for (int g = 0; g < HD / 4; ++g) {
-      const float4 b = vj[g];
+      const float4 b = vj[pos[HD / 4 + g]];
       out[4 * g] = fmaf(sc[j], b.x, out[4 * g]);
       out[4 * g + 1] = fmaf(sc[j], b.y, out[4 * g + 1]);
       out[4 * g + 2] = fmaf(sc[j], b.z, out[4 * g + 2]);
