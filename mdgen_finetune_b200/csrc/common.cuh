@@ -65,7 +65,7 @@ struct DevOnce {
 // CALL (read_switches() at the entry points), never per launch.
 struct Switches {
   bool no_gemm_ln = false, no_gemm_2cta = false, no_gemm_ws = false, no_l2_persist = false, no_attn_tc = false,
-       no_attn_bulk = false, gelu_2cta = false, no_graph = false, no_qkv_attn = false;
+       no_attn_bulk = false, gelu_2cta = false, no_graph = false, no_qkv_attn = false, no_pair16 = false, pair16_store = false;
   int attn_var = 0, attn_poly = 0, asb_seq = 4, attn_sb = 48;
 };
 extern thread_local Switches g_sw;

@@ -445,6 +445,47 @@ __device__ __forceinline__ void epilogue_staged_resid(const ResidLane& L, const 
   __syncwarp();
 }
 
+// The bf16 epilogue on ONE 32-column chunk, stored through a 32 x 32 SWIZZLE_64B tile (16-byte chunk j of row r at chunk
+// j ^ ((r >> 1) & 3)): the unit of work of the pair kernel's 16-epilogue-warp variant (gemm_tc2.cuh).  (16 epilogue warps
+// on THIS kernel were measured too -- GELU projection 53.5 vs 52.8 ms per rollout in the GEMM family, no gain: its
+// 128 x 128 mainloop is shared-memory-bandwidth bound -- and removed.)
+constexpr int TMA_TILE32_BYTES = 2048, EPI16_WARPS = 16;
+// PENDING = bulk stores of this warp that may still be reading OTHER tiles (1 when the warp alternates between two tiles)
+template <int EPI, int PENDING = 0>
+__device__ __forceinline__ void epilogue_tma_bf16_32(const CUtensorMap* mapC, uint8_t* tile, const float* sbias, int lane, int mrow0,
+                                                     int n0, uint32_t (&r)[32]) {
+  if (lane == 0) bulk_wait_read<PENDING>();        // the previous store from this tile has been read out
+  __syncwarp();
+  uint8_t* row = tile + lane * 64;
+  const uint32_t swz = (uint32_t)((lane >> 1) & 3);
+  float4 b4[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) b4[k] = *reinterpret_cast<const float4*>(sbias + k * 4);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    float v0 = __uint_as_float(r[4 * k]) + b4[k].x, v1 = __uint_as_float(r[4 * k + 1]) + b4[k].y;
+    float v2 = __uint_as_float(r[4 * k + 2]) + b4[k].z, v3 = __uint_as_float(r[4 * k + 3]) + b4[k].w;
+    if constexpr (EPI == EPI_GELU) {
+      v0 = gelu_erf_fast(v0);
+      v1 = gelu_erf_fast(v1);
+      v2 = gelu_erf_fast(v2);
+      v3 = gelu_erf_fast(v3);
+    }
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(v0, v1), hi = __floats2bfloat162_rn(v2, v3);
+    r[2 * k] = *reinterpret_cast<const uint32_t*>(&lo);
+    r[2 * k + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    *reinterpret_cast<uint4*>(row + (((uint32_t)k ^ swz) << 4)) = make_uint4(r[4 * k], r[4 * k + 1], r[4 * k + 2], r[4 * k + 3]);
+  fence_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_2d(mapC, tile, n0, mrow0);
+    bulk_commit();
+  }
+}
+
 // ---- the kernel ----------------------------------------------------------------------------
 template <int BN, int EPI, typename OT, int WS, int STG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)

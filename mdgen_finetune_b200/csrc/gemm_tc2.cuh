@@ -85,13 +85,26 @@ __device__ __forceinline__ void stamp_ns(const EpiParams& ep, int tile_i, int sl
   }
 }
 
-template <int EPI, typename OT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+// EW = epilogue warps per CTA.  8: two per TMEM lane quarter, 128 columns each (all epilogues).  16 (bf16 store / GELU
+// only): four per quarter, 64 columns each as two 32-column chunks through two alternating 32 x 32 SWIZZLE_64B store tiles.
+// Why: with K = 384 draining a 256 x 256 accumulator through the 64 B/clk TMEM read port takes 2048 cycles per tile against
+// 3072 cycles of MMA; on 8 warps that drain, the GELU (~11 instructions + 1 MUFU per element) and the staging run one
+// after the other in each warp and the epilogue, not the tensor pipe, sets the tile time.  (16 warps on the SINGLE-CTA
+// kernel change nothing -- gemm_tc.cuh STG 3 -- because its 128 x 128 mainloop is shared-memory-bandwidth bound.)
+constexpr int STAGES2_EW16 = 4;      // one operand stage goes to the second store tile of every warp
+constexpr int SMEM2_EW16_BYTES = STAGES2_EW16 * STAGE2_BYTES + 1024 + EPI16_WARPS * (2 * TMA_TILE32_BYTES + 256) + 1024 + 256;
+static_assert(SMEM2_EW16_BYTES <= 227 * 1024, "shared memory budget");
+__host__ __device__ constexpr int num_threads2(int ew) { return 64 + 32 * ew; }
+
+template <int EPI, typename OT, int EW = NUM_EPI_WARPS>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(num_threads2(EW), 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
                 const __grid_constant__ CUtensorMap tmapC, int M, int N, int K, EpiParams ep) {
   constexpr bool kResid = (EPI == EPI_GATE_RESID || EPI == EPI_RESID);
   constexpr bool kBf16 = (EPI == EPI_STORE || EPI == EPI_GELU) && sizeof(OT) == 2;
   static_assert(kResid || kBf16, "gemm_tc2: only the staged epilogues exist");
+  static_assert(EW == NUM_EPI_WARPS || (EW == EPI16_WARPS && kBf16), "16 epilogue warps: bf16 store / GELU only");
+  constexpr int STAGES2 = EW == EPI16_WARPS ? STAGES2_EW16 : tc2::STAGES2;
   // No integer round trip on this pointer: the compiler must keep seeing a shared-space address, otherwise every
   // staging access becomes a generic LD.E / ST.E (long-scoreboard latency instead of LDS / STS).
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -134,7 +147,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 2 * NUM_EPI_WARPS);
+      mbar_init(&tmem_empty[s], 2 * EW);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -215,6 +228,42 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
         }
       }
     }
+  } else if constexpr (EW == EPI16_WARPS) {
+    // ===== 16 epilogue warps: TMEM lane quarter = warp % 4, column quarter of the tile = (warp - 2) / 4 =====
+    const int quarter = warp & 3, part = (warp - 2) >> 2;
+    uint8_t* epi = smem + STAGES2 * STAGE2_BYTES + 1024;
+    uint8_t* tiles = epi + (warp - 2) * (2 * TMA_TILE32_BYTES);
+    float* cv = reinterpret_cast<float*>(epi + EW * 2 * TMA_TILE32_BYTES + (warp - 2) * 256);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int mb, nb, n_cur;
+    for (int i = 0; get_tile(i, mb, nb, n_cur); ++i) {
+      const int cpw = n_cur >> 7;                         // 32-column chunks per warp: 2 (n_cur 256) or 1 (128)
+      const int mrow0 = mb * TILE_M + (int)rank * BLOCK_M + quarter * 32;
+      const int col_in_tile = part * cpw * 32;
+      const int ncol0 = nb * TILE_N + col_in_tile;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * TILE_N + col_in_tile);
+      const uint32_t te = map_to_rank(smem_u32(&tmem_empty[acc]), 0);
+      __syncwarp();
+      for (int c = lane; c < cpw * 32; c += 32) cv[c] = (ep.bias && ncol0 + c < N) ? __ldg(ep.bias + ncol0 + c) : 0.f;
+      __syncwarp();
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tcgen05_fence_after();
+      uint32_t r0[32], r1[32];
+      tmem_ld_32x32b_x32(taddr, r0);
+      if (cpw == 2) tmem_ld_32x32b_x32(taddr + 32, r1);
+      tmem_ld_wait();
+      tcgen05_fence_before();                             // accumulator is in registers: hand the TMEM stage back
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(te);
+      epilogue_tma_bf16_32<EPI, 1>(&tmapC, tiles, cv, lane, mrow0, ncol0, r0);
+      if (cpw == 2) epilogue_tma_bf16_32<EPI, 1>(&tmapC, tiles + TMA_TILE32_BYTES, cv + 32, lane, mrow0, ncol0 + 32, r1);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (lane == 0) bulk_wait_read<0>();       // shared memory must outlive the last bulk store's read
   } else {
     // ===== epilogue warps 2..9: TMEM lane quarter = warp % 4, column half = (warp - 2) / 4 =====
     const int quarter = warp & 3, half = (warp - 2) >> 2;

@@ -47,6 +47,8 @@ void read_switches() {
   s.gelu_2cta = on("MDGEN_GELU_2CTA");
   s.no_graph = on("MDGEN_NO_GRAPH");
   s.no_qkv_attn = on("MDGEN_NO_QKV_ATTN");
+  s.no_pair16 = on("MDGEN_NO_PAIR16");
+  s.pair16_store = on("MDGEN_PAIR16_STORE");
   s.attn_var = num("MDGEN_ATTN_VAR", 0);
   s.attn_poly = num("MDGEN_ATTN_POLY", 0);
   s.asb_seq = num("MDGEN_ASB_SEQ", 4);
@@ -86,19 +88,22 @@ static int make_tmap_2d(CUtensorMap* m, const bf16* ptr, int rows, int cols, int
   return 0;
 }
 
-// generic 2-D row-major tensor map with a [box_rows, box_cols] box whose inner extent is 128 bytes (SWIZZLE_128B)
+// generic 2-D row-major tensor map with a [box_rows, box_cols] box whose inner extent is 128 bytes (SWIZZLE_128B) or
+// 64 bytes (SWIZZLE_64B)
 static int make_tmap_2d_box(CUtensorMap* m, const void* ptr, CUtensorMapDataType dt, int elem_bytes, int rows, int cols, int ld,
                             int box_cols, int box_rows) {
   EncodeTiledFn fn = get_encode_fn();
   MD_CHECK(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
-  MD_CHECK(((uintptr_t)ptr & 15) == 0 && ((size_t)ld * elem_bytes) % 16 == 0 && box_cols * elem_bytes == 128,
-           "TMA operand must be 16-byte aligned with a 128-byte inner box");
+  const int inner = box_cols * elem_bytes;
+  MD_CHECK(((uintptr_t)ptr & 15) == 0 && ((size_t)ld * elem_bytes) % 16 == 0 && (inner == 128 || inner == 64),
+           "TMA operand must be 16-byte aligned with a 128- or 64-byte inner box");
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * elem_bytes};
   cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, dt, 2, (void*)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(m, dt, 2, (void*)ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  inner == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   MD_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed");
   return 0;
 }
@@ -157,17 +162,18 @@ static int launch_tc_inst(const CUtensorMap& ta, const CUtensorMap& tw, const CU
 }
 
 // CTA-pair kernel (gemm_tc2.cuh): 256 x 256 tiles, one cluster of two CTAs per tile
-template <int EPI, typename OT>
+template <int EPI, typename OT, int EW = tc::NUM_EPI_WARPS>
 static int launch_tc2_inst(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K,
                            const EpiParams& ep, cudaStream_t st) {
-  auto kern = tc2::gemm_tc2_kernel<EPI, OT>;
-  MD_SMEM_ONCE(kern, tc2::SMEM2_BYTES);
+  auto kern = tc2::gemm_tc2_kernel<EPI, OT, EW>;
+  constexpr int SMEM = EW == tc::EPI16_WARPS ? tc2::SMEM2_EW16_BYTES : tc2::SMEM2_BYTES;
+  MD_SMEM_ONCE(kern, SMEM);
   MD_VARIANT(V_GEMM_TC2);
   const int tiles = ((M + tc2::TILE_M - 1) / tc2::TILE_M) * ((N + tc2::TILE_N - 1) / tc2::TILE_N);
   const int pairs = num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   ProfScope ps(PC_GEMM_TC, st);
-  kern<<<grid, tc::NUM_THREADS, tc2::SMEM2_BYTES, st>>>(ta, tw, tcm, M, N, K, ep);
+  kern<<<grid, tc2::num_threads2(EW), SMEM, st>>>(ta, tw, tcm, M, N, K, ep);
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
@@ -175,8 +181,12 @@ static int launch_tc2_inst(const CUtensorMap& ta, const CUtensorMap& tw, const C
 static int launch_tc2(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& tcm, int M, int N, int K, int epi,
                       const EpiParams& ep, cudaStream_t st) {
   switch (epi) {
-    case EPI_STORE: return launch_tc2_inst<EPI_STORE, bf16>(ta, tw, tcm, M, N, K, ep, st);
-    case EPI_GELU: return launch_tc2_inst<EPI_GELU, bf16>(ta, tw, tcm, M, N, K, ep, st);
+    case EPI_STORE:
+      return ep.staged == 3 ? launch_tc2_inst<EPI_STORE, bf16, tc::EPI16_WARPS>(ta, tw, tcm, M, N, K, ep, st)
+                            : launch_tc2_inst<EPI_STORE, bf16>(ta, tw, tcm, M, N, K, ep, st);
+    case EPI_GELU:
+      return ep.staged == 3 ? launch_tc2_inst<EPI_GELU, bf16, tc::EPI16_WARPS>(ta, tw, tcm, M, N, K, ep, st)
+                            : launch_tc2_inst<EPI_GELU, bf16>(ta, tw, tcm, M, N, K, ep, st);
     case EPI_GATE_RESID: return launch_tc2_inst<EPI_GATE_RESID, float>(ta, tw, tcm, M, N, K, ep, st);
     case EPI_RESID: return launch_tc2_inst<EPI_RESID, float>(ta, tw, tcm, M, N, K, ep, st);
   }
@@ -268,17 +278,21 @@ int launch_gemm_tc(const bf16* A, int lda, const bf16* W, int ldw, int M, int N,
   if (block_n == 256) MD_CHECK(pair_ok, "launch_gemm_tc: shape / epilogue not supported by the CTA-pair kernel");
   if (auto_bn && pair_ok && !g_sw.no_gemm_2cta) {
     const long t256 = (long)((M + 255) / 256) * ((N + 255) / 256);
-    // measured on config 3 (tools/gemm_probe.py): the pair kernel wins for the K = 1536 projection (fc2) and the plain
-    // bf16 stores of wide N; the K = 384 residual / GELU epilogues are shared-memory-bandwidth bound either way
-    const bool gelu_pair = g_sw.gelu_2cta;
+    // measured on config 3 (tools/gemm_probe.py): the pair kernel wins for the K = 1536 projection (fc2), the plain bf16
+    // stores of wide N and -- with 16 epilogue warps (gemm_tc2.cuh) -- the GELU projection; the K = 384 residual
+    // epilogue is shared-memory-bandwidth bound either way
+    const bool gelu_pair = g_sw.gelu_2cta || !g_sw.no_pair16;
     if (t256 >= num_sms() / 2 && (K >= 1024 || ((epi == EPI_STORE || (gelu_pair && epi == EPI_GELU)) && N >= 1024))) block_n = 256;
   }
   CUtensorMap ta, tw;
   MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
   MD_TRY(make_tmap_2d(&tw, W, N, K, ldw, block_n == 256 ? tc2::HALF_N : block_n));
   CUtensorMap tcm = ta;      // output map for the TMA-store epilogues (bf16 outputs, staged); unused otherwise
-  if (epp.staged && out_bf16 && (epi == EPI_STORE || epi == EPI_GELU) && block_n >= 128)
-    MD_TRY(make_tmap_2d_box(&tcm, ep.out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, M, N, ep.ldo, 64, 32));
+  if (epp.staged && out_bf16 && (epi == EPI_STORE || epi == EPI_GELU) && block_n >= 128) {
+    // staged == 3: the pair kernel's 16-epilogue-warp variant, which stores 32 x 32 tiles
+    if (block_n == 256 && !g_sw.no_pair16 && (g_sw.pair16_store || epi == EPI_GELU)) epp.staged = 3;
+    MD_TRY(make_tmap_2d_box(&tcm, ep.out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, M, N, ep.ldo, epp.staged == 3 ? 32 : 64, 32));
+  }
   if (block_n == 256) return launch_tc2(ta, tw, tcm, M, N, K, epi, epp, st);
   switch (block_n) {
     case 32: return launch_tc_bn<32>(ta, tw, tcm, M, N, K, epi, out_bf16, epp, st);
@@ -1382,7 +1396,7 @@ static unsigned switches_hash() {
   const Switches& s = g_sw;
   unsigned hsh = 0;
   const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta,
-                       s.no_qkv_attn};
+                       s.no_qkv_attn, s.no_pair16, s.pair16_store};
   for (bool b : bits) hsh = (hsh << 1) | (b ? 1u : 0u);
   return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009);
 }

@@ -63,6 +63,25 @@ def test_gemm_tcgen05_bf16_out_staged_epilogue(M, N, K, bn, mode):
     assert err < 4e-3, err          # one bf16 rounding of the output
 
 
+@pytest.mark.parametrize("env", ["MDGEN_PAIR16_STORE", "MDGEN_NO_PAIR16"])
+@pytest.mark.parametrize("M,N,K", [(4000, 1152, 384), (777, 1536, 384), (300, 128, 64), (20000, 1536, 384)])
+@pytest.mark.parametrize("mode", [2, 3])
+def test_gemm_pair_kernel_epilogue_warp_variants(M, N, K, mode, env, monkeypatch):
+    """gemm_tc2.cuh: 16 epilogue warps (default for GELU; MDGEN_PAIR16_STORE=1 also for plain stores) against 8
+    (MDGEN_NO_PAIR16=1) -- same tile arithmetic, so the outputs must be bit-identical to each other."""
+    g = torch.Generator().manual_seed(M + N + K)
+    A, W, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5, torch.randn(N, generator=g)
+    base = _gemm(A.cuda(), W.cuda(), b.cuda(), mode, 256).cpu()
+    monkeypatch.setenv(env, "1")
+    C = _gemm(A.cuda(), W.cuda(), b.cuda(), mode, 256).cpu()
+    assert torch.isfinite(C).all()
+    assert torch.equal(C, base)
+    ref = A.bfloat16().double() @ W.bfloat16().double().T + b.double()
+    if mode == 3:
+        ref = ref * 0.5 * (1.0 + torch.erf(ref / 2 ** 0.5))
+    assert float((C - ref.float()).norm() / ref.norm()) < 4e-3
+
+
 @pytest.mark.parametrize("M,N,K,bn", [(4000, 384, 1536, 0), (4000, 384, 384, 0), (777, 384, 384, 128), (129, 48, 384, 64),
                                       (300, 21, 384, 0), (100, 70, 64, 64),
                                       (256, 256, 384, 256), (4000, 384, 1536, 256), (777, 384, 384, 256), (20000, 1152, 384, 256)])

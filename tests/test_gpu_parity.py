@@ -267,7 +267,7 @@ def test_full_size_velocity_and_short_rollout_vs_reference(name, prec):
 
 
 @pytest.mark.parametrize("switch", ["MDGEN_NO_GEMM_LN", "MDGEN_NO_GEMM_2CTA", "MDGEN_NO_GEMM_WS", "MDGEN_NO_L2_PERSIST",
-                                    "MDGEN_NO_GRAPH", "MDGEN_NO_QKV_ATTN"])
+                                    "MDGEN_NO_GRAPH", "MDGEN_NO_QKV_ATTN", "MDGEN_NO_PAIR16", "MDGEN_PAIR16_STORE"])
 def test_config3_kernel_variants_agree(switch, monkeypatch):
     """Every variant switch of DESIGN.md section 2 must leave the config-3 result within bf16 rounding of the default
     dispatch and within the north_star tolerance of the reference golden."""
