@@ -370,6 +370,8 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem = bars->tmem_base;
+  pdl_trigger();       // common.cuh: after the TMEM allocation
+  pdl_wait();          // qkv (the previous kernel's output) is complete from here on
   if (tid == 0) dbg_stamp(dbg, 1);
   const uint32_t sK = smem_u32(smem + OFF_K), sV = smem_u32(smem + OFF_V), sQ = smem_u32(smem + OFF_Q);
 
@@ -632,8 +634,8 @@ inline cudaError_t launch_attention_tc_variant(const AttnParams<bf16>& p, int gr
     once.done(dev);
   }
   MD_VARIANT(V_ATTN_TC);
-  atc::attention_tc_kernel<DBG, POLY, SB, NBUF><<<grid, atc::THREADS, atc::SMEM_BYTES, st>>>(p, chunks, nunits, DBG ? g_dbg_buf : nullptr, g_dbg_cta, var);
-  return cudaSuccess;
+  return launch_pdl(atc::attention_tc_kernel<DBG, POLY, SB, NBUF>, grid, atc::THREADS, atc::SMEM_BYTES, st, p, chunks, nunits,
+                    DBG ? g_dbg_buf : nullptr, g_dbg_cta, var);
 }
 
 inline int launch_attention_tc(const AttnParams<bf16>& p, int head_dim, cudaStream_t st) {

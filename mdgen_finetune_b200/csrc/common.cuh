@@ -65,8 +65,8 @@ struct DevOnce {
 // CALL (read_switches() at the entry points), never per launch.
 struct Switches {
   bool no_gemm_ln = false, no_gemm_2cta = false, no_gemm_ws = false, no_l2_persist = false, no_attn_tc = false,
-       no_attn_bulk = false, gelu_2cta = false, no_graph = false, no_qkv_attn = false, no_pair16 = false, pair16_store = false;
-  int attn_var = 0, attn_poly = 0, asb_seq = 4, attn_sb = 48;
+       no_attn_bulk = false, gelu_2cta = false, no_graph = false, no_qkv_attn = false, no_pair16 = false, pair16_store = false, no_pdl = false;
+  int attn_var = 0, attn_poly = 0, asb_seq = 4, attn_sb = 48, gemm_ln_min_m = 8192;
 };
 extern thread_local Switches g_sw;
 void read_switches();
@@ -102,6 +102,34 @@ struct ProfScope {
     g_prof.recs.push_back(r);
   }
 };
+
+// ---- programmatic dependent launch ---------------------------------------------------
+// The per-evaluation kernels are launched with cudaLaunchAttributeProgrammaticStreamSerialization (also inside the captured
+// rollout graph, where the attribute becomes a programmatic edge): kernel N+1 may become resident -- barrier init, TMEM
+// allocation, tensor-map prefetch -- while kernel N is still running, and blocks in pdl_wait() until N has COMPLETED and
+// its memory is visible.  Rules every such kernel follows:
+//   * pdl_wait() comes before the first access to global memory (reads AND writes: write-after-read on reused scratch);
+//   * pdl_trigger() comes after the kernel's own TMEM allocation (a dependent that became resident on the same SM and
+//     allocated first would otherwise starve it while waiting for it: deadlock);
+//   * every thread executes pdl_wait(), so "N+1 complete" implies "N complete" and the ordering is transitive.
+// A kernel launched WITHOUT the attribute (plain <<<>>>) is an ordinary full dependency on both sides.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = g_sw.no_pdl ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 // ---- device helpers ------------------------------------------------------------------
 __device__ __forceinline__ float to_f(float v) { return v; }

@@ -19,6 +19,8 @@ ln_modulate_kernel(const float* __restrict__ x, OT* __restrict__ out, int M, con
                    const float* __restrict__ w, const float* __restrict__ bvec, float eps) {
   static_assert(C % 128 == 0, "C must be a multiple of 128");
   constexpr int V = C / 128;  // float4 per lane
+  pdl_trigger();       // common.cuh: programmatic dependent launch
+  pdl_wait();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   const int row0 = warp * LN_ROWS;
   if (row0 >= M) return;
@@ -187,6 +189,8 @@ embed_step_kernel(const float* __restrict__ x, int D, const float* __restrict__ 
   static_assert(NT >= EMB_STEP_TOK && EMB_STEP_TOK % G == 0, "one thread per staged token for the row table");
   __shared__ __align__(16) float sm[EMB_STEP_TOK][DP];
   __shared__ int ipa_row[EMB_STEP_TOK];
+  pdl_trigger();       // common.cuh: programmatic dependent launch
+  pdl_wait();
   const int c0 = threadIdx.x;
   const int m0 = blockIdx.x * EMB_STEP_TOK;
   float w[CH][DP];

@@ -117,6 +117,8 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   cluster_sync_all();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
+  pdl_trigger();       // common.cuh: after the TMEM allocation
+  pdl_wait();          // the previous kernel's outputs (A, the residual stream) are complete from here on
 
   if (warp == 0) {
     // ===== TMA producer: own 128 rows of A, own halves of the two W slices =====

@@ -289,6 +289,7 @@ gemm_qkv_attn4_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_co
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
   }
+  pdl_wait();          // common.cuh: nothing in global memory is touched before this
   // step-invariant tables: RoPE cos / sin of positions 0..4, the bias token (key rotated to position 4, value)
   for (int i = tid; i < (SEQ + 1) * (HD / 2); i += THREADS) {
     rope_cs[i] = rope ? p.cs[i] : 1.f;
@@ -321,6 +322,7 @@ gemm_qkv_attn4_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_co
   cluster_sync_all();       // the peer's barriers are initialised before anything is signalled across the pair
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
+  pdl_trigger();            // after the TMEM allocation
 
   if (warp == 0) {
     // ===== TMA producer: own 128 rows of A, own half (112 rows) of the head-major W tile =====

@@ -554,6 +554,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
+  pdl_trigger();       // common.cuh: after the TMEM allocation
+  pdl_wait();          // the previous kernel's outputs (A, residual) are complete from here on
 
   if (warp == 0) {
     // ===== TMA producer =====

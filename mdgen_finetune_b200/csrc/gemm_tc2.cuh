@@ -162,6 +162,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
   cluster_sync_all();       // the peer's barriers are initialised before anything is signalled across the pair
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
+  pdl_trigger();       // common.cuh: after the TMEM allocation
+  pdl_wait();          // the previous kernel's outputs are complete from here on
   if (threadIdx.x == 0) stamp(ep, 15, 1);      // setup done
 
   if (warp == 0) {

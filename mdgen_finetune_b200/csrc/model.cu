@@ -48,6 +48,8 @@ void read_switches() {
   s.no_graph = on("MDGEN_NO_GRAPH");
   s.no_qkv_attn = on("MDGEN_NO_QKV_ATTN");
   s.no_pair16 = on("MDGEN_NO_PAIR16");
+  s.no_pdl = on("MDGEN_NO_PDL");
+  s.gemm_ln_min_m = num("MDGEN_GEMM_LN_MIN_M", 8192);
   s.pair16_store = on("MDGEN_PAIR16_STORE");
   s.attn_var = num("MDGEN_ATTN_VAR", 0);
   s.attn_poly = num("MDGEN_ATTN_POLY", 0);
@@ -135,7 +137,7 @@ static int launch_tc_ws(const CUtensorMap& ta, const CUtensorMap& tw, const CUte
   int tiles = ((M + tc::BLOCK_M - 1) / tc::BLOCK_M) * ((N + BN - 1) / BN);
   int grid = tiles < num_sms() ? tiles : num_sms();
   ProfScope ps(PC_GEMM_TC, st);
-  kern<<<grid, tc::NUM_THREADS, smem, st>>>(ta, tw, tcm, M, N, K, ep);
+  MD_CUDA(launch_pdl(kern, grid, tc::NUM_THREADS, smem, st, ta, tw, tcm, M, N, K, ep));
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
@@ -173,7 +175,7 @@ static int launch_tc2_inst(const CUtensorMap& ta, const CUtensorMap& tw, const C
   const int pairs = num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   ProfScope ps(PC_GEMM_TC, st);
-  kern<<<grid, tc2::num_threads2(EW), SMEM, st>>>(ta, tw, tcm, M, N, K, ep);
+  MD_CUDA(launch_pdl(kern, grid, tc2::num_threads2(EW), SMEM, st, ta, tw, tcm, M, N, K, ep));
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
@@ -218,7 +220,7 @@ int launch_gemm_resid_ln(const bf16* A, int lda, const bf16* W, int ldw, int M, 
   EpiParams epp = ep;
   epp.dbg = g_dbg_buf;
   epp.dbg_cta = g_dbg_cta;
-  tcln::gemm_ln_kernel<<<grid, tc::NUM_THREADS, tcln::SMEM_BYTES, st>>>(ta, tw1, tw2, tx, th, M, K, epp, ln);
+  MD_CUDA(launch_pdl(tcln::gemm_ln_kernel, grid, tc::NUM_THREADS, tcln::SMEM_BYTES, st, ta, tw1, tw2, tx, th, M, K, epp, ln));
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
@@ -331,7 +333,7 @@ int launch_qkv_attn4(const bf16* A, int lda, const MhaW_view& m, int M, int K, i
   const int tiles = ((M + tqa::TILE_M - 1) / tqa::TILE_M) * num_n, pairs = num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   ProfScope ps(PC_QKV_ATTN, st);
-  tqa::gemm_qkv_attn4_kernel<<<grid, tqa::THREADS, tqa::SMEM_BYTES, st>>>(ta, tw, M, K, num_n, p);
+  MD_CUDA(launch_pdl(tqa::gemm_qkv_attn4_kernel, grid, tqa::THREADS, tqa::SMEM_BYTES, st, ta, tw, M, K, num_n, p));
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
@@ -899,7 +901,7 @@ struct Fwd {
       // The fused kernel owns whole 256-row slabs: M / 256 CTA pairs.  Below ~8k rows (config 1: 16 tiles on 74 pairs)
       // the machine is mostly idle and the plain 64-column-tile GEMM + a separate LayerNorm kernel is faster
       // (config 1: 36.3 -> 33.3 ms per rollout, tools/ab_small.sh).
-      if (nshift && nscale && ep.resid == h->xres && M >= 8192) {
+      if (nshift && nscale && ep.resid == h->xres && M >= g_sw.gemm_ln_min_m) {
         ep.bias = w.b;
         tcln::LnFuse ln;
         ln.out = (bf16*)h->hbuf;
@@ -932,8 +934,8 @@ struct Fwd {
   int lnmod(const float* x, AT* out, int M, const float* shift, const float* scale, int rows_per_batch, int nbatch) {
     if (M <= 0) return 0;
     ProfScope ps(PC_LN, st);
-    ln_modulate_kernel<AT, 384><<<((M + LN_ROWS - 1) / LN_ROWS * 32 + 255) / 256, 256, 0, st>>>(x, out, M, shift, scale, h->ada_cols,
-                                                                       rows_per_batch, nbatch, nullptr, nullptr, 1e-6f);
+    MD_CUDA(launch_pdl(ln_modulate_kernel<AT, 384>, ((M + LN_ROWS - 1) / LN_ROWS * 32 + 255) / 256, 256, 0, st, x, out, M, shift, scale,
+                       h->ada_cols, rows_per_batch, nbatch, nullptr, nullptr, 1e-6f));
     MD_LAUNCHED();
     MD_CUDA(cudaGetLastError());
     return 0;
@@ -1230,9 +1232,9 @@ static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state,
     MD_CHECK(D + (h->has_cond ? Dc : 0) <= 80, "latent_dim + cond_dim > 80 not supported by the embedding kernel");
     ProfScope ps(PC_EMBED, st);
     const dim3 sgrid((N + EMB_STEP_TOK - 1) / EMB_STEP_TOK);
-    if (D <= 24) embed_step_kernel<384, 24, 4><<<sgrid, 96, 0, st>>>(x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L);
-    else if (D <= 48) embed_step_kernel<384, 48, 2><<<sgrid, 192, 0, st>>>(x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L);
-    else embed_step_kernel<384, 80, 1><<<sgrid, 384, 0, st>>>(x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L);
+    if (D <= 24) MD_CUDA(launch_pdl(embed_step_kernel<384, 24, 4>, sgrid, 96, 0, st, x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L));
+    else if (D <= 48) MD_CUDA(launch_pdl(embed_step_kernel<384, 48, 2>, sgrid, 192, 0, st, x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L));
+    else MD_CUDA(launch_pdl(embed_step_kernel<384, 80, 1>, sgrid, 384, 0, st, x, D, h->emb_wt, h->emb_static, ipa_out, h->xres, N, T, L));
     MD_LAUNCHED();
     MD_CUDA(cudaGetLastError());
   }
@@ -1396,9 +1398,9 @@ static unsigned switches_hash() {
   const Switches& s = g_sw;
   unsigned hsh = 0;
   const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta,
-                       s.no_qkv_attn, s.no_pair16, s.pair16_store};
+                       s.no_qkv_attn, s.no_pair16, s.pair16_store, s.no_pdl};
   for (bool b : bits) hsh = (hsh << 1) | (b ? 1u : 0u);
-  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009);
+  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009 + s.gemm_ln_min_m * 7);
 }
 
 static void rollout_graph_drop(MdgenHandle* h) {
