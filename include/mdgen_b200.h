@@ -179,7 +179,8 @@ int mdgen_launches_per_forward(MdgenHandle* h);
 long long mdgen_launch_count(void);
 /* Launches per kernel variant since load: 0 gemm_ln (fused projection + residual + LayerNorm), 1 gemm_tc2 (CTA pair),
  * 2 gemm_tc, 3 attention_tc, 4 attention_seq4 (residue axis, 5 keys), 5 whole-rollout graph replays, 6 qkv_attn4 (q/k/v
- * projection fused with the residue-axis attention at L = 4); -1 if out of range.
+ * projection fused with the residue-axis attention at L = 4), 7 gemm_mlp (fc1 + GELU + fc2 + residual + LayerNorm in one
+ * kernel); -1 if out of range.
  * Launches captured into a rollout graph are counted once, at capture. */
 long long mdgen_variant_launches(int32_t which);
 /* Bytes of device workspace currently held by the handle. */

@@ -68,6 +68,240 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// The residual + LayerNorm epilogue of one 128-row x 384-column accumulator (TMEM columns 0..383 of this CTA), shared by
+// gemm_ln_kernel and gemm_mlp_ln_kernel (gemm_mlp.cuh).  One instance per epilogue thread (warps 2..9, thread = row, two
+// warps per TMEM lane quarter each owning 6 of the 12 32-column chunks).
+//   All arithmetic happens in the TMEM row layout (per-row statistics need no shuffles, x_new can live in TMEM between
+//   the passes); every global access goes through TMA: per warp two 32 x 128 B tiles in the SWIZZLE_128B layout, which a
+//   thread = row reads / writes conflict-free (16-byte chunk j of row r sits at chunk j ^ (r & 7)).  Row-per-thread global
+//   accesses were measured 10x slower (no L1 left to merge the 16-byte pieces of a line with the shared-memory carve-out at
+//   its maximum), and the LSU path (LDG/STG + shared-memory transposition) moved only ~25 B/clk/SM.
+struct LnEpilogue {
+  static constexpr int CH = 6;                             // 32-column chunks per warp
+  int lane, quarter, half, et, row_in_cta, col0;
+  uint32_t trow, te, swz;
+  uint8_t *ebuf, *myrow0;
+  uint64_t *xb, *tmem_full;
+  float *cv, *stats, *stats2;
+  bool st0;
+  int staged_q;
+  uint32_t acc_phase, xph0, xph1;
+
+  // ebuf_all: [8 warps][2] tiles of EBUF_BYTES, 1024-byte aligned; cv_all: [NVEC][384] + STATS_BYTES; xbar: [8 warps][2]
+  __device__ __forceinline__ void init(int warp, int lane_, uint32_t tmem_base, uint8_t* ebuf_all, float* cv_all, uint64_t* xbar,
+                                       uint64_t* tmem_full_, uint64_t* tmem_empty) {
+    lane = lane_;
+    quarter = warp & 3;
+    half = (warp - 2) >> 2;
+    et = (warp - 2) * 32 + lane;                           // 0..255 among the epilogue threads
+    row_in_cta = quarter * 32 + lane;
+    trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    te = map_to_rank(smem_u32(tmem_empty), 0);
+    ebuf = ebuf_all + (warp - 2) * 2 * EBUF_BYTES;
+    xb = xbar + (warp - 2) * 2;
+    swz = (uint32_t)(lane & 7);
+    myrow0 = ebuf + lane * 128;
+    col0 = half * CH * 32;
+    cv = cv_all;
+    stats = cv + NVEC * LN_N;                              // row sums [2][128]
+    stats2 = stats + 2 * 128;                              // centred squares [2][128]
+    tmem_full = tmem_full_;
+    st0 = (warp == 2 && lane == 0);
+    staged_q = -1;
+    acc_phase = xph0 = xph1 = 0;
+  }
+
+  // the first two residual tiles of this slab start moving (the previous tile's stores have left the buffers)
+  __device__ __forceinline__ void prefetch(const CUtensorMap& tmapX, int cta_row0) {
+    const int slab_row0 = cta_row0 + quarter * 32;
+    if (lane == 0) {
+      bulk_wait_read<0>();
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        mbar_expect_tx(&xb[u], EBUF_BYTES);
+        tma_load_2d(&tmapX, &xb[u], ebuf + u * EBUF_BYTES, col0 + u * 32, slab_row0);
+      }
+    }
+    __syncwarp();
+  }
+
+  // waits for the accumulator, runs the three passes, hands the accumulator back (arrival on `te`)
+  __device__ __forceinline__ void tile(const CUtensorMap& tmapX, const CUtensorMap& tmapH, const EpiParams& ep, const LnFuse& ln,
+                                       int cta_row0, int ti) {
+    const int slab_row0 = cta_row0 + quarter * 32;
+    // ---- per-column vectors of the (at most two) batch elements this CTA's 128 rows touch
+    const int q0 = cta_row0 / ep.rows_per_batch;
+    const int split = (q0 + 1) * ep.rows_per_batch - cta_row0;        // rows >= split belong to the next batch element
+    if (q0 != staged_q) {
+      named_bar_sync(5, 32 * NUM_EPI_WARPS);                          // everyone is done with the previous vectors
+      const int b0 = q0 % ep.nbatch, b1 = (q0 + 1) % ep.nbatch;
+      for (int i = et; i < NVEC * (LN_N / 4); i += 32 * NUM_EPI_WARPS) {
+        const int v = i / (LN_N / 4), cc = (i % (LN_N / 4)) * 4;
+        float4 val;
+        if (v == 0) {
+          val = ep.bias ? __ldg(reinterpret_cast<const float4*>(ep.bias + cc)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else if (v <= 2) {
+          val = ep.gate ? __ldg(reinterpret_cast<const float4*>(ep.gate + (size_t)(v == 1 ? b0 : b1) * ep.gate_stride + cc))
+                        : make_float4(1.f, 1.f, 1.f, 1.f);
+        } else if (v <= 4) {
+          val = __ldg(reinterpret_cast<const float4*>(ln.scale + (size_t)(v == 3 ? b0 : b1) * ep.gate_stride + cc));
+          val = make_float4(1.f + val.x, 1.f + val.y, 1.f + val.z, 1.f + val.w);
+        } else {
+          val = __ldg(reinterpret_cast<const float4*>(ln.shift + (size_t)(v == 5 ? b0 : b1) * ep.gate_stride + cc));
+        }
+        *reinterpret_cast<float4*>(cv + v * LN_N + cc) = val;
+      }
+      named_bar_sync(5, 32 * NUM_EPI_WARPS);
+      staged_q = q0;
+    }
+    const int sel = row_in_cta < split ? 0 : 1;
+    const float* cbias = cv + col0;
+    const float* cgate = cv + (1 + sel) * LN_N + col0;
+    const float* cmul = cv + (3 + sel) * LN_N + col0;
+    const float* cadd = cv + (5 + sel) * LN_N + col0;
+    if (st0) stamp(ep, ti, 2);
+    mbar_wait(tmem_full, acc_phase);
+    tcgen05_fence_after();
+    if (st0) stamp(ep, ti, 3);
+    // ---- pass 1: residual update, row sum, x_new back into TMEM and (in place in the tile) out to global
+    float sum = 0.f;
+#pragma unroll 1
+    for (int c2 = 0; c2 < CH; c2 += 2) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int c = c2 + u;
+        uint8_t* row = myrow0 + u * EBUF_BYTES;
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(trow + col0 + c * 32, r);
+        float4 bb[8], gg[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          bb[j] = *reinterpret_cast<const float4*>(cbias + c * 32 + j * 4);
+          gg[j] = *reinterpret_cast<const float4*>(cgate + c * 32 + j * 4);
+        }
+        mbar_wait(&xb[u], u ? xph1 : xph0);               // this chunk's residual tile has landed
+        if (u) xph1 ^= 1; else xph0 ^= 1;
+        float4 xr[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) xr[j] = *reinterpret_cast<const float4*>(row + ((j ^ swz) << 4));
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float o0 = fmaf(gg[j].x, __uint_as_float(r[4 * j]) + bb[j].x, xr[j].x);
+          const float o1 = fmaf(gg[j].y, __uint_as_float(r[4 * j + 1]) + bb[j].y, xr[j].y);
+          const float o2 = fmaf(gg[j].z, __uint_as_float(r[4 * j + 2]) + bb[j].z, xr[j].z);
+          const float o3 = fmaf(gg[j].w, __uint_as_float(r[4 * j + 3]) + bb[j].w, xr[j].w);
+          sum += (o0 + o1) + (o2 + o3);
+          r[4 * j] = __float_as_uint(o0);
+          r[4 * j + 1] = __float_as_uint(o1);
+          r[4 * j + 2] = __float_as_uint(o2);
+          r[4 * j + 3] = __float_as_uint(o3);
+          *reinterpret_cast<uint4*>(row + ((j ^ swz) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        }
+        tmem_st_32x32b_x32(trow + col0 + c * 32, r);
+        fence_async_smem();                               // this thread's row is visible to the bulk-copy engine
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmapX, ebuf + u * EBUF_BYTES, col0 + c * 32, slab_row0);
+          bulk_commit();
+          if (c + 2 < CH) {                               // refill the tile as soon as the store has read it
+            bulk_wait_read<0>();
+            mbar_expect_tx(&xb[u], EBUF_BYTES);
+            tma_load_2d(&tmapX, &xb[u], ebuf + u * EBUF_BYTES, col0 + (c + 2) * 32, slab_row0);
+          }
+        }
+        __syncwarp();
+      }
+    }
+    tmem_st_wait();
+    if (st0) stamp(ep, ti, 4);
+    stats[half * 128 + row_in_cta] = sum;
+    named_bar_sync(1 + quarter, 64);
+    const float mean = (sum + stats[(half ^ 1) * 128 + row_in_cta]) * (1.0f / LN_N);
+    named_bar_sync(1 + quarter, 64);                      // both partial sums consumed before the slots are reused
+    // ---- pass 2: centred second moment
+    float sq = 0.f;
+    {
+      uint32_t ra[32], rb[32];
+      tmem_ld_32x32b_x32(trow + col0, ra);
+#pragma unroll 1
+      for (int c = 0; c < CH; c += 2) {
+        tmem_ld_wait();
+        tmem_ld_32x32b_x32(trow + col0 + (c + 1) * 32, rb);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float d = __uint_as_float(ra[j]) - mean;
+          sq = fmaf(d, d, sq);
+        }
+        tmem_ld_wait();
+        if (c + 2 < CH) tmem_ld_32x32b_x32(trow + col0 + (c + 2) * 32, ra);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float d = __uint_as_float(rb[j]) - mean;
+          sq = fmaf(d, d, sq);
+        }
+      }
+    }
+    if (st0) stamp(ep, ti, 5);
+    stats2[half * 128 + row_in_cta] = sq;
+    named_bar_sync(1 + quarter, 64);
+    const float rstd = rsqrtf((sq + stats2[(half ^ 1) * 128 + row_in_cta]) * (1.0f / LN_N) + ln.eps);
+    // ---- pass 3: normalise + modulate -> bf16 tile (64 columns = 128 B per row) -> bulk store
+    auto pack_h = [&](int c, int pbase, uint8_t* row, const uint32_t (&r)[32]) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint32_t pk[4];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float4 mu = *reinterpret_cast<const float4*>(cmul + c * 32 + j * 8 + e * 4);
+          const float4 ad = *reinterpret_cast<const float4*>(cadd + c * 32 + j * 8 + e * 4);
+          const float y0 = fmaf((__uint_as_float(r[8 * j + 4 * e]) - mean) * rstd, mu.x, ad.x);
+          const float y1 = fmaf((__uint_as_float(r[8 * j + 4 * e + 1]) - mean) * rstd, mu.y, ad.y);
+          const float y2 = fmaf((__uint_as_float(r[8 * j + 4 * e + 2]) - mean) * rstd, mu.z, ad.z);
+          const float y3 = fmaf((__uint_as_float(r[8 * j + 4 * e + 3]) - mean) * rstd, mu.w, ad.w);
+          const __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
+          pk[2 * e] = *reinterpret_cast<const uint32_t*>(&lo);
+          pk[2 * e + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+        }
+        *reinterpret_cast<uint4*>(row + (((uint32_t)(pbase + j) ^ swz) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      }
+    };
+    {
+      uint32_t ra[32], rb[32];
+      tmem_ld_32x32b_x32(trow + col0, ra);
+      tmem_ld_32x32b_x32(trow + col0 + 32, rb);
+#pragma unroll 1
+      for (int c = 0; c < CH; c += 2) {
+        const int u = (c >> 1) & 1;
+        uint8_t* row = myrow0 + u * EBUF_BYTES;
+        if (lane == 0) {                                    // the tile's previous store (pass 1 / pair c - 4) has been read out
+          if (c == 0) bulk_wait_read<0>(); else bulk_wait_read<1>();
+        }
+        __syncwarp();
+        tmem_ld_wait();
+        pack_h(c, 0, row, ra);
+        pack_h(c + 1, 4, row, rb);
+        if (c + 2 < CH) {
+          tmem_ld_32x32b_x32(trow + col0 + (c + 2) * 32, ra);
+          tmem_ld_32x32b_x32(trow + col0 + (c + 3) * 32, rb);
+        } else {                                            // every accumulator column has been read: free the stage
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(te);
+        }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmapH, ebuf + u * EBUF_BYTES, col0 + c * 32, slab_row0);
+          bulk_commit();
+        }
+      }
+    }
+    if (st0) stamp(ep, ti, 6);
+    acc_phase ^= 1;
+  }
+};
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW1,
                const __grid_constant__ CUtensorMap tmapW2, const __grid_constant__ CUtensorMap tmapX,
@@ -76,8 +310,6 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
   uint8_t* smem = smem_raw;
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   float* cv = reinterpret_cast<float*>(smem + OFF_CV);                        // [NVEC][384]
-  float* stats = cv + NVEC * LN_N;                                            // row sums [2][128]
-  float* stats2 = stats + 2 * 128;                                            // centred squares [2][128]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
@@ -179,211 +411,13 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     }
   } else {
     // ===== epilogue warps 2..9 =====
-    // All arithmetic happens in the TMEM row layout (thread = row: per-row statistics need no shuffles, x_new can live
-    // in TMEM between the passes); every global access goes through a per-warp 32 x 32 staging tile so that it is
-    // coalesced (lane = 4 columns x 8 rows).  Row-per-thread global accesses were measured 10x slower here: with the
-    // shared-memory carve-out at its maximum there is no L1 left to merge the 16-byte pieces of a line.
-    const int quarter = warp & 3, half = (warp - 2) >> 2;
-    const int et = threadIdx.x - 64;                       // 0..255 among the epilogue threads
-    const int row_in_cta = quarter * 32 + lane;
-    const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t te = map_to_rank(smem_u32(tmem_empty), 0);
-    // Global I/O of the epilogue goes through TMA: per warp two 32 x 128 B tiles in the SWIZZLE_128B layout, which a
-    // thread = row reads / writes conflict-free (16-byte chunk j of row r sits at chunk j ^ (r & 7)).  The LSU path
-    // (LDG/STG + shared-memory transposition) moved only ~25 B/clk/SM here; the bulk path needs no registers, no L1.
-    uint8_t* ebuf = smem + OFF_EBUF + (warp - 2) * 2 * EBUF_BYTES;
-    uint64_t* xb = xbar + (warp - 2) * 2;
-    const uint32_t swz = (uint32_t)(lane & 7);
-    uint8_t* myrow0 = ebuf + lane * 128;
-    constexpr int CH = 6;                                  // 32-column chunks per warp
-    const int col0 = half * CH * 32;
-    int staged_q = -1;
-    uint32_t acc_phase = 0, xph0 = 0, xph1 = 0;
+    LnEpilogue epi;
+    epi.init(warp, lane, tmem_base, smem + OFF_EBUF, cv, xbar, tmem_full, tmem_empty);
     int ti = 0;
-    const bool st0 = (warp == 2 && lane == 0);
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
       const int cta_row0 = tile * TILE_M + (int)rank * BLOCK_M;
-      const int slab_row0 = cta_row0 + quarter * 32;
-      // ---- the first two residual tiles of this slab start moving now (the previous tile's stores have left the buffers)
-      if (lane == 0) {
-        bulk_wait_read<0>();
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          mbar_expect_tx(&xb[u], EBUF_BYTES);
-          tma_load_2d(&tmapX, &xb[u], ebuf + u * EBUF_BYTES, col0 + u * 32, slab_row0);
-        }
-      }
-      __syncwarp();
-      // ---- per-column vectors of the (at most two) batch elements this CTA's 128 rows touch
-      const int q0 = cta_row0 / ep.rows_per_batch;
-      const int split = (q0 + 1) * ep.rows_per_batch - cta_row0;        // rows >= split belong to the next batch element
-      if (q0 != staged_q) {
-        named_bar_sync(5, 32 * NUM_EPI_WARPS);                          // everyone is done with the previous vectors
-        const int b0 = q0 % ep.nbatch, b1 = (q0 + 1) % ep.nbatch;
-        for (int i = et; i < NVEC * (LN_N / 4); i += 32 * NUM_EPI_WARPS) {
-          const int v = i / (LN_N / 4), cc = (i % (LN_N / 4)) * 4;
-          float4 val;
-          if (v == 0) {
-            val = ep.bias ? __ldg(reinterpret_cast<const float4*>(ep.bias + cc)) : make_float4(0.f, 0.f, 0.f, 0.f);
-          } else if (v <= 2) {
-            val = ep.gate ? __ldg(reinterpret_cast<const float4*>(ep.gate + (size_t)(v == 1 ? b0 : b1) * ep.gate_stride + cc))
-                          : make_float4(1.f, 1.f, 1.f, 1.f);
-          } else if (v <= 4) {
-            val = __ldg(reinterpret_cast<const float4*>(ln.scale + (size_t)(v == 3 ? b0 : b1) * ep.gate_stride + cc));
-            val = make_float4(1.f + val.x, 1.f + val.y, 1.f + val.z, 1.f + val.w);
-          } else {
-            val = __ldg(reinterpret_cast<const float4*>(ln.shift + (size_t)(v == 5 ? b0 : b1) * ep.gate_stride + cc));
-          }
-          *reinterpret_cast<float4*>(cv + v * LN_N + cc) = val;
-        }
-        named_bar_sync(5, 32 * NUM_EPI_WARPS);
-        staged_q = q0;
-      }
-      const int sel = row_in_cta < split ? 0 : 1;
-      const float* cbias = cv + col0;
-      const float* cgate = cv + (1 + sel) * LN_N + col0;
-      const float* cmul = cv + (3 + sel) * LN_N + col0;
-      const float* cadd = cv + (5 + sel) * LN_N + col0;
-      if (st0) stamp(ep, ti, 2);
-      mbar_wait(tmem_full, acc_phase);
-      tcgen05_fence_after();
-      if (st0) stamp(ep, ti, 3);
-      // ---- pass 1: residual update, row sum, x_new back into TMEM and (in place in the tile) out to global
-      float sum = 0.f;
-#pragma unroll 1
-      for (int c2 = 0; c2 < CH; c2 += 2) {
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          const int c = c2 + u;
-          uint8_t* row = myrow0 + u * EBUF_BYTES;
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(trow + col0 + c * 32, r);
-          float4 bb[8], gg[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            bb[j] = *reinterpret_cast<const float4*>(cbias + c * 32 + j * 4);
-            gg[j] = *reinterpret_cast<const float4*>(cgate + c * 32 + j * 4);
-          }
-          mbar_wait(&xb[u], u ? xph1 : xph0);               // this chunk's residual tile has landed
-          if (u) xph1 ^= 1; else xph0 ^= 1;
-          float4 xr[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) xr[j] = *reinterpret_cast<const float4*>(row + ((j ^ swz) << 4));
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float o0 = fmaf(gg[j].x, __uint_as_float(r[4 * j]) + bb[j].x, xr[j].x);
-            const float o1 = fmaf(gg[j].y, __uint_as_float(r[4 * j + 1]) + bb[j].y, xr[j].y);
-            const float o2 = fmaf(gg[j].z, __uint_as_float(r[4 * j + 2]) + bb[j].z, xr[j].z);
-            const float o3 = fmaf(gg[j].w, __uint_as_float(r[4 * j + 3]) + bb[j].w, xr[j].w);
-            sum += (o0 + o1) + (o2 + o3);
-            r[4 * j] = __float_as_uint(o0);
-            r[4 * j + 1] = __float_as_uint(o1);
-            r[4 * j + 2] = __float_as_uint(o2);
-            r[4 * j + 3] = __float_as_uint(o3);
-            *reinterpret_cast<uint4*>(row + ((j ^ swz) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-          }
-          tmem_st_32x32b_x32(trow + col0 + c * 32, r);
-          fence_async_smem();                               // this thread's row is visible to the bulk-copy engine
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_2d(&tmapX, ebuf + u * EBUF_BYTES, col0 + c * 32, slab_row0);
-            bulk_commit();
-            if (c + 2 < CH) {                               // refill the tile as soon as the store has read it
-              bulk_wait_read<0>();
-              mbar_expect_tx(&xb[u], EBUF_BYTES);
-              tma_load_2d(&tmapX, &xb[u], ebuf + u * EBUF_BYTES, col0 + (c + 2) * 32, slab_row0);
-            }
-          }
-          __syncwarp();
-        }
-      }
-      tmem_st_wait();
-      if (st0) stamp(ep, ti, 4);
-      stats[half * 128 + row_in_cta] = sum;
-      named_bar_sync(1 + quarter, 64);
-      const float mean = (sum + stats[(half ^ 1) * 128 + row_in_cta]) * (1.0f / LN_N);
-      named_bar_sync(1 + quarter, 64);                      // both partial sums consumed before the slots are reused
-      // ---- pass 2: centred second moment
-      float sq = 0.f;
-      {
-        uint32_t ra[32], rb[32];
-        tmem_ld_32x32b_x32(trow + col0, ra);
-#pragma unroll 1
-        for (int c = 0; c < CH; c += 2) {
-          tmem_ld_wait();
-          tmem_ld_32x32b_x32(trow + col0 + (c + 1) * 32, rb);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float d = __uint_as_float(ra[j]) - mean;
-            sq = fmaf(d, d, sq);
-          }
-          tmem_ld_wait();
-          if (c + 2 < CH) tmem_ld_32x32b_x32(trow + col0 + (c + 2) * 32, ra);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float d = __uint_as_float(rb[j]) - mean;
-            sq = fmaf(d, d, sq);
-          }
-        }
-      }
-      if (st0) stamp(ep, ti, 5);
-      stats2[half * 128 + row_in_cta] = sq;
-      named_bar_sync(1 + quarter, 64);
-      const float rstd = rsqrtf((sq + stats2[(half ^ 1) * 128 + row_in_cta]) * (1.0f / LN_N) + ln.eps);
-      // ---- pass 3: normalise + modulate -> bf16 tile (64 columns = 128 B per row) -> bulk store
-      auto pack_h = [&](int c, int pbase, uint8_t* row, const uint32_t (&r)[32]) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint32_t pk[4];
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const float4 mu = *reinterpret_cast<const float4*>(cmul + c * 32 + j * 8 + e * 4);
-            const float4 ad = *reinterpret_cast<const float4*>(cadd + c * 32 + j * 8 + e * 4);
-            const float y0 = fmaf((__uint_as_float(r[8 * j + 4 * e]) - mean) * rstd, mu.x, ad.x);
-            const float y1 = fmaf((__uint_as_float(r[8 * j + 4 * e + 1]) - mean) * rstd, mu.y, ad.y);
-            const float y2 = fmaf((__uint_as_float(r[8 * j + 4 * e + 2]) - mean) * rstd, mu.z, ad.z);
-            const float y3 = fmaf((__uint_as_float(r[8 * j + 4 * e + 3]) - mean) * rstd, mu.w, ad.w);
-            const __nv_bfloat162 lo = __floats2bfloat162_rn(y0, y1), hi = __floats2bfloat162_rn(y2, y3);
-            pk[2 * e] = *reinterpret_cast<const uint32_t*>(&lo);
-            pk[2 * e + 1] = *reinterpret_cast<const uint32_t*>(&hi);
-          }
-          *reinterpret_cast<uint4*>(row + (((uint32_t)(pbase + j) ^ swz) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        }
-      };
-      {
-        uint32_t ra[32], rb[32];
-        tmem_ld_32x32b_x32(trow + col0, ra);
-        tmem_ld_32x32b_x32(trow + col0 + 32, rb);
-#pragma unroll 1
-        for (int c = 0; c < CH; c += 2) {
-          const int u = (c >> 1) & 1;
-          uint8_t* row = myrow0 + u * EBUF_BYTES;
-          if (lane == 0) {                                    // the tile's previous store (pass 1 / pair c - 4) has been read out
-            if (c == 0) bulk_wait_read<0>(); else bulk_wait_read<1>();
-          }
-          __syncwarp();
-          tmem_ld_wait();
-          pack_h(c, 0, row, ra);
-          pack_h(c + 1, 4, row, rb);
-          if (c + 2 < CH) {
-            tmem_ld_32x32b_x32(trow + col0 + (c + 2) * 32, ra);
-            tmem_ld_32x32b_x32(trow + col0 + (c + 3) * 32, rb);
-          } else {                                            // every accumulator column has been read: free the stage
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(te);
-          }
-          fence_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            tma_store_2d(&tmapH, ebuf + u * EBUF_BYTES, col0 + c * 32, slab_row0);
-            bulk_commit();
-          }
-        }
-      }
-      if (st0) stamp(ep, ti, 6);
-      acc_phase ^= 1;
+      epi.prefetch(tmapX, cta_row0);
+      epi.tile(tmapX, tmapH, ep, ln, cta_row0, ti);
     }
     if (lane == 0) bulk_wait_read<0>();                       // shared memory must outlive the last bulk stores' reads
   }

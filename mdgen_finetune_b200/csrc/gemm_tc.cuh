@@ -140,8 +140,7 @@ __device__ __forceinline__ float gelu_erf_fast(float x) {
   q = fmaf(a, q, 1.000037670135498f);
   float h;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(h) : "f"(-q));
-  const float t = x * h;              // x * Phi(-|x|)
-  return x > 0.f ? x - t : t;
+  return fmaf(-a, h, fmaxf(x, 0.f));  // x > 0: x - x Phi(-x);  x < 0: x Phi(x) -- one FMNMX + one FFMA, no select
 }
 
 // ---- epilogue on 32 consecutive accumulator columns of one row --------------------------

@@ -20,6 +20,7 @@
 #include "gemm_tc.cuh"
 #include "gemm_tc2.cuh"
 #include "gemm_ln.cuh"
+#include "gemm_mlp.cuh"
 #include "gemm_qkv_attn.cuh"
 #include "ipa.cuh"
 
@@ -49,6 +50,7 @@ void read_switches() {
   s.no_qkv_attn = on("MDGEN_NO_QKV_ATTN");
   s.no_pair16 = on("MDGEN_NO_PAIR16");
   s.no_pdl = on("MDGEN_NO_PDL");
+  s.no_mlp_fused = on("MDGEN_NO_MLP_FUSED");
   s.gemm_ln_min_m = num("MDGEN_GEMM_LN_MIN_M", 8192);
   s.pair16_store = on("MDGEN_PAIR16_STORE");
   s.attn_var = num("MDGEN_ATTN_VAR", 0);
@@ -221,6 +223,36 @@ int launch_gemm_resid_ln(const bf16* A, int lda, const bf16* W, int ldw, int M, 
   epp.dbg = g_dbg_buf;
   epp.dbg_cta = g_dbg_cta;
   MD_CUDA(launch_pdl(tcln::gemm_ln_kernel, grid, tc::NUM_THREADS, tcln::SMEM_BYTES, st, ta, tw1, tw2, tx, th, M, K, epp, ln));
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// The whole MLP block in one kernel (gemm_mlp.cuh): hid = GELU(A W1^T + b1); x += gate * (hid W2^T + b2); h' = LN-modulate(x).
+// Returns 1 when the shape / alignment is not supported (caller falls back to fc1 + the fused fc2 kernel).
+int launch_gemm_mlp_ln(const bf16* A, int lda, const bf16* W1, const float* b1, const bf16* W2, int M, int Cdim, int F,
+                       const EpiParams& ep, const tcln::LnFuse& ln, cudaStream_t st) {
+  auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
+  if (g_sw.no_mlp_fused) return 1;
+  if (Cdim != tcmlp::C || F != tcmlp::F || M < tcmlp::TILE_M || ep.rows_per_batch < tc::BLOCK_M) return 1;
+  if (!al16(ep.resid) || ep.ldr % 4 != 0 || (ep.bias && !al16(ep.bias)) || (ep.gate && !al16(ep.gate)) || ep.gate_stride % 4 != 0 ||
+      !al16(ln.shift) || !al16(ln.scale) || !al16(ln.out) || (b1 && !al16(b1)))
+    return 1;
+  MD_SMEM_ONCE(tcmlp::gemm_mlp_ln_kernel, tcmlp::SMEM_BYTES);
+  MD_VARIANT(V_GEMM_MLP);
+  CUtensorMap ta, tw1, tw2, tx, th;
+  MD_TRY(make_tmap_2d(&ta, A, M, Cdim, lda, tc::BLOCK_M));
+  MD_TRY(make_tmap_2d(&tw1, W1, F, Cdim, Cdim, tcmlp::BOX_ROWS));
+  MD_TRY(make_tmap_2d(&tw2, W2, Cdim, F, F, tcmlp::BOX_ROWS));
+  MD_TRY(make_tmap_2d_box(&tx, ep.resid, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, M, Cdim, ep.ldr, 32, 32));
+  MD_TRY(make_tmap_2d_box(&th, ln.out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, M, Cdim, Cdim, 64, 32));
+  const int tiles = (M + tcmlp::TILE_M - 1) / tcmlp::TILE_M, pairs = num_sms() / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  ProfScope ps(PC_GEMM_TC, st);
+  EpiParams epp = ep;
+  epp.dbg = g_dbg_buf;
+  epp.dbg_cta = g_dbg_cta;
+  MD_CUDA(launch_pdl(tcmlp::gemm_mlp_ln_kernel, grid, tcmlp::THREADS, tcmlp::SMEM_BYTES, st, ta, tw1, tw2, tx, th, M, b1, epp, ln));
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
@@ -1005,10 +1037,6 @@ struct Fwd {
     const float* scale = ada_row + (size_t)(chunk0 + 1) * C;
     const float* gate = ada_row + (size_t)(chunk0 + 2) * C;
     if (!h_ready) MD_TRY(lnmod(x, (AT*)h->hbuf, M, shift, scale, rows_per_batch, nbatch));
-    EpiParams e1;
-    e1.out = h->mlp;
-    e1.ldo = fc1.N;
-    MD_TRY(gemm((const AT*)h->hbuf, C, fc1, M, EPI_GELU, e1, true));
     EpiParams e2;
     e2.resid = x;
     e2.ldr = C;
@@ -1016,6 +1044,27 @@ struct Fwd {
     e2.gate_stride = h->ada_cols;
     e2.rows_per_batch = rows_per_batch;
     e2.nbatch = nbatch;
+    if constexpr (sizeof(AT) == 2) {
+      // fc1 -> GELU -> fc2 -> residual -> next LayerNorm in one kernel (gemm_mlp.cuh): same size threshold as gemm_ln
+      if (nshift && nscale && x == h->xres && M >= g_sw.gemm_ln_min_m && fc1.K == C && fc2.N == C && fc2.K == fc1.N) {
+        EpiParams e = e2;
+        e.bias = fc2.b;
+        tcln::LnFuse ln;
+        ln.out = (bf16*)h->hbuf;       // in place: a tile's h rows are read before its h' rows are written
+        ln.shift = nshift;
+        ln.scale = nscale;
+        ln.eps = 1e-6f;
+        const int r = launch_gemm_mlp_ln((const bf16*)h->hbuf, C, fc1.wb, fc1.b, fc2.wb, M, C, fc1.N, e, ln, st);
+        if (r <= 0) {
+          h_ready = (r == 0);
+          return r;
+        }
+      }
+    }
+    EpiParams e1;
+    e1.out = h->mlp;
+    e1.ldo = fc1.N;
+    MD_TRY(gemm((const AT*)h->hbuf, C, fc1, M, EPI_GELU, e1, true));
     return resid_gemm((const AT*)h->mlp, fc1.N, fc2, M, e2, nshift, nscale);
   }
 };
@@ -1398,7 +1447,7 @@ static unsigned switches_hash() {
   const Switches& s = g_sw;
   unsigned hsh = 0;
   const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta,
-                       s.no_qkv_attn, s.no_pair16, s.pair16_store, s.no_pdl};
+                       s.no_qkv_attn, s.no_pair16, s.pair16_store, s.no_pdl, s.no_mlp_fused};
   for (bool b : bits) hsh = (hsh << 1) | (b ? 1u : 0u);
   return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009 + s.gemm_ln_min_m * 7);
 }
@@ -1828,9 +1877,10 @@ int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float
   if (!use_tc) return launch_gemm_simt<float, float>(A, K, W, K, M, N, K, EPI_STORE, ep, st);
   bf16 *Ab = nullptr, *Wb = nullptr;
   MD_CUDA(cudaMalloc((void**)&Ab, (size_t)M * K * 2));
-  MD_CUDA(cudaMalloc((void**)&Wb, (size_t)N * K * 2));
+  const size_t wn = use_tc == 6 ? (size_t)2 * tcmlp::F * tcmlp::C : (size_t)N * K;      // mode 6: W = [W1 | W2]
+  MD_CUDA(cudaMalloc((void**)&Wb, wn * 2));
   f32_to_bf16_kernel<<<(unsigned)(((size_t)M * K + 255) / 256), 256, 0, st>>>(A, Ab, (size_t)M * K, 1.f);
-  f32_to_bf16_kernel<<<(unsigned)(((size_t)N * K + 255) / 256), 256, 0, st>>>(W, Wb, (size_t)N * K, 1.f);
+  f32_to_bf16_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, st>>>(W, Wb, wn, 1.f);
   // use_tc: 1 fp32 store | 2 bf16 store | 3 bf16 erf-GELU | 4 C += bias[n] * (acc + bias[n])  (gate = bias, one batch)
   bf16* Cb = nullptr;
   int r = 0;
@@ -1871,6 +1921,31 @@ int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float
     r = launch_gemm_resid_ln(Ab, K, Wb, K, M, N, K, ep, ln, st);
     if (r == 1) {
       set_error("mdgen_test_gemm: shape not supported by the fused residual + LayerNorm kernel");
+      r = MDGEN_EINVAL;
+    }
+    if (r == 0) bf16_rows_to_f32_kernel<<<(unsigned)(((size_t)M * N + 255) / 256), 256, 0, st>>>(Cb, N, Cout + (size_t)M * N, N, M, N);
+  } else if (use_tc == 6) {
+    // the whole MLP block (gemm_mlp.cuh), N = K = 384: W = [W1 (1536, 384) | W2 (384, 1536)], bias = [b1 (1536) | b2 (384) |
+    // gate (2, 384) | shift (2, 384) | scale (2, 384)], batch element and Cout as in mode 5
+    MD_CHECK(N == tcmlp::C && K == tcmlp::C, "mdgen_test_gemm mode 6: N = K = 384");
+    const float* v = bias + tcmlp::F;
+    ep.bias = v;
+    ep.out = nullptr;
+    ep.resid = Cout;
+    ep.ldr = N;
+    ep.gate = v + N;
+    ep.gate_stride = N;
+    ep.rows_per_batch = 200;
+    ep.nbatch = 2;
+    MD_CUDA(cudaMalloc((void**)&Cb, (size_t)M * N * 2));
+    tcln::LnFuse ln;
+    ln.out = Cb;
+    ln.shift = v + 3 * N;
+    ln.scale = v + 5 * N;
+    ln.eps = 1e-6f;
+    r = launch_gemm_mlp_ln(Ab, K, Wb, bias, Wb + (size_t)tcmlp::F * tcmlp::C, M, N, tcmlp::F, ep, ln, st);
+    if (r == 1) {
+      set_error("mdgen_test_gemm: shape not supported by the fused MLP kernel");
       r = MDGEN_EINVAL;
     }
     if (r == 0) bf16_rows_to_f32_kernel<<<(unsigned)(((size_t)M * N + 255) / 256), 256, 0, st>>>(Cb, N, Cout + (size_t)M * N, N, M, N);

@@ -259,6 +259,7 @@ def test_full_size_velocity_and_short_rollout_vs_reference(name, prec):
         assert used["graph_replays"] > 0, used            # the sampler call replays the whole-rollout graph
         if N >= 8192:
             assert used["gemm_ln"] > 0, used              # fused projection + residual + next LayerNorm
+            assert used["gemm_mlp"] > 0, used             # fc1 + GELU + fc2 + residual + next LayerNorm in one kernel
         if N >= 74 * 256:
             assert used["gemm_tc2"] > 0, used             # CTA-pair kernel (cta_group::2)
         if c["L"] == 4:
@@ -267,7 +268,8 @@ def test_full_size_velocity_and_short_rollout_vs_reference(name, prec):
 
 
 @pytest.mark.parametrize("switch", ["MDGEN_NO_GEMM_LN", "MDGEN_NO_GEMM_2CTA", "MDGEN_NO_GEMM_WS", "MDGEN_NO_L2_PERSIST",
-                                    "MDGEN_NO_GRAPH", "MDGEN_NO_QKV_ATTN", "MDGEN_NO_PAIR16", "MDGEN_PAIR16_STORE"])
+                                    "MDGEN_NO_GRAPH", "MDGEN_NO_QKV_ATTN", "MDGEN_NO_PAIR16", "MDGEN_PAIR16_STORE",
+                                    "MDGEN_NO_MLP_FUSED", "MDGEN_NO_PDL"])
 def test_config3_kernel_variants_agree(switch, monkeypatch):
     """Every variant switch of DESIGN.md section 2 must leave the config-3 result within bf16 rounding of the default
     dispatch and within the north_star tolerance of the reference golden."""
