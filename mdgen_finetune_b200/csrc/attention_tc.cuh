@@ -34,6 +34,7 @@
 namespace mdgen {
 namespace atc {
 
+using tc::elect_one;
 using tc::mbar_arrive;
 using tc::mbar_init;
 using tc::mbar_wait;
@@ -377,24 +378,26 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
 
   if (warp < SOFT_WARP0) {
     // =============================== MMA issuers ===============================
-    // Lane 0 of warp w issues every tcgen05.mma of warpgroup w.  Queue order per unit:
+    // Warp w walks the issue loop of warpgroup w warp-uniformly; one elected lane issues the tcgen05.mma / commits
+    // (tc::elect_one: from a `lane == 0` branch every MMA costs ~10 dependent instructions).  Queue order per unit:
     //   QK(0) QK(1) | PV(0) QK(2) | PV(1) QK(3) | ... | PV(n-2) | PV(n-1)
     // each group behind "P(j) ready" and followed by a commit on s_full[j & 1], which therefore means both
     // "S(j+2) has landed" and "P.V(j) and everything before it has retired".
     setmaxnreg_dec<REGS_MMA>();
     const int w = warp;
-    if (lane == 0) {
+    {
       uint32_t np0 = 0, np1 = 0, np2 = 0; // P-ready phases consumed per S buffer
       uint32_t gblk = 0, quse = 0;        // ring blocks consumed by earlier units, units this warpgroup was active in
       const uint32_t id_qk = idesc(QT, SB, false), id_pv = idesc(QT, DP, true);
-      if (w == 0) dbg_stamp(dbg, 14);
+      if (w == 0 && lane == 0) dbg_stamp(dbg, 14);
       for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x, gblk += nkb) {
         const Unit u = decode_unit(p, unit, chunks_per_seq);
         if (w >= u.ntiles) {              // idle warpgroup: only hands the ring slots back
           for (int kb = 0; kb < nkb; ++kb) {
             const uint32_t g = gblk + kb, slot = g % NSLOT;
             mbar_wait(&bars->kv_full[slot], (g / NSLOT) & 1);
-            mbar_arrive(&bars->kv_empty[slot]);
+            if (elect_one()) mbar_arrive(&bars->kv_empty[slot]);
+            __syncwarp();
           }
           continue;
         }
@@ -414,18 +417,22 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
             tcgen05_fence_after();
           }
           const uint32_t ka = sK + slot * RBLK_BYTES + sub * (SB * 16);
-          if (!(var & 8) || j < NBUF) {
+          if (elect_one()) {
+            if (!(var & 8) || j < NBUF) {
 #pragma unroll
-            for (int jj = 0; jj < DP / 16; ++jj)
-              umma_bf16(tW + TM_S + (j % NBUF) * SB, desc_nosw(qa + jj * 2 * GRP_BYTES, GRP_BYTES, 128),
-                        desc_nosw(ka + jj * 2 * RGRP_BYTES, RGRP_BYTES, 128), id_qk, jj);
+              for (int jj = 0; jj < DP / 16; ++jj)
+                umma_bf16(tW + TM_S + (j % NBUF) * SB, desc_nosw(qa + jj * 2 * GRP_BYTES, GRP_BYTES, 128),
+                          desc_nosw(ka + jj * 2 * RGRP_BYTES, RGRP_BYTES, 128), id_qk, jj);
+            }
+            if (j == nsb - 1) tcgen05_commit(&bars->q_empty[qbuf][w]);   // every Q.K^T of the unit is queued: Q buffer free when they retire
           }
-          if (j == nsb - 1) tcgen05_commit(&bars->q_empty[qbuf][w]);   // every Q.K^T of the unit is queued: Q buffer free when they retire
+          __syncwarp();
         };
 #pragma unroll
         for (int j0 = 0; j0 < NBUF; ++j0) {                        // prime every S buffer (nsb >= NBUF)
           issue_qk(j0);
-          tcgen05_commit(&bars->s_full[w][j0]);
+          if (elect_one()) tcgen05_commit(&bars->s_full[w][j0]);
+          __syncwarp();
         }
         for (int j = 0; j < nsb; ++j) {
           const int b = j % NBUF, sub = j % BPR;
@@ -435,19 +442,23 @@ attention_tc_kernel(AttnParams<bf16> p, int chunks_per_seq, int nunits, long lon
           tcgen05_fence_after();
           const uint32_t g = gblk + j / BPR, slot = g % NSLOT;
           const uint32_t va = sV + slot * RBLK_BYTES + sub * (SB * 16);
-          if (!(var & 4)) {
+          if (elect_one()) {
+            if (!(var & 4)) {
 #pragma unroll
-            for (int kk = 0; kk < SB / 16; ++kk)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
-              umma_bf16_ts(tW + TM_O, tW + TM_S + b * SB + kk * 8, desc_nosw(va + kk * 256, 128, RGRP_BYTES), id_pv,
-                           (j == 0 && kk == 0) ? 0u : 1u);
+              for (int kk = 0; kk < SB / 16; ++kk)      // 16 keys per MMA: 8 packed P columns, two 8-key groups of V
+                umma_bf16_ts(tW + TM_O, tW + TM_S + b * SB + kk * 8, desc_nosw(va + kk * 256, 128, RGRP_BYTES), id_pv,
+                             (j == 0 && kk == 0) ? 0u : 1u);
+            }
+            if (sub == BPR - 1 || j == nsb - 1) tcgen05_commit(&bars->kv_empty[slot]);   // this warpgroup is done with the ring block
           }
-          if (sub == BPR - 1 || j == nsb - 1) tcgen05_commit(&bars->kv_empty[slot]);   // this warpgroup is done with the ring block
+          __syncwarp();
           if (j + NBUF < nsb) issue_qk(j + NBUF);
-          tcgen05_commit(&bars->s_full[w][b]);
+          if (elect_one()) tcgen05_commit(&bars->s_full[w][b]);
+          __syncwarp();
         }
         ++quse;
       }
-      if (w == 0) dbg_stamp(dbg, 15);
+      if (w == 0 && lane == 0) dbg_stamp(dbg, 15);
     }
   } else if (warp < PROD_WARP0) {
     // =============================== softmax warps ===============================

@@ -375,8 +375,8 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (leader CTA): per k-step one N = 256 and one N = 128 MMA =====
-    if (lane == 0 && rank == 0) {
+    // ===== MMA issuer (leader CTA, warp-uniform, one elected lane issues): per k-step one N = 256 and one N = 128 MMA =====
+    if (rank == 0) {
       constexpr uint32_t idesc1 = make_idesc_bf16(TILE_M, 256), idesc2 = make_idesc_bf16(TILE_M, 128);
       int stage = 0;
       uint32_t phase = 0, acc_phase = 0;
@@ -384,7 +384,7 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
         mbar_wait(tmem_empty, acc_phase ^ 1);
         tcgen05_fence_after();
-        stamp(ep, ti, 0);
+        if (lane == 0) stamp(ep, ti, 0);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tcgen05_fence_after();
@@ -392,20 +392,23 @@ gemm_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           const uint64_t adesc = make_smem_desc_sw128(sa);
           const uint64_t b1desc = make_smem_desc_sw128(sa + A_STAGE_BYTES);
           const uint64_t b2desc = make_smem_desc_sw128(sa + A_STAGE_BYTES + W1_ROWS * BLOCK_K * 2);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            const uint32_t accum = (kb | k) != 0 ? 1u : 0u;
-            umma_bf16_pair(tmem_base, adesc + (uint64_t)(k * 2), b1desc + (uint64_t)(k * 2), idesc1, accum);
-            umma_bf16_pair(tmem_base + 256, adesc + (uint64_t)(k * 2), b2desc + (uint64_t)(k * 2), idesc2, accum);
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+              const uint32_t accum = (kb | k) != 0 ? 1u : 0u;
+              umma_bf16_pair(tmem_base, adesc + (uint64_t)(k * 2), b1desc + (uint64_t)(k * 2), idesc1, accum);
+              umma_bf16_pair(tmem_base + 256, adesc + (uint64_t)(k * 2), b2desc + (uint64_t)(k * 2), idesc2, accum);
+            }
+            tcgen05_commit_pair(&empty_bar[stage]);
+            if (kb == num_kb - 1) tcgen05_commit_pair(tmem_full);
           }
-          tcgen05_commit_pair(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tcgen05_commit_pair(tmem_full);
-        stamp(ep, ti, 1);
+        if (lane == 0) stamp(ep, ti, 1);
         acc_phase ^= 1;
       }
     }

@@ -82,19 +82,6 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
       "r"(parity)
       : "memory");
 }
-// one lane of a converged warp.  The MMA issuer runs its loop warp-uniformly and issues under elect_one(): descriptors stay in
-// uniform registers and one tcgen05.mma costs ~3 instructions.  Issued from a `lane == 0` branch instead, the compiler
-// wraps every tcgen05.mma in a uniformising loop (R2UR / ELECT / BRA.U.ANY, ~10 dependent instructions), and with two
-// GELU warps competing for the same scheduler the ISSUE of the MMAs became slower than their execution (tools/mlp_trace.py).
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile(
-      "{\n\t.reg .pred P;\n\t"
-      "elect.sync _|P, 0xffffffff;\n\t"
-      "selp.u32 %0, 1, 0, P;\n\t}"
-      : "=r"(pred));
-  return pred != 0;
-}
 // publishes this thread's (fenced) shared-memory writes to the waiter in the leader CTA
 __device__ __forceinline__ void mbar_arrive_release_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");

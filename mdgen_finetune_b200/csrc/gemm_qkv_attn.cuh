@@ -348,8 +348,8 @@ gemm_qkv_attn4_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_co
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: one thread of the leader CTA drives both tensor cores =====
-    if (lane == 0 && rank == 0) {
+    // ===== MMA issuer: warp 1 of the leader CTA walks the loop, one elected lane drives both tensor cores (tc::elect_one) =====
+    if (rank == 0) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -366,16 +366,19 @@ gemm_qkv_attn4_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_co
           const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
           const uint64_t adesc = make_smem_desc_sw128(sa);
           const uint64_t bdesc = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-            umma_bf16_pair(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
-          tcgen05_commit_pair(&empty_bar[stage]);   // frees this stage in both CTAs
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+              umma_bf16_pair(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+            tcgen05_commit_pair(&empty_bar[stage]);   // frees this stage in both CTAs
+            if (kb == num_kb - 1) tcgen05_commit_pair(&tmem_full[acc]);
+          }
+          __syncwarp();
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tcgen05_commit_pair(&tmem_full[acc]);
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;

@@ -73,6 +73,19 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* ba
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// one lane of a converged warp.  The MMA issuer runs its loop warp-uniformly and issues under elect_one(): descriptors stay in
+// uniform registers and one tcgen05.mma costs ~3 instructions.  Issued from a `lane == 0` branch instead, the compiler
+// wraps every tcgen05.mma in a uniformising loop (R2UR / ELECT / BRA.U.ANY, ~10 dependent instructions), and with two
+// GELU warps competing for the same scheduler the ISSUE of the MMAs became slower than their execution (tools/mlp_trace.py; first seen in gemm_mlp.cuh).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_commit(uint64_t* bar) {
@@ -583,8 +596,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer: the warp walks the loop, one elected lane issues (elect_one) =====
+    {
       constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN);
       int stage = 0;
       uint32_t phase = 0;
@@ -604,18 +617,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
           const uint32_t sa = smem_u32(ring + stage * STAGE_BYTES);
           const uint64_t adesc = make_smem_desc_sw128(sa);
           const uint64_t bdesc = make_smem_desc_sw128(WS ? smem_u32(smem + kb * W_KB_BYTES) : sa + A_STAGE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
-            umma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+              // advance 16 bf16 = 32 B inside the 128 B swizzle row: +2 in the (addr >> 4) field
+              umma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            tcgen05_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+            if (kb == num_kb - 1) tcgen05_commit(&tmem_full[acc]);  // accumulator ready for the epilogue
           }
-          tcgen05_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          __syncwarp();
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tcgen05_commit(&tmem_full[acc]);  // accumulator ready for the epilogue
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;

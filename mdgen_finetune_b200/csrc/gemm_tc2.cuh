@@ -192,8 +192,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: one thread of the leader CTA drives both tensor cores =====
-    if (lane == 0 && rank == 0) {
+    // ===== MMA issuer: warp 1 of the leader CTA walks the loop, one elected lane drives both tensor cores (tc::elect_one) =====
+    if (rank == 0) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -201,29 +201,32 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant
       int mb, nb, n_cur;
       for (int i = 0; get_tile(i, mb, nb, n_cur); ++i) {
         const uint32_t idesc = make_idesc_bf16(TILE_M, n_cur);
-        stamp(ep, i, 0);
+        if (lane == 0) stamp(ep, i, 0);
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tcgen05_fence_after();
-        stamp(ep, i, 1);
+        if (lane == 0) stamp(ep, i, 1);
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TILE_N);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tcgen05_fence_after();
-          if (kb < 6) stamp(ep, i, 2 + kb);
+          if (kb < 6 && lane == 0) stamp(ep, i, 2 + kb);
           const uint32_t sa = smem_u32(smem + stage * STAGE2_BYTES);
           const uint64_t adesc = make_smem_desc_sw128(sa);
           const uint64_t bdesc = make_smem_desc_sw128(sa + A_STAGE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-            umma_bf16_pair(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
-          tcgen05_commit_pair(&empty_bar[stage]);   // frees this stage in both CTAs
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+              umma_bf16_pair(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+            tcgen05_commit_pair(&empty_bar[stage]);   // frees this stage in both CTAs
+            if (kb == num_kb - 1) tcgen05_commit_pair(&tmem_full[acc]);
+          }
+          __syncwarp();
           if (++stage == STAGES2) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tcgen05_commit_pair(&tmem_full[acc]);
-        stamp(ep, i, 8);
+        if (lane == 0) stamp(ep, i, 8);
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
