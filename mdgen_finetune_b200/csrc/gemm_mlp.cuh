@@ -65,7 +65,8 @@ constexpr int OFF_RING1 = OFF_H + H_BYTES;
 constexpr int OFF_RING2 = OFF_RING1 + STAGES * STAGE_BYTES;
 constexpr int OFF_B1 = OFF_RING2 + STAGES * STAGE_BYTES;     // [8 warps][64] the current chunk's fc1 bias
 constexpr int OFF_BAR = OFF_B1 + NUM_EPI_WARPS * 256;
-constexpr int SMEM_BYTES = OFF_BAR + 512;
+constexpr int OFF_TRACE = OFF_BAR + 512;                      // 64 clock stamps of the traced epilogue thread (tools/mlp_trace.py)
+constexpr int SMEM_BYTES = OFF_TRACE + 512;
 static_assert(OFF_CV + CV_BYTES + STATS_BYTES <= A1_BYTES, "epilogue tiles and vectors must fit in the h rows they alias");
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 static_assert(OFF_H % 1024 == 0 && OFF_RING1 % 1024 == 0 && OFF_RING2 % 1024 == 0 && STAGE_BYTES % 1024 == 0, "SWIZZLE_128B bases");
@@ -82,9 +83,13 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
       "r"(parity)
       : "memory");
 }
-// publishes this thread's (fenced) shared-memory writes to the waiter in the leader CTA
-__device__ __forceinline__ void mbar_arrive_release_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+// Publishes this thread's (proxy-fenced) shared-memory writes to the MMA issuer in the leader CTA: release at CTA scope on a
+// barrier that may be remote -- the form CUTLASS's ClusterBarrier::arrive(cta_id) emits.  The data itself never crosses
+// the pair: each SM's tensor core reads its OWN CTA's rows of the A operand, and fence.proxy.async has made this thread's
+// stores visible to that SM's async proxy before the arrival is sent.  A release at CLUSTER scope costs a GPU-scope
+// membar here: 1850 clocks per chunk on the critical path (tools/mlp_trace.py: 4250 -> 3400 clocks per chunk without it).
+__device__ __forceinline__ void mbar_arrive_release_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cta.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
@@ -304,6 +309,8 @@ gemm_mlp_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_const
     tcln::LnEpilogue epi;
     epi.init(warp, lane, tmem_base, smem + OFF_EBUF, cv, xbar, tmem_full, tmem_empty);
     float* bj = b1s + (warp - 2) * 64;                       // this warp's 64 fc1 bias values of the current chunk
+    long long* trace = reinterpret_cast<long long*>(smem + OFF_TRACE);   // stamps stay in shared memory until the tile is done:
+                                                                         // global stores would sit in front of the release-arrive
     const int quarter = warp & 3, half = (warp - 2) >> 2;
     const uint32_t tacc1 = tmem_base + ((uint32_t)(quarter * 32) << 16) + ACC1_COL + (uint32_t)(half * 64);
     const uint32_t a1e = map_to_rank(smem_u32(acc1_empty), 0), hf = map_to_rank(smem_u32(h_full), 0);
@@ -324,7 +331,7 @@ gemm_mlp_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         mbar_wait(acc1_full, acc1_phase);
         acc1_phase ^= 1;
         tcgen05_fence_after();
-        if (tr) ep.dbg[2 * 16 + j] = clock64();
+        if (tr) trace[0 * NCHUNK + j] = clock64();
         uint32_t r[64];
         tmem_ld_32x32b_x32(tacc1, r);
         tmem_ld_32x32b_x32(tacc1 + 32, r + 32);
@@ -334,7 +341,6 @@ gemm_mlp_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         tcgen05_fence_before();          // acc1 is in registers: fc1(j+1) may overwrite it
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(a1e);
-        if (tr) ep.dbg[5 * 16 + j] = clock64();
         // bias, erf-GELU, bf16 into registers while fc2(j-1) still reads the previous hidden chunk ...
         uint32_t pk[32];
 #pragma unroll
@@ -351,20 +357,21 @@ gemm_mlp_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_const
           pk[4 * c + 2] = *reinterpret_cast<const uint32_t*>(&p2);
           pk[4 * c + 3] = *reinterpret_cast<const uint32_t*>(&p3);
         }
-        if (tr) ep.dbg[7 * 16 + j] = clock64();
+        if (tr) trace[2 * NCHUNK + j] = clock64();
         // ... then this thread's row of the A operand (8 chunks of 16 bytes) once fc2(j-1) has retired
         mbar_wait(h_empty, h_phase ^ 1);
         h_phase ^= 1;
 #pragma unroll
         for (int c = 0; c < 8; ++c)
           *reinterpret_cast<uint4*>(hrow + (((uint32_t)c ^ swz) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-        if (tr) ep.dbg[6 * 16 + j] = clock64();
         fence_async_smem();                    // visible to the tensor core's (async proxy) reads
+        if (tr) trace[1 * NCHUNK + j] = clock64();
         __syncwarp();                          // ... and every lane is done with this chunk's bias
-        if (lane == 0) mbar_arrive_release_cluster(hf);
+        if (lane == 0) mbar_arrive_release_remote(hf);
+        if (tr) trace[3 * NCHUNK + j] = clock64();
         if (lane < 16) reinterpret_cast<float4*>(bj)[lane] = bnext;
         __syncwarp();
-        if (tr) ep.dbg[3 * 16 + j] = clock64();
+        if (tr) trace[4 * NCHUNK + j] = clock64();
       }
       // ---- acc2 complete (which also means every MMA that read the h rows has retired: the I/O tiles may overwrite them)
       mbar_wait(tmem_full, epi.acc_phase);
@@ -373,7 +380,12 @@ gemm_mlp_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_const
       epi.staged_q = -1;                       // the per-column vectors share the h rows' memory: staged again every tile
       epi.prefetch(tmapX, cta_row0);
       epi.tile(tmapX, tmapH, ep, ln, cta_row0, ti + 8);       // its stamps go to rows 8.. of the timeline buffer
-      if (tr) ep.dbg[4 * 16 + 3] = clock64();
+      if (tr) {
+        ep.dbg[4 * 16 + 3] = clock64();
+        const int rows[5] = {2, 5, 7, 6, 3};
+        for (int q = 0; q < 5; ++q)
+          for (int j = 0; j < NCHUNK; ++j) ep.dbg[rows[q] * 16 + j] = trace[q * NCHUNK + j];
+      }
       if (lane == 0) {
         bulk_wait_read<0>();                   // the last h' tiles have left shared memory: the next tile's h may land
         mbar_arrive(a1_empty);

@@ -31,7 +31,7 @@ print("h rows landed at 0; MMAs all issued %d; acc2 seen by epilogue %d; LayerNo
 print("  j  fc1 issue..end  fc2 issue..end (MMA thread)")
 for j in range(12):
     print("%3d %10d %6d %10d %6d" % (j, d[0][j] - t0, d[10][j] - t0, d[1][j] - t0, d[11][j] - t0))
-print("  j  fc1 issue   fc2 issue | GELU: acc1 seen  drained  math done  stored  published   (clk after the h rows landed)")
+print("  j  fc1 issue   fc2 issue | GELU: acc1 seen  math done  stored+fenced  arrived  bias stored   (clk after the h rows landed)")
 for j in range(12):
-    print("%3d %10d %11d | %14d %8d %10d %7d %11d" % (j, d[0][j] - t0, d[1][j] - t0, d[2][j] - t0, d[5][j] - t0, d[7][j] - t0, d[6][j] - t0, d[3][j] - t0))
+    print("%3d %10d %11d | %14d %8d %10d %7d %11d" % (j, d[0][j] - t0, d[1][j] - t0, d[2][j] - t0, d[7][j] - t0, d[5][j] - t0, d[6][j] - t0, d[3][j] - t0))
 print("LayerNorm epilogue: start %d, acc2 seen %d, pass 1 done %d, pass 2 done %d, pass 3 done %d" % tuple(d[9][k] - t0 for k in (2, 3, 4, 5, 6)))
