@@ -66,7 +66,7 @@ struct DevOnce {
 struct Switches {
   bool no_gemm_ln = false, no_gemm_2cta = false, no_gemm_ws = false, no_l2_persist = false, no_attn_tc = false,
        no_attn_bulk = false, gelu_2cta = false, no_graph = false, no_qkv_attn = false, no_pair16 = false, pair16_store = false, no_pdl = false, no_mlp_fused = false;
-  int attn_var = 0, attn_poly = 0, asb_seq = 4, attn_sb = 48, gemm_ln_min_m = 8192;
+  int attn_var = 0, attn_poly = 0, asb_seq = 4, attn_sb = 48, gemm_ln_min_m = 8192, mlp_min_m = 8192;
 };
 extern thread_local Switches g_sw;
 void read_switches();

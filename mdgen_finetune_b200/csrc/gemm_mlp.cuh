@@ -332,6 +332,9 @@ gemm_mlp_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_const
         acc1_phase ^= 1;
         tcgen05_fence_after();
         if (tr) trace[0 * NCHUNK + j] = clock64();
+        // the last fc1 has retired: the h rows are dead, and the first residual tiles of the LayerNorm epilogue (whose
+        // buffers alias them) can start moving under the last GELU and the last fc2
+        if (j == NCHUNK - 1) epi.prefetch(tmapX, cta_row0);
         uint32_t r[64];
         tmem_ld_32x32b_x32(tacc1, r);
         tmem_ld_32x32b_x32(tacc1 + 32, r + 32);
@@ -378,7 +381,6 @@ gemm_mlp_ln_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_const
       tcgen05_fence_after();
       if (tr) ep.dbg[4 * 16 + 2] = clock64();
       epi.staged_q = -1;                       // the per-column vectors share the h rows' memory: staged again every tile
-      epi.prefetch(tmapX, cta_row0);
       epi.tile(tmapX, tmapH, ep, ln, cta_row0, ti + 8);       // its stamps go to rows 8.. of the timeline buffer
       if (tr) {
         ep.dbg[4 * 16 + 3] = clock64();

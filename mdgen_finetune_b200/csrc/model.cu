@@ -52,6 +52,7 @@ void read_switches() {
   s.no_pdl = on("MDGEN_NO_PDL");
   s.no_mlp_fused = on("MDGEN_NO_MLP_FUSED");
   s.gemm_ln_min_m = num("MDGEN_GEMM_LN_MIN_M", 8192);
+  s.mlp_min_m = num("MDGEN_MLP_MIN_M", 8192);
   s.pair16_store = on("MDGEN_PAIR16_STORE");
   s.attn_var = num("MDGEN_ATTN_VAR", 0);
   s.attn_poly = num("MDGEN_ATTN_POLY", 0);
@@ -1046,7 +1047,7 @@ struct Fwd {
     e2.nbatch = nbatch;
     if constexpr (sizeof(AT) == 2) {
       // fc1 -> GELU -> fc2 -> residual -> next LayerNorm in one kernel (gemm_mlp.cuh): same size threshold as gemm_ln
-      if (nshift && nscale && x == h->xres && M >= g_sw.gemm_ln_min_m && fc1.K == C && fc2.N == C && fc2.K == fc1.N) {
+      if (nshift && nscale && x == h->xres && M >= g_sw.mlp_min_m && fc1.K == C && fc2.N == C && fc2.K == fc1.N) {
         EpiParams e = e2;
         e.bias = fc2.b;
         tcln::LnFuse ln;
@@ -1449,7 +1450,7 @@ static unsigned switches_hash() {
   const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta,
                        s.no_qkv_attn, s.no_pair16, s.pair16_store, s.no_pdl, s.no_mlp_fused};
   for (bool b : bits) hsh = (hsh << 1) | (b ? 1u : 0u);
-  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009 + s.gemm_ln_min_m * 7);
+  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009 + s.gemm_ln_min_m * 7 + s.mlp_min_m * 11);
 }
 
 static void rollout_graph_drop(MdgenHandle* h) {
