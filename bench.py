@@ -140,7 +140,7 @@ def reference_time_forward(cfg_id, B, nfwd=3, warm=1):
 def ncu_traffic(category, cfg_id):
     """DRAM bytes (read + write) per launch of the dominant kernel family from the committed `ncu --set full` capture
     (profiles/r02/traffic_cfg<id>.json, else r01; written by tools/ncu_traffic.py); None when no capture exists for this config."""
-    names = {"gemm_tcgen05": ("gemm_tc_kernel", "gemm_tc2_kernel", "gemm_ln_kernel"), "attention_tcgen05": ("attention_tc_kernel",),
+    names = {"gemm_tcgen05": ("gemm_tc_kernel", "gemm_tc2_kernel", "gemm_ln_kernel", "gemm_mlp_ln_kernel"), "attention_tcgen05": ("attention_tc_kernel",),
              "attention_short": ("attention_seq4_bulk_kernel", "attention_seq_kernel", "attention_short_kernel"),
              "layernorm_modulate": ("ln_modulate_kernel",), "embed": ("embed_step_kernel", "embed_kernel"),
              "qkv_attention_fused": ("gemm_qkv_attn4_kernel",)}
