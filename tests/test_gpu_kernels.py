@@ -160,6 +160,39 @@ def test_gemm_tcgen05_fused_mlp_block(M):
     assert float((out[M:] - hn.float()).norm() / hn.norm()) < 4e-3
 
 
+@pytest.mark.parametrize("M", [256, 300, 1000, 5001, 20000, 37999])
+def test_fused_mlp_block_bit_identical_to_the_two_kernel_path(M):
+    """The one-kernel MLP block accumulates in the same order as fc1 + GELU (pair GEMM) followed by fc2 + residual +
+    LayerNorm (gemm_ln.cuh): both the residual stream and the normalised rows must agree BIT FOR BIT, ragged M included."""
+    C, F = 384, 1536
+    g = torch.Generator().manual_seed(7 * M)
+    A = torch.randn(M, C, generator=g)
+    W1, W2 = torch.randn(F, C, generator=g) / C ** 0.5, torch.randn(C, F, generator=g) / F ** 0.5
+    b1 = torch.randn(F, generator=g) * 0.5
+    vec = torch.randn(7, C, generator=g) * 0.5
+    x0 = torch.randn(M, C, generator=g)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    L = _lib.lib()
+    dA = A.cuda()
+    fused = torch.cat([x0, torch.zeros(M, C)]).cuda()
+    dW = torch.cat([W1.flatten(), W2.flatten()]).cuda()
+    dv = torch.cat([b1, vec.flatten()]).contiguous().cuda()
+    _lib.check(L.mdgen_test_gemm(M, C, C, _p(dA), _p(dW), _p(dv), _p(fused), 6, 0, st), "test_gemm")
+    hid = _gemm(dA, W1.cuda(), b1.cuda(), 3, 0)                       # bf16 values, returned as fp32: exact A operand of fc2
+    two = torch.cat([x0, torch.zeros(M, C)]).cuda()
+    dW2, dvec = W2.contiguous().cuda(), vec.contiguous().cuda()
+    _lib.check(L.mdgen_test_gemm(M, C, F, _p(hid), _p(dW2), _p(dvec), _p(two), 5, 0, st), "test_gemm")
+    torch.cuda.synchronize()
+    assert torch.isfinite(fused).all()
+    assert torch.equal(fused[:M], two[:M]), float((fused[:M] - two[:M]).abs().max())
+    assert torch.equal(fused[M:], two[M:]), float((fused[M:] - two[M:]).abs().max())
+    for _ in range(8):                    # the same launch again and again: a race in the hand-offs would show as a changed bit
+        again = torch.cat([x0, torch.zeros(M, C)]).cuda()
+        _lib.check(L.mdgen_test_gemm(M, C, C, _p(dA), _p(dW), _p(dv), _p(again), 6, 0, st), "test_gemm")
+        torch.cuda.synchronize()
+        assert torch.equal(again, fused)
+
+
 def _attn_ref(qkv, bk, bv, valid, nb, S, inner, H, hd, rope):
     from oracle import mdgen_oracle as O
     C = H * hd
