@@ -402,15 +402,24 @@ __global__ void gather_rows_kernel(const float* __restrict__ table, const int64_
 }
 
 // mean over the frame axis of a [B,T,L,W] tensor slice: out[b,l,w] = mean_t in[b,t,l,off+w]
+// block = (b, l) x 64 channels; its 256 threads are 64 channels x 4 interleaved slices of the frame axis (the one-thread-
+// per-output version walked T serially: 21 us for 100 frames on the design config, launched twice per evaluation)
+constexpr int MOT_W = 64, MOT_S = 4;
 template <typename IT>
-__global__ void mean_over_T_kernel(const IT* __restrict__ in, int ld, int off, int B, int T, int L, int W,
-                                   float* __restrict__ out) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B * L * W) return;
-  int w = i % W, l = (i / W) % L, b = i / (W * L);
+__global__ void __launch_bounds__(MOT_W * MOT_S)
+mean_over_T_kernel(const IT* __restrict__ in, int ld, int off, int B, int T, int L, int W, float* __restrict__ out) {
+  __shared__ float part[MOT_S][MOT_W];
+  const int bl = blockIdx.x, b = bl / L, l = bl % L;
+  const int wl = threadIdx.x % MOT_W, sl = threadIdx.x / MOT_W, w = blockIdx.y * MOT_W + wl;
   float s = 0.f;
-  for (int t = 0; t < T; ++t) s += to_f(in[((size_t)(b * T + t) * L + l) * ld + off + w]);
-  out[i] = s / (float)T;
+  if (w < W) {
+    const IT* src = in + ((size_t)b * T * L + l) * ld + off + w;
+#pragma unroll 4
+    for (int t = sl; t < T; t += MOT_S) s += to_f(src[(size_t)t * L * ld]);
+  }
+  part[sl][wl] = s;
+  __syncthreads();
+  if (sl == 0 && w < W) out[(size_t)bl * W + w] = ((part[0][wl] + part[1][wl]) + (part[2][wl] + part[3][wl])) / (float)T;
 }
 
 // design head tail: latent[b,t,l,D-20+k] += logits[b,l,k]   (latent_model.py:268)

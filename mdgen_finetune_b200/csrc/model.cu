@@ -1180,7 +1180,7 @@ static int ipa_stack(Fwd<AT>& f, int nt, const float* ada_base, const float* x_f
   if (h->flag(MDGEN_F_DESIGN)) {  // x_d = x[..., -20:].mean(1)  (latent_model.py:237-240, 193-194, 205-207)
     MD_CHECK(nt == 1 && x_for_design, "design mode cannot batch time rows (x_d depends on x)");
     const int D = h->D();
-    mean_over_T_kernel<float><<<(BL * 20 + 255) / 256, 256, 0, st>>>(x_for_design, D, D - 20, B, T, L, 20, h->xd);
+    mean_over_T_kernel<float><<<dim3(BL, 1), MOT_W * MOT_S, 0, st>>>(x_for_design, D, D - 20, B, T, L, 20, h->xd);
     MD_LAUNCHED();
     const Tensor* w = find_w(h, "x_d_to_emb.weight");
     const Tensor* b = find_w(h, "x_d_to_emb.bias");
@@ -1323,7 +1323,7 @@ static int trunk(Fwd<AT>& f, const float* x, int step, float* out, float* state,
     } else {
       MD_TRY(f.gemm((const AT*)h->xres, C, h->design_fc1, N, EPI_GELU, e, true));
     }
-    mean_over_T_kernel<AT><<<(B * L * C + 255) / 256, 256, 0, st>>>((const AT*)h->mlp, C, 0, B, T, L, C, h->dh_mean);
+    mean_over_T_kernel<AT><<<dim3(B * L, (C + MOT_W - 1) / MOT_W), MOT_W * MOT_S, 0, st>>>((const AT*)h->mlp, C, 0, B, T, L, C, h->dh_mean);
     MD_LAUNCHED();
     const int BL = B * L;
     EpiParams e2;
