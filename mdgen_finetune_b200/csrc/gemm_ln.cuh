@@ -10,7 +10,7 @@
 // MMAs -- the TMA producer keeps prefetching the next tile's operands meanwhile.
 // Epilogue (warps 2..9, thread = row, two warps per TMEM lane quarter each owning 6 of the 12 32-column chunks):
 //   pass 1  acc -> x_new = x + gate * (acc + bias) -> global x, x_new written back over the accumulator in TMEM, row sum
-//   pass 2  sum of (x_new - mean)^2 from TMEM            (two-pass variance, like ln_modulate_kernel)
+//   (the centred second moment comes from shifted sums accumulated in pass 1; round 1 re-read the row from TMEM for it)
 //   pass 3  normalise, modulate, bf16 -> global h
 // Global x / h traffic of the epilogue moves by TMA: per warp two SWIZZLE_128B tiles (residual tile in, x_new in place and
 // the bf16 h tile out through bulk tensor stores) -- the LDG/STG path reached only ~25 B/clk/SM here.
@@ -163,8 +163,11 @@ struct LnEpilogue {
     mbar_wait(tmem_full, acc_phase);
     tcgen05_fence_after();
     if (st0) stamp(ep, ti, 3);
-    // ---- pass 1: residual update, row sum, x_new back into TMEM and (in place in the tile) out to global
-    float sum = 0.f;
+    // ---- pass 1: residual update, x_new back into TMEM and (in place in the tile) out to global; row statistics in the
+    // same pass as SHIFTED sums (shift = the row's first new value in this column half: s1 = sum(x - shift), q1 = sum((x -
+    // shift)^2), so that the centred second moment q1 - 2 (mean - shift) s1 + n (mean - shift)^2 loses no digits to a
+    // large row mean).  A separate pass over TMEM for the centred squares cost 1300 of the epilogue's 15400 clocks.
+    float s1 = 0.f, q1 = 0.f, shiftv = 0.f;
 #pragma unroll 1
     for (int c2 = 0; c2 < CH; c2 += 2) {
 #pragma unroll
@@ -191,7 +194,13 @@ struct LnEpilogue {
           const float o1 = fmaf(gg[j].y, __uint_as_float(r[4 * j + 1]) + bb[j].y, xr[j].y);
           const float o2 = fmaf(gg[j].z, __uint_as_float(r[4 * j + 2]) + bb[j].z, xr[j].z);
           const float o3 = fmaf(gg[j].w, __uint_as_float(r[4 * j + 3]) + bb[j].w, xr[j].w);
-          sum += (o0 + o1) + (o2 + o3);
+          if (u == 0 && j == 0) shiftv = c2 == 0 ? o0 : shiftv;
+          const float d0 = o0 - shiftv, d1 = o1 - shiftv, d2 = o2 - shiftv, d3 = o3 - shiftv;
+          s1 += (d0 + d1) + (d2 + d3);
+          q1 = fmaf(d0, d0, q1);
+          q1 = fmaf(d1, d1, q1);
+          q1 = fmaf(d2, d2, q1);
+          q1 = fmaf(d3, d3, q1);
           r[4 * j] = __float_as_uint(o0);
           r[4 * j + 1] = __float_as_uint(o1);
           r[4 * j + 2] = __float_as_uint(o2);
@@ -215,33 +224,15 @@ struct LnEpilogue {
     }
     tmem_st_wait();
     if (st0) stamp(ep, ti, 4);
+    constexpr float NH = (float)(CH * 32);                 // columns of this half
+    const float sum = fmaf(NH, shiftv, s1);
     stats[half * 128 + row_in_cta] = sum;
     named_bar_sync(1 + quarter, 64);
     const float mean = (sum + stats[(half ^ 1) * 128 + row_in_cta]) * (1.0f / LN_N);
     named_bar_sync(1 + quarter, 64);                      // both partial sums consumed before the slots are reused
-    // ---- pass 2: centred second moment
-    float sq = 0.f;
-    {
-      uint32_t ra[32], rb[32];
-      tmem_ld_32x32b_x32(trow + col0, ra);
-#pragma unroll 1
-      for (int c = 0; c < CH; c += 2) {
-        tmem_ld_wait();
-        tmem_ld_32x32b_x32(trow + col0 + (c + 1) * 32, rb);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float d = __uint_as_float(ra[j]) - mean;
-          sq = fmaf(d, d, sq);
-        }
-        tmem_ld_wait();
-        if (c + 2 < CH) tmem_ld_32x32b_x32(trow + col0 + (c + 2) * 32, ra);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float d = __uint_as_float(rb[j]) - mean;
-          sq = fmaf(d, d, sq);
-        }
-      }
-    }
+    // ---- centred second moment of this half from the shifted sums
+    const float dm = mean - shiftv;
+    const float sq = fmaf(NH * dm, dm, fmaf(-2.0f * dm, s1, q1));
     if (st0) stamp(ep, ti, 5);
     stats2[half * 128 + row_in_cta] = sq;
     named_bar_sync(1 + quarter, 64);

@@ -100,8 +100,9 @@ def test_gemm_tcgen05_gated_residual_epilogue(M, N, K, bn):
     assert float((C.cpu() - ref).norm() / ref.norm()) < 1e-5
 
 
+@pytest.mark.parametrize("offset", [0.3, 40.0])        # 40: row mean 20 standard deviations away from zero (shifted one-pass variance)
 @pytest.mark.parametrize("M,K", [(256, 384), (1000, 384), (4000, 384), (4000, 1536), (20000, 384), (777, 64)])
-def test_gemm_tcgen05_fused_residual_layernorm(M, K):
+def test_gemm_tcgen05_fused_residual_layernorm(M, K, offset):
     """gemm_ln.cuh: x += gate * (A W^T + b); h = LN(x) * (1 + scale) + shift, batch element switching every 200 rows."""
     N = 384
     g = torch.Generator().manual_seed(M + K)
@@ -110,7 +111,7 @@ def test_gemm_tcgen05_fused_residual_layernorm(M, K):
     # vec = [linear bias (1, N) | gate (2, N) | shift (2, N) | scale (2, N)], row b of each pair = batch element b
     vec = torch.randn(7, N, generator=g) * 0.5
     bias, gate, shift, scale = vec[0], vec[1:3], vec[3:5], vec[5:7]
-    x0 = torch.randn(M, N, generator=g) * 2.0 + 0.3
+    x0 = torch.randn(M, N, generator=g) * 2.0 + offset
     C = torch.cat([x0, torch.zeros(M, N)]).cuda()
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     dA, dW, dv = A.cuda(), W.cuda(), vec.contiguous().cuda()
