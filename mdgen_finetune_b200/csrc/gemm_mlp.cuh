@@ -23,8 +23,10 @@
 //   * after chunk 11 the residual + LayerNorm epilogue of gemm_ln.cuh (tcln::LnEpilogue) runs on acc2; its 64 KB of I/O
 //     tiles and its per-column vectors alias the h rows, which are dead by then (the next tile's h load waits for the
 //     epilogue; the vectors are re-staged every tile).
-// Shared-memory traffic per chunk per CTA: 224 KB of MMA operand reads + 96 KB of TMA writes + 32 KB of hidden-chunk
-// stores in 3072 MMA clocks = 115 B/clk of the ~128 B/clk port -- the A rows being resident is what makes this fit.
+// Shared-memory traffic per chunk per CTA: 256 KB of MMA operand reads (fc1: h 96 + W1 48; fc2: the hidden chunk twice --
+// once per MMA shape -- 64 + W2 48) + 96 KB of TMA writes + 32 KB of hidden-chunk stores = 384 KB in 3072 MMA clocks =
+// 125 B/clk of the ~128 B/clk port: the A rows being resident is what makes this fit at all, and the measured period is
+// 3400 clocks per chunk (fc1 runs at 82 % of its MMA rate while the port is that busy; tools/mlp_trace.py).
 #pragma once
 #include "gemm_ln.cuh"
 
