@@ -25,6 +25,28 @@ def test_library_exports_every_declared_symbol():
     assert lib.mdgen_abi_version() == 1
 
 
+
+def test_variant_names_and_switch_docs_match_the_sources():
+    """_lib.VARIANTS mirrors `enum Variant` of csrc/common.cuh (index = what mdgen_variant_launches takes, as the header says),
+    and every MDGEN_* switch read_switches() reads is described in INTEGRATION.md or DESIGN.md."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    common = open(os.path.join(root, "mdgen_finetune_b200", "csrc", "common.cuh")).read()
+    m = re.search(r"enum Variant : int \{([^}]*)\}", common)
+    names = [v.strip().split("=")[0].strip() for v in m.group(1).split(",")]
+    assert names[-1] == "V_COUNT" and len(names) - 1 == len(_lib.VARIANTS), (names, _lib.VARIANTS)
+    header = open(os.path.join(root, "include", "mdgen_b200.h")).read()
+    for i, v in enumerate(_lib.VARIANTS):
+        assert re.search(r"\b%d %s\b" % (i, v.replace("graph_replays", "whole-rollout graph replays")), header), (i, v)
+    model = open(os.path.join(root, "mdgen_finetune_b200", "csrc", "model.cu")).read()
+    body = model[model.index("void read_switches()"):]
+    body = body[:body.index("\n}\n")]
+    switches = set(re.findall(r'"(MDGEN_[A-Z0-9_]+)"', body))
+    docs = open(os.path.join(root, "INTEGRATION.md")).read() + open(os.path.join(root, "DESIGN.md")).read()
+    missing = sorted(v for v in switches if v not in docs)
+    assert not missing, missing
+
+
 @pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5])
 def test_state_dict_layout_and_strict_load(cfg):
     from mdgen_finetune_b200 import LatentMDGenModel
