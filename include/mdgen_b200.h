@@ -180,7 +180,8 @@ long long mdgen_launch_count(void);
 /* Launches per kernel variant since load: 0 gemm_ln (fused projection + residual + LayerNorm), 1 gemm_tc2 (CTA pair),
  * 2 gemm_tc, 3 attention_tc, 4 attention_seq4 (residue axis, 5 keys), 5 whole-rollout graph replays, 6 qkv_attn4 (q/k/v
  * projection fused with the residue-axis attention at L = 4), 7 gemm_mlp (fc1 + GELU + fc2 + residual + LayerNorm in one
- * kernel); -1 if out of range.
+ * kernel), 8 gemm_ln4 (projection + residual + LayerNorm for fewer than 8192 rows, row split over a cluster of 4 CTAs);
+ * -1 if out of range.
  * Launches captured into a rollout graph are counted once, at capture. */
 long long mdgen_variant_launches(int32_t which);
 /* Bytes of device workspace currently held by the handle. */

@@ -25,7 +25,7 @@ EXPORTS = ["mdgen_create", "mdgen_destroy", "mdgen_last_error", "mdgen_abi_versi
            "mdgen_variant_launches", "mdgen_gemm_noalloc", "mdgen_backward"]
 NOALLOC_MAX_OPERAND_ELEMS = 1 << 21      # MDGEN_NOALLOC_MAX_OPERAND_ELEMS
 # kernel variants counted by mdgen_variant_launches(i) (tests assert that the full-size cases reach the timed kernels)
-VARIANTS = ["gemm_ln", "gemm_tc2", "gemm_tc", "attention_tc", "attention_seq4", "graph_replays", "qkv_attn4", "gemm_mlp"]
+VARIANTS = ["gemm_ln", "gemm_tc2", "gemm_tc", "attention_tc", "attention_seq4", "graph_replays", "qkv_attn4", "gemm_mlp", "gemm_ln4"]
 
 
 class MdgenConfig(ctypes.Structure):

@@ -65,14 +65,14 @@ struct DevOnce {
 // CALL (read_switches() at the entry points), never per launch.
 struct Switches {
   bool no_gemm_ln = false, no_gemm_2cta = false, no_gemm_ws = false, no_l2_persist = false, no_attn_tc = false,
-       no_attn_bulk = false, gelu_2cta = false, no_graph = false, no_qkv_attn = false, no_pair16 = false, pair16_store = false, no_pdl = false, no_mlp_fused = false;
-  int attn_var = 0, attn_poly = 0, asb_seq = 4, attn_sb = 48, gemm_ln_min_m = 8192, mlp_min_m = 8192;
+       no_attn_bulk = false, gelu_2cta = false, no_graph = false, no_qkv_attn = false, no_pair16 = false, pair16_store = false, no_pdl = false, no_mlp_fused = false, no_gemm_ln4 = false;
+  int attn_var = 0, attn_poly = 0, asb_seq = 4, attn_sb = 48, gemm_ln_min_m = 8192, mlp_min_m = 8192, ln4_min_m = 1024;
 };
 extern thread_local Switches g_sw;
 void read_switches();
 
 // launches per kernel variant (mdgen_variant_launches): tests assert that the full-size cases reach the timed kernels
-enum Variant : int { V_GEMM_LN = 0, V_GEMM_TC2, V_GEMM_TC, V_ATTN_TC, V_ATTN_SEQ4, V_GRAPH_REPLAY, V_QKV_ATTN, V_GEMM_MLP, V_COUNT };
+enum Variant : int { V_GEMM_LN = 0, V_GEMM_TC2, V_GEMM_TC, V_ATTN_TC, V_ATTN_SEQ4, V_GRAPH_REPLAY, V_QKV_ATTN, V_GEMM_MLP, V_GEMM_LN4, V_COUNT };
 extern std::atomic<long long> g_variant[V_COUNT];
 #define MD_VARIANT(v) (mdgen::g_variant[v].fetch_add(1, std::memory_order_relaxed))
 

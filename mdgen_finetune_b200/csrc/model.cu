@@ -21,6 +21,7 @@
 #include "gemm_tc2.cuh"
 #include "gemm_ln.cuh"
 #include "gemm_mlp.cuh"
+#include "gemm_ln4.cuh"
 #include "gemm_qkv_attn.cuh"
 #include "ipa.cuh"
 
@@ -51,6 +52,8 @@ void read_switches() {
   s.no_pair16 = on("MDGEN_NO_PAIR16");
   s.no_pdl = on("MDGEN_NO_PDL");
   s.no_mlp_fused = on("MDGEN_NO_MLP_FUSED");
+  s.no_gemm_ln4 = on("MDGEN_NO_GEMM_LN4");
+  s.ln4_min_m = num("MDGEN_LN4_MIN_M", 1024);
   s.gemm_ln_min_m = num("MDGEN_GEMM_LN_MIN_M", 8192);
   s.mlp_min_m = num("MDGEN_MLP_MIN_M", 8192);
   s.pair16_store = on("MDGEN_PAIR16_STORE");
@@ -224,6 +227,34 @@ int launch_gemm_resid_ln(const bf16* A, int lda, const bf16* W, int ldw, int M, 
   epp.dbg = g_dbg_buf;
   epp.dbg_cta = g_dbg_cta;
   MD_CUDA(launch_pdl(tcln::gemm_ln_kernel, grid, tc::NUM_THREADS, tcln::SMEM_BYTES, st, ta, tw1, tw2, tx, th, M, K, epp, ln));
+  MD_LAUNCHED();
+  MD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// The same fusion for small token counts (gemm_ln4.cuh): a cluster of 4 CTAs per 128-row tile, 96 columns each.
+// Returns 1 when the shape / alignment is not supported.
+int launch_gemm_resid_ln4(const bf16* A, int lda, const bf16* W, int ldw, int M, int N, int K, const EpiParams& ep,
+                          const tcln::LnFuse& ln, cudaStream_t st, bool force = false) {
+  auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
+  if (g_sw.no_gemm_ln4) return 1;
+  if (N != tcln4::LN_N || K % tc::BLOCK_K != 0 || M < tcln4::TILE_M || ep.rows_per_batch < tcln4::TILE_M) return 1;
+  // one CTA per SM (215 KB of shared memory) and no persistence: beyond one wave of clusters the plain GEMM + LayerNorm wins
+  // (config 2, 6400 rows = 200 CTAs: 34.3 vs 31.7 ms per rollout); `force` is the unit-test entry
+  if (!force && tcln4::CL * ((M + tcln4::TILE_M - 1) / tcln4::TILE_M) > num_sms()) return 1;
+  if (!al16(ep.resid) || ep.ldr % 4 != 0 || (ep.bias && !al16(ep.bias)) || (ep.gate && !al16(ep.gate)) || ep.gate_stride % 4 != 0 ||
+      !al16(ln.shift) || !al16(ln.scale) || !al16(ln.out))
+    return 1;
+  MD_SMEM_ONCE(tcln4::gemm_ln4_kernel, tcln4::SMEM_BYTES);
+  MD_VARIANT(V_GEMM_LN4);
+  CUtensorMap ta, tw, tx, th;
+  MD_TRY(make_tmap_2d(&ta, A, M, K, lda, tc::BLOCK_M));
+  MD_TRY(make_tmap_2d(&tw, W, N, K, ldw, tcln4::N_CTA));
+  MD_TRY(make_tmap_2d_box(&tx, ep.resid, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, M, N, ep.ldr, 32, 32));
+  MD_TRY(make_tmap_2d_box(&th, ln.out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, M, N, N, 32, 32));
+  const int tiles = (M + tcln4::TILE_M - 1) / tcln4::TILE_M;
+  ProfScope ps(PC_GEMM_TC, st);
+  MD_CUDA(launch_pdl(tcln4::gemm_ln4_kernel, tcln4::CL * tiles, tcln4::THREADS, tcln4::SMEM_BYTES, st, ta, tw, tx, th, M, K, ep, ln));
   MD_LAUNCHED();
   MD_CUDA(cudaGetLastError());
   return 0;
@@ -946,6 +977,19 @@ struct Fwd {
           h_ready = (r == 0);
           return r;
         }
+      } else if (nshift && nscale && ep.resid == h->xres && M >= g_sw.ln4_min_m) {
+        // small token counts: the row split over a cluster of 4 CTAs (gemm_ln4.cuh)
+        ep.bias = w.b;
+        tcln::LnFuse ln;
+        ln.out = (bf16*)h->hbuf;
+        ln.shift = nshift;
+        ln.scale = nscale;
+        ln.eps = 1e-6f;
+        const int r = launch_gemm_resid_ln4((const bf16*)A, lda, w.wb, w.K, M, w.N, w.K, ep, ln, st);
+        if (r <= 0) {
+          h_ready = (r == 0);
+          return r;
+        }
       }
     }
     return gemm(A, lda, w, M, EPI_GATE_RESID, ep, false);
@@ -1448,9 +1492,9 @@ static unsigned switches_hash() {
   const Switches& s = g_sw;
   unsigned hsh = 0;
   const bool bits[] = {s.no_gemm_ln, s.no_gemm_2cta, s.no_gemm_ws, s.no_l2_persist, s.no_attn_tc, s.no_attn_bulk, s.gelu_2cta,
-                       s.no_qkv_attn, s.no_pair16, s.pair16_store, s.no_pdl, s.no_mlp_fused};
+                       s.no_qkv_attn, s.no_pair16, s.pair16_store, s.no_pdl, s.no_mlp_fused, s.no_gemm_ln4};
   for (bool b : bits) hsh = (hsh << 1) | (b ? 1u : 0u);
-  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009 + s.gemm_ln_min_m * 7 + s.mlp_min_m * 11);
+  return hsh * 1000003u + (unsigned)(s.attn_var * 97 + s.attn_poly * 13 + s.asb_seq + s.attn_sb * 1009 + s.gemm_ln_min_m * 7 + s.mlp_min_m * 11 + s.ln4_min_m * 17);
 }
 
 static void rollout_graph_drop(MdgenHandle* h) {
@@ -1919,7 +1963,8 @@ int mdgen_test_gemm(int32_t M, int32_t N, int32_t K, const float* A, const float
     ln.shift = bias + 3 * N;
     ln.scale = bias + 5 * N;
     ln.eps = 1e-6f;
-    r = launch_gemm_resid_ln(Ab, K, Wb, K, M, N, K, ep, ln, st);
+    r = block_n == 4 ? launch_gemm_resid_ln4(Ab, K, Wb, K, M, N, K, ep, ln, st, true)  // block_n 4: the cluster-of-4 kernel
+                     : launch_gemm_resid_ln(Ab, K, Wb, K, M, N, K, ep, ln, st);
     if (r == 1) {
       set_error("mdgen_test_gemm: shape not supported by the fused residual + LayerNorm kernel");
       r = MDGEN_EINVAL;

@@ -63,6 +63,48 @@ def test_gemm_tcgen05_bf16_out_staged_epilogue(M, N, K, bn, mode):
     assert err < 4e-3, err          # one bf16 rounding of the output
 
 
+@pytest.mark.parametrize("offset", [0.3, 40.0])
+@pytest.mark.parametrize("M,K", [(128, 384), (300, 384), (1000, 384), (4000, 384), (4000, 1536), (6400, 384), (777, 64)])
+def test_gemm_tcgen05_fused_residual_layernorm_cluster_of_four(M, K, offset):
+    """gemm_ln4.cuh (small token counts): the row split over a cluster of 4 CTAs, LayerNorm statistics exchanged through
+    distributed shared memory.  Same operands and reference as the pair kernel's test; the residual stream must equal the
+    pair kernel's bit for bit (same accumulation order), the normalised rows to bf16 rounding."""
+    N = 384
+    g = torch.Generator().manual_seed(M + K)
+    A, W = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / K ** 0.5
+    vec = torch.randn(7, N, generator=g) * 0.5
+    bias, gate, shift, scale = vec[0], vec[1:3], vec[3:5], vec[5:7]
+    x0 = torch.randn(M, N, generator=g) * 2.0 + offset
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    dA, dW, dv = A.cuda(), W.cuda(), vec.contiguous().cuda()
+    L = _lib.lib()
+    idx = _lib.VARIANTS.index("gemm_ln4")
+    before = L.mdgen_variant_launches(idx)
+    C = torch.cat([x0, torch.zeros(M, N)]).cuda()
+    _lib.check(L.mdgen_test_gemm(M, N, K, _p(dA), _p(dW), _p(dv), _p(C), 5, 4, st), "test_gemm")
+    torch.cuda.synchronize()
+    assert L.mdgen_variant_launches(idx) == before + 1
+    b = (torch.arange(M) // 200) % 2
+    acc = A.bfloat16().double() @ W.bfloat16().double().T + bias.double()
+    x = x0.double() + gate[b].double() * acc
+    h = torch.nn.functional.layer_norm(x, (N,), eps=1e-6) * (1 + scale[b].double()) + shift[b].double()
+    out = C.cpu()
+    assert torch.isfinite(out).all()
+    assert float((out[:M] - x.float()).norm() / x.norm()) < 1e-5
+    assert float((out[M:] - h.float()).norm() / h.norm()) < 4e-3
+    if M >= 256:
+        P = torch.cat([x0, torch.zeros(M, N)]).cuda()
+        _lib.check(L.mdgen_test_gemm(M, N, K, _p(dA), _p(dW), _p(dv), _p(P), 5, 0, st), "test_gemm")
+        torch.cuda.synchronize()
+        assert torch.equal(P[:M], C[:M])
+        assert float((P[M:] - C[M:]).abs().max()) <= 0.0625       # at most one bf16 ulp apart at |h| < 8
+    for _ in range(4):                                             # repeatable (the exchange has no race)
+        R = torch.cat([x0, torch.zeros(M, N)]).cuda()
+        _lib.check(L.mdgen_test_gemm(M, N, K, _p(dA), _p(dW), _p(dv), _p(R), 5, 4, st), "test_gemm")
+        torch.cuda.synchronize()
+        assert torch.equal(R, C)
+
+
 @pytest.mark.parametrize("env", ["MDGEN_PAIR16_STORE", "MDGEN_NO_PAIR16"])
 @pytest.mark.parametrize("M,N,K", [(4000, 1152, 384), (777, 1536, 384), (300, 128, 64), (20000, 1536, 384)])
 @pytest.mark.parametrize("mode", [2, 3])

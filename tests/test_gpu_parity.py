@@ -1,5 +1,7 @@
 """Parity of the CUDA path (through LatentMDGenModel -> C ABI) against the CPU oracle and the
 committed reference goldens.  Tolerances are north_star's: fp32 check mode 1e-4 rel-L2, bf16 2e-2."""
+import os
+
 import pytest
 import torch
 
@@ -156,6 +158,24 @@ def test_full_size_config1_velocity_and_launch_count():
             v = m.forward(inp["x0"].cuda(), t.cuda(), **kw).cpu()
         assert rel_l2(v, g["v_t0"]) < TOL[prec], (prec, rel_l2(v, g["v_t0"]))
         assert m.launches_per_forward() > 0
+    # 4000 rows: the bf16 path fuses projection + residual + LayerNorm on clusters of 4 CTAs (gemm_ln4.cuh); without it the
+    # result stays within bf16 rounding
+    from mdgen_finetune_b200 import _lib
+    idx = _lib.VARIANTS.index("gemm_ln4")
+    m = build(args, c["D"], sd, "bf16")
+    before = _lib.lib().mdgen_variant_launches(idx)
+    with torch.no_grad():
+        v1 = m.forward(inp["x0"].cuda(), t.cuda(), **kw).cpu()
+    assert _lib.lib().mdgen_variant_launches(idx) >= before + 15          # 2 out_proj + fc2 per main layer
+    os.environ["MDGEN_NO_GEMM_LN4"] = "1"
+    try:
+        mid = _lib.lib().mdgen_variant_launches(idx)
+        with torch.no_grad():
+            v0 = m.forward(inp["x0"].cuda(), t.cuda(), **kw).cpu()
+        assert _lib.lib().mdgen_variant_launches(idx) == mid
+    finally:
+        del os.environ["MDGEN_NO_GEMM_LN4"]
+    assert rel_l2(v1, v0) < 5e-3, rel_l2(v1, v0)
 
 
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
