@@ -176,9 +176,10 @@ embed_kernel(const float* __restrict__ x, int D, const float* __restrict__ xc, i
 // registers, so one broadcast LDS.128 of the staged inputs feeds 4 * CH FMAs: the one-channel kernel above was
 // LSU-bound (ncu: 78 % LSU, 68 us for config 3).
 constexpr int EMB_STEP_TOK = 16;    // tokens per block: 2000 blocks on config 3, ~13 resident warps per SM stay busy
-constexpr int EMB_STEP_GRP = 4;     // tokens whose loads are in flight together
-// Round 2: the tokens of a block are processed four at a time with every load of the group issued before the first FMA
+constexpr int EMB_STEP_GRP = 8;     // tokens whose loads are in flight together
+// Round 2: the tokens of a block are processed four (then eight) at a time with every load of the group issued before the first FMA
 // (the one-token loop had ~8 loads in flight per thread at ~15 warps per SM): 2.29 -> 2.07 ms per rollout on config 3.
+// Eight at a time: 2.08 -> 1.90 ms (168 registers, no spills).
 // Fusing the first block's LayerNorm + modulate in here (block reductions for the row statistics) was measured SLOWER than
 // the separate ln_modulate launch (3.32 vs 3.01 ms per rollout for the two together) and is not kept.
 template <int C, int DP, int CH>
